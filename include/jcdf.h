@@ -1,0 +1,160 @@
+/*
+ * libjcdf — B200-native (sm_100a) density-fitted RHF Fock build behind JuliaChem.jl's DF-RHF seam.
+ *
+ * C-ABI boundary (plain pointers and sizes, no C++/torch types).  Every entry point names the reference interface it
+ * replaces; file:line are relative to the reference checkout (j-hayes/JuliaChem.jl @ 2064729).  The Julia side that
+ * binds these with `ccall` is shown in INTEGRATION.md and shipped as julia/B200DF.jl; the in-repo precedent for a
+ * pointer-level C call from this module is `call_gemm!` (src/rhf/energy/DensityFitting/ScreenedDF.jl:645-673).
+ *
+ * Conventions
+ *   - all matrices are column-major FP64 exactly as Julia passes them; index maps are Int64, 1-based, 0 = screened;
+ *     Bool arrays are 1 byte per element (Julia `Array{Bool}`).
+ *   - every function returns 0 on success and a negative jcdf_status on failure; jcdf_last_error() then returns a
+ *     thread-local, NUL-terminated description.  No C++ exception crosses this boundary.
+ *   - host pointers are borrowed for the duration of the call only; all device memory is owned by the handle.
+ *   - calls on one handle are serial (one caller thread at a time); the library selects its devices itself on
+ *     entry, so the caller may migrate between OS threads (Julia tasks).
+ */
+#ifndef JCDF_H
+#define JCDF_H
+
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+typedef struct jcdf_handle jcdf_handle;
+
+typedef enum jcdf_status {
+    JCDF_OK = 0,
+    JCDF_ERR_INVALID = -1,   /* bad argument / call order */
+    JCDF_ERR_CUDA = -2,      /* CUDA runtime / cuSOLVER / cuBLAS failure */
+    JCDF_ERR_NCCL = -3,      /* NCCL failure or libnccl not loadable */
+    JCDF_ERR_NOMEM = -4,     /* device allocation failed */
+    JCDF_ERR_NUMERIC = -5    /* metric not positive definite, eigensolver did not converge */
+} jcdf_status;
+
+/* stage_seconds[] slots filled by jcdf_fock_build — the reference's per-iteration JCTiming keys
+ * (src/shared/JCTiming.jl:58-65; filled at ScreenedDF.jl:238-239, 362-364, DensityFitting.jl:64,70, GPUDF.jl:281-301) */
+enum {
+    JCDF_T_W = 0,         /* W_time      half-transform                           */
+    JCDF_T_K = 1,         /* K_time      exchange                                 */
+    JCDF_T_V = 2,         /* V_time      Coulomb intermediate                     */
+    JCDF_T_J = 3,         /* J_time      Coulomb matrix                           */
+    JCDF_T_ALLREDUCE = 4, /* fock_MPI_time  (NCCL all-reduce)                     */
+    JCDF_T_DENSITY = 5,   /* density_time   (C_occ re-layout + packed density)    */
+    JCDF_T_H2D = 6,       /* C_occ upload                                         */
+    JCDF_T_D2H = 7,       /* Fock download (fock_gpu_cpu_copy_reduce_time)        */
+    JCDF_T_TOTAL = 8,     /* fock_time   whole call, host clock                   */
+    JCDF_T_EPILOGUE = 9,  /* H add + J scatter + symmetrise (H_add_time, gpu_copy_J_time, gpu_copy_sym_time) */
+    JCDF_N_STAGES = 10
+};
+
+const char* jcdf_last_error(void);
+/* number of visible CUDA devices, or a negative status (replaces length(CUDA.devices()), GPUDF.jl:39) */
+int32_t jcdf_device_count(void);
+
+/* Create the per-SCF state the reference keeps in scf_data / scf_data.gpu_data from iteration 1
+ * (DensityFitting.jl:34-47; GPUDF.jl:79-155; types src/shared/SCFData.jl:19-37, GPUData_cuda.jl:4-38).
+ *   N    primary basis functions (scf_data.mu), Q auxiliary functions (scf_data.A), occ = nels / 2
+ *   ndev devices of THIS process (scf_options.num_devices, Constants.jl:67-68); dev_ids NULL = 0..ndev-1          */
+int32_t jcdf_create(int64_t N, int64_t Q, int64_t occ, int32_t ndev, const int32_t* dev_ids, jcdf_handle** out);
+int32_t jcdf_destroy(jcdf_handle* h);
+
+/* Q sharding.  q_begin/q_len (0-based first auxiliary function, count) for each of this process's devices:
+ * the ranges static_load_rank_indicies returns (DynamicLoad.jl:160-203; per device GPUDF.jl:1026-1056).
+ * Default when never called: one process owning all of Q, split evenly by function count over its devices.      */
+int32_t jcdf_set_shards(jcdf_handle* h, const int64_t* q_begin, const int64_t* q_len);
+
+/* Screening mask and pair compaction (schwarz_screen_itegrals_df, SchwarzScreening.jl:9-83):
+ *   fn_mask               N x N Bool, basis_function_screen_matrix (symmetric, diagonal kept)
+ *   sparse_pq_index_map   N x N Int64, [q,p] -> 1-based column of T/B in the reference pair order, 0 = screened
+ * Both NULL = unscreened ("dense") with column (q,p) -> q + N*p + 1 (setup_unscreened_screening_matricies :97-111
+ * modulo its transposed fill, which is the same map for a symmetric tensor).
+ * Builds the tile-compacted HBM layout.  Must precede any upload.                                */
+int32_t jcdf_set_mask(jcdf_handle* h, const uint8_t* fn_mask, const int64_t* sparse_pq_index_map);
+
+/* Rows of the raw three-centre integrals (P|mn) of device `dev`'s shard: T is (q_len[dev] x P) column-major with
+ * leading dimension ld, columns in the reference pair order — exactly three_center_integrals[device_id] of
+ * GPUDF.jl:51-57 / calculate_three_center_integrals (ThreeCenterIntegrals.jl:9).  Stored until
+ * jcdf_factor_and_form_B.                                                                                        */
+int32_t jcdf_upload_three_center(jcdf_handle* h, int32_t dev, const double* T, int64_t ld);
+/* Same, for a column window [col_begin, col_begin+col_count) that already lives in device memory on device `dev`
+ * (leading dimension ld).  Windows may arrive in any order and may be freed by the caller after the call.        */
+int32_t jcdf_upload_three_center_device(jcdf_handle* h, int32_t dev, const double* T_dev, int64_t ld,
+                                        int64_t col_begin, int64_t col_count);
+/* Two-centre metric (P|Q), Q x Q column-major, lower triangle valid (calculate_two_center_intgrals,
+ * TwoCenterIntegrals.jl:7; only the lower triangle is filled :39-41).                                            */
+int32_t jcdf_upload_metric(jcdf_handle* h, const double* J_PQ);
+/* On-device potrf!('L') + trtri!('L','N') + B = Linv * T (calculate_B!, DensityFitting.jl:128-183;
+ * ScreenedDF.jl:92-103; calculate_B_GPU!, GPUDF.jl:828-1008 which does the factorisation on the CPU :890-891).
+ * No CPU fallback.  Requires every device's T and the metric.                                                    */
+int32_t jcdf_factor_and_form_B(jcdf_handle* h);
+/* Alternative to the three calls above when the caller already holds B = L^-1 (P|mn) rows of the shard
+ * (scf_data.D of ScreenedDF.jl:103 / gpu_data.device_B): same layout as jcdf_upload_three_center.                 */
+int32_t jcdf_set_B(jcdf_handle* h, int32_t dev, const double* B, int64_t ld);
+int32_t jcdf_set_B_device(jcdf_handle* h, int32_t dev, const double* B_dev, int64_t ld, int64_t col_begin,
+                          int64_t col_count);
+/* Copy the inverse Cholesky factor Linv (Q x Q, lower, column-major) back — for tests (J_AB_invt, ScreenedDF.jl:95) */
+int32_t jcdf_get_metric_inverse(jcdf_handle* h, double* Linv_out);
+
+/* One Fock build: replaces the body of df_rhf_fock_build! after `occupied_orbital_coefficients = coefficients[:,1:occ]`
+ * (DensityFitting.jl:49-71) for contraction_mode == "B200":
+ *     F = [H on the shard-0 device] + sum over devices of ( 2 J[Dm] - K[Dm] ),  Dm = C_occ C_occ^T,
+ * i.e. calculate_exchange_screened! + calculate_coulomb_screened (ScreenedDF.jl:227-378), `+= H` on rank 0
+ * (DensityFitting.jl:62-65) and the reduce over devices/ranks (GPUDF.jl:267-277, DensityFitting.jl:68-71) done as one
+ * NCCL all-reduce on the devices.
+ *   C_occ  N x occ column-major, leading dimension ldc (host)
+ *   H      N x N column-major or NULL (host); only added when this process owns global shard 0
+ *   F_out  N x N column-major (host), fully overwritten, exactly symmetric; not retained
+ *   stage_seconds  NULL or double[JCDF_N_STAGES]                                                                 */
+int32_t jcdf_fock_build(jcdf_handle* h, const double* C_occ, int64_t ldc, const double* H, double* F_out,
+                        double* stage_seconds);
+/* Device-resident variant: C_occ, H and F_out are device pointers on this process's first device; no host copies.
+ * Used to measure the contraction with inputs resident in HBM.                                                   */
+int32_t jcdf_fock_build_device(jcdf_handle* h, const double* C_occ_dev, int64_t ldc, const double* H_dev,
+                               double* F_out_dev, double* stage_seconds);
+
+/* On-device replacement of iteration()'s linear algebra (src/rhf/energy/SCF.jl:1072-1099):
+ *   Fp = X^T F X ; (evals, U) = eigen(Hermitian(Fp)) ascending ; C = X U.
+ * F, X: N x N column-major (host).  evals: N.  C: N x N.                                                         */
+int32_t jcdf_eigh(jcdf_handle* h, const double* F, const double* X, double* evals, double* C);
+
+/* ---- one process per GPU (torchrun / MPI ranks > 1) --------------------------------------------------------------
+ * The reference sums rank-partial Fock matrices with MPI.Allreduce! (DensityFitting.jl:68-71).  Here rank 0 calls
+ * jcdf_comm_unique_id, ships the 128 bytes to the other ranks by any means, and every rank calls jcdf_comm_init_rank;
+ * jcdf_fock_build then all-reduces across all devices of all ranks and H is added by global rank 0 only.          */
+int32_t jcdf_comm_unique_id(uint8_t id_out[128]);
+int32_t jcdf_comm_init_rank(jcdf_handle* h, int32_t n_ranks, int32_t rank, const uint8_t id[128]);
+
+/* ---- introspection (tests, bench, DESIGN.md numbers) ------------------------------------------------------------- */
+typedef struct jcdf_layout_info {
+    int64_t N, Q, occ;
+    int64_t n_pad;            /* N rounded up to the 32-wide tile edge                      */
+    int64_t occ_pad;          /* occ rounded up to 8                                        */
+    int64_t tiles_total;      /* lower-triangular 32x32 tiles incl. diagonal                */
+    int64_t tiles_kept;       /* tiles holding at least one unscreened pair                 */
+    int64_t pairs_kept;       /* P   = screened_indices_count (ordered pairs)               */
+    int64_t pairs_tri;        /* P_tri = kept pairs with q >= p                             */
+    int64_t packed_row_len;   /* doubles per auxiliary row in HBM = tiles_kept * 1024       */
+    int64_t q_local;          /* auxiliary functions held by this process                   */
+    int64_t bytes_B, bytes_W; /* device bytes, summed over this process's devices           */
+    int64_t kernel_launches_per_build; /* launches of this library's own kernels per build  */
+} jcdf_layout_info;
+int32_t jcdf_get_layout(jcdf_handle* h, jcdf_layout_info* out);
+
+/* Deterministic synthetic shard for benchmarks at sizes no host array can hold: fills the packed B of every device
+ * directly in HBM with B[Q,(p,q)] = decay(p,q) * gauss(seed, Q, min(p,q), max(p,q)) / sqrt(Q_total) for kept pairs.
+ * jcdf_synthetic_value returns the same value on the host so tests can rebuild the tensor for the oracle.        */
+int32_t jcdf_fill_synthetic_B(jcdf_handle* h, uint64_t seed, double decay_length);
+double jcdf_synthetic_value(uint64_t seed, int64_t Q_total, int64_t q_aux, int64_t p, int64_t q, double decay_length);
+
+/* Per-kernel device time of the last build of device `dev` in ms (CUDA events on the launching stream):
+ * out[0..JCDF_N_STAGES) in the stage order above.                                                                */
+int32_t jcdf_last_kernel_ms(jcdf_handle* h, int32_t dev, double* out);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* JCDF_H */

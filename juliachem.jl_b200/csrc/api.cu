@@ -1,0 +1,796 @@
+// C-ABI of libjcdf (include/jcdf.h): host-side state, layout construction, uploads, metric factorisation, the
+// per-iteration Fock build sequence and the NCCL reduce.  All arithmetic of the hot path lives in kernels_*.cu.
+#include <algorithm>
+#include <chrono>
+#include <cmath>
+#include <cstdio>
+#include <cstring>
+#include <string>
+#include <vector>
+
+#include <cublas_v2.h>
+#include <cusolverDn.h>
+
+#include "jcdf_internal.h"
+#include "nccl_dyn.h"
+
+namespace jcdf {
+
+static thread_local std::string g_err;
+void set_error(const std::string& msg) { g_err = msg; }
+
+#define JC_CUDA(call)                                                                                   \
+    do {                                                                                                \
+        cudaError_t e__ = (call);                                                                       \
+        if (e__ != cudaSuccess) {                                                                       \
+            set_error(std::string(#call) + ": " + cudaGetErrorString(e__) + " (" + __FILE__ + ":" +     \
+                      std::to_string(__LINE__) + ")");                                                  \
+            return (e__ == cudaErrorMemoryAllocation) ? JCDF_ERR_NOMEM : JCDF_ERR_CUDA;                 \
+        }                                                                                               \
+    } while (0)
+#define JC_CUBLAS(call)                                                                                 \
+    do {                                                                                                \
+        cublasStatus_t s__ = (call);                                                                    \
+        if (s__ != CUBLAS_STATUS_SUCCESS) {                                                             \
+            set_error(std::string(#call) + ": cuBLAS status " + std::to_string((int)s__));              \
+            return JCDF_ERR_CUDA;                                                                       \
+        }                                                                                               \
+    } while (0)
+#define JC_CUSOLVER(call)                                                                               \
+    do {                                                                                                \
+        cusolverStatus_t s__ = (call);                                                                  \
+        if (s__ != CUSOLVER_STATUS_SUCCESS) {                                                           \
+            set_error(std::string(#call) + ": cuSOLVER status " + std::to_string((int)s__));            \
+            return JCDF_ERR_CUDA;                                                                       \
+        }                                                                                               \
+    } while (0)
+#define JC_NCCL(call)                                                                                   \
+    do {                                                                                                \
+        int r__ = (call);                                                                               \
+        if (r__ != 0) {                                                                                 \
+            set_error(std::string(#call) + ": " + nccl().GetErrorString(r__));                          \
+            return JCDF_ERR_NCCL;                                                                       \
+        }                                                                                               \
+    } while (0)
+#define JC_REQUIRE(cond, msg)                    \
+    do {                                         \
+        if (!(cond)) {                           \
+            set_error(msg);                      \
+            return JCDF_ERR_INVALID;             \
+        }                                        \
+    } while (0)
+
+static inline int64_t round_up(int64_t x, int64_t m) { return (x + m - 1) / m * m; }
+
+template <typename T>
+static int dev_alloc(T** p, size_t count) {
+    *p = nullptr;
+    if (count == 0) count = 1;
+    JC_CUDA(cudaMalloc(reinterpret_cast<void**>(p), count * sizeof(T)));
+    return JCDF_OK;
+}
+
+static void free_shard_buffers(Shard& s) {
+    cudaSetDevice(s.dev);
+    void* ptrs[] = {s.Bp, s.W, s.Cs, s.Craw, s.dt, s.Jt, s.V, s.Kpart, s.F, s.Hdev, s.Traw, s.d_tile_index, s.d_tile_a,
+                    s.d_tile_b, s.d_dest_of_col, s.d_fn_mask, s.Linv, s.Metric};
+    for (void* p : ptrs)
+        if (p) cudaFree(p);
+    s.Bp = s.W = s.Cs = s.Craw = s.dt = s.Jt = s.V = s.Kpart = s.F = s.Hdev = s.Traw = s.Linv = s.Metric = nullptr;
+    s.d_tile_index = s.d_tile_a = s.d_tile_b = nullptr;
+    s.d_dest_of_col = nullptr;
+    s.d_fn_mask = nullptr;
+    s.traw_capacity = 0;
+    s.b_ready = s.t_uploaded = s.has_H = false;
+}
+
+// Split of the exchange contraction index: items = tiles x slices dealt round-robin to one CTA per SM.
+static void plan_exchange(const Layout& L, Shard& s, int sm_count) {
+    ExchangePlan& x = s.xplan;
+    x.chunks = (int)((s.q_len * L.occ_pad + 31) / 32);
+    x.n_tiles = L.n128 * (L.n128 + 1) / 2;
+    int max_slices = std::max(1, x.chunks / 8);
+    int want = std::max(1, (12 * sm_count + x.n_tiles - 1) / x.n_tiles);
+    int s0 = std::min(want, max_slices);
+    int best = s0;
+    double best_eff = -1;
+    for (int c = s0; c <= std::min(max_slices, s0 + 48); c++) {
+        int64_t items = (int64_t)x.n_tiles * c;
+        int64_t waves = (items + sm_count - 1) / sm_count;
+        double eff = (double)items / (double)(waves * sm_count);
+        if (eff > best_eff + 1e-9) { best_eff = eff; best = c; }
+    }
+    x.chunks_per_slice = (x.chunks + best - 1) / best;
+    if (x.chunks_per_slice < 1) x.chunks_per_slice = 1;
+    x.n_slices = std::max(1, (x.chunks + x.chunks_per_slice - 1) / x.chunks_per_slice);
+}
+
+static int alloc_shard_buffers(jcdf_handle* h, Shard& s) {
+    const Layout& L = h->lay;
+    JC_CUDA(cudaSetDevice(s.dev));
+    plan_exchange(L, s, h->sm_count);
+    int rc;
+    const size_t nB = (size_t)s.q_len * (size_t)L.row_len;
+    if ((rc = dev_alloc(&s.Bp, nB))) return rc;
+    JC_CUDA(cudaMemsetAsync(s.Bp, 0, std::max<size_t>(nB, 1) * sizeof(double), s.stream));
+    const size_t nW = (size_t)s.xplan.chunks * L.npt64 * 2048;
+    if ((rc = dev_alloc(&s.W, nW))) return rc;
+    JC_CUDA(cudaMemsetAsync(s.W, 0, std::max<size_t>(nW, 1) * sizeof(double), s.stream));
+    if ((rc = dev_alloc(&s.Cs, (size_t)L.nb * L.n_mt * 32 * L.bm))) return rc;
+    if ((rc = dev_alloc(&s.Craw, (size_t)L.N * L.occ))) return rc;
+    if ((rc = dev_alloc(&s.dt, (size_t)L.row_len))) return rc;
+    if ((rc = dev_alloc(&s.Jt, (size_t)L.row_len))) return rc;
+    if ((rc = dev_alloc(&s.V, (size_t)std::max<int64_t>(s.q_len, 1)))) return rc;
+    if ((rc = dev_alloc(&s.Kpart, (size_t)s.xplan.n_tiles * s.xplan.n_slices * 128 * 128))) return rc;
+    if ((rc = dev_alloc(&s.F, (size_t)L.N * L.N))) return rc;
+    if ((rc = dev_alloc(&s.Hdev, (size_t)L.N * L.N))) return rc;
+    if ((rc = dev_alloc(&s.d_tile_index, (size_t)L.nb * L.nb))) return rc;
+    if ((rc = dev_alloc(&s.d_tile_a, (size_t)L.tiles_kept))) return rc;
+    if ((rc = dev_alloc(&s.d_tile_b, (size_t)L.tiles_kept))) return rc;
+    if ((rc = dev_alloc(&s.d_dest_of_col, (size_t)L.pairs_kept))) return rc;
+    JC_CUDA(cudaMemcpyAsync(s.d_tile_index, L.tile_index.data(), sizeof(int32_t) * L.tile_index.size(),
+                            cudaMemcpyHostToDevice, s.stream));
+    JC_CUDA(cudaMemcpyAsync(s.d_tile_a, L.tile_a.data(), sizeof(int32_t) * L.tile_a.size(), cudaMemcpyHostToDevice,
+                            s.stream));
+    JC_CUDA(cudaMemcpyAsync(s.d_tile_b, L.tile_b.data(), sizeof(int32_t) * L.tile_b.size(), cudaMemcpyHostToDevice,
+                            s.stream));
+    JC_CUDA(cudaMemcpyAsync(s.d_dest_of_col, L.dest_of_col.data(), sizeof(int64_t) * L.dest_of_col.size(),
+                            cudaMemcpyHostToDevice, s.stream));
+    JC_CUDA(cudaStreamSynchronize(s.stream));
+    return JCDF_OK;
+}
+
+static int default_shards(jcdf_handle* h) {
+    const int nd = (int)h->shards.size();
+    const int64_t Q = h->lay.Q;
+    for (int d = 0; d < nd; d++) {
+        h->shards[d].q_begin = Q * d / nd;
+        h->shards[d].q_len = Q * (d + 1) / nd - Q * d / nd;
+    }
+    return JCDF_OK;
+}
+
+static int ensure_comm(jcdf_handle* h) {
+    if (h->comm_ready) return JCDF_OK;
+    const int nd = (int)h->shards.size();
+    if (h->n_ranks == 1 && nd == 1) { h->comm_ready = true; return JCDF_OK; }
+    const NcclApi& n = nccl();
+    if (!n.ok) { set_error(std::string("NCCL unavailable: ") + n.why); return JCDF_ERR_NCCL; }
+    if (h->n_ranks == 1) {
+        std::vector<int> devs(nd);
+        std::vector<void*> comms(nd, nullptr);
+        for (int d = 0; d < nd; d++) devs[d] = h->shards[d].dev;
+        JC_NCCL(n.CommInitAll(comms.data(), nd, devs.data()));
+        for (int d = 0; d < nd; d++) h->shards[d].nccl_comm = comms[d];
+        h->comm_ready = true;
+        return JCDF_OK;
+    }
+    set_error("multi-rank communicator not initialised: call jcdf_comm_init_rank first");
+    return JCDF_ERR_INVALID;
+}
+
+}  // namespace jcdf
+
+using namespace jcdf;
+
+extern "C" {
+
+const char* jcdf_last_error(void) { return g_err.c_str(); }
+
+int32_t jcdf_device_count(void) {
+    int n = 0;
+    cudaError_t e = cudaGetDeviceCount(&n);
+    if (e != cudaSuccess) {
+        set_error(std::string("cudaGetDeviceCount: ") + cudaGetErrorString(e));
+        return JCDF_ERR_CUDA;
+    }
+    return n;
+}
+
+int32_t jcdf_create(int64_t N, int64_t Q, int64_t occ, int32_t ndev, const int32_t* dev_ids, jcdf_handle** out) {
+    JC_REQUIRE(out != nullptr, "jcdf_create: out is NULL");
+    *out = nullptr;
+    JC_REQUIRE(N > 0 && Q > 0 && occ > 0 && occ <= N, "jcdf_create: need N > 0, Q > 0, 0 < occ <= N");
+    JC_REQUIRE(N < (1 << 21) && Q < (1 << 21), "jcdf_create: N and Q must be below 2^21");
+    JC_REQUIRE(ndev >= 1, "jcdf_create: ndev must be >= 1");
+    int avail = 0;
+    JC_CUDA(cudaGetDeviceCount(&avail));
+    // mirrors error("Number of devices requested is greater than the number of devices available") GPUDF.jl:39-41
+    JC_REQUIRE(ndev <= avail, "Number of devices requested is greater than the number of devices available");
+    jcdf_handle* h = new (std::nothrow) jcdf_handle();
+    JC_REQUIRE(h != nullptr, "jcdf_create: out of host memory");
+    Layout& L = h->lay;
+    L.N = N; L.Q = Q; L.occ = occ;
+    L.nb = (int)((N + 31) / 32);
+    L.n_pad = 32 * L.nb;
+    L.occ_pad = (int)round_up(occ, 8);
+    L.n_mt = (L.occ_pad + 127) / 128;
+    L.bm = (int)round_up((L.occ_pad + L.n_mt - 1) / L.n_mt, 16);
+    L.npt64 = (L.n_pad + 63) / 64;
+    L.n_pt128 = (L.nb + 3) / 4;
+    L.n128 = (L.npt64 + 1) / 2;
+    h->shards.resize(ndev);
+    for (int d = 0; d < ndev; d++) {
+        Shard& s = h->shards[d];
+        s.dev = dev_ids ? dev_ids[d] : d;
+        if (s.dev < 0 || s.dev >= avail) {
+            delete h;
+            set_error("jcdf_create: device id out of range");
+            return JCDF_ERR_INVALID;
+        }
+        cudaError_t e = cudaSetDevice(s.dev);
+        if (e == cudaSuccess) e = cudaStreamCreateWithFlags(&s.stream, cudaStreamNonBlocking);
+        for (int i = 0; i < EV_COUNT && e == cudaSuccess; i++) e = cudaEventCreate(&s.ev[i]);
+        if (e != cudaSuccess) {
+            set_error(std::string("jcdf_create: ") + cudaGetErrorString(e));
+            delete h;
+            return JCDF_ERR_CUDA;
+        }
+    }
+    cudaDeviceProp prop;
+    JC_CUDA(cudaGetDeviceProperties(&prop, h->shards[0].dev));
+    h->sm_count = prop.multiProcessorCount;
+    if (prop.major < 10) {
+        delete h;
+        set_error("libjcdf is built for sm_100a (Blackwell B200) only; device compute capability is " +
+                  std::to_string(prop.major) + "." + std::to_string(prop.minor));
+        return JCDF_ERR_CUDA;
+    }
+    default_shards(h);
+    *out = h;
+    return JCDF_OK;
+}
+
+int32_t jcdf_destroy(jcdf_handle* h) {
+    if (!h) return JCDF_OK;
+    for (Shard& s : h->shards) {
+        cudaSetDevice(s.dev);
+        if (s.stream) cudaStreamSynchronize(s.stream);
+        if (s.nccl_comm && nccl().ok) nccl().CommDestroy(s.nccl_comm);
+        free_shard_buffers(s);
+        for (int i = 0; i < EV_COUNT; i++)
+            if (s.ev[i]) cudaEventDestroy(s.ev[i]);
+        if (s.stream) cudaStreamDestroy(s.stream);
+    }
+    delete h;
+    return JCDF_OK;
+}
+
+int32_t jcdf_set_shards(jcdf_handle* h, const int64_t* q_begin, const int64_t* q_len) {
+    JC_REQUIRE(h && q_begin && q_len, "jcdf_set_shards: NULL argument");
+    JC_REQUIRE(!h->lay.mask_set, "jcdf_set_shards must precede jcdf_set_mask");
+    for (size_t d = 0; d < h->shards.size(); d++) {
+        JC_REQUIRE(q_begin[d] >= 0 && q_len[d] >= 0 && q_begin[d] + q_len[d] <= h->lay.Q,
+                   "jcdf_set_shards: shard outside [0, Q)");
+        h->shards[d].q_begin = q_begin[d];
+        h->shards[d].q_len = q_len[d];
+    }
+    h->shards_set = true;
+    return JCDF_OK;
+}
+
+int32_t jcdf_set_mask(jcdf_handle* h, const uint8_t* fn_mask, const int64_t* map) {
+    JC_REQUIRE(h != nullptr, "jcdf_set_mask: NULL handle");
+    JC_REQUIRE((fn_mask == nullptr) == (map == nullptr), "jcdf_set_mask: pass both fn_mask and sparse_pq_index_map or neither");
+    Layout& L = h->lay;
+    const int64_t N = L.N;
+    const int nb = L.nb;
+    for (Shard& s : h->shards) free_shard_buffers(s);
+    auto kept = [&](int64_t r, int64_t c) -> bool { return fn_mask ? fn_mask[r + N * c] != 0 : true; };
+    // tile table: a tile is stored iff it holds at least one unscreened pair
+    L.tile_index.assign((size_t)nb * nb, -1);
+    L.tile_a.clear();
+    L.tile_b.clear();
+    L.tiles_total = (int64_t)nb * (nb + 1) / 2;
+    int64_t P = 0, Ptri = 0;
+    for (int a = 0; a < nb; a++)
+        for (int b = 0; b <= a; b++) {
+            bool any = false;
+            const int64_t r1 = std::min<int64_t>(N, 32 * (a + 1)), c1 = std::min<int64_t>(N, 32 * (b + 1));
+            for (int64_t c = 32 * b; c < c1 && !any; c++)
+                for (int64_t r = 32 * a; r < r1; r++)
+                    if (kept(r, c)) { any = true; break; }
+            if (any) {
+                L.tile_index[(size_t)a * nb + b] = (int32_t)L.tile_a.size();
+                L.tile_a.push_back(a);
+                L.tile_b.push_back(b);
+            }
+        }
+    L.tiles_kept = (int64_t)L.tile_a.size();
+    L.row_len = L.tiles_kept * 1024;
+    for (int64_t c = 0; c < N; c++)
+        for (int64_t r = 0; r < N; r++)
+            if (kept(r, c)) {
+                P++;
+                if (r >= c) Ptri++;
+                if (fn_mask && !fn_mask[c + N * r]) {
+                    set_error("jcdf_set_mask: basis_function_screen_matrix is not symmetric");
+                    return JCDF_ERR_INVALID;
+                }
+            }
+    for (int64_t r = 0; r < N; r++) JC_REQUIRE(kept(r, r), "jcdf_set_mask: a diagonal pair (p,p) is screened");
+    L.pairs_kept = P;
+    L.pairs_tri = Ptri;
+    // reference column -> packed offset.  Column of pair (row r, col c) is map[r + N*c] - 1 (SchwarzScreening.jl:72-81).
+    L.dest_of_col.assign((size_t)P, -1);
+    for (int64_t c = 0; c < N; c++)
+        for (int64_t r = 0; r < N; r++) {
+            if (!kept(r, c)) {
+                if (map) JC_REQUIRE(map[r + N * c] == 0, "jcdf_set_mask: index map non-zero on a screened pair");
+                continue;
+            }
+            const int64_t col = map ? map[r + N * c] - 1 : r + N * c;
+            JC_REQUIRE(col >= 0 && col < P, "jcdf_set_mask: sparse_pq_index_map entry out of range");
+            const int a = (int)(r / 32), b = (int)(c / 32);
+            if (a < b) continue;  // mirror copy; the (c, r) column fills tile (b, a)
+            const int32_t ti = L.tile_index[(size_t)a * nb + b];
+            const int rr = (int)(r % 32), cc = (int)(c % 32);
+            L.dest_of_col[(size_t)col] = (int64_t)ti * 1024 + rr * 32 + (cc ^ ((rr & 3) << 2));
+        }
+    L.mask_set = true;
+    for (Shard& s : h->shards) {
+        int rc = alloc_shard_buffers(h, s);
+        if (rc) return rc;
+        if (fn_mask) {
+            JC_CUDA(cudaSetDevice(s.dev));
+            if ((rc = dev_alloc(&s.d_fn_mask, (size_t)N * N))) return rc;
+            JC_CUDA(cudaMemcpy(s.d_fn_mask, fn_mask, (size_t)N * N, cudaMemcpyHostToDevice));
+        }
+    }
+    return JCDF_OK;
+}
+
+static int upload_window(jcdf_handle* h, int32_t dev, const double* T_dev, int64_t ld, int64_t col_begin,
+                         int64_t col_count) {
+    Shard& s = h->shards[dev];
+    launch_scatter_pairs(h->lay, s, T_dev, ld, col_begin, col_count);
+    JC_CUDA(cudaGetLastError());
+    JC_CUDA(cudaStreamSynchronize(s.stream));
+    return JCDF_OK;
+}
+
+static int upload_host(jcdf_handle* h, int32_t dev, const double* T, int64_t ld) {
+    JC_REQUIRE(h && T, "upload: NULL argument");
+    JC_REQUIRE(h->lay.mask_set, "upload: call jcdf_set_mask first");
+    JC_REQUIRE(dev >= 0 && dev < (int)h->shards.size(), "upload: device index out of range");
+    Shard& s = h->shards[dev];
+    JC_REQUIRE(ld >= s.q_len, "upload: ld smaller than the shard's row count");
+    JC_CUDA(cudaSetDevice(s.dev));
+    if (s.q_len == 0) return JCDF_OK;
+    const int64_t P = h->lay.pairs_kept;
+    // staging window of at most 1 GiB
+    int64_t win = std::max<int64_t>(1, std::min<int64_t>(P, ((int64_t)1 << 27) / std::max<int64_t>(s.q_len, 1)));
+    if (s.traw_capacity < win * s.q_len) {
+        if (s.Traw) cudaFree(s.Traw);
+        s.Traw = nullptr;
+        int rc = dev_alloc(&s.Traw, (size_t)(win * s.q_len));
+        if (rc) return rc;
+        s.traw_capacity = win * s.q_len;
+    }
+    for (int64_t c0 = 0; c0 < P; c0 += win) {
+        const int64_t nc = std::min(win, P - c0);
+        JC_CUDA(cudaMemcpy2DAsync(s.Traw, sizeof(double) * s.q_len, T + ld * c0, sizeof(double) * ld,
+                                  sizeof(double) * s.q_len, (size_t)nc, cudaMemcpyHostToDevice, s.stream));
+        int rc = upload_window(h, dev, s.Traw, s.q_len, c0, nc);
+        if (rc) return rc;
+    }
+    cudaFree(s.Traw);
+    s.Traw = nullptr;
+    s.traw_capacity = 0;
+    return JCDF_OK;
+}
+
+int32_t jcdf_upload_three_center(jcdf_handle* h, int32_t dev, const double* T, int64_t ld) {
+    int rc = upload_host(h, dev, T, ld);
+    if (rc) return rc;
+    h->shards[dev].t_uploaded = true;
+    h->shards[dev].b_ready = false;
+    return JCDF_OK;
+}
+
+int32_t jcdf_upload_three_center_device(jcdf_handle* h, int32_t dev, const double* T_dev, int64_t ld, int64_t col_begin,
+                                        int64_t col_count) {
+    JC_REQUIRE(h && T_dev, "jcdf_upload_three_center_device: NULL argument");
+    JC_REQUIRE(h->lay.mask_set, "jcdf_upload_three_center_device: call jcdf_set_mask first");
+    JC_REQUIRE(dev >= 0 && dev < (int)h->shards.size(), "device index out of range");
+    JC_REQUIRE(col_begin >= 0 && col_count >= 0 && col_begin + col_count <= h->lay.pairs_kept, "column window out of range");
+    JC_CUDA(cudaSetDevice(h->shards[dev].dev));
+    JC_CUDA(cudaDeviceSynchronize());  // the caller's producer stream is unknown
+    int rc = upload_window(h, dev, T_dev, ld, col_begin, col_count);
+    if (rc) return rc;
+    h->shards[dev].t_uploaded = true;
+    h->shards[dev].b_ready = false;
+    return JCDF_OK;
+}
+
+int32_t jcdf_set_B(jcdf_handle* h, int32_t dev, const double* B, int64_t ld) {
+    int rc = upload_host(h, dev, B, ld);
+    if (rc) return rc;
+    h->shards[dev].b_ready = true;
+    return JCDF_OK;
+}
+
+int32_t jcdf_set_B_device(jcdf_handle* h, int32_t dev, const double* B_dev, int64_t ld, int64_t col_begin,
+                          int64_t col_count) {
+    int rc = jcdf_upload_three_center_device(h, dev, B_dev, ld, col_begin, col_count);
+    if (rc) return rc;
+    h->shards[dev].b_ready = true;
+    return JCDF_OK;
+}
+
+int32_t jcdf_upload_metric(jcdf_handle* h, const double* J_PQ) {
+    JC_REQUIRE(h && J_PQ, "jcdf_upload_metric: NULL argument");
+    const int64_t Q = h->lay.Q;
+    h->host_metric.assign(J_PQ, J_PQ + Q * Q);
+    return JCDF_OK;
+}
+
+// potrf!('L') + trtri!('L','N') on the device, then B_g = sum_{h<=g} Linv[Q_g, Q_h] T_h per packed column window.
+int32_t jcdf_factor_and_form_B(jcdf_handle* h) {
+    JC_REQUIRE(h != nullptr, "jcdf_factor_and_form_B: NULL handle");
+    JC_REQUIRE(h->lay.mask_set, "jcdf_factor_and_form_B: call jcdf_set_mask first");
+    JC_REQUIRE(!h->host_metric.empty(), "jcdf_factor_and_form_B: call jcdf_upload_metric first");
+    JC_REQUIRE(h->n_ranks == 1, "jcdf_factor_and_form_B: multi-process B formation is not implemented; form B per rank and call jcdf_set_B");
+    const Layout& L = h->lay;
+    const int64_t Q = L.Q;
+    const int nd = (int)h->shards.size();
+    int64_t covered = 0;
+    for (int d = 0; d < nd; d++) {
+        JC_REQUIRE(h->shards[d].t_uploaded || h->shards[d].q_len == 0, "jcdf_factor_and_form_B: a shard has no three-centre integrals");
+        JC_REQUIRE(h->shards[d].q_begin == covered, "jcdf_factor_and_form_B: shards must tile [0, Q) contiguously in device order");
+        covered += h->shards[d].q_len;
+    }
+    JC_REQUIRE(covered == Q, "jcdf_factor_and_form_B: shards do not cover all auxiliary functions");
+
+    // --- factorisation on the first device -----------------------------------------------------------------------
+    Shard& s0 = h->shards[0];
+    JC_CUDA(cudaSetDevice(s0.dev));
+    int rc;
+    if (!s0.Metric && (rc = dev_alloc(&s0.Metric, (size_t)Q * Q))) return rc;
+    if (!s0.Linv && (rc = dev_alloc(&s0.Linv, (size_t)Q * Q))) return rc;
+    JC_CUDA(cudaMemcpyAsync(s0.Metric, h->host_metric.data(), sizeof(double) * Q * Q, cudaMemcpyHostToDevice, s0.stream));
+    cusolverDnHandle_t sol = nullptr;
+    cublasHandle_t blas = nullptr;
+    JC_CUSOLVER(cusolverDnCreate(&sol));
+    JC_CUSOLVER(cusolverDnSetStream(sol, s0.stream));
+    JC_CUBLAS(cublasCreate(&blas));
+    JC_CUBLAS(cublasSetStream(blas, s0.stream));
+    int lwork = 0;
+    JC_CUSOLVER(cusolverDnDpotrf_bufferSize(sol, CUBLAS_FILL_MODE_LOWER, (int)Q, s0.Metric, (int)Q, &lwork));
+    double* work = nullptr;
+    int* dinfo = nullptr;
+    if ((rc = dev_alloc(&work, (size_t)lwork))) return rc;
+    if ((rc = dev_alloc(&dinfo, 1))) return rc;
+    JC_CUSOLVER(cusolverDnDpotrf(sol, CUBLAS_FILL_MODE_LOWER, (int)Q, s0.Metric, (int)Q, work, lwork, dinfo));
+    int info = 0;
+    JC_CUDA(cudaMemcpyAsync(&info, dinfo, sizeof(int), cudaMemcpyDeviceToHost, s0.stream));
+    JC_CUDA(cudaStreamSynchronize(s0.stream));
+    cudaFree(work);
+    cudaFree(dinfo);
+    if (info != 0) {
+        cusolverDnDestroy(sol);
+        cublasDestroy(blas);
+        set_error("two-centre metric is not positive definite (potrf info = " + std::to_string(info) + ")");
+        return JCDF_ERR_NUMERIC;
+    }
+    // Linv = L^-1: triangular solve against the identity (same result as trtri!('L','N'))
+    {
+        std::vector<double> eye((size_t)Q * Q, 0.0);
+        for (int64_t i = 0; i < Q; i++) eye[(size_t)(i + Q * i)] = 1.0;
+        JC_CUDA(cudaMemcpyAsync(s0.Linv, eye.data(), sizeof(double) * Q * Q, cudaMemcpyHostToDevice, s0.stream));
+        JC_CUDA(cudaStreamSynchronize(s0.stream));
+    }
+    const double one = 1.0, zero = 0.0;
+    JC_CUBLAS(cublasDtrsm(blas, CUBLAS_SIDE_LEFT, CUBLAS_FILL_MODE_LOWER, CUBLAS_OP_N, CUBLAS_DIAG_NON_UNIT, (int)Q, (int)Q,
+                          &one, s0.Metric, (int)Q, s0.Linv, (int)Q));
+    JC_CUDA(cudaStreamSynchronize(s0.stream));
+    cusolverDnDestroy(sol);
+    cublasDestroy(blas);
+
+    // --- B formation, packed column windows ---------------------------------------------------------------------------
+    // Row-major packed rows [q][row_len] viewed column-major are (row_len x q) with ld = row_len, so
+    //   R_g^T (w x Qg) = sum_h  T_h^T (w x Qh) * Linv[Qg, Qh]^T .
+    std::vector<double*> linv_d(nd, nullptr), tmpT(nd, nullptr), R(nd, nullptr);
+    std::vector<cublasHandle_t> bl(nd, nullptr);
+    int64_t max_q = 0;
+    for (int d = 0; d < nd; d++) max_q = std::max(max_q, h->shards[d].q_len);
+    const int64_t win = std::max<int64_t>(1024, std::min<int64_t>(L.row_len, (((int64_t)1 << 26) / std::max<int64_t>(max_q, 1)) / 1024 * 1024));
+    for (int d = 0; d < nd; d++) {
+        Shard& s = h->shards[d];
+        JC_CUDA(cudaSetDevice(s.dev));
+        if (d == 0) linv_d[d] = s0.Linv;
+        else {
+            if ((rc = dev_alloc(&linv_d[d], (size_t)Q * Q))) return rc;
+            JC_CUDA(cudaMemcpyPeer(linv_d[d], s.dev, s0.Linv, s0.dev, sizeof(double) * Q * Q));
+        }
+        if (nd > 1 && (rc = dev_alloc(&tmpT[d], (size_t)(win * max_q)))) return rc;
+        if ((rc = dev_alloc(&R[d], (size_t)(win * std::max<int64_t>(s.q_len, 1))))) return rc;
+        JC_CUBLAS(cublasCreate(&bl[d]));
+        JC_CUBLAS(cublasSetStream(bl[d], s.stream));
+    }
+    for (int64_t c0 = 0; c0 < L.row_len; c0 += win) {
+        const int64_t w = std::min(win, L.row_len - c0);
+        for (int g = 0; g < nd; g++) {
+            Shard& sg = h->shards[g];
+            if (sg.q_len == 0) continue;
+            JC_CUDA(cudaSetDevice(sg.dev));
+            for (int hh = 0; hh <= g; hh++) {
+                Shard& sh = h->shards[hh];
+                if (sh.q_len == 0) continue;
+                const double* Tsrc;
+                int64_t ldT;
+                if (hh == g) { Tsrc = sg.Bp + c0; ldT = L.row_len; }
+                else {
+                    JC_CUDA(cudaMemcpy2DAsync(tmpT[g], sizeof(double) * w, sh.Bp + c0, sizeof(double) * L.row_len,
+                                              sizeof(double) * w, (size_t)sh.q_len, cudaMemcpyDefault, sg.stream));
+                    Tsrc = tmpT[g];
+                    ldT = w;
+                }
+                const double* Lblk = linv_d[g] + sg.q_begin + Q * sh.q_begin;
+                JC_CUBLAS(cublasDgemm(bl[g], CUBLAS_OP_N, CUBLAS_OP_T, (int)w, (int)sg.q_len, (int)sh.q_len, &one, Tsrc,
+                                      (int)ldT, Lblk, (int)Q, hh == 0 ? &zero : &one, R[g], (int)w));
+            }
+        }
+        for (int g = 0; g < nd; g++) { JC_CUDA(cudaSetDevice(h->shards[g].dev)); JC_CUDA(cudaStreamSynchronize(h->shards[g].stream)); }
+        for (int g = 0; g < nd; g++) {
+            Shard& sg = h->shards[g];
+            if (sg.q_len == 0) continue;
+            JC_CUDA(cudaSetDevice(sg.dev));
+            JC_CUDA(cudaMemcpy2DAsync(sg.Bp + c0, sizeof(double) * L.row_len, R[g], sizeof(double) * w, sizeof(double) * w,
+                                      (size_t)sg.q_len, cudaMemcpyDeviceToDevice, sg.stream));
+        }
+        for (int g = 0; g < nd; g++) { JC_CUDA(cudaSetDevice(h->shards[g].dev)); JC_CUDA(cudaStreamSynchronize(h->shards[g].stream)); }
+    }
+    for (int d = 0; d < nd; d++) {
+        JC_CUDA(cudaSetDevice(h->shards[d].dev));
+        if (d > 0 && linv_d[d]) cudaFree(linv_d[d]);
+        if (tmpT[d]) cudaFree(tmpT[d]);
+        if (R[d]) cudaFree(R[d]);
+        if (bl[d]) cublasDestroy(bl[d]);
+        h->shards[d].b_ready = true;
+    }
+    return JCDF_OK;
+}
+
+int32_t jcdf_get_metric_inverse(jcdf_handle* h, double* Linv_out) {
+    JC_REQUIRE(h && Linv_out, "jcdf_get_metric_inverse: NULL argument");
+    JC_REQUIRE(h->shards[0].Linv != nullptr, "jcdf_get_metric_inverse: no factorisation yet");
+    JC_CUDA(cudaSetDevice(h->shards[0].dev));
+    JC_CUDA(cudaMemcpy(Linv_out, h->shards[0].Linv, sizeof(double) * h->lay.Q * h->lay.Q, cudaMemcpyDeviceToHost));
+    return JCDF_OK;
+}
+
+int32_t jcdf_set_core_hamiltonian(jcdf_handle* h, const double* H) {
+    JC_REQUIRE(h && H, "jcdf_set_core_hamiltonian: NULL argument");
+    JC_REQUIRE(h->lay.mask_set, "jcdf_set_core_hamiltonian: call jcdf_set_mask first");
+    Shard& s = h->shards[0];
+    JC_CUDA(cudaSetDevice(s.dev));
+    JC_CUDA(cudaMemcpy(s.Hdev, H, sizeof(double) * h->lay.N * h->lay.N, cudaMemcpyHostToDevice));
+    s.has_H = true;
+    return JCDF_OK;
+}
+
+static int fock_build_impl(jcdf_handle* h, const double* C_occ, int64_t ldc, const double* H, double* F_out,
+                           double* stage_seconds, bool device_ptrs) {
+    JC_REQUIRE(h && C_occ && F_out, "jcdf_fock_build: NULL argument");
+    const Layout& L = h->lay;
+    JC_REQUIRE(L.mask_set, "jcdf_fock_build: call jcdf_set_mask first");
+    JC_REQUIRE(ldc >= L.N, "jcdf_fock_build: ldc < N");
+    const int nd = (int)h->shards.size();
+    for (int d = 0; d < nd; d++) JC_REQUIRE(h->shards[d].b_ready, "jcdf_fock_build: B has not been formed on every device");
+    int rc = ensure_comm(h);
+    if (rc) return rc;
+    auto t0 = std::chrono::steady_clock::now();
+    const bool owns_rank0 = (h->rank == 0);
+    const bool reduce = (h->n_ranks * nd > 1);
+    const size_t nn = (size_t)L.N * L.N;
+
+    for (int d = 0; d < nd; d++) {
+        Shard& s = h->shards[d];
+        JC_CUDA(cudaSetDevice(s.dev));
+        JC_CUDA(cudaEventRecord(s.ev[EV_START], s.stream));
+        // C_occ -> device, compacted to ld = N
+        if (device_ptrs) {
+            JC_CUDA(cudaMemcpy2DAsync(s.Craw, sizeof(double) * L.N, C_occ, sizeof(double) * ldc, sizeof(double) * L.N,
+                                      (size_t)L.occ, cudaMemcpyDefault, s.stream));
+        } else {
+            JC_CUDA(cudaMemcpy2DAsync(s.Craw, sizeof(double) * L.N, C_occ, sizeof(double) * ldc, sizeof(double) * L.N,
+                                      (size_t)L.occ, cudaMemcpyHostToDevice, s.stream));
+        }
+        bool add_H = false;
+        if (d == 0 && owns_rank0) {
+            if (H != nullptr) {
+                JC_CUDA(cudaMemcpyAsync(s.Hdev, H, sizeof(double) * nn, device_ptrs ? cudaMemcpyDefault : cudaMemcpyHostToDevice,
+                                        s.stream));
+                s.has_H = true;
+            }
+            add_H = s.has_H;
+        }
+        JC_CUDA(cudaEventRecord(s.ev[EV_H2D], s.stream));
+        launch_prep(L, s, L.N);
+        JC_CUDA(cudaEventRecord(s.ev[EV_PREP], s.stream));
+        launch_half_transform(L, s, h->sm_count);
+        JC_CUDA(cudaEventRecord(s.ev[EV_W], s.stream));
+        launch_exchange(L, s, h->sm_count);
+        JC_CUDA(cudaEventRecord(s.ev[EV_K], s.stream));
+        JC_CUDA(cudaEventRecord(s.ev[EV_V], s.stream));  // overwritten inside launch_coulomb when q_len > 0
+        launch_coulomb(L, s, h->sm_count);
+        JC_CUDA(cudaEventRecord(s.ev[EV_J], s.stream));
+        launch_epilogue(L, s, add_H);
+        JC_CUDA(cudaEventRecord(s.ev[EV_EPI], s.stream));
+        JC_CUDA(cudaGetLastError());
+    }
+    if (reduce) {
+        const NcclApi& n = nccl();
+        JC_NCCL(n.GroupStart());
+        for (int d = 0; d < nd; d++) {
+            Shard& s = h->shards[d];
+            JC_NCCL(n.AllReduce(s.F, s.F, nn, NCCL_DOUBLE, NCCL_SUM, s.nccl_comm, s.stream));
+        }
+        JC_NCCL(n.GroupEnd());
+    }
+    for (int d = 0; d < nd; d++) {
+        Shard& s = h->shards[d];
+        JC_CUDA(cudaSetDevice(s.dev));
+        JC_CUDA(cudaEventRecord(s.ev[EV_AR], s.stream));
+    }
+    {
+        Shard& s = h->shards[0];
+        JC_CUDA(cudaSetDevice(s.dev));
+        JC_CUDA(cudaMemcpyAsync(F_out, s.F, sizeof(double) * nn, device_ptrs ? cudaMemcpyDefault : cudaMemcpyDeviceToHost,
+                                s.stream));
+        JC_CUDA(cudaEventRecord(s.ev[EV_D2H], s.stream));
+    }
+    for (int d = 0; d < nd; d++) {
+        Shard& s = h->shards[d];
+        JC_CUDA(cudaSetDevice(s.dev));
+        JC_CUDA(cudaStreamSynchronize(s.stream));
+    }
+    auto t1 = std::chrono::steady_clock::now();
+    double mx[JCDF_N_STAGES] = {};
+    for (int d = 0; d < nd; d++) {
+        Shard& s = h->shards[d];
+        JC_CUDA(cudaSetDevice(s.dev));
+        auto el = [&](int a, int b) { float ms = 0; cudaEventElapsedTime(&ms, s.ev[a], s.ev[b]); return (double)ms; };
+        s.last_ms[JCDF_T_H2D] = el(EV_START, EV_H2D);
+        s.last_ms[JCDF_T_DENSITY] = el(EV_H2D, EV_PREP);
+        s.last_ms[JCDF_T_W] = el(EV_PREP, EV_W);
+        s.last_ms[JCDF_T_K] = el(EV_W, EV_K);
+        s.last_ms[JCDF_T_V] = el(EV_K, EV_V);
+        s.last_ms[JCDF_T_J] = el(EV_V, EV_J);
+        s.last_ms[JCDF_T_EPILOGUE] = el(EV_J, EV_EPI);
+        s.last_ms[JCDF_T_ALLREDUCE] = el(EV_EPI, EV_AR);
+        s.last_ms[JCDF_T_D2H] = d == 0 ? el(EV_AR, EV_D2H) : 0.0;
+        s.last_ms[JCDF_T_TOTAL] = std::chrono::duration<double, std::milli>(t1 - t0).count();
+        for (int i = 0; i < JCDF_N_STAGES; i++) mx[i] = std::max(mx[i], s.last_ms[i]);
+    }
+    if (stage_seconds)
+        for (int i = 0; i < JCDF_N_STAGES; i++) stage_seconds[i] = mx[i] * 1e-3;
+    return JCDF_OK;
+}
+
+int32_t jcdf_fock_build(jcdf_handle* h, const double* C_occ, int64_t ldc, const double* H, double* F_out,
+                        double* stage_seconds) {
+    return fock_build_impl(h, C_occ, ldc, H, F_out, stage_seconds, false);
+}
+
+int32_t jcdf_fock_build_device(jcdf_handle* h, const double* C_occ_dev, int64_t ldc, const double* H_dev,
+                               double* F_out_dev, double* stage_seconds) {
+    return fock_build_impl(h, C_occ_dev, ldc, H_dev, F_out_dev, stage_seconds, true);
+}
+
+int32_t jcdf_eigh(jcdf_handle* h, const double* F, const double* X, double* evals, double* C) {
+    JC_REQUIRE(h && F && X && evals && C, "jcdf_eigh: NULL argument");
+    const int64_t N = h->lay.N;
+    Shard& s = h->shards[0];
+    JC_CUDA(cudaSetDevice(s.dev));
+    double *dF = nullptr, *dX = nullptr, *dT = nullptr, *dW = nullptr, *work = nullptr;
+    int* dinfo = nullptr;
+    int rc;
+    if ((rc = dev_alloc(&dF, (size_t)N * N))) return rc;
+    if ((rc = dev_alloc(&dX, (size_t)N * N))) return rc;
+    if ((rc = dev_alloc(&dT, (size_t)N * N))) return rc;
+    if ((rc = dev_alloc(&dW, (size_t)N))) return rc;
+    if ((rc = dev_alloc(&dinfo, 1))) return rc;
+    cublasHandle_t blas = nullptr;
+    cusolverDnHandle_t sol = nullptr;
+    JC_CUBLAS(cublasCreate(&blas));
+    JC_CUBLAS(cublasSetStream(blas, s.stream));
+    JC_CUSOLVER(cusolverDnCreate(&sol));
+    JC_CUSOLVER(cusolverDnSetStream(sol, s.stream));
+    JC_CUDA(cudaMemcpyAsync(dF, F, sizeof(double) * N * N, cudaMemcpyHostToDevice, s.stream));
+    JC_CUDA(cudaMemcpyAsync(dX, X, sizeof(double) * N * N, cudaMemcpyHostToDevice, s.stream));
+    const double one = 1.0, zero = 0.0;
+    // workspace_a = X^T F ; Fp = workspace_a X   (symm!/gemm!, SCF.jl:1083-1084)
+    JC_CUBLAS(cublasDgemm(blas, CUBLAS_OP_T, CUBLAS_OP_N, (int)N, (int)N, (int)N, &one, dX, (int)N, dF, (int)N, &zero, dT, (int)N));
+    JC_CUBLAS(cublasDgemm(blas, CUBLAS_OP_N, CUBLAS_OP_N, (int)N, (int)N, (int)N, &one, dT, (int)N, dX, (int)N, &zero, dF, (int)N));
+    int lwork = 0;
+    JC_CUSOLVER(cusolverDnDsyevd_bufferSize(sol, CUSOLVER_EIG_MODE_VECTOR, CUBLAS_FILL_MODE_UPPER, (int)N, dF, (int)N, dW, &lwork));
+    if ((rc = dev_alloc(&work, (size_t)lwork))) return rc;
+    JC_CUSOLVER(cusolverDnDsyevd(sol, CUSOLVER_EIG_MODE_VECTOR, CUBLAS_FILL_MODE_UPPER, (int)N, dF, (int)N, dW, work, lwork, dinfo));
+    // C = X U  (symm!, SCF.jl:1095)
+    JC_CUBLAS(cublasDgemm(blas, CUBLAS_OP_N, CUBLAS_OP_N, (int)N, (int)N, (int)N, &one, dX, (int)N, dF, (int)N, &zero, dT, (int)N));
+    int info = 0;
+    JC_CUDA(cudaMemcpyAsync(&info, dinfo, sizeof(int), cudaMemcpyDeviceToHost, s.stream));
+    JC_CUDA(cudaMemcpyAsync(evals, dW, sizeof(double) * N, cudaMemcpyDeviceToHost, s.stream));
+    JC_CUDA(cudaMemcpyAsync(C, dT, sizeof(double) * N * N, cudaMemcpyDeviceToHost, s.stream));
+    JC_CUDA(cudaStreamSynchronize(s.stream));
+    cublasDestroy(blas);
+    cusolverDnDestroy(sol);
+    cudaFree(dF); cudaFree(dX); cudaFree(dT); cudaFree(dW); cudaFree(work); cudaFree(dinfo);
+    if (info != 0) {
+        set_error("syevd did not converge (info = " + std::to_string(info) + ")");
+        return JCDF_ERR_NUMERIC;
+    }
+    return JCDF_OK;
+}
+
+int32_t jcdf_comm_unique_id(uint8_t id_out[128]) {
+    JC_REQUIRE(id_out != nullptr, "jcdf_comm_unique_id: NULL argument");
+    const NcclApi& n = nccl();
+    if (!n.ok) { set_error(std::string("NCCL unavailable: ") + n.why); return JCDF_ERR_NCCL; }
+    NcclApi::UniqueId id;
+    JC_NCCL(n.GetUniqueId(&id));
+    memcpy(id_out, id.internal, 128);
+    return JCDF_OK;
+}
+
+int32_t jcdf_comm_init_rank(jcdf_handle* h, int32_t n_ranks, int32_t rank, const uint8_t id_bytes[128]) {
+    JC_REQUIRE(h && id_bytes, "jcdf_comm_init_rank: NULL argument");
+    JC_REQUIRE(n_ranks >= 1 && rank >= 0 && rank < n_ranks, "jcdf_comm_init_rank: bad rank");
+    JC_REQUIRE(!h->comm_ready, "jcdf_comm_init_rank: communicator already initialised");
+    const NcclApi& n = nccl();
+    if (!n.ok) { set_error(std::string("NCCL unavailable: ") + n.why); return JCDF_ERR_NCCL; }
+    const int nd = (int)h->shards.size();
+    h->n_ranks = n_ranks;
+    h->rank = rank;
+    NcclApi::UniqueId id;
+    memcpy(id.internal, id_bytes, 128);
+    JC_NCCL(n.GroupStart());
+    for (int d = 0; d < nd; d++) {
+        JC_CUDA(cudaSetDevice(h->shards[d].dev));
+        JC_NCCL(n.CommInitRank(&h->shards[d].nccl_comm, n_ranks * nd, id, rank * nd + d));
+    }
+    JC_NCCL(n.GroupEnd());
+    h->comm_ready = true;
+    return JCDF_OK;
+}
+
+int32_t jcdf_get_layout(jcdf_handle* h, jcdf_layout_info* o) {
+    JC_REQUIRE(h && o, "jcdf_get_layout: NULL argument");
+    const Layout& L = h->lay;
+    memset(o, 0, sizeof(*o));
+    o->N = L.N; o->Q = L.Q; o->occ = L.occ;
+    o->n_pad = L.n_pad; o->occ_pad = L.occ_pad;
+    o->tiles_total = L.tiles_total; o->tiles_kept = L.tiles_kept;
+    o->pairs_kept = L.pairs_kept; o->pairs_tri = L.pairs_tri;
+    o->packed_row_len = L.row_len;
+    for (const Shard& s : h->shards) {
+        o->q_local += s.q_len;
+        o->bytes_B += s.q_len * L.row_len * 8;
+        o->bytes_W += (int64_t)s.xplan.chunks * L.npt64 * 2048 * 8;
+    }
+    o->kernel_launches_per_build = 7;  // prep_cs, density, half_transform, exchange, coulomb_v, coulomb_j, epilogue
+    return JCDF_OK;
+}
+
+int32_t jcdf_fill_synthetic_B(jcdf_handle* h, uint64_t seed, double decay_length) {
+    JC_REQUIRE(h != nullptr, "jcdf_fill_synthetic_B: NULL handle");
+    JC_REQUIRE(h->lay.mask_set, "jcdf_fill_synthetic_B: call jcdf_set_mask first");
+    for (Shard& s : h->shards) {
+        JC_CUDA(cudaSetDevice(s.dev));
+        launch_fill_synthetic(h->lay, s, seed, decay_length);
+        JC_CUDA(cudaGetLastError());
+        s.b_ready = true;
+    }
+    return JCDF_OK;
+}
+
+int32_t jcdf_last_kernel_ms(jcdf_handle* h, int32_t dev, double* out) {
+    JC_REQUIRE(h && out, "jcdf_last_kernel_ms: NULL argument");
+    JC_REQUIRE(dev >= 0 && dev < (int)h->shards.size(), "jcdf_last_kernel_ms: device index out of range");
+    for (int i = 0; i < JCDF_N_STAGES; i++) out[i] = h->shards[dev].last_ms[i];
+    return JCDF_OK;
+}
+
+}  // extern "C"

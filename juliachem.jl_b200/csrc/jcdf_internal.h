@@ -1,0 +1,104 @@
+// Internal types shared by the libjcdf translation units (not part of the C ABI).
+#pragma once
+#include <cstdint>
+#include <string>
+#include <vector>
+#include <cuda_runtime.h>
+
+#include "../../include/jcdf.h"
+
+namespace jcdf {
+
+// Geometry of the tile-compacted layout; replicated on every device.
+struct Layout {
+    int64_t N = 0, Q = 0, occ = 0;
+    int nb = 0;         // 32-wide blocks per dimension
+    int n_pad = 0;      // 32 * nb
+    int occ_pad = 0;    // occ rounded up to 8
+    int bm = 0;         // half-transform M tile (rows i per work item), multiple of 16, <= 128
+    int n_mt = 0;       // M tiles: bm * n_mt >= occ_pad
+    int npt64 = 0;      // 64-wide W column tiles
+    int n_pt128 = 0;    // 128-wide half-transform p tiles = ceil(nb / 4)
+    int n128 = 0;       // 128-wide exchange tiles per dimension
+    int64_t pairs_kept = 0, pairs_tri = 0;
+    int64_t tiles_total = 0, tiles_kept = 0;
+    int64_t row_len = 0;  // tiles_kept * 1024 doubles per auxiliary row
+    bool mask_set = false;
+    std::vector<int32_t> tile_index;  // [a * nb + b], a >= b: index of the stored tile or -1
+    std::vector<int32_t> tile_a, tile_b;
+    std::vector<int64_t> dest_of_col;  // reference pair column -> offset inside a packed row, or -1
+};
+
+// event points recorded on the shard's stream during one build, in launch order
+enum EvPoint { EV_START = 0, EV_H2D, EV_PREP, EV_W, EV_K, EV_V, EV_J, EV_EPI, EV_AR, EV_D2H, EV_COUNT };
+
+struct ExchangePlan {
+    int n_tiles = 0;     // lower-triangular 128x128 output tiles
+    int n_slices = 0;    // split of the contraction index per tile
+    int chunks = 0;      // 32-row k chunks held by the shard
+    int chunks_per_slice = 0;
+};
+
+struct Shard {
+    int dev = 0;
+    int64_t q_begin = 0, q_len = 0;
+    cudaStream_t stream = nullptr;
+    // HBM-resident operands
+    double* Bp = nullptr;      // [q_len][row_len] packed, swizzled tiles
+    double* W = nullptr;       // [chunks][npt64][32][64] half-transformed tensor
+    double* Cs = nullptr;      // [nb][n_mt][32][bm] C_occ slabs for the half-transform
+    double* Craw = nullptr;    // N x occ column-major upload
+    double* dt = nullptr;      // [row_len] packed, weighted density
+    double* Jt = nullptr;      // [row_len] packed Coulomb vector
+    double* V = nullptr;       // [q_len]
+    double* Kpart = nullptr;   // [n_tiles * n_slices][128*128]
+    double* F = nullptr;       // N x N column-major partial / reduced Fock
+    double* Hdev = nullptr;    // N x N (only where H is added)
+    double* Traw = nullptr;    // staging window for uploads
+    int64_t traw_capacity = 0;
+    int32_t* d_tile_index = nullptr;
+    int32_t* d_tile_a = nullptr;
+    int32_t* d_tile_b = nullptr;
+    int64_t* d_dest_of_col = nullptr;
+    uint8_t* d_fn_mask = nullptr;   // N x N or nullptr when unscreened
+    double* Linv = nullptr;    // Q x Q on the first device only
+    double* Metric = nullptr;
+    bool has_H = false;
+    bool b_ready = false;
+    bool t_uploaded = false;
+    ExchangePlan xplan;
+    cudaEvent_t ev[EV_COUNT] = {};
+    double last_ms[JCDF_N_STAGES] = {};
+    void* nccl_comm = nullptr;
+};
+
+}  // namespace jcdf
+
+struct jcdf_handle {
+    jcdf::Layout lay;
+    std::vector<jcdf::Shard> shards;
+    int n_ranks = 1, rank = 0;   // process-level (one process per GPU mode)
+    bool comm_ready = false;
+    bool shards_set = false;
+    int sm_count = 148;
+    std::vector<double> host_metric;
+};
+
+namespace jcdf {
+
+// ---- kernel launchers (kernels_k.cu / kernels_j.cu / kernels_misc.cu) ----------------------------------------------
+void launch_prep(const Layout& L, Shard& s, int64_t ldc);
+void launch_half_transform(const Layout& L, Shard& s, int sm_count);
+void launch_exchange(const Layout& L, Shard& s, int sm_count);
+void launch_coulomb(const Layout& L, Shard& s, int sm_count);
+void launch_epilogue(const Layout& L, Shard& s, bool add_H);
+void launch_scatter_pairs(const Layout& L, Shard& s, const double* T_dev, int64_t ld, int64_t col_begin,
+                          int64_t col_count);
+void launch_fill_synthetic(const Layout& L, Shard& s, uint64_t seed, double decay_length);
+size_t half_transform_smem_bytes(int bm);
+size_t exchange_smem_bytes();
+int kernels_per_build();
+
+void set_error(const std::string& msg);
+
+}  // namespace jcdf

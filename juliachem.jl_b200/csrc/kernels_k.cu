@@ -1,0 +1,438 @@
+// Exchange (K) path of the DF-RHF Fock build on sm_100a: FP64 tensor-core (DMMA m8n8k4) tiles fed by 1-D bulk
+// async copies (TMA unit) through an mbarrier ring.
+//
+//   half-transform   W[(Q,i), p] = sum_q C_occ[q,i] * B[Q,p,q]        replaces calculate_W_screened
+//                                                                      (ScreenedDF.jl:242-289; dense :216 of DensityFitting.jl)
+//   exchange         K[p,q]     = sum_(Q,i) W[(Q,i),p] * W[(Q,i),q]    replaces calculate_K_lower_diagonal_block_no_screen
+//                                                                      (ScreenedDF.jl:548-641; dense DensityFitting.jl:219)
+//
+// Both kernels are persistent (one CTA per SM, static round-robin over work items), warp-specialised: warp 8 is
+// the copy producer, warps 0-7 issue DMMA.  All operands are stored in HBM pre-swizzled (dmma_common.cuh: swz) so a
+// dense bulk copy lands bank-conflict-free in shared memory.
+#include "dmma_common.cuh"
+#include "jcdf_internal.h"
+
+namespace jcdf {
+
+constexpr int NSTAGE = 3;
+constexpr int CONSUMER_WARPS = 8;
+constexpr int CTA_THREADS = (CONSUMER_WARPS + 1) * 32;
+
+// =====================================================================================================================
+// C_occ re-layout and packed density
+// =====================================================================================================================
+// Cs[kb][mt][kr][swz(kr, m)] = C_occ[q = 32 kb + kr, i = mt*bm + m]   (zero beyond N / occ)
+__global__ void k_prep_cs(const double* __restrict__ Craw, int64_t ldc, double* __restrict__ Cs, int N, int occ, int nb,
+                          int n_mt, int bm) {
+    int64_t total = (int64_t)nb * n_mt * 32 * bm;
+    for (int64_t idx = blockIdx.x * (int64_t)blockDim.x + threadIdx.x; idx < total;
+         idx += (int64_t)gridDim.x * blockDim.x) {
+        int kr = (int)(idx % 32);
+        int64_t r1 = idx / 32;
+        int m = (int)(r1 % bm);
+        int64_t r2 = r1 / bm;
+        int mt = (int)(r2 % n_mt);
+        int kb = (int)(r2 / n_mt);
+        int q = kb * 32 + kr, i = mt * bm + m;
+        double v = (q < N && i < occ) ? Craw[q + ldc * i] : 0.0;
+        Cs[(((int64_t)kb * n_mt + mt) * 32 + kr) * bm + swz(kr, m)] = v;
+    }
+}
+
+// dt[tile][r][swz(r,c)] = w * sum_i C[p,i] C[q,i],  p = 32 a + r, q = 32 b + c,  w = 1 on diagonal tiles (full
+// square stored) and 2 on off-diagonal tiles — the doubled off-diagonal density of copy_screened_density_to_array
+// (ScreenedDF.jl:305-316) expressed in tile space.
+__global__ void k_density_packed(const double* __restrict__ Craw, int64_t ldc, double* __restrict__ dt,
+                                 const int32_t* __restrict__ tile_a, const int32_t* __restrict__ tile_b, int N, int occ) {
+    int tile = blockIdx.x;
+    int a = tile_a[tile], b = tile_b[tile];
+    double w = (a == b) ? 1.0 : 2.0;
+    int c = threadIdx.x & 31;
+    int q = b * 32 + c;
+    for (int r = threadIdx.x >> 5; r < 32; r += blockDim.x >> 5) {
+        int p = a * 32 + r;
+        double acc = 0.0;
+        if (p < N && q < N) {
+            for (int i = 0; i < occ; i++) acc = fma(Craw[p + ldc * i], Craw[q + ldc * i], acc);
+        }
+        dt[(int64_t)tile * TILE_ELEMS + r * 32 + swz(r, c)] = w * acc;
+    }
+}
+
+void launch_prep(const Layout& L, Shard& s, int64_t ldc) {
+    int64_t total = (int64_t)L.nb * L.n_mt * 32 * L.bm;
+    int blocks = (int)std::min<int64_t>((total + 255) / 256, 148 * 16);
+    k_prep_cs<<<blocks, 256, 0, s.stream>>>(s.Craw, ldc, s.Cs, (int)L.N, (int)L.occ, L.nb, L.n_mt, L.bm);
+    k_density_packed<<<(int)L.tiles_kept, 256, 0, s.stream>>>(s.Craw, ldc, s.dt, s.d_tile_a, s.d_tile_b, (int)L.N,
+                                                               (int)L.occ);
+}
+
+// =====================================================================================================================
+// Half-transform
+// =====================================================================================================================
+struct HTParams {
+    const double* Bp;
+    int64_t row_len;
+    const int32_t* tile_index;
+    const double* Cs;
+    double* W;
+    int q_len, nb, n_mt, n_pt128, npt64, occ_pad;
+    int64_t n_items;
+};
+
+// One work item = (auxiliary row Q, 128-wide p tile, M tile of BM = 8*MT occupied orbitals):
+//   out[i, p] = sum_q Cs[q][i] * Bsym_Q[q][p]      (M = i, N = p, K = q)
+// The k loop walks the 32-wide q blocks; for p block pb and q block kb the stored tile is (max, min): read as
+// [k][n] when kb >= pb and transposed as [n][k] when kb < pb, so each stored tile serves both triangles.
+template <int MT, bool TRANSPOSED>
+__device__ __forceinline__ void ht_slab(double (&acc)[MT][2][2], const double* __restrict__ sA,
+                                        const double* __restrict__ sB, int nl0, int g, int t) {
+    constexpr int BM = 8 * MT;
+#pragma unroll
+    for (int k0 = 0; k0 < KSLAB; k0 += 4) {
+        const int kr = k0 + t;
+        double a[MT], b[2];
+#pragma unroll
+        for (int jm = 0; jm < MT; jm++) a[jm] = sA[kr * BM + ((8 * jm + g) ^ (t << 2))];
+#pragma unroll
+        for (int jn = 0; jn < 2; jn++) {
+            const int n = nl0 + 8 * jn + g;
+            b[jn] = TRANSPOSED ? sB[n * 32 + (kr ^ ((n & 3) << 2))] : sB[kr * 32 + (n ^ (t << 2))];
+        }
+#pragma unroll
+        for (int jm = 0; jm < MT; jm++)
+#pragma unroll
+            for (int jn = 0; jn < 2; jn++) dmma(acc[jm][jn][0], acc[jm][jn][1], a[jm], b[jn]);
+    }
+}
+
+template <int MT>
+__global__ void __launch_bounds__(CTA_THREADS, 1) k_half_transform(HTParams prm) {
+    constexpr int BM = 8 * MT;
+    constexpr int STAGE_DOUBLES = 32 * BM + 4 * TILE_ELEMS;
+    extern __shared__ __align__(128) unsigned char smem_raw[];
+    double* stages = reinterpret_cast<double*>(smem_raw);
+    uint64_t* full = reinterpret_cast<uint64_t*>(stages + (size_t)NSTAGE * STAGE_DOUBLES);
+    uint64_t* empty = full + NSTAGE;
+    int* present = reinterpret_cast<int*>(empty + NSTAGE);
+
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    if (threadIdx.x == 0) {
+        for (int s = 0; s < NSTAGE; s++) {
+            mbar_init(&full[s], 1);
+            mbar_init(&empty[s], CONSUMER_WARPS);
+        }
+        fence_barrier_init();
+        fence_proxy_async();
+    }
+    __syncthreads();
+
+    const int nb = prm.nb, n_mt = prm.n_mt, n_pt = prm.n_pt128;
+    PipeState ps;
+
+    if (warp == CONSUMER_WARPS) {
+        // ------------------------------------------------ producer ------------------------------------------------
+        if (lane == 0) {
+            for (int64_t item = blockIdx.x; item < prm.n_items; item += gridDim.x) {
+                const int mt = (int)(item % n_mt);
+                const int64_t r1 = item / n_mt;
+                const int pt = (int)(r1 % n_pt);
+                const int64_t qrow = r1 / n_pt;
+                const double* Brow = prm.Bp + qrow * prm.row_len;
+                for (int kb = 0; kb < nb; kb++) {
+                    mbar_wait(&empty[ps.stage], ps.phase ^ 1u);
+                    int mask = 0;
+                    int tix[4];
+#pragma unroll
+                    for (int j = 0; j < 4; j++) {
+                        const int pb = 4 * pt + j;
+                        tix[j] = -1;
+                        if (pb < nb) {
+                            const int a = max(pb, kb), b = min(pb, kb);
+                            tix[j] = prm.tile_index[a * nb + b];
+                            if (tix[j] >= 0) mask |= 1 << j;
+                        }
+                    }
+                    present[ps.stage] = mask;
+                    double* st = stages + (size_t)ps.stage * STAGE_DOUBLES;
+                    if (mask) {
+                        const uint32_t bytes = 32u * BM * 8u + (uint32_t)__popc(mask) * (TILE_ELEMS * 8u);
+                        mbar_arrive_expect_tx(&full[ps.stage], bytes);
+                        bulk_g2s(st, prm.Cs + ((int64_t)kb * n_mt + mt) * (32 * BM), 32u * BM * 8u, &full[ps.stage]);
+#pragma unroll
+                        for (int j = 0; j < 4; j++)
+                            if (tix[j] >= 0)
+                                bulk_g2s(st + 32 * BM + j * TILE_ELEMS, Brow + (int64_t)tix[j] * TILE_ELEMS,
+                                         TILE_ELEMS * 8u, &full[ps.stage]);
+                    } else {
+                        mbar_arrive(&full[ps.stage]);
+                    }
+                    ps.advance<NSTAGE>();
+                }
+            }
+        }
+        return;
+    }
+
+    // ---------------------------------------------------- consumers ----------------------------------------------------
+    const int g = lane >> 2, t = lane & 3;
+    const int j = warp >> 1;           // p block inside the 128-wide tile
+    const int nl0 = (warp & 1) * 16;   // 16-column strip inside the block
+    for (int64_t item = blockIdx.x; item < prm.n_items; item += gridDim.x) {
+        const int mt = (int)(item % n_mt);
+        const int64_t r1 = item / n_mt;
+        const int pt = (int)(r1 % n_pt);
+        const int64_t qrow = r1 / n_pt;
+        const int pbg = 4 * pt + j;
+        double acc[MT][2][2];
+#pragma unroll
+        for (int jm = 0; jm < MT; jm++)
+#pragma unroll
+            for (int jn = 0; jn < 2; jn++) acc[jm][jn][0] = acc[jm][jn][1] = 0.0;
+
+        for (int kb = 0; kb < nb; kb++) {
+            mbar_wait(&full[ps.stage], ps.phase);
+            const int mask = present[ps.stage];
+            if ((mask >> j) & 1) {
+                const double* sA = stages + (size_t)ps.stage * STAGE_DOUBLES;
+                const double* sB = sA + 32 * BM + j * TILE_ELEMS;
+                if (kb < pbg) ht_slab<MT, true>(acc, sA, sB, nl0, g, t);
+                else ht_slab<MT, false>(acc, sA, sB, nl0, g, t);
+            }
+            __syncwarp();
+            if (lane == 0) mbar_arrive(&empty[ps.stage]);
+            ps.advance<NSTAGE>();
+        }
+        // epilogue: W[(Q,i)][p], 16-byte stores into the swizzled [32 x 64] W tiles
+#pragma unroll
+        for (int jm = 0; jm < MT; jm++) {
+            const int i = mt * BM + 8 * jm + g;
+            if (i < prm.occ_pad) {
+                const int64_t krow = qrow * prm.occ_pad + i;
+                const int64_t kc = krow >> 5;
+                const int kr = (int)(krow & 31);
+#pragma unroll
+                for (int jn = 0; jn < 2; jn++) {
+                    const int p = 128 * pt + 32 * j + nl0 + 8 * jn + 2 * t;
+                    const int p64 = p >> 6, pc = p & 63;
+                    if (p64 < prm.npt64) {
+                        double2 v = make_double2(acc[jm][jn][0], acc[jm][jn][1]);
+                        *reinterpret_cast<double2*>(prm.W + ((kc * prm.npt64 + p64) * 32 + kr) * 64 + swz(kr, pc)) = v;
+                    }
+                }
+            }
+        }
+    }
+}
+
+size_t half_transform_smem_bytes(int bm) {
+    return (size_t)NSTAGE * (32 * bm + 4 * TILE_ELEMS) * 8 + 2 * NSTAGE * 8 + NSTAGE * 4 + 16;
+}
+
+template <int MT>
+static void launch_ht_t(const HTParams& prm, int grid, cudaStream_t st) {
+    size_t smem = half_transform_smem_bytes(8 * MT);
+    cudaFuncSetAttribute(k_half_transform<MT>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+    k_half_transform<MT><<<grid, CTA_THREADS, smem, st>>>(prm);
+}
+
+void launch_half_transform(const Layout& L, Shard& s, int sm_count) {
+    HTParams prm;
+    prm.Bp = s.Bp;
+    prm.row_len = L.row_len;
+    prm.tile_index = s.d_tile_index;
+    prm.Cs = s.Cs;
+    prm.W = s.W;
+    prm.q_len = (int)s.q_len;
+    prm.nb = L.nb;
+    prm.n_mt = L.n_mt;
+    prm.n_pt128 = L.n_pt128;
+    prm.npt64 = L.npt64;
+    prm.occ_pad = L.occ_pad;
+    prm.n_items = (int64_t)s.q_len * L.n_pt128 * L.n_mt;
+    int grid = (int)std::min<int64_t>(prm.n_items, sm_count);
+    if (grid <= 0) return;
+    switch (L.bm / 8) {
+        case 2: launch_ht_t<2>(prm, grid, s.stream); break;
+        case 4: launch_ht_t<4>(prm, grid, s.stream); break;
+        case 6: launch_ht_t<6>(prm, grid, s.stream); break;
+        case 8: launch_ht_t<8>(prm, grid, s.stream); break;
+        case 10: launch_ht_t<10>(prm, grid, s.stream); break;
+        case 12: launch_ht_t<12>(prm, grid, s.stream); break;
+        case 14: launch_ht_t<14>(prm, grid, s.stream); break;
+        case 16: launch_ht_t<16>(prm, grid, s.stream); break;
+        default: break;
+    }
+}
+
+// =====================================================================================================================
+// Exchange (SYRK-like):  Kpart[item][m][n] = sum_{k in slice} W[k][128 ta + m] * W[k][128 tb + n]
+// =====================================================================================================================
+struct XParams {
+    const double* W;
+    double* Kpart;
+    int npt64, n_tiles, n_slices, chunks, chunks_per_slice;
+    int64_t n_items;
+};
+
+constexpr int X_STAGE_DOUBLES = 4 * 32 * 64;  // A0 A1 B0 B1, each a [32 x 64] W tile
+
+__global__ void __launch_bounds__(CTA_THREADS, 1) k_exchange(XParams prm) {
+    extern __shared__ __align__(128) unsigned char smem_raw[];
+    double* stages = reinterpret_cast<double*>(smem_raw);
+    uint64_t* full = reinterpret_cast<uint64_t*>(stages + (size_t)NSTAGE * X_STAGE_DOUBLES);
+    uint64_t* empty = full + NSTAGE;
+
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    if (threadIdx.x == 0) {
+        for (int s = 0; s < NSTAGE; s++) {
+            mbar_init(&full[s], 1);
+            mbar_init(&empty[s], CONSUMER_WARPS);
+        }
+        fence_barrier_init();
+        fence_proxy_async();
+    }
+    __syncthreads();
+
+    PipeState ps;
+    const int npt64 = prm.npt64;
+
+    auto decode = [&](int64_t item, int& ta, int& tb, int& kc0, int& kc1) {
+        const int tile = (int)(item % prm.n_tiles);
+        const int slice = (int)(item / prm.n_tiles);
+        int a = 0;
+        while ((a + 1) * (a + 2) / 2 <= tile) a++;
+        ta = a;
+        tb = tile - a * (a + 1) / 2;
+        kc0 = slice * prm.chunks_per_slice;
+        kc1 = min(prm.chunks, kc0 + prm.chunks_per_slice);
+    };
+
+    if (warp == CONSUMER_WARPS) {
+        if (lane == 0) {
+            for (int64_t item = blockIdx.x; item < prm.n_items; item += gridDim.x) {
+                int ta, tb, kc0, kc1;
+                decode(item, ta, tb, kc0, kc1);
+                int col[4] = {2 * ta, 2 * ta + 1, 2 * tb, 2 * tb + 1};
+                int nvalid = 0;
+#pragma unroll
+                for (int x = 0; x < 4; x++) nvalid += (col[x] < npt64);
+                for (int kc = kc0; kc < kc1; kc++) {
+                    mbar_wait(&empty[ps.stage], ps.phase ^ 1u);
+                    double* st = stages + (size_t)ps.stage * X_STAGE_DOUBLES;
+                    mbar_arrive_expect_tx(&full[ps.stage], (uint32_t)nvalid * 32u * 64u * 8u);
+#pragma unroll
+                    for (int x = 0; x < 4; x++)
+                        if (col[x] < npt64)
+                            bulk_g2s(st + x * 2048, prm.W + ((int64_t)kc * npt64 + col[x]) * 2048, 2048u * 8u,
+                                     &full[ps.stage]);
+                    ps.advance<NSTAGE>();
+                }
+            }
+        }
+        return;
+    }
+
+    const int g = lane >> 2, t = lane & 3;
+    const int wm = warp >> 2, wn = warp & 3;
+    const int nl0 = (wn & 1) * 32;
+    for (int64_t item = blockIdx.x; item < prm.n_items; item += gridDim.x) {
+        int ta, tb, kc0, kc1;
+        decode(item, ta, tb, kc0, kc1);
+        const bool active = (2 * ta + wm < npt64) && (2 * tb + (wn >> 1) < npt64);
+        double acc[8][4][2];
+#pragma unroll
+        for (int jm = 0; jm < 8; jm++)
+#pragma unroll
+            for (int jn = 0; jn < 4; jn++) acc[jm][jn][0] = acc[jm][jn][1] = 0.0;
+
+        for (int kc = kc0; kc < kc1; kc++) {
+            mbar_wait(&full[ps.stage], ps.phase);
+            if (active) {
+                const double* sA = stages + (size_t)ps.stage * X_STAGE_DOUBLES + wm * 2048;
+                const double* sB = stages + (size_t)ps.stage * X_STAGE_DOUBLES + (2 + (wn >> 1)) * 2048;
+#pragma unroll
+                for (int k0 = 0; k0 < KSLAB; k0 += 4) {
+                    const int kr = k0 + t;
+                    double a[8], b[4];
+#pragma unroll
+                    for (int jm = 0; jm < 8; jm++) a[jm] = sA[kr * 64 + ((8 * jm + g) ^ (t << 2))];
+#pragma unroll
+                    for (int jn = 0; jn < 4; jn++) b[jn] = sB[kr * 64 + ((nl0 + 8 * jn + g) ^ (t << 2))];
+#pragma unroll
+                    for (int jm = 0; jm < 8; jm++)
+#pragma unroll
+                        for (int jn = 0; jn < 4; jn++) dmma(acc[jm][jn][0], acc[jm][jn][1], a[jm], b[jn]);
+                }
+            }
+            __syncwarp();
+            if (lane == 0) mbar_arrive(&empty[ps.stage]);
+            ps.advance<NSTAGE>();
+        }
+        double* out = prm.Kpart + item * (128 * 128);
+#pragma unroll
+        for (int jm = 0; jm < 8; jm++) {
+            const int m = 64 * wm + 8 * jm + g;
+#pragma unroll
+            for (int jn = 0; jn < 4; jn++) {
+                const int n = 32 * wn + 8 * jn + 2 * t;
+                *reinterpret_cast<double2*>(out + m * 128 + n) = make_double2(acc[jm][jn][0], acc[jm][jn][1]);
+            }
+        }
+    }
+}
+
+size_t exchange_smem_bytes() { return (size_t)NSTAGE * X_STAGE_DOUBLES * 8 + 2 * NSTAGE * 8 + 16; }
+
+void launch_exchange(const Layout& L, Shard& s, int sm_count) {
+    XParams prm;
+    prm.W = s.W;
+    prm.Kpart = s.Kpart;
+    prm.npt64 = L.npt64;
+    prm.n_tiles = s.xplan.n_tiles;
+    prm.n_slices = s.xplan.n_slices;
+    prm.chunks = s.xplan.chunks;
+    prm.chunks_per_slice = s.xplan.chunks_per_slice;
+    prm.n_items = (int64_t)s.xplan.n_tiles * s.xplan.n_slices;
+    int grid = (int)std::min<int64_t>(prm.n_items, sm_count);
+    if (grid <= 0) return;
+    size_t smem = exchange_smem_bytes();
+    cudaFuncSetAttribute(k_exchange, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+    k_exchange<<<grid, CTA_THREADS, smem, s.stream>>>(prm);
+}
+
+// =====================================================================================================================
+// Fock epilogue:  F = [H] + Jt (scatter from tile space) - sum_slices Kpart, mirrored to both triangles
+// (copy_screened_coulomb_to_fock!, ScreenedDF.jl:367-378; H add DensityFitting.jl:62-65; block mirror :598-601)
+// =====================================================================================================================
+__global__ void k_fock_epilogue(double* __restrict__ F, const double* __restrict__ H, const double* __restrict__ Jt,
+                                const double* __restrict__ Kpart, const int32_t* __restrict__ tile_index, int N, int nb,
+                                int n_tiles, int n_slices) {
+    const int q = blockIdx.x * blockDim.x + threadIdx.x;
+    const int p = blockIdx.y;
+    if (q > p || p >= N) return;
+    const int ta = p >> 7, tb = q >> 7;
+    const int tile = ta * (ta + 1) / 2 + tb;
+    const int64_t off = (int64_t)(p & 127) * 128 + (q & 127);
+    double k = 0.0;
+    for (int s = 0; s < n_slices; s++) k += Kpart[((int64_t)s * n_tiles + tile) * (128 * 128) + off];
+    double v = -k;
+    const int ti = tile_index[(p >> 5) * nb + (q >> 5)];
+    if (ti >= 0) v += Jt[(int64_t)ti * TILE_ELEMS + (p & 31) * 32 + swz(p & 31, q & 31)];
+    double vpq = v, vqp = v;
+    if (H != nullptr) {
+        vpq += H[p + (int64_t)N * q];
+        vqp += H[q + (int64_t)N * p];
+    }
+    F[p + (int64_t)N * q] = vpq;
+    F[q + (int64_t)N * p] = vqp;
+}
+
+void launch_epilogue(const Layout& L, Shard& s, bool add_H) {
+    dim3 block(128);
+    dim3 grid((unsigned)((L.N + 127) / 128), (unsigned)L.N);
+    k_fock_epilogue<<<grid, block, 0, s.stream>>>(s.F, add_H ? s.Hdev : nullptr, s.Jt, s.Kpart, s.d_tile_index, (int)L.N,
+                                                  L.nb, s.xplan.n_tiles, s.xplan.n_slices);
+}
+
+}  // namespace jcdf
