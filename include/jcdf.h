@@ -98,6 +98,9 @@ int32_t jcdf_set_B_device(jcdf_handle* h, int32_t dev, const double* B_dev, int6
                           int64_t col_count);
 /* Copy the inverse Cholesky factor Linv (Q x Q, lower, column-major) back — for tests (J_AB_invt, ScreenedDF.jl:95) */
 int32_t jcdf_get_metric_inverse(jcdf_handle* h, double* Linv_out);
+/* Keep H resident on the shard-0 device so later jcdf_fock_build calls may pass H = NULL (H is constant over an SCF:
+ * scf_data-level state in the reference, SCF.jl:141-181).                                                        */
+int32_t jcdf_set_core_hamiltonian(jcdf_handle* h, const double* H);
 
 /* One Fock build: replaces the body of df_rhf_fock_build! after `occupied_orbital_coefficients = coefficients[:,1:occ]`
  * (DensityFitting.jl:49-71) for contraction_mode == "B200":
@@ -149,6 +152,10 @@ int32_t jcdf_get_layout(jcdf_handle* h, jcdf_layout_info* out);
  * jcdf_synthetic_value returns the same value on the host so tests can rebuild the tensor for the oracle.        */
 int32_t jcdf_fill_synthetic_B(jcdf_handle* h, uint64_t seed, double decay_length);
 double jcdf_synthetic_value(uint64_t seed, int64_t Q_total, int64_t q_aux, int64_t p, int64_t q, double decay_length);
+
+/* Tuning knobs (tests, bench).  Names: "coulomb_fused" (0 two-pass sweeps, 1 single-pass fused J kernel),
+ * "exchange_slices" (0 = automatic split of the K contraction index).  Unknown names -> JCDF_ERR_INVALID.     */
+int32_t jcdf_set_option(jcdf_handle* h, const char* name, int64_t value);
 
 /* Per-kernel device time of the last build of device `dev` in ms (CUDA events on the launching stream):
  * out[0..JCDF_N_STAGES) in the stage order above.                                                                */

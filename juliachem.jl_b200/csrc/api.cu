@@ -786,6 +786,20 @@ int32_t jcdf_fill_synthetic_B(jcdf_handle* h, uint64_t seed, double decay_length
     return JCDF_OK;
 }
 
+int32_t jcdf_set_option(jcdf_handle* h, const char* name, int64_t value) {
+    JC_REQUIRE(h && name, "jcdf_set_option: NULL argument");
+    const std::string n(name);
+    if (n == "coulomb_fused") h->opt_coulomb_fused = value;
+    else if (n == "exchange_slices") {
+        h->opt_exchange_slices = value;
+        for (Shard& s : h->shards) JC_REQUIRE(s.Bp == nullptr, "exchange_slices must be set before jcdf_set_mask");
+    } else {
+        set_error("jcdf_set_option: unknown option '" + n + "'");
+        return JCDF_ERR_INVALID;
+    }
+    return JCDF_OK;
+}
+
 int32_t jcdf_last_kernel_ms(jcdf_handle* h, int32_t dev, double* out) {
     JC_REQUIRE(h && out, "jcdf_last_kernel_ms: NULL argument");
     JC_REQUIRE(dev >= 0 && dev < (int)h->shards.size(), "jcdf_last_kernel_ms: device index out of range");

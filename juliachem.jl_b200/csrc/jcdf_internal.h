@@ -82,6 +82,8 @@ struct jcdf_handle {
     bool shards_set = false;
     int sm_count = 148;
     std::vector<double> host_metric;
+    int64_t opt_coulomb_fused = 0;
+    int64_t opt_exchange_slices = 0;
 };
 
 namespace jcdf {

@@ -1,0 +1,185 @@
+"""GPU parity tests proper: libjcdf (through the C-ABI, via the ctypes binding) against the CPU oracle on the same
+seeded inputs.  Tolerance: 1e-10 absolute per Fock element (BASELINE.json north_star)."""
+import numpy as np
+import pytest
+
+from helpers import banded_mask, jc, oracle_fock, orc, random_inputs, reference_layout_rows, wl
+
+pytestmark = pytest.mark.gpu
+TOL = 1e-10
+
+
+def _build(N, Q, occ, B, C_occ, H, mask, ndev=1, shards=None, fused=0):
+    gd = jc.B200Data(N, Q, occ, ndev)
+    if shards is not None:
+        gd.set_shards(shards)
+    gd.set_option("coulomb_fused", fused)
+    gd.set_mask(jc.ScreeningData(mask, N))
+    shards = shards or jc.balanced_function_shards(Q, ndev)
+    for d, r in enumerate(shards):
+        gd.set_B(d, reference_layout_rows(B, r, mask))
+    F, st = gd.fock_build(C_occ, H)
+    return gd, F, st
+
+
+@pytest.mark.parametrize("N,Q,occ", [(25, 96, 5), (64, 32, 8), (70, 40, 9), (33, 7, 1), (129, 50, 17), (203, 131, 27)])
+def test_dense_parity(N, Q, occ):
+    B, C_occ, H = random_inputs(N, Q, occ, seed=N * 1000 + Q)
+    F_ref = oracle_fock(B, C_occ, H, None)
+    gd, F, st = _build(N, Q, occ, B, C_occ, H, None)
+    assert np.abs(F - F_ref).max() < TOL
+    assert np.array_equal(F, F.T)
+    gd.close()
+
+
+@pytest.mark.parametrize("N,Q,occ,hw", [(70, 40, 9, 20), (203, 131, 27, 60), (160, 64, 16, 33), (300, 90, 40, 70)])
+def test_screened_parity(N, Q, occ, hw):
+    mask = banded_mask(N, hw, seed=N)
+    B, C_occ, H = random_inputs(N, Q, occ, seed=N + 17, mask=mask, decay=hw / 2.0)
+    F_ref = oracle_fock(B, C_occ, H, mask)
+    gd, F, st = _build(N, Q, occ, B, C_occ, H, mask)
+    li = gd.layout()
+    assert li.pairs_kept == int(mask.sum())
+    assert li.pairs_tri == int(np.tril(mask).sum())
+    assert li.tiles_kept <= li.tiles_total
+    assert np.abs(F - F_ref).max() < TOL
+    assert np.array_equal(F, F.T)
+    gd.close()
+
+
+def test_screened_equals_dense_algorithm_when_mask_full():
+    N, Q, occ = 96, 48, 12
+    mask = np.asfortranarray(np.ones((N, N), dtype=bool))
+    B, C_occ, H = random_inputs(N, Q, occ, seed=5)
+    F_ref = oracle_fock(B, C_occ, H, None)
+    gd, F, _ = _build(N, Q, occ, B, C_occ, H, mask)
+    assert np.abs(F - F_ref).max() < TOL
+    gd.close()
+
+
+def test_repeat_builds_and_H_none():
+    """H stays resident after the first call; F_out is fully overwritten each call; builds are repeatable."""
+    N, Q, occ = 70, 40, 9
+    B, C_occ, H = random_inputs(N, Q, occ, seed=11)
+    gd, F1, _ = _build(N, Q, occ, B, C_occ, H, None)
+    F_out = np.full((N, N), np.nan, order="F")
+    F2, _ = gd.fock_build(C_occ, None, F_out)
+    assert F2 is F_out
+    assert np.array_equal(F1, F2)
+    C2 = np.asfortranarray(np.linalg.qr(np.random.default_rng(3).standard_normal((N, occ)))[0])
+    F3, _ = gd.fock_build(C2, H)
+    assert np.abs(F3 - oracle_fock(B, C2, H, None)).max() < TOL
+    gd.close()
+
+
+def test_ldc_larger_than_N():
+    """C_occ passed as the leading occ columns of the full N x N coefficient matrix (DensityFitting.jl:49 slices it)."""
+    N, Q, occ = 70, 40, 9
+    B, C_occ, H = random_inputs(N, Q, occ, seed=12)
+    big = np.asfortranarray(np.random.default_rng(1).standard_normal((N + 5, N)))
+    Cfull = big[:N, :]
+    Cfull[:, :occ] = C_occ
+    assert Cfull.strides[1] == 8 * (N + 5)
+    gd = jc.B200Data(N, Q, occ, 1)
+    gd.set_mask(jc.ScreeningData(None, N))
+    gd.set_B(0, reference_layout_rows(B, range(0, Q), None))
+    F, _ = gd.fock_build(Cfull, H)
+    assert np.abs(F - oracle_fock(B, C_occ, H, None)).max() < TOL
+    gd.close()
+
+
+def test_B_formation_on_device():
+    """jcdf_upload_metric + jcdf_upload_three_center + jcdf_factor_and_form_B against potrf/trtri/trmm (a4)."""
+    N, Q, occ = 70, 60, 9
+    rng = np.random.default_rng(21)
+    mask = banded_mask(N, 30, seed=2)
+    T, C_occ, H = random_inputs(N, Q, occ, seed=22, mask=mask)
+    A = rng.standard_normal((Q, Q))
+    J = A @ A.T + Q * np.eye(Q)
+    J_lower = np.asfortranarray(np.tril(J))  # only the lower triangle is valid (TwoCenterIntegrals.jl:39-41)
+    sd = orc.ScreeningData(mask)
+    B_ref = orc.calculate_B(J_lower, orc.dense_to_screened(T, sd))
+    F_ref = orc.df_rhf_fock_build([B_ref], np.hstack([C_occ, np.zeros((N, N - occ))]), occ, H, sd, "screened")
+    gd = jc.B200Data(N, Q, occ, 1)
+    gd.set_mask(jc.ScreeningData(mask, N))
+    gd.upload_metric(J_lower)
+    gd.upload_three_center(0, reference_layout_rows(T, range(0, Q), mask))
+    gd.factor_and_form_B()
+    Linv = gd.get_metric_inverse()
+    assert np.abs(np.tril(Linv) - orc.metric_inverse_cholesky(J_lower)).max() < 1e-12
+    F, _ = gd.fock_build(C_occ, H)
+    assert np.abs(F - F_ref).max() < TOL
+    gd.close()
+
+
+def test_not_positive_definite_metric_is_an_error():
+    N, Q, occ = 33, 8, 2
+    T, C_occ, H = random_inputs(N, Q, occ, seed=1)
+    gd = jc.B200Data(N, Q, occ, 1)
+    gd.set_mask(jc.ScreeningData(None, N))
+    gd.upload_metric(np.asfortranarray(-np.eye(Q)))
+    gd.upload_three_center(0, reference_layout_rows(T, range(0, Q), None))
+    with pytest.raises(jc.JCDFError) as e:
+        gd.factor_and_form_B()
+    assert e.value.status == -5
+    gd.close()
+
+
+def test_call_order_errors():
+    gd = jc.B200Data(33, 8, 2, 1)
+    with pytest.raises(jc.JCDFError):
+        gd.fock_build(np.zeros((33, 2), order="F"), None)  # no mask / B yet
+    gd.set_mask(jc.ScreeningData(None, 33))
+    with pytest.raises(jc.JCDFError):
+        gd.fock_build(np.zeros((33, 2), order="F"), None)  # B missing
+    with pytest.raises(jc.JCDFError):
+        jc.B200Data(33, 8, 2, 4096)  # more devices than exist (GPUDF.jl:39-41)
+    gd.close()
+
+
+def test_eigh_on_device():
+    N = 90
+    rng = np.random.default_rng(4)
+    S = rng.standard_normal((N, N))
+    S = S @ S.T + N * np.eye(N)
+    w, U = np.linalg.eigh(S)
+    X = np.asfortranarray(U @ np.diag(w ** -0.5) @ U.T)
+    F = rng.standard_normal((N, N))
+    F = np.asfortranarray(0.5 * (F + F.T))
+    gd = jc.B200Data(N, 8, 2, 1)
+    ev, C = gd.eigh(F, X)
+    ev_ref = np.linalg.eigvalsh(X.T @ F @ X)
+    assert np.abs(ev - ev_ref).max() < 1e-10
+    # F C = S C diag(ev)
+    assert np.abs(F @ C - S @ C @ np.diag(ev)).max() < 1e-8
+    gd.close()
+
+
+def test_synthetic_fill_matches_host_twin():
+    """jcdf_fill_synthetic_B (device) == workloads.synthetic_B_rows (host twin) through a full Fock build."""
+    w = wl.WORKLOADS["small"]
+    mask = wl.screening_mask(w)
+    B = wl.synthetic_B_rows(w, range(0, w.Q), mask)
+    C_occ, H = wl.occupied_coefficients(w), wl.core_hamiltonian(w)
+    F_ref = oracle_fock(B, C_occ, H, mask)
+    gd = jc.B200Data(w.N, w.Q, w.occ, 1)
+    gd.set_mask(jc.ScreeningData(mask, w.N))
+    gd.fill_synthetic_B(w.seed, w.decay_length)
+    F, _ = gd.fock_build(C_occ, H)
+    assert np.abs(F - F_ref).max() < TOL
+    gd.close()
+
+
+def test_two_shards_on_one_device_sum_to_whole():
+    """Q-sharding (a12): two handles owning disjoint Q ranges; H added by shard 0 only; partials sum to the full F."""
+    N, Q, occ = 70, 41, 9
+    B, C_occ, H = random_inputs(N, Q, occ, seed=31)
+    F_ref = oracle_fock(B, C_occ, H, None, shards=[range(0, 20), range(20, 41)])
+    parts = []
+    for r, Hr in ((range(0, 20), H), (range(20, 41), None)):
+        gd = jc.B200Data(N, len(r), occ, 1)
+        gd.set_mask(jc.ScreeningData(None, N))
+        gd.set_B(0, reference_layout_rows(B, r, None))
+        parts.append(gd.fock_build(C_occ, Hr)[0].copy())
+        gd.close()
+    assert np.abs(parts[0] + parts[1] - F_ref).max() < TOL
