@@ -161,6 +161,11 @@ int32_t jcdf_set_option(jcdf_handle* h, const char* name, int64_t value);
  * out[0..JCDF_N_STAGES) in the stage order above.                                                                */
 int32_t jcdf_last_kernel_ms(jcdf_handle* h, int32_t dev, double* out);
 
+/* The CUDA stream (cudaStream_t, returned as void*) every kernel, copy and all-reduce of device `dev` is issued on —
+ * so a caller can bracket builds with its own CUDA events or order its own work against them (the fork's CUDA.jl
+ * path uses the task-local default stream and CUDA.synchronize() instead, GPUDF.jl:206-263).                     */
+int32_t jcdf_get_stream(jcdf_handle* h, int32_t dev, void** stream_out);
+
 #ifdef __cplusplus
 }
 #endif

@@ -55,6 +55,7 @@ SIGNATURES = {
     "jcdf_synthetic_value": (_f64, [_u64, _i64, _i64, _i64, _i64, _f64]),
     "jcdf_last_kernel_ms": (_i32, [_p, _i32, _p]),
     "jcdf_set_option": (_i32, [_p, C.c_char_p, _i64]),
+    "jcdf_get_stream": (_i32, [_p, _i32, C.POINTER(_p)]),
 }
 
 _lib = None

@@ -807,4 +807,11 @@ int32_t jcdf_last_kernel_ms(jcdf_handle* h, int32_t dev, double* out) {
     return JCDF_OK;
 }
 
+int32_t jcdf_get_stream(jcdf_handle* h, int32_t dev, void** stream_out) {
+    JC_REQUIRE(h && stream_out, "jcdf_get_stream: NULL argument");
+    JC_REQUIRE(dev >= 0 && dev < (int)h->shards.size(), "jcdf_get_stream: device index out of range");
+    *stream_out = reinterpret_cast<void*>(h->shards[dev].stream);
+    return JCDF_OK;
+}
+
 }  // extern "C"

@@ -237,6 +237,12 @@ class B200Data:
         check(self._lib.jcdf_last_kernel_ms(self._h, dev, _ptr(out)))
         return dict(zip(STAGE_NAMES, out.tolist()))
 
+    def stream(self, dev: int = 0) -> int:
+        """cudaStream_t (as an integer) the builds of device `dev` run on — wrap with torch.cuda.ExternalStream."""
+        out = C.c_void_p()
+        check(self._lib.jcdf_get_stream(self._h, dev, C.byref(out)))
+        return int(out.value or 0)
+
     def close(self) -> None:
         if getattr(self, "_h", None) is not None and self._h.value:
             self._lib.jcdf_destroy(self._h)

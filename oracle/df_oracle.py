@@ -371,3 +371,55 @@ def iteration(F: np.ndarray, H: np.ndarray, ortho: np.ndarray, nocc: int):
     D = 2.0 * (Cocc @ Cocc.T)
     E = 0.5 * (np.vdot(D, F) + np.vdot(D, H))
     return float(E), evals, np.asfortranarray(C), np.asfortranarray(D)
+
+
+# --------------------------------------------------------------------------------------------------------------
+# threaded form of a8-a10, as the reference runs it: Julia tasks over p / over K blocks with BLAS pinned to one
+# thread inside (ScreenedDF.jl:244-289, 476-516, 568-616).  Same arithmetic as the serial functions above; used by
+# bench.py's cpu_baseline / --impl reference legs so the CPU number is the reference's own parallel decomposition.
+# --------------------------------------------------------------------------------------------------------------
+def fock_build_screened_rank_threaded(B: np.ndarray, C_occ: np.ndarray, sd: ScreeningData, n_threads: int,
+                                      df_exchange_n_blocks: int = 0, timings: dict | None = None) -> np.ndarray:
+    import time
+    from concurrent.futures import ThreadPoolExecutor
+
+    from threadpoolctl import threadpool_limits
+
+    C_occ_T = np.asfortranarray(np.asarray(C_occ).T)
+    occ, N = C_occ_T.shape
+    Q = B.shape[0]
+    fock = np.zeros((N, N), dtype=np.float64, order="F")
+    n_blocks, width, batch = exchange_block_layout(N, df_exchange_n_blocks, 10)
+    mask = sd.basis_function_screen_matrix
+    W = np.zeros((Q, occ, N), dtype=np.float64, order="F")
+    Wv = W.reshape((Q * occ, N), order="F")
+    t0 = time.perf_counter()
+    with ThreadPoolExecutor(max_workers=n_threads) as pool:
+        with threadpool_limits(limits=1, user_api="blas"):  # BLAS.set_num_threads(1), ScreenedDF.jl:246
+            def w_of_p(p):
+                nz = np.asfortranarray(C_occ_T[:, mask[:, p]])
+                K_p = int(sd.non_screened_p_indices_count[p])
+                s = int(sd.sparse_p_start_indices[p]) - 1
+                W[:, :, p] = np.dot(B[:, s:s + K_p], nz.T)  # numpy's dgemm call releases the GIL (f2py's does not)
+            list(pool.map(w_of_p, range(N)))
+            t1 = time.perf_counter()
+
+            def k_block(b):
+                bp, bq = b
+                ps, qs = (bp - 1) * width, (bq - 1) * width
+                blk = -np.dot(Wv[:, ps:ps + width].T, Wv[:, qs:qs + width])
+                fock[ps:ps + width, qs:qs + width] = blk
+                if bp != bq:
+                    fock[qs:qs + width, ps:ps + width] = blk.T
+            list(pool.map(k_block, batch))
+        if N % n_blocks != 0:  # remainder strip: one multi-threaded GEMM (ScreenedDF.jl:619-640)
+            q0 = N - (N % n_blocks)
+            strip = sblas.dgemm(-1.0, Wv, Wv[:, q0:], trans_a=1)
+            fock[:, q0:] = strip
+            fock[q0:, :] = strip.T
+    t2 = time.perf_counter()
+    calculate_coulomb_screened(B, C_occ_T, sd, fock)  # gemv sweeps with threaded BLAS (ScreenedDF.jl:326-358)
+    t3 = time.perf_counter()
+    if timings is not None:
+        timings.update({"W": t1 - t0, "K": t2 - t1, "J": t3 - t2})
+    return fock
