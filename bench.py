@@ -226,15 +226,12 @@ def run_b200(args):
     N, Q, occ = w.N, w.Q, w.occ
     mask = wl.screening_mask(w)
     gd = jc.B200Data(N, Q, occ, ndev_local, dev_ids)
-    allr = jc.balanced_function_shards(Q, n_total)
-    gd.set_shards(allr[rank * ndev_local:(rank + 1) * ndev_local])
+    from juliachem_jl_b200 import multi
+    my_shards = multi.rank_shards(Q, world if world > 1 else 1, rank, ndev_local)
+    gd.set_shards(my_shards)
     gd.set_mask(jc.ScreeningData(mask, N))
     if world > 1:
-        idt = torch.zeros(128, dtype=torch.uint8, device=dev0)
-        if rank == 0:
-            idt = torch.tensor(list(jc.unique_id()), dtype=torch.uint8, device=dev0)
-        dist.broadcast(idt, 0)
-        gd.comm_init_rank(world, rank, bytes(idt.cpu().tolist()))
+        gd.comm_init_rank(world, rank, multi.exchange_unique_id(dist, rank, dev0))
     t_fill = time.perf_counter()
     gd.fill_synthetic_B(w.seed, w.decay_length)
     t_fill = time.perf_counter() - t_fill
@@ -314,7 +311,7 @@ def run_b200(args):
                "d2h_bytes_per_step": int(F_pin.numel() * 8) * (world if world > 1 else 1), "ms_per_step": ms_e2e}
 
     # ---- roofline of the dominant kernels (rank 0's shard) -----------------------------------------------------------
-    q_local0 = len(allr[rank * ndev_local])
+    q_local0 = len(my_shards[0])
     work = wl.algorithmic_work(N, q_local0, occ, li.pairs_kept, li.pairs_tri)
     peak_tf, peak_src = None, None
     if rank == 0:

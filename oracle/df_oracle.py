@@ -326,7 +326,9 @@ def df_rhf_fock_build(B_shards, C: np.ndarray, occ: int, H: np.ndarray, sd: Scre
     C_occ = np.asfortranarray(C[:, :occ])
     total = None
     for rank, Bs in enumerate(B_shards):
-        if contraction_mode == "dense":
+        if Bs.shape[0] == 0:  # a rank that owns no auxiliary shell contributes a zero matrix (BLAS calls with M = 0)
+            f = np.zeros_like(H)
+        elif contraction_mode == "dense":
             f = fock_build_dense_rank(Bs, C_occ)
         else:
             f = fock_build_screened_rank(Bs, C_occ, sd, df_exchange_n_blocks)

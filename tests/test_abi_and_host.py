@@ -1,0 +1,115 @@
+"""CPU-side checks: libjcdf.so loads and exports every symbol include/jcdf.h declares (no compute calls — there is no
+GPU here), the host-side mirror of the reference interface (df.py) agrees with the oracle's restatement of the same
+reference functions, and the product path has no CPU fallback."""
+import ctypes
+import os
+import re
+
+import numpy as np
+import pytest
+
+from helpers import ROOT, jc, orc, wl
+
+
+def _declared_symbols():
+    src = open(os.path.join(ROOT, "include", "jcdf.h")).read()
+    src = re.sub(r"/\*.*?\*/", "", src, flags=re.S)
+    return sorted(set(re.findall(r"\b(jcdf_[A-Za-z_0-9]+)\s*\(", src)))
+
+
+def test_library_exports_every_declared_symbol():
+    lib = jc.load_library()
+    from juliachem_jl_b200 import _lib
+    names = _declared_symbols()
+    assert len(names) >= 24
+    for n in names:
+        assert hasattr(lib, n), "libjcdf.so does not export %s" % n
+        assert n in _lib.SIGNATURES, "ctypes table misses %s" % n
+    assert sorted(_lib.SIGNATURES) == names
+
+
+def test_status_enum_and_stage_slots_match_header():
+    src = open(os.path.join(ROOT, "include", "jcdf.h")).read()
+    from juliachem_jl_b200 import _lib
+    for name, val in re.findall(r"(JCDF_ERR_[A-Z]+) = (-\d+)", src):
+        assert getattr(_lib, name) == int(val)
+    assert int(re.search(r"JCDF_N_STAGES = (\d+)", src).group(1)) == _lib.N_STAGES == len(_lib.STAGE_NAMES)
+
+
+def test_no_gpu_means_error_not_fallback():
+    """Without a CUDA device every entry point that needs one fails with a status + message; nothing computes on the CPU."""
+    lib = jc.load_library()
+    if lib.jcdf_device_count() > 0:
+        pytest.skip("a GPU is present")
+    with pytest.raises(jc.JCDFError):
+        jc.B200Data(25, 96, 5, 1)
+    assert lib.jcdf_last_error()
+
+
+def test_product_package_never_imports_the_oracle():
+    pkg = os.path.join(ROOT, "juliachem.jl_b200")
+    for dp, _, files in os.walk(pkg):
+        for f in files:
+            if f.endswith((".py", ".cu", ".cuh", ".cpp", ".h", ".jl")):
+                txt = open(os.path.join(dp, f)).read()
+                assert "oracle" not in txt.replace("the CPU oracle", "").replace("oracle/", "oracle/") or \
+                    not re.search(r"^\s*(from|import)\s+oracle", txt, flags=re.M), f
+
+
+def test_synthetic_value_host_twin_is_bit_identical():
+    """jcdf_synthetic_value is a pure host function of libjcdf; workloads.synthetic_B_rows is its numpy twin."""
+    lib = jc.load_library()
+    w = wl.WORKLOADS["tiny"]
+    rows = wl.synthetic_B_rows(w, range(3, 6), None)
+    for (qa, p, q) in [(3, 0, 0), (4, 10, 3), (5, 69, 69), (3, 7, 60)]:
+        v = lib.jcdf_synthetic_value(w.seed, w.Q, qa, p, q, w.decay_length)
+        assert v == rows[qa - 3, p, q] == rows[qa - 3, q, p]
+
+
+@pytest.mark.parametrize("n_shells,n_ranks", [(30, 1), (30, 4), (7, 8), (96, 3), (5, 5)])
+def test_static_shard_rule_matches_oracle(n_shells, n_ranks):
+    nbas = np.random.default_rng(n_shells).choice([1, 3, 6, 10, 15], size=n_shells)
+    cover = []
+    for r in range(n_ranks):
+        assert jc.get_df_static_shell_indices(n_shells, n_ranks, r) == orc.get_df_static_shell_indices(n_shells, n_ranks, r)
+        a, b = jc.static_load_rank_indicies(r, n_ranks, nbas), orc.static_load_rank_indicies(r, n_ranks, nbas)
+        assert a == b
+        cover += list(a[1])
+    assert cover == list(range(int(nbas.sum())))  # contiguous, disjoint, complete
+
+
+def test_pair_compaction_matches_oracle_and_reference_order():
+    m = wl.screening_mask(wl.WORKLOADS["tiny"])
+    a, b = jc.sparse_pq_index_map(m), orc.sparse_pq_index_map(m)
+    assert np.array_equal(a, b) and a.dtype == np.int64
+    # outer loop p (column), inner loop q (row), 1-based running index (SchwarzScreening.jl:72-81)
+    k = 0
+    for p in range(m.shape[0]):
+        for q in range(m.shape[0]):
+            if m[q, p]:
+                k += 1
+                assert a[q, p] == k
+            else:
+                assert a[q, p] == 0
+    sd = jc.ScreeningData(m, m.shape[0])
+    assert sd.screened_indices_count == k
+
+
+def test_workload_shapes_and_algorithmic_work():
+    for name, (N, Q, occ) in {"water": (25, 96, 5), "benzene_dimer": (600, 1632, 42), "w50": (1250, 4800, 250),
+                              "c20h42": (1330, 3490, 81), "gly18": (3395, 9333, 275)}.items():
+        w = wl.WORKLOADS[name]
+        assert (w.N, w.Q, w.occ) == (N, Q, occ)
+    work = wl.algorithmic_work(1250, 4800, 250, 1250 * 1250, 1250 * 1251 // 2)
+    assert abs(work["w_flops"] + work["k_flops"] - 5.63e12) < 0.01e12   # SURVEY.md §8(d) worked value
+    assert abs(work["j_bytes"] - 30.0e9) < 0.1e9
+    for name in ("tiny", "small", "c20h42"):
+        m = wl.screening_mask(wl.WORKLOADS[name])
+        assert m.dtype == bool and np.array_equal(m, m.T) and m.diagonal().all()
+    assert 0.2 < wl.screening_mask(wl.WORKLOADS["c20h42"]).mean() < 0.7
+
+
+def test_balanced_shards_cover_Q():
+    for Q, n in [(4800, 8), (131, 3), (7, 8)]:
+        r = jc.balanced_function_shards(Q, n)
+        assert r[0].start == 0 and r[-1].stop == Q and all(r[i].stop == r[i + 1].start for i in range(n - 1))

@@ -1,0 +1,90 @@
+"""The oracle's two restated algorithms against an independent statement of the maths
+F = H + 2 J[D] - K[D] (einsum), edge cases of the screened bookkeeping, B formation and iteration()."""
+import numpy as np
+import pytest
+
+from helpers import banded_mask, oracle_fock, orc, random_inputs
+
+
+def _einsum_fock(B, C_occ, H):
+    D = C_occ @ C_occ.T
+    V = np.einsum("Qrs,rs->Q", B, D)
+    J = np.einsum("Qpq,Q->pq", B, V)
+    W = np.einsum("Qpr,ri->Qip", B, C_occ)
+    K = np.einsum("Qip,Qiq->pq", W, W)
+    return H + 2.0 * J - K
+
+
+@pytest.mark.parametrize("N,Q,occ", [(25, 96, 5), (33, 7, 1), (101, 20, 9), (127, 31, 13)])
+def test_dense_algorithm_is_the_maths(N, Q, occ):
+    B, C_occ, H = random_inputs(N, Q, occ, seed=N)
+    assert np.abs(oracle_fock(B, C_occ, H, None) - _einsum_fock(B, C_occ, H)).max() < 1e-11
+
+
+@pytest.mark.parametrize("N,Q,occ,hw", [(70, 40, 9, 20), (101, 17, 6, 40), (130, 25, 11, 129), (203, 31, 27, 60)])
+def test_screened_algorithm_is_the_maths_on_masked_B(N, Q, occ, hw):
+    """N >= 100 exercises the 10-block K tiling incl. the N % 10 remainder strip (ScreenedDF.jl:619-640)."""
+    mask = banded_mask(N, hw, seed=N)
+    B, C_occ, H = random_inputs(N, Q, occ, seed=N + 1, mask=mask)
+    F = oracle_fock(B, C_occ, H, mask)
+    assert np.abs(F - _einsum_fock(B, C_occ, H)).max() < 1e-11
+    assert np.array_equal(F, F.T)
+    Ft = orc.fock_build_screened_rank_threaded(orc.dense_to_screened(B, orc.ScreeningData(mask)), C_occ,
+                                               orc.ScreeningData(mask), 4) + H
+    assert np.abs(Ft - F).max() < 1e-11
+
+
+def test_rank_sum_equals_whole_and_H_added_once():
+    N, Q, occ = 70, 41, 9
+    B, C_occ, H = random_inputs(N, Q, occ, seed=3)
+    whole = oracle_fock(B, C_occ, H, None)
+    parts = oracle_fock(B, C_occ, H, None, shards=[range(0, 13), range(13, 13), range(13, 41)])  # one empty rank
+    assert np.abs(whole - parts).max() < 1e-11
+
+
+def test_screening_metadata_ranges():
+    mask = np.array([[1, 1, 0, 1], [1, 1, 1, 0], [0, 1, 1, 1], [1, 0, 1, 1]], dtype=bool)
+    sd = orc.ScreeningData(mask)
+    assert sd.screened_indices_count == 12
+    assert list(sd.sparse_p_start_indices) == [1, 4, 7, 10]
+    assert list(sd.non_screened_p_indices_count) == [3, 3, 3, 3]
+    assert sd.non_zero_ranges[0] == [(1, 2), (4, 4)] and sd.non_zero_sparse_ranges[0] == [(1, 2), (3, 3)]
+    with pytest.raises(ValueError):
+        orc.ScreeningData(np.array([[1, 0], [0, 0]], dtype=bool))
+
+
+def test_exchange_block_layout_rules():
+    assert orc.exchange_block_layout(99)[:2] == (1, 99)          # N < 100 -> single block (ScreenedDF.jl:396-400)
+    nb, w, batch = orc.exchange_block_layout(1250)
+    assert (nb, w, len(batch)) == (10, 125, 55)
+    assert orc.exchange_block_layout(203, 4)[:2] == (4, 50)
+
+
+def test_B_formation_is_cholesky_inverse_not_symmetric_root():
+    rng = np.random.default_rng(0)
+    Q, P = 30, 50
+    A = rng.standard_normal((Q, Q))
+    J = A @ A.T + Q * np.eye(Q)
+    T = np.asfortranarray(rng.standard_normal((Q, P)))
+    B = orc.calculate_B(np.tril(J), T)       # only the lower triangle may be read
+    L = np.linalg.cholesky(J)
+    assert np.abs(B - np.linalg.solve(L, T)).max() < 1e-12
+    assert np.abs(B.T @ B - T.T @ np.linalg.solve(J, T)).max() < 1e-11   # the fitted 4-index tensor is the invariant
+    rows = orc.calculate_B_rows(orc.metric_inverse_cholesky(np.tril(J)), T, range(7, 19))
+    assert np.abs(rows - B[7:19]).max() < 1e-12
+    with pytest.raises(np.linalg.LinAlgError):
+        orc.calculate_B(-np.eye(4), np.zeros((4, 3), order="F"))
+
+
+def test_iteration_energy_and_density():
+    rng = np.random.default_rng(1)
+    N, nocc = 12, 3
+    A = rng.standard_normal((N, N)); S = A @ A.T + N * np.eye(N)
+    w, U = np.linalg.eigh(S); X = U @ np.diag(w ** -0.5) @ U.T
+    F = rng.standard_normal((N, N)); F = F + F.T
+    H = rng.standard_normal((N, N)); H = H + H.T
+    E, ev, C, D = orc.iteration(F, H, X, nocc)
+    assert np.abs(C.T @ S @ C - np.eye(N)).max() < 1e-10
+    assert np.abs(F @ C - S @ C @ np.diag(ev)).max() < 1e-9
+    assert abs(np.trace(D @ S) - 2 * nocc) < 1e-10
+    assert abs(E - 0.5 * np.sum(D * (F + H))) < 1e-12
