@@ -49,6 +49,7 @@ def parse_args():
     ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-e2e", action="store_true")
+    ap.add_argument("--opt", action="append", default=[], help="library option name=value (jcdf_set_option)")
     ap.add_argument("--cpu-seconds", type=float, default=4.0, help="target seconds per CPU sample build")
     return ap.parse_args()
 
@@ -229,6 +230,9 @@ def run_b200(args):
     from juliachem_jl_b200 import multi
     my_shards = multi.rank_shards(Q, world if world > 1 else 1, rank, ndev_local)
     gd.set_shards(my_shards)
+    for kv in args.opt:
+        k, v = kv.split("=")
+        gd.set_option(k, int(v))
     gd.set_mask(jc.ScreeningData(mask, N))
     if world > 1:
         gd.comm_init_rank(world, rank, multi.exchange_unique_id(dist, rank, dev0))
@@ -381,7 +385,7 @@ def run_b200(args):
     line = {
         "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": n_total, "steps": args.steps, "warmup": max(args.warmup, 3),
         "ms_per_step": ms_per_step, "higher_is_better": True, "scaling": "strong", "vs_baseline": None, "dtype": "f64",
-        "data": "synthetic", "config": cfg, "e2e": e2e,
+        "data": "synthetic", "config": cfg, "e2e": e2e, "options": args.opt,
         "gpu_launches": int(li.kernel_launches_per_build) * args.steps * n_total,
         "gpu_launches_per_build_per_gpu": int(li.kernel_launches_per_build),
         "clocks": clocks, "roofline": roofline, "cpu_baseline": cpu,

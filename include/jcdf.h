@@ -153,8 +153,10 @@ int32_t jcdf_get_layout(jcdf_handle* h, jcdf_layout_info* out);
 int32_t jcdf_fill_synthetic_B(jcdf_handle* h, uint64_t seed, double decay_length);
 double jcdf_synthetic_value(uint64_t seed, int64_t Q_total, int64_t q_aux, int64_t p, int64_t q, double decay_length);
 
-/* Tuning knobs (tests, bench).  Names: "coulomb_fused" (0 two-pass sweeps, 1 single-pass fused J kernel),
- * "exchange_slices" (0 = automatic split of the K contraction index).  Unknown names -> JCDF_ERR_INVALID.     */
+/* Tuning knobs (tests, bench).  Names: "coulomb_fused" (1 = default: single-pass cooperative J kernel whenever a
+ * row segment fits the shared-memory ring, 0 = two-pass sweeps), "coulomb_overlap" (two-pass sweeps on a second
+ * stream, concurrent with the tensor-core kernels; default 0), "exchange_slices" (0 = automatic split of the K
+ * contraction index).  Unknown names -> JCDF_ERR_INVALID.                                                       */
 int32_t jcdf_set_option(jcdf_handle* h, const char* name, int64_t value);
 
 /* Per-kernel device time of the last build of device `dev` in ms (CUDA events on the launching stream):

@@ -72,12 +72,14 @@ static int dev_alloc(T** p, size_t count) {
 
 static void free_shard_buffers(Shard& s) {
     cudaSetDevice(s.dev);
-    void* ptrs[] = {s.Bp, s.W, s.Cs, s.Craw, s.dt, s.Jt, s.V, s.Kpart, s.F, s.Hdev, s.Traw, s.d_tile_index, s.d_tile_a,
+    void* ptrs[] = {s.Vpart, s.Vready, s.Bp, s.W, s.Cs, s.Craw, s.dt, s.Jt, s.V, s.Kpart, s.F, s.Hdev, s.Traw, s.d_tile_index, s.d_tile_a,
                     s.d_tile_b, s.d_dest_of_col, s.d_fn_mask, s.Linv, s.Metric};
     for (void* p : ptrs)
         if (p) cudaFree(p);
     s.Bp = s.W = s.Cs = s.Craw = s.dt = s.Jt = s.V = s.Kpart = s.F = s.Hdev = s.Traw = s.Linv = s.Metric = nullptr;
     s.d_tile_index = s.d_tile_a = s.d_tile_b = nullptr;
+    s.Vpart = nullptr;
+    s.Vready = nullptr;
     s.d_dest_of_col = nullptr;
     s.d_fn_mask = nullptr;
     s.traw_capacity = 0;
@@ -121,6 +123,8 @@ static int alloc_shard_buffers(jcdf_handle* h, Shard& s) {
     if ((rc = dev_alloc(&s.dt, (size_t)L.row_len))) return rc;
     if ((rc = dev_alloc(&s.Jt, (size_t)L.row_len))) return rc;
     if ((rc = dev_alloc(&s.V, (size_t)std::max<int64_t>(s.q_len, 1)))) return rc;
+    if ((rc = dev_alloc(&s.Vpart, (size_t)std::max<int64_t>(s.q_len, 1) * h->sm_count))) return rc;
+    if ((rc = dev_alloc(&s.Vready, (size_t)std::max<int64_t>(s.q_len, 1)))) return rc;
     if ((rc = dev_alloc(&s.Kpart, (size_t)s.xplan.n_tiles * s.xplan.n_slices * 128 * 128))) return rc;
     if ((rc = dev_alloc(&s.F, (size_t)L.N * L.N))) return rc;
     if ((rc = dev_alloc(&s.Hdev, (size_t)L.N * L.N))) return rc;
@@ -219,7 +223,10 @@ int32_t jcdf_create(int64_t N, int64_t Q, int64_t occ, int32_t ndev, const int32
             return JCDF_ERR_INVALID;
         }
         cudaError_t e = cudaSetDevice(s.dev);
-        if (e == cudaSuccess) e = cudaStreamCreateWithFlags(&s.stream, cudaStreamNonBlocking);
+        int prio_lo = 0, prio_hi = 0;
+        if (e == cudaSuccess) e = cudaDeviceGetStreamPriorityRange(&prio_lo, &prio_hi);
+        if (e == cudaSuccess) e = cudaStreamCreateWithPriority(&s.stream, cudaStreamNonBlocking, prio_hi);
+        if (e == cudaSuccess) e = cudaStreamCreateWithPriority(&s.stream_j, cudaStreamNonBlocking, prio_lo);
         for (int i = 0; i < EV_COUNT && e == cudaSuccess; i++) e = cudaEventCreate(&s.ev[i]);
         if (e != cudaSuccess) {
             set_error(std::string("jcdf_create: ") + cudaGetErrorString(e));
@@ -250,6 +257,7 @@ int32_t jcdf_destroy(jcdf_handle* h) {
         free_shard_buffers(s);
         for (int i = 0; i < EV_COUNT; i++)
             if (s.ev[i]) cudaEventDestroy(s.ev[i]);
+        if (s.stream_j) cudaStreamDestroy(s.stream_j);
         if (s.stream) cudaStreamDestroy(s.stream);
     }
     delete h;
@@ -613,9 +621,18 @@ static int fock_build_impl(jcdf_handle* h, const double* C_occ, int64_t ldc, con
         JC_CUDA(cudaEventRecord(s.ev[EV_W], s.stream));
         launch_exchange(L, s, h->sm_count);
         JC_CUDA(cudaEventRecord(s.ev[EV_K], s.stream));
-        JC_CUDA(cudaEventRecord(s.ev[EV_V], s.stream));  // overwritten inside launch_coulomb when q_len > 0
-        launch_coulomb(L, s, h->sm_count);
-        JC_CUDA(cudaEventRecord(s.ev[EV_J], s.stream));
+        // Coulomb sweeps (HBM-bound, 32-40 registers, no dynamic smem).  With coulomb_overlap they go to a second,
+        // lower-priority stream: their CTAs co-reside with the persistent tensor-core CTAs (one per SM, compute-bound,
+        // issue slots ~16 % busy) and soak up the idle HBM bandwidth instead of queueing behind them.
+        const bool overlap = h->opt_coulomb_overlap && !h->opt_coulomb_fused;
+        cudaStream_t sj = overlap ? s.stream_j : s.stream;
+        if (overlap) JC_CUDA(cudaStreamWaitEvent(sj, s.ev[EV_PREP], 0));
+        JC_CUDA(cudaEventRecord(s.ev[EV_JBEGIN], sj));
+        JC_CUDA(cudaEventRecord(s.ev[EV_V], sj));  // two-pass: overwritten at the V | J boundary; fused: V time reads 0
+        s.last_coulomb_fused = h->opt_coulomb_fused && launch_coulomb_fused(L, s, h->sm_count, sj);
+        if (!s.last_coulomb_fused) launch_coulomb(L, s, h->sm_count, sj);
+        JC_CUDA(cudaEventRecord(s.ev[EV_J], sj));
+        if (overlap) JC_CUDA(cudaStreamWaitEvent(s.stream, s.ev[EV_J], 0));
         launch_epilogue(L, s, add_H);
         JC_CUDA(cudaEventRecord(s.ev[EV_EPI], s.stream));
         JC_CUDA(cudaGetLastError());
@@ -656,9 +673,9 @@ static int fock_build_impl(jcdf_handle* h, const double* C_occ, int64_t ldc, con
         s.last_ms[JCDF_T_DENSITY] = el(EV_H2D, EV_PREP);
         s.last_ms[JCDF_T_W] = el(EV_PREP, EV_W);
         s.last_ms[JCDF_T_K] = el(EV_W, EV_K);
-        s.last_ms[JCDF_T_V] = el(EV_K, EV_V);
+        s.last_ms[JCDF_T_V] = el(EV_JBEGIN, EV_V);
         s.last_ms[JCDF_T_J] = el(EV_V, EV_J);
-        s.last_ms[JCDF_T_EPILOGUE] = el(EV_J, EV_EPI);
+        s.last_ms[JCDF_T_EPILOGUE] = (h->opt_coulomb_overlap && !h->opt_coulomb_fused) ? el(EV_K, EV_EPI) : el(EV_J, EV_EPI);
         s.last_ms[JCDF_T_ALLREDUCE] = el(EV_EPI, EV_AR);
         s.last_ms[JCDF_T_D2H] = d == 0 ? el(EV_AR, EV_D2H) : 0.0;
         s.last_ms[JCDF_T_TOTAL] = std::chrono::duration<double, std::milli>(t1 - t0).count();
@@ -770,7 +787,8 @@ int32_t jcdf_get_layout(jcdf_handle* h, jcdf_layout_info* o) {
         o->bytes_B += s.q_len * L.row_len * 8;
         o->bytes_W += (int64_t)s.xplan.chunks * L.npt64 * 2048 * 8;
     }
-    o->kernel_launches_per_build = 7;  // prep_cs, density, half_transform, exchange, coulomb_v, coulomb_j, epilogue
+    // prep_cs, density, half_transform, exchange, coulomb (fused: 1, two-pass: 2), epilogue
+    o->kernel_launches_per_build = (!h->shards.empty() && h->shards[0].last_coulomb_fused) ? 6 : 7;
     return JCDF_OK;
 }
 
@@ -790,6 +808,7 @@ int32_t jcdf_set_option(jcdf_handle* h, const char* name, int64_t value) {
     JC_REQUIRE(h && name, "jcdf_set_option: NULL argument");
     const std::string n(name);
     if (n == "coulomb_fused") h->opt_coulomb_fused = value;
+    else if (n == "coulomb_overlap") h->opt_coulomb_overlap = value;
     else if (n == "exchange_slices") {
         h->opt_exchange_slices = value;
         for (Shard& s : h->shards) JC_REQUIRE(s.Bp == nullptr, "exchange_slices must be set before jcdf_set_mask");

@@ -30,7 +30,7 @@ struct Layout {
 };
 
 // event points recorded on the shard's stream during one build, in launch order
-enum EvPoint { EV_START = 0, EV_H2D, EV_PREP, EV_W, EV_K, EV_V, EV_J, EV_EPI, EV_AR, EV_D2H, EV_COUNT };
+enum EvPoint { EV_START = 0, EV_H2D, EV_PREP, EV_W, EV_K, EV_JBEGIN, EV_V, EV_J, EV_EPI, EV_AR, EV_D2H, EV_COUNT };
 
 struct ExchangePlan {
     int n_tiles = 0;     // lower-triangular 128x128 output tiles
@@ -43,6 +43,7 @@ struct Shard {
     int dev = 0;
     int64_t q_begin = 0, q_len = 0;
     cudaStream_t stream = nullptr;
+    cudaStream_t stream_j = nullptr;  // Coulomb sweeps, concurrent with the tensor-core kernels when coulomb_overlap = 1
     // HBM-resident operands
     double* Bp = nullptr;      // [q_len][row_len] packed, swizzled tiles
     double* W = nullptr;       // [chunks][npt64][32][64] half-transformed tensor
@@ -51,6 +52,8 @@ struct Shard {
     double* dt = nullptr;      // [row_len] packed, weighted density
     double* Jt = nullptr;      // [row_len] packed Coulomb vector
     double* V = nullptr;       // [q_len]
+    double* Vpart = nullptr;   // [q_len][sm_count] per-CTA partial V of the fused Coulomb kernel
+    unsigned int* Vready = nullptr;  // [q_len] chunk flags of the fused Coulomb kernel
     double* Kpart = nullptr;   // [n_tiles * n_slices][128*128]
     double* F = nullptr;       // N x N column-major partial / reduced Fock
     double* Hdev = nullptr;    // N x N (only where H is added)
@@ -64,6 +67,7 @@ struct Shard {
     double* Linv = nullptr;    // Q x Q on the first device only
     double* Metric = nullptr;
     bool has_H = false;
+    bool last_coulomb_fused = false;
     bool b_ready = false;
     bool t_uploaded = false;
     ExchangePlan xplan;
@@ -82,7 +86,8 @@ struct jcdf_handle {
     bool shards_set = false;
     int sm_count = 148;
     std::vector<double> host_metric;
-    int64_t opt_coulomb_fused = 0;
+    int64_t opt_coulomb_fused = 1;    // single-pass cooperative Coulomb kernel whenever the row segment fits in smem
+    int64_t opt_coulomb_overlap = 0;  // two-pass sweeps on a second stream, concurrent with the tensor-core kernels
     int64_t opt_exchange_slices = 0;
 };
 
@@ -92,7 +97,8 @@ namespace jcdf {
 void launch_prep(const Layout& L, Shard& s, int64_t ldc);
 void launch_half_transform(const Layout& L, Shard& s, int sm_count);
 void launch_exchange(const Layout& L, Shard& s, int sm_count);
-void launch_coulomb(const Layout& L, Shard& s, int sm_count);
+void launch_coulomb(const Layout& L, Shard& s, int sm_count, cudaStream_t st);
+bool launch_coulomb_fused(const Layout& L, Shard& s, int sm_count, cudaStream_t st);
 void launch_epilogue(const Layout& L, Shard& s, bool add_H);
 void launch_scatter_pairs(const Layout& L, Shard& s, const double* T_dev, int64_t ld, int64_t col_begin,
                           int64_t col_count);

@@ -6,9 +6,9 @@
 //   exchange         K[p,q]     = sum_(Q,i) W[(Q,i),p] * W[(Q,i),q]    replaces calculate_K_lower_diagonal_block_no_screen
 //                                                                      (ScreenedDF.jl:548-641; dense DensityFitting.jl:219)
 //
-// Both kernels are persistent (one CTA per SM, static round-robin over work items), warp-specialised: warp 8 is
-// the copy producer, warps 0-7 issue DMMA.  All operands are stored in HBM pre-swizzled (dmma_common.cuh: swz) so a
-// dense bulk copy lands bank-conflict-free in shared memory.
+// Both kernels are persistent (one CTA per SM, static round-robin over work items); 8 warps issue DMMA and thread 0 is
+// also the copy producer, running NSTAGE - 1 slabs ahead through a full/empty mbarrier ring.  All operands are stored
+// in HBM pre-swizzled (dmma_common.cuh: swz) so a dense bulk copy lands bank-conflict-free in shared memory.
 #include "dmma_common.cuh"
 #include "jcdf_internal.h"
 
@@ -16,7 +16,12 @@ namespace jcdf {
 
 constexpr int NSTAGE = 3;
 constexpr int CONSUMER_WARPS = 8;
-constexpr int CTA_THREADS = (CONSUMER_WARPS + 1) * 32;
+// 8 warps = 2 per SM sub-partition: every warp issues DMMA, thread 0 additionally issues the bulk copies.  (A ninth,
+// dedicated producer warp would put 3 warps on one sub-partition, which caps the kernel at 168 registers/thread and
+// fills that sub-partition's register file, so no Coulomb CTA could co-reside.)
+constexpr int CTA_THREADS = CONSUMER_WARPS * 32;
+constexpr int HT_THREADS = CTA_THREADS + 32;  // half-transform: plus one dedicated producer warp (168 registers/thread)
+constexpr int MAX_REGS = 208;  // leaves (16384 - 2*32*208) = 3072 registers per sub-partition for the Coulomb sweeps
 
 // =====================================================================================================================
 // C_occ re-layout and packed density
@@ -42,20 +47,35 @@ __global__ void k_prep_cs(const double* __restrict__ Craw, int64_t ldc, double* 
 // dt[tile][r][swz(r,c)] = w * sum_i C[p,i] C[q,i],  p = 32 a + r, q = 32 b + c,  w = 1 on diagonal tiles (full
 // square stored) and 2 on off-diagonal tiles — the doubled off-diagonal density of copy_screened_density_to_array
 // (ScreenedDF.jl:305-316) expressed in tile space.
-__global__ void k_density_packed(const double* __restrict__ Craw, int64_t ldc, double* __restrict__ dt,
-                                 const int32_t* __restrict__ tile_a, const int32_t* __restrict__ tile_b, int N, int occ) {
-    int tile = blockIdx.x;
-    int a = tile_a[tile], b = tile_b[tile];
-    double w = (a == b) ? 1.0 : 2.0;
-    int c = threadIdx.x & 31;
-    int q = b * 32 + c;
-    for (int r = threadIdx.x >> 5; r < 32; r += blockDim.x >> 5) {
-        int p = a * 32 + r;
-        double acc = 0.0;
-        if (p < N && q < N) {
-            for (int i = 0; i < occ; i++) acc = fma(Craw[p + ldc * i], Craw[q + ldc * i], acc);
+__global__ void __launch_bounds__(256) k_density_packed(const double* __restrict__ Craw, int64_t ldc,
+                                                         double* __restrict__ dt, const int32_t* __restrict__ tile_a,
+                                                         const int32_t* __restrict__ tile_b, int N, int occ) {
+    constexpr int IC = 64;                      // occupied orbitals staged per pass
+    __shared__ double sa[IC][33], sb[IC][33];   // [i][p] / [i][q], padded against bank conflicts
+    const int tile = blockIdx.x;
+    const int a = tile_a[tile], b = tile_b[tile];
+    const double w = (a == b) ? 1.0 : 2.0;
+    const int c = threadIdx.x & 31, r0 = threadIdx.x >> 5;
+    double acc[4] = {0.0, 0.0, 0.0, 0.0};
+    for (int i0 = 0; i0 < occ; i0 += IC) {
+        for (int ii = r0; ii < IC; ii += 8) {
+            const int i = i0 + ii, p = a * 32 + c, q = b * 32 + c;
+            sa[ii][c] = (i < occ && p < N) ? Craw[p + ldc * i] : 0.0;
+            sb[ii][c] = (i < occ && q < N) ? Craw[q + ldc * i] : 0.0;
         }
-        dt[(int64_t)tile * TILE_ELEMS + r * 32 + swz(r, c)] = w * acc;
+        __syncthreads();
+#pragma unroll 8
+        for (int ii = 0; ii < IC; ii++) {
+            const double vb = sb[ii][c];
+#pragma unroll
+            for (int k = 0; k < 4; k++) acc[k] = fma(sa[ii][r0 + 8 * k], vb, acc[k]);
+        }
+        __syncthreads();
+    }
+#pragma unroll
+    for (int k = 0; k < 4; k++) {
+        const int r = r0 + 8 * k;
+        dt[(int64_t)tile * TILE_ELEMS + r * 32 + swz(r, c)] = w * acc[k];
     }
 }
 
@@ -76,7 +96,7 @@ struct HTParams {
     const int32_t* tile_index;
     const double* Cs;
     double* W;
-    int q_len, nb, n_mt, n_pt128, npt64, occ_pad;
+    int q_len, nb, n_mt, n_pt128, npt64, occ_pad, n_valid_last;
     int64_t n_items;
 };
 
@@ -84,31 +104,39 @@ struct HTParams {
 //   out[i, p] = sum_q Cs[q][i] * Bsym_Q[q][p]      (M = i, N = p, K = q)
 // The k loop walks the 32-wide q blocks; for p block pb and q block kb the stored tile is (max, min): read as
 // [k][n] when kb >= pb and transposed as [n][k] when kb < pb, so each stored tile serves both triangles.
+// Each consumer warp owns a (BM/2) x 32 block of the item: wm = warp >> 2 selects the M half, j = warp & 3 the 32-wide
+// p block (= one stored B tile per k slab), so a k-step of 4 costs MH + 4 fragment loads for MH * 4 DMMAs.
 template <int MT, bool TRANSPOSED>
-__device__ __forceinline__ void ht_slab(double (&acc)[MT][2][2], const double* __restrict__ sA,
-                                        const double* __restrict__ sB, int nl0, int g, int t) {
+__device__ __forceinline__ void ht_slab(double (&acc)[MT / 2][4][2], const double* __restrict__ sA,
+                                        const double* __restrict__ sB, int m0, int g, int t, int ksteps) {
     constexpr int BM = 8 * MT;
+    constexpr int MH = MT / 2;
+#pragma unroll 2
+    for (int ks = 0; ks < ksteps; ks++) {
+        const int kr = 4 * ks + t;
+        double a[MH], b[4];
 #pragma unroll
-    for (int k0 = 0; k0 < KSLAB; k0 += 4) {
-        const int kr = k0 + t;
-        double a[MT], b[2];
+        for (int jm = 0; jm < MH; jm++) a[jm] = sA[kr * BM + ((m0 + 8 * jm + g) ^ (t << 2))];
 #pragma unroll
-        for (int jm = 0; jm < MT; jm++) a[jm] = sA[kr * BM + ((8 * jm + g) ^ (t << 2))];
-#pragma unroll
-        for (int jn = 0; jn < 2; jn++) {
-            const int n = nl0 + 8 * jn + g;
+        for (int jn = 0; jn < 4; jn++) {
+            const int n = 8 * jn + g;
             b[jn] = TRANSPOSED ? sB[n * 32 + (kr ^ ((n & 3) << 2))] : sB[kr * 32 + (n ^ (t << 2))];
         }
 #pragma unroll
-        for (int jm = 0; jm < MT; jm++)
+        for (int jm = 0; jm < MH; jm++)
 #pragma unroll
-            for (int jn = 0; jn < 2; jn++) dmma(acc[jm][jn][0], acc[jm][jn][1], a[jm], b[jn]);
+            for (int jn = 0; jn < 4; jn++) dmma(acc[jm][jn][0], acc[jm][jn][1], a[jm], b[jn]);
     }
 }
 
-template <int MT>
-__global__ void __launch_bounds__(CTA_THREADS, 1) k_half_transform(HTParams prm) {
+// DEDICATED (launched with HT_THREADS = 288): warp 8 is a dedicated copy producer (its lane 0 runs the whole produce() sequence, as
+// far ahead as the ring allows) and warps 0-7 only compute — measured 4 % faster here than thread 0 doubling as the
+// producer, because the tile-table lookups and the empty-barrier wait no longer sit on a DMMA warp's critical path.
+// DEDICATED = false (CTA_THREADS = 256) is the merged scheme of k_exchange; not instantiated.
+template <int MT, bool DEDICATED>
+__global__ void __launch_bounds__(HT_THREADS, 1) k_half_transform(HTParams prm) {
     constexpr int BM = 8 * MT;
+    constexpr int MH = MT / 2;
     constexpr int STAGE_DOUBLES = 32 * BM + 4 * TILE_ELEMS;
     extern __shared__ __align__(128) unsigned char smem_raw[];
     double* stages = reinterpret_cast<double*>(smem_raw);
@@ -128,67 +156,80 @@ __global__ void __launch_bounds__(CTA_THREADS, 1) k_half_transform(HTParams prm)
     __syncthreads();
 
     const int nb = prm.nb, n_mt = prm.n_mt, n_pt = prm.n_pt128;
-    PipeState ps;
+    constexpr bool dedicated = DEDICATED;
+    const bool is_producer = !dedicated && (threadIdx.x == 0);
 
-    if (warp == CONSUMER_WARPS) {
-        // ------------------------------------------------ producer ------------------------------------------------
-        if (lane == 0) {
-            for (int64_t item = blockIdx.x; item < prm.n_items; item += gridDim.x) {
-                const int mt = (int)(item % n_mt);
-                const int64_t r1 = item / n_mt;
-                const int pt = (int)(r1 % n_pt);
-                const int64_t qrow = r1 / n_pt;
-                const double* Brow = prm.Bp + qrow * prm.row_len;
-                for (int kb = 0; kb < nb; kb++) {
-                    mbar_wait(&empty[ps.stage], ps.phase ^ 1u);
-                    int mask = 0;
-                    int tix[4];
+    // ---- copy issue: walks the same (item, kb) sequence ahead of the consumers ----
+    PipeState pp;
+    int64_t p_item = blockIdx.x;
+    int p_kb = 0;
+    auto produce = [&]() {
+        if (p_item >= prm.n_items) return;
+        const int mt = (int)(p_item % n_mt);
+        const int64_t r1 = p_item / n_mt;
+        const int pt = (int)(r1 % n_pt);
+        const int64_t qrow = r1 / n_pt;
+        const double* Brow = prm.Bp + qrow * prm.row_len;
+        const int kb = p_kb;
+        mbar_wait(&empty[pp.stage], pp.phase ^ 1u);
+        int mask = 0;
+        int tix[4];
 #pragma unroll
-                    for (int j = 0; j < 4; j++) {
-                        const int pb = 4 * pt + j;
-                        tix[j] = -1;
-                        if (pb < nb) {
-                            const int a = max(pb, kb), b = min(pb, kb);
-                            tix[j] = prm.tile_index[a * nb + b];
-                            if (tix[j] >= 0) mask |= 1 << j;
-                        }
-                    }
-                    present[ps.stage] = mask;
-                    double* st = stages + (size_t)ps.stage * STAGE_DOUBLES;
-                    if (mask) {
-                        const uint32_t bytes = 32u * BM * 8u + (uint32_t)__popc(mask) * (TILE_ELEMS * 8u);
-                        mbar_arrive_expect_tx(&full[ps.stage], bytes);
-                        bulk_g2s(st, prm.Cs + ((int64_t)kb * n_mt + mt) * (32 * BM), 32u * BM * 8u, &full[ps.stage]);
-#pragma unroll
-                        for (int j = 0; j < 4; j++)
-                            if (tix[j] >= 0)
-                                bulk_g2s(st + 32 * BM + j * TILE_ELEMS, Brow + (int64_t)tix[j] * TILE_ELEMS,
-                                         TILE_ELEMS * 8u, &full[ps.stage]);
-                    } else {
-                        mbar_arrive(&full[ps.stage]);
-                    }
-                    ps.advance<NSTAGE>();
-                }
+        for (int j = 0; j < 4; j++) {
+            const int pb = 4 * pt + j;
+            tix[j] = -1;
+            if (pb < nb) {
+                const int a = max(pb, kb), b = min(pb, kb);
+                tix[j] = prm.tile_index[a * nb + b];
+                if (tix[j] >= 0) mask |= 1 << j;
             }
         }
+        present[pp.stage] = mask;
+        double* st = stages + (size_t)pp.stage * STAGE_DOUBLES;
+        if (mask) {
+            const uint32_t bytes = 32u * BM * 8u + (uint32_t)__popc(mask) * (TILE_ELEMS * 8u);
+            mbar_arrive_expect_tx(&full[pp.stage], bytes);
+            bulk_g2s(st, prm.Cs + ((int64_t)kb * n_mt + mt) * (32 * BM), 32u * BM * 8u, &full[pp.stage]);
+#pragma unroll
+            for (int j = 0; j < 4; j++)
+                if (tix[j] >= 0)
+                    bulk_g2s(st + 32 * BM + j * TILE_ELEMS, Brow + (int64_t)tix[j] * TILE_ELEMS, TILE_ELEMS * 8u,
+                             &full[pp.stage]);
+        } else {
+            mbar_arrive(&full[pp.stage]);
+        }
+        pp.advance<NSTAGE>();
+        if (++p_kb == nb) {
+            p_kb = 0;
+            p_item += gridDim.x;
+        }
+    };
+    if (dedicated && warp == CONSUMER_WARPS) {
+        if (lane == 0)
+            while (p_item < prm.n_items) produce();
         return;
     }
+    if (is_producer)
+        for (int s = 0; s < NSTAGE - 1; s++) produce();
 
     // ---------------------------------------------------- consumers ----------------------------------------------------
+    PipeState ps;
     const int g = lane >> 2, t = lane & 3;
-    const int j = warp >> 1;           // p block inside the 128-wide tile
-    const int nl0 = (warp & 1) * 16;   // 16-column strip inside the block
+    const int j = warp & 3;                 // p block inside the 128-wide tile
+    const int m0 = (warp >> 2) * (BM / 2);  // first occupied-orbital row of this warp's half
+    // the last q block holds N - 32 (nb - 1) valid rows: trim its k loop to whole DMMA k-steps (the rest is zero padding)
+    const int last_ksteps = (prm.n_valid_last + 3) >> 2;
     for (int64_t item = blockIdx.x; item < prm.n_items; item += gridDim.x) {
         const int mt = (int)(item % n_mt);
         const int64_t r1 = item / n_mt;
         const int pt = (int)(r1 % n_pt);
         const int64_t qrow = r1 / n_pt;
         const int pbg = 4 * pt + j;
-        double acc[MT][2][2];
+        double acc[MH][4][2];
 #pragma unroll
-        for (int jm = 0; jm < MT; jm++)
+        for (int jm = 0; jm < MH; jm++)
 #pragma unroll
-            for (int jn = 0; jn < 2; jn++) acc[jm][jn][0] = acc[jm][jn][1] = 0.0;
+            for (int jn = 0; jn < 4; jn++) acc[jm][jn][0] = acc[jm][jn][1] = 0.0;
 
         for (int kb = 0; kb < nb; kb++) {
             mbar_wait(&full[ps.stage], ps.phase);
@@ -196,24 +237,28 @@ __global__ void __launch_bounds__(CTA_THREADS, 1) k_half_transform(HTParams prm)
             if ((mask >> j) & 1) {
                 const double* sA = stages + (size_t)ps.stage * STAGE_DOUBLES;
                 const double* sB = sA + 32 * BM + j * TILE_ELEMS;
-                if (kb < pbg) ht_slab<MT, true>(acc, sA, sB, nl0, g, t);
-                else ht_slab<MT, false>(acc, sA, sB, nl0, g, t);
+                const int ksteps = (kb == nb - 1) ? last_ksteps : KSLAB / 4;
+                if (kb < pbg) ht_slab<MT, true>(acc, sA, sB, m0, g, t, ksteps);
+                else ht_slab<MT, false>(acc, sA, sB, m0, g, t, ksteps);
             }
             __syncwarp();
             if (lane == 0) mbar_arrive(&empty[ps.stage]);
             ps.advance<NSTAGE>();
+            // refill the slab released one iteration ago (every warp is past it by now) with the slab NSTAGE - 1 ahead
+            if (is_producer) produce();
+            __syncwarp();
         }
         // epilogue: W[(Q,i)][p], 16-byte stores into the swizzled [32 x 64] W tiles
 #pragma unroll
-        for (int jm = 0; jm < MT; jm++) {
-            const int i = mt * BM + 8 * jm + g;
+        for (int jm = 0; jm < MH; jm++) {
+            const int i = mt * BM + m0 + 8 * jm + g;
             if (i < prm.occ_pad) {
                 const int64_t krow = qrow * prm.occ_pad + i;
                 const int64_t kc = krow >> 5;
                 const int kr = (int)(krow & 31);
 #pragma unroll
-                for (int jn = 0; jn < 2; jn++) {
-                    const int p = 128 * pt + 32 * j + nl0 + 8 * jn + 2 * t;
+                for (int jn = 0; jn < 4; jn++) {
+                    const int p = 128 * pt + 32 * j + 8 * jn + 2 * t;
                     const int p64 = p >> 6, pc = p & 63;
                     if (p64 < prm.npt64) {
                         double2 v = make_double2(acc[jm][jn][0], acc[jm][jn][1]);
@@ -232,8 +277,8 @@ size_t half_transform_smem_bytes(int bm) {
 template <int MT>
 static void launch_ht_t(const HTParams& prm, int grid, cudaStream_t st) {
     size_t smem = half_transform_smem_bytes(8 * MT);
-    cudaFuncSetAttribute(k_half_transform<MT>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
-    k_half_transform<MT><<<grid, CTA_THREADS, smem, st>>>(prm);
+    cudaFuncSetAttribute(k_half_transform<MT, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+    k_half_transform<MT, true><<<grid, HT_THREADS, smem, st>>>(prm);
 }
 
 void launch_half_transform(const Layout& L, Shard& s, int sm_count) {
@@ -249,6 +294,7 @@ void launch_half_transform(const Layout& L, Shard& s, int sm_count) {
     prm.n_pt128 = L.n_pt128;
     prm.npt64 = L.npt64;
     prm.occ_pad = L.occ_pad;
+    prm.n_valid_last = (int)(L.N - 32 * (L.nb - 1));
     prm.n_items = (int64_t)s.q_len * L.n_pt128 * L.n_mt;
     int grid = (int)std::min<int64_t>(prm.n_items, sm_count);
     if (grid <= 0) return;
@@ -277,7 +323,7 @@ struct XParams {
 
 constexpr int X_STAGE_DOUBLES = 4 * 32 * 64;  // A0 A1 B0 B1, each a [32 x 64] W tile
 
-__global__ void __launch_bounds__(CTA_THREADS, 1) k_exchange(XParams prm) {
+__global__ void __maxnreg__(MAX_REGS) k_exchange(XParams prm) {
     extern __shared__ __align__(128) unsigned char smem_raw[];
     double* stages = reinterpret_cast<double*>(smem_raw);
     uint64_t* full = reinterpret_cast<uint64_t*>(stages + (size_t)NSTAGE * X_STAGE_DOUBLES);
@@ -294,8 +340,8 @@ __global__ void __launch_bounds__(CTA_THREADS, 1) k_exchange(XParams prm) {
     }
     __syncthreads();
 
-    PipeState ps;
     const int npt64 = prm.npt64;
+    const bool is_producer = (threadIdx.x == 0);
 
     auto decode = [&](int64_t item, int& ta, int& tb, int& kc0, int& kc1) {
         const int tile = (int)(item % prm.n_tiles);
@@ -308,31 +354,37 @@ __global__ void __launch_bounds__(CTA_THREADS, 1) k_exchange(XParams prm) {
         kc1 = min(prm.chunks, kc0 + prm.chunks_per_slice);
     };
 
-    if (warp == CONSUMER_WARPS) {
-        if (lane == 0) {
-            for (int64_t item = blockIdx.x; item < prm.n_items; item += gridDim.x) {
-                int ta, tb, kc0, kc1;
-                decode(item, ta, tb, kc0, kc1);
-                int col[4] = {2 * ta, 2 * ta + 1, 2 * tb, 2 * tb + 1};
-                int nvalid = 0;
+    // ---- copy issue (thread 0 only), NSTAGE - 1 chunks ahead of the consumers ----
+    PipeState pp;
+    int64_t p_item = blockIdx.x;
+    int p_kc = -1, p_kc1 = 0, p_col[4] = {0, 0, 0, 0}, p_nvalid = 0;
+    auto produce = [&]() {
+        while (p_kc < 0 || p_kc >= p_kc1) {  // next item (skips empty slices)
+            if (p_kc >= 0) p_item += gridDim.x;
+            if (p_item >= prm.n_items) return;
+            int ta, tb, kc0, kc1;
+            decode(p_item, ta, tb, kc0, kc1);
+            p_col[0] = 2 * ta; p_col[1] = 2 * ta + 1; p_col[2] = 2 * tb; p_col[3] = 2 * tb + 1;
+            p_nvalid = 0;
 #pragma unroll
-                for (int x = 0; x < 4; x++) nvalid += (col[x] < npt64);
-                for (int kc = kc0; kc < kc1; kc++) {
-                    mbar_wait(&empty[ps.stage], ps.phase ^ 1u);
-                    double* st = stages + (size_t)ps.stage * X_STAGE_DOUBLES;
-                    mbar_arrive_expect_tx(&full[ps.stage], (uint32_t)nvalid * 32u * 64u * 8u);
-#pragma unroll
-                    for (int x = 0; x < 4; x++)
-                        if (col[x] < npt64)
-                            bulk_g2s(st + x * 2048, prm.W + ((int64_t)kc * npt64 + col[x]) * 2048, 2048u * 8u,
-                                     &full[ps.stage]);
-                    ps.advance<NSTAGE>();
-                }
-            }
+            for (int x = 0; x < 4; x++) p_nvalid += (p_col[x] < npt64);
+            p_kc = kc0;
+            p_kc1 = kc1;
         }
-        return;
-    }
+        mbar_wait(&empty[pp.stage], pp.phase ^ 1u);
+        double* st = stages + (size_t)pp.stage * X_STAGE_DOUBLES;
+        mbar_arrive_expect_tx(&full[pp.stage], (uint32_t)p_nvalid * 32u * 64u * 8u);
+#pragma unroll
+        for (int x = 0; x < 4; x++)
+            if (p_col[x] < npt64)
+                bulk_g2s(st + x * 2048, prm.W + ((int64_t)p_kc * npt64 + p_col[x]) * 2048, 2048u * 8u, &full[pp.stage]);
+        pp.advance<NSTAGE>();
+        p_kc++;
+    };
+    if (is_producer)
+        for (int s = 0; s < NSTAGE - 1; s++) produce();
 
+    PipeState ps;
     const int g = lane >> 2, t = lane & 3;
     const int wm = warp >> 2, wn = warp & 3;
     const int nl0 = (wn & 1) * 32;
@@ -351,7 +403,7 @@ __global__ void __launch_bounds__(CTA_THREADS, 1) k_exchange(XParams prm) {
             if (active) {
                 const double* sA = stages + (size_t)ps.stage * X_STAGE_DOUBLES + wm * 2048;
                 const double* sB = stages + (size_t)ps.stage * X_STAGE_DOUBLES + (2 + (wn >> 1)) * 2048;
-#pragma unroll
+#pragma unroll 2
                 for (int k0 = 0; k0 < KSLAB; k0 += 4) {
                     const int kr = k0 + t;
                     double a[8], b[4];
@@ -368,6 +420,8 @@ __global__ void __launch_bounds__(CTA_THREADS, 1) k_exchange(XParams prm) {
             __syncwarp();
             if (lane == 0) mbar_arrive(&empty[ps.stage]);
             ps.advance<NSTAGE>();
+            if (is_producer) produce();
+            __syncwarp();
         }
         double* out = prm.Kpart + item * (128 * 128);
 #pragma unroll

@@ -33,6 +33,9 @@ WORKLOADS = {
                     0.0, 400.0, 1003),
     "w50_screened": Workload("w50_screened", "w50 water cluster DF-RHF cc-pVDZ, Schwarz mask", 1250, 4800, 250,
                              "cluster", 50, 2.6, 400.0, 1013),
+    # one rank's share of w50 when Q is sharded over 8 GPUs (profiling stand-in for the 8-GPU per-device work)
+    "w50_q600": Workload("w50_q600", "w50 water cluster DF-RHF cc-pVDZ, the 600 auxiliary rows one of 8 GPUs owns", 1250, 600,
+                         250, "none", 50, 0.0, 400.0, 1003),
     "c20h42": Workload("c20h42", "C20H42 alkane DF-RHF cc-pVTZ with shell-pair screening mask", 1330, 3490, 81,
                        "chain", 20, 6.5, 300.0, 1004),
     "gly18": Workload("gly18", "glycine oligomer DF-RHF cc-pVTZ, largest B tensor, 8 B200", 3395, 9333, 275, "chain",

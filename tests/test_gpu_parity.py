@@ -9,11 +9,12 @@ pytestmark = pytest.mark.gpu
 TOL = 1e-10
 
 
-def _build(N, Q, occ, B, C_occ, H, mask, ndev=1, shards=None, fused=0):
+def _build(N, Q, occ, B, C_occ, H, mask, ndev=1, shards=None, fused=1, overlap=0):
     gd = jc.B200Data(N, Q, occ, ndev)
     if shards is not None:
         gd.set_shards(shards)
     gd.set_option("coulomb_fused", fused)
+    gd.set_option("coulomb_overlap", overlap)
     gd.set_mask(jc.ScreeningData(mask, N))
     shards = shards or jc.balanced_function_shards(Q, ndev)
     for d, r in enumerate(shards):
@@ -23,21 +24,25 @@ def _build(N, Q, occ, B, C_occ, H, mask, ndev=1, shards=None, fused=0):
 
 
 @pytest.mark.parametrize("N,Q,occ", [(25, 96, 5), (64, 32, 8), (70, 40, 9), (33, 7, 1), (129, 50, 17), (203, 131, 27)])
-def test_dense_parity(N, Q, occ):
+@pytest.mark.parametrize("fused", [1, 0])
+def test_dense_parity(N, Q, occ, fused):
     B, C_occ, H = random_inputs(N, Q, occ, seed=N * 1000 + Q)
     F_ref = oracle_fock(B, C_occ, H, None)
-    gd, F, st = _build(N, Q, occ, B, C_occ, H, None)
+    gd, F, st = _build(N, Q, occ, B, C_occ, H, None, fused=fused)
     assert np.abs(F - F_ref).max() < TOL
     assert np.array_equal(F, F.T)
     gd.close()
 
 
+@pytest.mark.parametrize("fused,overlap", [(1, 0), (0, 0), (0, 1)])
 @pytest.mark.parametrize("N,Q,occ,hw", [(70, 40, 9, 20), (203, 131, 27, 60), (160, 64, 16, 33), (300, 90, 40, 70)])
-def test_screened_parity(N, Q, occ, hw):
+def test_screened_parity(N, Q, occ, hw, fused, overlap):
+    """All three Coulomb schedules: single-pass cooperative kernel, two-pass sweeps, two-pass on the second stream."""
     mask = banded_mask(N, hw, seed=N)
     B, C_occ, H = random_inputs(N, Q, occ, seed=N + 17, mask=mask, decay=hw / 2.0)
     F_ref = oracle_fock(B, C_occ, H, mask)
-    gd, F, st = _build(N, Q, occ, B, C_occ, H, mask)
+    gd, F, st = _build(N, Q, occ, B, C_occ, H, mask, fused=fused, overlap=overlap)
+    assert gd.layout().kernel_launches_per_build == (6 if fused else 7)
     li = gd.layout()
     assert li.pairs_kept == int(mask.sum())
     assert li.pairs_tri == int(np.tril(mask).sum())
@@ -54,6 +59,23 @@ def test_screened_equals_dense_algorithm_when_mask_full():
     F_ref = oracle_fock(B, C_occ, H, None)
     gd, F, _ = _build(N, Q, occ, B, C_occ, H, mask)
     assert np.abs(F - F_ref).max() < TOL
+    gd.close()
+
+
+def test_fused_coulomb_is_deterministic_and_long_rows_fall_back():
+    """The cooperative kernel sums per-CTA partials in a fixed order: repeated builds are bit-identical.  A shard whose
+    row segment exceeds the per-thread register segment (N = 1500 unmasked: 62 KB per CTA > 56 KB) silently uses the two-pass sweeps."""
+    N, Q, occ = 203, 131, 27
+    B, C_occ, H = random_inputs(N, Q, occ, seed=9)
+    gd, F1, _ = _build(N, Q, occ, B, C_occ, H, None, fused=1)
+    for _ in range(3):
+        assert np.array_equal(gd.fock_build(C_occ, None)[0], F1)
+    gd.close()
+    N, Q, occ = 1500, 3, 2
+    B, C_occ, H = random_inputs(N, Q, occ, seed=10)
+    gd, F, _ = _build(N, Q, occ, B, C_occ, H, None, fused=1)
+    assert gd.layout().kernel_launches_per_build == 7
+    assert np.abs(F - oracle_fock(B, C_occ, H, None)).max() < TOL
     gd.close()
 
 
