@@ -124,6 +124,26 @@ int32_t jcdf_fock_build_device(jcdf_handle* h, const double* C_occ_dev, int64_t 
  * F, X: N x N column-major (host).  evals: N.  C: N x N.                                                         */
 int32_t jcdf_eigh(jcdf_handle* h, const double* F, const double* X, double* evals, double* C);
 
+/* ---- on-device SCF step: F, C, D and the DIIS history never leave the GPU between builds ------------
+ * jcdf_scf_init replaces the set-up part of rhf_kernel (src/rhf/energy/SCF.jl:141-183): uploads S and H (N x N
+ * column-major, host), builds the symmetric orthogonaliser X = U_good diag(s_good^-1/2) U_good^T on the device
+ * (overlap eigenvalues below 1e-6 dropped, :141-163) and runs the hcore guess iteration(F = H) (:178-181).
+ * ndiis = scf_flags["ndiis"] (0 disables DIIS); E_nuc is added to every reported energy (:524).
+ * E_guess_out (NULL allowed) receives E_elec(hcore guess) + E_nuc.  Requires B to be formed (jcdf_fock_build ready). */
+int32_t jcdf_scf_init(jcdf_handle* h, const double* S, const double* H, double E_nuc, int32_t ndiis, double* E_guess_out);
+/* One pass of the `while !iter_converged` body of scf_cycles_kernel (SCF.jl:399-551): Fock build from the resident
+ * C[:,1:occ] (:463), DIIS on e = FDS - (FDS)^T with the newest-first history (:471-501; DIIS(), EnergyHelpers.jl:234-258;
+ * a singular system takes the "Faulty DIIS!" branch), dynamic damping (:504-508), iteration() (:510-512, :1072-1125),
+ * dE and D_rms (:521-525).  result (NULL allowed) = { E, dE, D_rms, E_elec, t_fock, t_diis, t_iteration, t_total } (s). */
+int32_t jcdf_scf_step(jcdf_handle* h, double* result);
+/* Repeat jcdf_scf_step until |dE| <= dele and D_rms <= rmsd (SCF.jl:527-530, :551) or max_iterations.
+ * history: NULL or double[3 * max_iterations] receiving (E, dE, D_rms) per iteration.                             */
+int32_t jcdf_scf_run(jcdf_handle* h, int32_t max_iterations, double dele, double rmsd, double* E_out,
+                     int32_t* iterations_out, int32_t* converged_out, double* history);
+/* Copy a resident matrix back to the host: name = "F" (last extrapolated/damped Fock), "D", "C", "X", "S", "H"
+ * (N x N column-major) or "evals" (N) — the entries of the Dict rhf_kernel returns (SCF.jl:251-259).              */
+int32_t jcdf_scf_get(jcdf_handle* h, const char* name, double* out);
+
 /* ---- one process per GPU (torchrun / MPI ranks > 1) --------------------------------------------------------------
  * The reference sums rank-partial Fock matrices with MPI.Allreduce! (DensityFitting.jl:68-71).  Here rank 0 calls
  * jcdf_comm_unique_id, ships the 128 bytes to the other ranks by any means, and every rank calls jcdf_comm_init_rank;

@@ -56,6 +56,10 @@ SIGNATURES = {
     "jcdf_last_kernel_ms": (_i32, [_p, _i32, _p]),
     "jcdf_set_option": (_i32, [_p, C.c_char_p, _i64]),
     "jcdf_get_stream": (_i32, [_p, _i32, C.POINTER(_p)]),
+    "jcdf_scf_init": (_i32, [_p, _p, _p, _f64, _i32, C.POINTER(_f64)]),
+    "jcdf_scf_step": (_i32, [_p, _p]),
+    "jcdf_scf_run": (_i32, [_p, _i32, _f64, _f64, C.POINTER(_f64), C.POINTER(_i32), C.POINTER(_i32), _p]),
+    "jcdf_scf_get": (_i32, [_p, C.c_char_p, _p]),
 }
 
 _lib = None

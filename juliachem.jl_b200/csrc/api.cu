@@ -12,53 +12,13 @@
 #include <cusolverDn.h>
 
 #include "jcdf_internal.h"
+#include "jcdf_macros.h"
 #include "nccl_dyn.h"
 
 namespace jcdf {
 
 static thread_local std::string g_err;
 void set_error(const std::string& msg) { g_err = msg; }
-
-#define JC_CUDA(call)                                                                                   \
-    do {                                                                                                \
-        cudaError_t e__ = (call);                                                                       \
-        if (e__ != cudaSuccess) {                                                                       \
-            set_error(std::string(#call) + ": " + cudaGetErrorString(e__) + " (" + __FILE__ + ":" +     \
-                      std::to_string(__LINE__) + ")");                                                  \
-            return (e__ == cudaErrorMemoryAllocation) ? JCDF_ERR_NOMEM : JCDF_ERR_CUDA;                 \
-        }                                                                                               \
-    } while (0)
-#define JC_CUBLAS(call)                                                                                 \
-    do {                                                                                                \
-        cublasStatus_t s__ = (call);                                                                    \
-        if (s__ != CUBLAS_STATUS_SUCCESS) {                                                             \
-            set_error(std::string(#call) + ": cuBLAS status " + std::to_string((int)s__));              \
-            return JCDF_ERR_CUDA;                                                                       \
-        }                                                                                               \
-    } while (0)
-#define JC_CUSOLVER(call)                                                                               \
-    do {                                                                                                \
-        cusolverStatus_t s__ = (call);                                                                  \
-        if (s__ != CUSOLVER_STATUS_SUCCESS) {                                                           \
-            set_error(std::string(#call) + ": cuSOLVER status " + std::to_string((int)s__));            \
-            return JCDF_ERR_CUDA;                                                                       \
-        }                                                                                               \
-    } while (0)
-#define JC_NCCL(call)                                                                                   \
-    do {                                                                                                \
-        int r__ = (call);                                                                               \
-        if (r__ != 0) {                                                                                 \
-            set_error(std::string(#call) + ": " + nccl().GetErrorString(r__));                          \
-            return JCDF_ERR_NCCL;                                                                       \
-        }                                                                                               \
-    } while (0)
-#define JC_REQUIRE(cond, msg)                    \
-    do {                                         \
-        if (!(cond)) {                           \
-            set_error(msg);                      \
-            return JCDF_ERR_INVALID;             \
-        }                                        \
-    } while (0)
 
 static inline int64_t round_up(int64_t x, int64_t m) { return (x + m - 1) / m * m; }
 
@@ -250,6 +210,7 @@ int32_t jcdf_create(int64_t N, int64_t Q, int64_t occ, int32_t ndev, const int32
 
 int32_t jcdf_destroy(jcdf_handle* h) {
     if (!h) return JCDF_OK;
+    scf_destroy(h);
     for (Shard& s : h->shards) {
         cudaSetDevice(s.dev);
         if (s.stream) cudaStreamSynchronize(s.stream);
@@ -578,7 +539,7 @@ int32_t jcdf_set_core_hamiltonian(jcdf_handle* h, const double* H) {
     return JCDF_OK;
 }
 
-static int fock_build_impl(jcdf_handle* h, const double* C_occ, int64_t ldc, const double* H, double* F_out,
+int fock_build_impl(jcdf_handle* h, const double* C_occ, int64_t ldc, const double* H, double* F_out,
                            double* stage_seconds, bool device_ptrs) {
     JC_REQUIRE(h && C_occ && F_out, "jcdf_fock_build: NULL argument");
     const Layout& L = h->lay;

@@ -76,6 +76,8 @@ struct Shard {
     void* nccl_comm = nullptr;
 };
 
+struct ScfState;  // scf.cu
+
 }  // namespace jcdf
 
 struct jcdf_handle {
@@ -89,6 +91,7 @@ struct jcdf_handle {
     int64_t opt_coulomb_fused = 1;    // single-pass cooperative Coulomb kernel whenever the row segment fits in smem
     int64_t opt_coulomb_overlap = 0;  // two-pass sweeps on a second stream, concurrent with the tensor-core kernels
     int64_t opt_exchange_slices = 0;
+    jcdf::ScfState* scf = nullptr;    // on-device SCF driver state (jcdf_scf_*), owned
 };
 
 namespace jcdf {
@@ -108,5 +111,11 @@ size_t exchange_smem_bytes();
 int kernels_per_build();
 
 void set_error(const std::string& msg);
+void scf_destroy(jcdf_handle* h);  // scf.cu
 
 }  // namespace jcdf
+
+// One Fock build over host (device_ptrs = false) or device-resident operands; defined in api.cu, also driven by scf.cu.
+extern "C" __attribute__((visibility("hidden"))) int fock_build_impl(jcdf_handle* h, const double* C_occ, int64_t ldc,
+                                                                      const double* H, double* F_out,
+                                                                      double* stage_seconds, bool device_ptrs);

@@ -226,6 +226,35 @@ class B200Data:
         check(self._lib.jcdf_eigh(self._h, _ptr(Fc), _ptr(Xc), _ptr(ev), _ptr(Cm)))
         return ev, Cm
 
+    # -- on-device SCF step -------------------------------------------------------------------------
+    def scf_init(self, S: np.ndarray, H: np.ndarray, E_nuc: float, ndiis: int = 10) -> float:
+        """rhf_kernel's set-up (SCF.jl:141-183) on the device: X = S^-1/2, hcore guess.  Returns the guess energy."""
+        N = self.N
+        Sc, Hc = _f64_colmajor(S, (N, N)), _f64_colmajor(H, (N, N))
+        e = C.c_double()
+        check(self._lib.jcdf_scf_init(self._h, _ptr(Sc), _ptr(Hc), float(E_nuc), int(ndiis), C.byref(e)))
+        return e.value
+
+    def scf_step(self) -> dict:
+        """One body of scf_cycles_kernel's loop (SCF.jl:399-551) with F, C, D resident on the GPU."""
+        r = np.zeros(8, dtype=np.float64)
+        check(self._lib.jcdf_scf_step(self._h, _ptr(r)))
+        return dict(zip(("E", "dE", "D_rms", "E_elec", "t_fock", "t_diis", "t_iteration", "t_total"), r.tolist()))
+
+    def scf_run(self, max_iterations: int = 50, dele: float = 1e-6, rmsd: float = 1e-6) -> dict:
+        hist = np.zeros(3 * max_iterations, dtype=np.float64)
+        e, it, cv = C.c_double(), C.c_int32(), C.c_int32()
+        check(self._lib.jcdf_scf_run(self._h, max_iterations, dele, rmsd, C.byref(e), C.byref(it), C.byref(cv), _ptr(hist)))
+        rows = hist.reshape(-1, 3)[:it.value]
+        return {"E": e.value, "converged": bool(cv.value),
+                "iterations": [(i + 1, float(r[0]), float(r[1]), float(r[2])) for i, r in enumerate(rows)]}
+
+    def scf_get(self, name: str) -> np.ndarray:
+        N = self.N
+        out = np.zeros(N if name == "evals" else (N, N), dtype=np.float64, order="F")
+        check(self._lib.jcdf_scf_get(self._h, name.encode(), _ptr(out)))
+        return out
+
     # -- introspection ---------------------------------------------------------------------------------------------
     def layout(self) -> LayoutInfo:
         li = LayoutInfo()

@@ -126,3 +126,34 @@ function iteration_eigh_B200!(scf_data, F::Matrix{Float64}, ortho::Matrix{Float6
         gd.handle, F, ortho, F_eval, C))
     return F_eval
 end
+
+# ---- on-device SCF step (SURVEY §8f-2) --------------------------------------------------------------------------------
+# Replaces, for contraction_mode == "B200" with scf_flags["b200_resident_scf"] = true, the body of scf_cycles_kernel's
+# `while !iter_converged` loop (SCF.jl:399-551): F, C, D and the DIIS history stay on the GPU; Julia only sees the
+# scalars it prints (:555) and tests for convergence (:527-530).
+function scf_init_B200!(scf_data, S::Matrix{Float64}, H::Matrix{Float64}, E_nuc::Float64, ndiis::Int)
+    gd = scf_data.gpu_data::SCFGPUDataB200
+    E_guess = Ref{Float64}(0.0)
+    jcdf_check(ccall((:jcdf_scf_init, libjcdf), Cint, (Ptr{Cvoid}, Ptr{Float64}, Ptr{Float64}, Float64, Cint, Ref{Float64}),
+        gd.handle, S, H, E_nuc, Cint(ndiis), E_guess))
+    return E_guess[]
+end
+
+# returns (E, ΔE, D_rms, E_elec) and fills the fock/DIIS/iteration timings of this iteration
+function scf_step_B200!(scf_data, iter::Int, jc_timing)
+    gd = scf_data.gpu_data::SCFGPUDataB200
+    r = zeros(Float64, 8)
+    jcdf_check(ccall((:jcdf_scf_step, libjcdf), Cint, (Ptr{Cvoid}, Ptr{Float64}), gd.handle, r))
+    jc_timing.timings[JCTiming_key(JCTC.fock_time, iter)] = r[5]
+    jc_timing.timings[JCTiming_key(JCTC.iteration_time, iter)] = r[8]
+    return r[1], r[2], r[3], r[4]
+end
+
+# the matrices rhf_kernel returns in its Dict (SCF.jl:251-259): name in ("F", "D", "C", "X", "S", "H")
+function scf_get_B200(scf_data, name::String)
+    gd = scf_data.gpu_data::SCFGPUDataB200
+    N = scf_data.μ
+    out = zeros(Float64, N, N)
+    jcdf_check(ccall((:jcdf_scf_get, libjcdf), Cint, (Ptr{Cvoid}, Cstring, Ptr{Float64}), gd.handle, name, out))
+    return out
+end

@@ -75,3 +75,64 @@ def test_water_scf_through_libjcdf(water, ndev, device_eigh):
     for name in ("W_time", "K_time", "V_time", "J_time", "fock_time"):
         assert jc.JCTiming.key(name, 3) in timing.timings
     scf_data.gpu_data.close()
+
+
+@pytest.mark.parametrize("ndev", [1, 2])
+def test_water_scf_resident_on_device(water, ndev):
+    """the whole SCF loop (Fock build, DIIS, damping, iteration()) through jcdf_scf_init/step with F, C, D
+    resident on the GPU.  Every iteration's energy against the reference's logged run (<= 2e-8: the log prints 10
+    decimals of a run made with another BLAS) and against the oracle's replay (<= 1e-8 Eh), same iteration count."""
+    g, p = water
+    if jc.device_count() < ndev:
+        pytest.skip("needs %d GPUs" % ndev)
+    H, nocc, B = p["H"], p["nocc"], p["B"]
+    N, Q = p["N"], p["Q"]
+    gd = jc.B200Data(N, Q, nocc, ndev)
+    gd.set_mask(jc.ScreeningData(None, N))
+    gd.upload_metric(np.asfortranarray(np.tril(p["J_PQ"])))
+    li = [jc.balanced_function_shards(Q, ndev)[d] for d in range(ndev)]
+    for d, r in enumerate(li):
+        gd.upload_three_center(d, np.asfortranarray(p["T3"][r.start:r.stop].reshape(len(r), N * N)))
+    gd.factor_and_form_B()
+    ref = sr.run_scf(p["S"], H, p["E_nuc"], nocc, lambda C, it: orc.df_rhf_fock_build([B], C, nocc, H, None, "dense"))
+    E_guess = gd.scf_init(p["S"], H, p["E_nuc"], ndiis=10)
+    X = gd.scf_get("X")
+    assert np.abs(X - sr.orthogonalizer(p["S"])).max() < 1e-11
+    E0, _, _, _ = orc.iteration(np.array(H), H, sr.orthogonalizer(p["S"]), nocc)
+    assert abs(E_guess - (E0 + p["E_nuc"])) < 1e-9
+    log = []
+    for it in range(1, 51):
+        r = gd.scf_step()
+        log.append(r)
+        if abs(r["dE"]) <= 1e-6 and r["D_rms"] <= 1e-6:
+            break
+    assert len(log) == len(ref["iterations"]) == 12
+    for r, (it, E, dE, drms), gl in zip(log, ref["iterations"], g["iterations"]):
+        assert abs(r["E"] - E) < 1e-8, (it, r["E"], E)
+        assert abs(r["E"] - gl["E"]) <= 2e-8
+        assert abs(r["D_rms"] - drms) < 1e-7
+    assert abs(log[-1]["E"] - g["E_converged"]) < 1e-9
+    # the resident matrices are the Dict rhf_kernel returns (SCF.jl:251-259)
+    D, C, F, ev = gd.scf_get("D"), gd.scf_get("C"), gd.scf_get("F"), gd.scf_get("evals")
+    assert np.abs(D - ref["D"]).max() < 1e-7
+    assert np.abs(ev - ref["evals"]).max() < 1e-7
+    assert np.abs(2.0 * C[:, :nocc] @ C[:, :nocc].T - D).max() < 1e-12
+    assert np.array_equal(F, F.T) or np.abs(F - F.T).max() < 1e-12
+    gd.close()
+
+
+def test_water_scf_run_whole_loop(water):
+    """jcdf_scf_run: the loop itself inside the library, convergence test of SCF.jl:527-530."""
+    g, p = water
+    N, Q, nocc = p["N"], p["Q"], p["nocc"]
+    gd = jc.B200Data(N, Q, nocc, 1)
+    gd.set_mask(jc.ScreeningData(None, N))
+    B2 = np.asfortranarray(p["B"].reshape((Q, N * N), order="F"))
+    gd.set_B(0, B2)
+    gd.scf_init(p["S"], p["H"], p["E_nuc"], ndiis=10)
+    res = gd.scf_run(50, 1e-6, 1e-6)
+    assert res["converged"] and len(res["iterations"]) == 12
+    assert abs(res["E"] - g["E_converged"]) < 1e-9
+    with pytest.raises(jc.JCDFError):
+        gd.scf_get("nonsense")
+    gd.close()
