@@ -96,6 +96,10 @@ int32_t jcdf_factor_and_form_B(jcdf_handle* h);
 int32_t jcdf_set_B(jcdf_handle* h, int32_t dev, const double* B, int64_t ld);
 int32_t jcdf_set_B_device(jcdf_handle* h, int32_t dev, const double* B_dev, int64_t ld, int64_t col_begin,
                           int64_t col_count);
+/* Copy device `dev`'s packed shard back in the reference layout (q_len[dev] x P column-major, leading dimension ld,
+ * columns in the reference pair order): T after jcdf_upload_three_center / jcdf_compute_three_center, B after
+ * jcdf_factor_and_form_B / jcdf_set_B — scf_data.D of ScreenedDF.jl:103.  For tests and debugging.                */
+int32_t jcdf_get_B(jcdf_handle* h, int32_t dev, double* out, int64_t ld);
 /* Copy the inverse Cholesky factor Linv (Q x Q, lower, column-major) back — for tests (J_AB_invt, ScreenedDF.jl:95) */
 int32_t jcdf_get_metric_inverse(jcdf_handle* h, double* Linv_out);
 /* Keep H resident on the shard-0 device so later jcdf_fock_build calls may pass H = NULL (H is constant over an SCF:
@@ -123,6 +127,32 @@ int32_t jcdf_fock_build_device(jcdf_handle* h, const double* C_occ_dev, int64_t 
  *   Fp = X^T F X ; (evals, U) = eigen(Hermitian(Fp)) ascending ; C = X U.
  * F, X: N x N column-major (host).  evals: N.  C: N x N.                                                         */
 int32_t jcdf_eigh(jcdf_handle* h, const double* F, const double* X, double* evals, double* C);
+
+/* ---- integral front-end on the GPU -------------------------------------------------------------------
+ * Replaces, for contraction_mode == "B200", the host integral drivers of iteration 1 and the H2D copy of their
+ * results (GPUDF.jl:44-57): calculate_two_center_intgrals (TwoCenterIntegrals.jl:7), schwarz_screen_itegrals_df
+ * (SchwarzScreening.jl:9), calculate_three_center_integrals (ThreeCenterIntegrals.jl:9 / ...Screened.jl) and the C++
+ * libint engine behind them (deps/src/jeri-df-tei.hpp:22-96).  Conventions are the reference's: Cartesian functions in
+ * libint/CCA order, libint Shell::renorm() on the raw basis-set-exchange coefficients (jeri-core.hpp:41-62), JuliaChem's
+ * axial normalisation on every component (Globals.jl:20-44, EnergyHelpers.jl:320-411).
+ *
+ * jcdf_set_basis: which = 0 primary (shells must add up to N functions, l <= 3), 1 auxiliary (Q functions, l <= 4).
+ *   am[nshell], nprim[nshell]; centers 3 x nshell column-major in bohr (after the centre-of-mass shift of
+ *   JCBasis.jl:86-101); exponents / coefficients concatenated shell by shell, raw values as in the basis-set file
+ *   (L shells already split into s + p, JCBasis.jl:245-290).                                                       */
+int32_t jcdf_set_basis(jcdf_handle* h, int32_t which, int64_t nshell, const int32_t* am, const int32_t* nprim,
+                       const double* centers, const double* exponents, const double* coefficients);
+/* (P|Q) on the shard-0 device; stays there for jcdf_factor_and_form_B (no jcdf_upload_metric needed).
+ * J_out: NULL or Q x Q column-major host buffer receiving the full symmetric matrix.                              */
+int32_t jcdf_compute_two_center(jcdf_handle* h, double* J_out);
+/* Schwarz screening with threshold sigma^2 / max_P (P|P) (SchwarzScreening.jl:22): shell pair kept iff |sum of the whole
+ * (ab|ab) block| >= threshold (:44-50), function pair inside a kept shell pair kept iff |(mn|mn)| >= threshold (:60-66);
+ * pair compaction outer p, inner q (:72-81).  Ends with jcdf_set_mask on the result.  sigma <= 0: unscreened (:97-111).
+ * fn_mask_out: NULL or N x N bytes; pairs_kept_out: NULL or the count P.  Needs the metric (either route) first.    */
+int32_t jcdf_compute_schwarz_mask(jcdf_handle* h, double sigma, uint8_t* fn_mask_out, int64_t* pairs_kept_out);
+/* (P|mn) of every device's Q shard, written directly into the tile-packed layout (screened pairs and shell pairs the
+ * Schwarz test dropped are never computed).  Follow with jcdf_factor_and_form_B.                                   */
+int32_t jcdf_compute_three_center(jcdf_handle* h);
 
 /* ---- on-device SCF step: F, C, D and the DIIS history never leave the GPU between builds ------------
  * jcdf_scf_init replaces the set-up part of rhf_kernel (src/rhf/energy/SCF.jl:141-183): uploads S and H (N x N

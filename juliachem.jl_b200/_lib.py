@@ -43,6 +43,7 @@ SIGNATURES = {
     "jcdf_factor_and_form_B": (_i32, [_p]),
     "jcdf_set_B": (_i32, [_p, _i32, _p, _i64]),
     "jcdf_set_B_device": (_i32, [_p, _i32, _p, _i64, _i64, _i64]),
+    "jcdf_get_B": (_i32, [_p, _i32, _p, _i64]),
     "jcdf_get_metric_inverse": (_i32, [_p, _p]),
     "jcdf_set_core_hamiltonian": (_i32, [_p, _p]),
     "jcdf_fock_build": (_i32, [_p, _p, _i64, _p, _p, _p]),
@@ -56,6 +57,10 @@ SIGNATURES = {
     "jcdf_last_kernel_ms": (_i32, [_p, _i32, _p]),
     "jcdf_set_option": (_i32, [_p, C.c_char_p, _i64]),
     "jcdf_get_stream": (_i32, [_p, _i32, C.POINTER(_p)]),
+    "jcdf_set_basis": (_i32, [_p, _i32, _i64, _p, _p, _p, _p, _p]),
+    "jcdf_compute_two_center": (_i32, [_p, _p]),
+    "jcdf_compute_schwarz_mask": (_i32, [_p, _f64, _p, C.POINTER(_i64)]),
+    "jcdf_compute_three_center": (_i32, [_p]),
     "jcdf_scf_init": (_i32, [_p, _p, _p, _f64, _i32, C.POINTER(_f64)]),
     "jcdf_scf_step": (_i32, [_p, _p]),
     "jcdf_scf_run": (_i32, [_p, _i32, _f64, _f64, C.POINTER(_f64), C.POINTER(_i32), C.POINTER(_i32), _p]),

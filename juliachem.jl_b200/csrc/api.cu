@@ -30,13 +30,19 @@ static int dev_alloc(T** p, size_t count) {
     return JCDF_OK;
 }
 
-static void free_shard_buffers(Shard& s) {
+// keep_metric: the two-centre metric / its inverse factor do not depend on the mask (jcdf_set_mask keeps them)
+static void free_shard_buffers(Shard& s, bool keep_metric = false) {
     cudaSetDevice(s.dev);
     void* ptrs[] = {s.Vpart, s.Vready, s.Bp, s.W, s.Cs, s.Craw, s.dt, s.Jt, s.V, s.Kpart, s.F, s.Hdev, s.Traw, s.d_tile_index, s.d_tile_a,
-                    s.d_tile_b, s.d_dest_of_col, s.d_fn_mask, s.Linv, s.Metric};
+                    s.d_tile_b, s.d_dest_of_col, s.d_fn_mask};
     for (void* p : ptrs)
         if (p) cudaFree(p);
-    s.Bp = s.W = s.Cs = s.Craw = s.dt = s.Jt = s.V = s.Kpart = s.F = s.Hdev = s.Traw = s.Linv = s.Metric = nullptr;
+    if (!keep_metric) {
+        if (s.Linv) cudaFree(s.Linv);
+        if (s.Metric) cudaFree(s.Metric);
+        s.Linv = s.Metric = nullptr;
+    }
+    s.Bp = s.W = s.Cs = s.Craw = s.dt = s.Jt = s.V = s.Kpart = s.F = s.Hdev = s.Traw = nullptr;
     s.d_tile_index = s.d_tile_a = s.d_tile_b = nullptr;
     s.Vpart = nullptr;
     s.Vready = nullptr;
@@ -211,6 +217,7 @@ int32_t jcdf_create(int64_t N, int64_t Q, int64_t occ, int32_t ndev, const int32
 int32_t jcdf_destroy(jcdf_handle* h) {
     if (!h) return JCDF_OK;
     scf_destroy(h);
+    integrals_destroy(h);
     for (Shard& s : h->shards) {
         cudaSetDevice(s.dev);
         if (s.stream) cudaStreamSynchronize(s.stream);
@@ -244,7 +251,7 @@ int32_t jcdf_set_mask(jcdf_handle* h, const uint8_t* fn_mask, const int64_t* map
     Layout& L = h->lay;
     const int64_t N = L.N;
     const int nb = L.nb;
-    for (Shard& s : h->shards) free_shard_buffers(s);
+    for (Shard& s : h->shards) free_shard_buffers(s, true);
     auto kept = [&](int64_t r, int64_t c) -> bool { return fn_mask ? fn_mask[r + N * c] != 0 : true; };
     // tile table: a tile is stored iff it holds at least one unscreened pair
     L.tile_index.assign((size_t)nb * nb, -1);
@@ -282,6 +289,7 @@ int32_t jcdf_set_mask(jcdf_handle* h, const uint8_t* fn_mask, const int64_t* map
     L.pairs_tri = Ptri;
     // reference column -> packed offset.  Column of pair (row r, col c) is map[r + N*c] - 1 (SchwarzScreening.jl:72-81).
     L.dest_of_col.assign((size_t)P, -1);
+    L.src_of_col.assign((size_t)P, 0);
     for (int64_t c = 0; c < N; c++)
         for (int64_t r = 0; r < N; r++) {
             if (!kept(r, c)) {
@@ -291,10 +299,16 @@ int32_t jcdf_set_mask(jcdf_handle* h, const uint8_t* fn_mask, const int64_t* map
             const int64_t col = map ? map[r + N * c] - 1 : r + N * c;
             JC_REQUIRE(col >= 0 && col < P, "jcdf_set_mask: sparse_pq_index_map entry out of range");
             const int a = (int)(r / 32), b = (int)(c / 32);
-            if (a < b) continue;  // mirror copy; the (c, r) column fills tile (b, a)
+            if (a < b) {  // mirror copy; the (c, r) column fills tile (b, a)
+                const int32_t tm = L.tile_index[(size_t)b * nb + a];
+                const int rm = (int)(c % 32), cm = (int)(r % 32);
+                L.src_of_col[(size_t)col] = (int64_t)tm * 1024 + rm * 32 + (cm ^ ((rm & 3) << 2));
+                continue;
+            }
             const int32_t ti = L.tile_index[(size_t)a * nb + b];
             const int rr = (int)(r % 32), cc = (int)(c % 32);
             L.dest_of_col[(size_t)col] = (int64_t)ti * 1024 + rr * 32 + (cc ^ ((rr & 3) << 2));
+            L.src_of_col[(size_t)col] = L.dest_of_col[(size_t)col];
         }
     L.mask_set = true;
     for (Shard& s : h->shards) {
@@ -387,10 +401,43 @@ int32_t jcdf_set_B_device(jcdf_handle* h, int32_t dev, const double* B_dev, int6
     return JCDF_OK;
 }
 
+int32_t jcdf_get_B(jcdf_handle* h, int32_t dev, double* out, int64_t ld) {
+    JC_REQUIRE(h && out, "jcdf_get_B: NULL argument");
+    JC_REQUIRE(h->lay.mask_set, "jcdf_get_B: call jcdf_set_mask first");
+    JC_REQUIRE(dev >= 0 && dev < (int)h->shards.size(), "jcdf_get_B: device index out of range");
+    Shard& s = h->shards[dev];
+    JC_REQUIRE(ld >= s.q_len, "jcdf_get_B: ld smaller than the shard's row count");
+    if (s.q_len == 0) return JCDF_OK;
+    const Layout& L = h->lay;
+    const int64_t P = L.pairs_kept;
+    JC_CUDA(cudaSetDevice(s.dev));
+    int64_t* d_src = nullptr;
+    double* win_buf = nullptr;
+    int rc;
+    if ((rc = dev_alloc(&d_src, (size_t)P))) return rc;
+    JC_CUDA(cudaMemcpyAsync(d_src, L.src_of_col.data(), sizeof(int64_t) * P, cudaMemcpyHostToDevice, s.stream));
+    const int64_t win = std::max<int64_t>(1, std::min<int64_t>(P, ((int64_t)1 << 26) / std::max<int64_t>(s.q_len, 1)));
+    if ((rc = dev_alloc(&win_buf, (size_t)(win * s.q_len)))) return rc;
+    for (int64_t c0 = 0; c0 < P; c0 += win) {
+        const int64_t nc = std::min(win, P - c0);
+        launch_gather_pairs(L, s, win_buf, s.q_len, c0, nc, d_src);
+        JC_CUDA(cudaGetLastError());
+        JC_CUDA(cudaMemcpy2DAsync(out + ld * c0, sizeof(double) * ld, win_buf, sizeof(double) * s.q_len, sizeof(double) * s.q_len,
+                                  (size_t)nc, cudaMemcpyDeviceToHost, s.stream));
+        JC_CUDA(cudaStreamSynchronize(s.stream));
+    }
+    cudaFree(d_src);
+    cudaFree(win_buf);
+    return JCDF_OK;
+}
+
 int32_t jcdf_upload_metric(jcdf_handle* h, const double* J_PQ) {
     JC_REQUIRE(h && J_PQ, "jcdf_upload_metric: NULL argument");
     const int64_t Q = h->lay.Q;
     h->host_metric.assign(J_PQ, J_PQ + Q * Q);
+    h->metric_on_device = false;
+    h->max_PP = 0.0;
+    for (int64_t i = 0; i < Q; i++) h->max_PP = std::max(h->max_PP, std::fabs(J_PQ[i + Q * i]));
     return JCDF_OK;
 }
 
@@ -398,7 +445,8 @@ int32_t jcdf_upload_metric(jcdf_handle* h, const double* J_PQ) {
 int32_t jcdf_factor_and_form_B(jcdf_handle* h) {
     JC_REQUIRE(h != nullptr, "jcdf_factor_and_form_B: NULL handle");
     JC_REQUIRE(h->lay.mask_set, "jcdf_factor_and_form_B: call jcdf_set_mask first");
-    JC_REQUIRE(!h->host_metric.empty(), "jcdf_factor_and_form_B: call jcdf_upload_metric first");
+    JC_REQUIRE(!h->host_metric.empty() || h->metric_on_device,
+               "jcdf_factor_and_form_B: call jcdf_upload_metric or jcdf_compute_two_center first");
     JC_REQUIRE(h->n_ranks == 1, "jcdf_factor_and_form_B: multi-process B formation is not implemented; form B per rank and call jcdf_set_B");
     const Layout& L = h->lay;
     const int64_t Q = L.Q;
@@ -417,7 +465,9 @@ int32_t jcdf_factor_and_form_B(jcdf_handle* h) {
     int rc;
     if (!s0.Metric && (rc = dev_alloc(&s0.Metric, (size_t)Q * Q))) return rc;
     if (!s0.Linv && (rc = dev_alloc(&s0.Linv, (size_t)Q * Q))) return rc;
-    JC_CUDA(cudaMemcpyAsync(s0.Metric, h->host_metric.data(), sizeof(double) * Q * Q, cudaMemcpyHostToDevice, s0.stream));
+    if (!h->metric_on_device)
+        JC_CUDA(cudaMemcpyAsync(s0.Metric, h->host_metric.data(), sizeof(double) * Q * Q, cudaMemcpyHostToDevice, s0.stream));
+    h->metric_on_device = false;  // potrf overwrites it with L
     cusolverDnHandle_t sol = nullptr;
     cublasHandle_t blas = nullptr;
     JC_CUSOLVER(cusolverDnCreate(&sol));

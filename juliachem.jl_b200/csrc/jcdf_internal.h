@@ -27,6 +27,7 @@ struct Layout {
     std::vector<int32_t> tile_index;  // [a * nb + b], a >= b: index of the stored tile or -1
     std::vector<int32_t> tile_a, tile_b;
     std::vector<int64_t> dest_of_col;  // reference pair column -> offset inside a packed row, or -1
+    std::vector<int64_t> src_of_col;   // reference pair column -> packed offset holding its value (mirror columns included)
 };
 
 // event points recorded on the shard's stream during one build, in launch order
@@ -76,7 +77,8 @@ struct Shard {
     void* nccl_comm = nullptr;
 };
 
-struct ScfState;  // scf.cu
+struct ScfState;        // scf.cu
+struct IntegralsState;  // integrals.cu
 
 }  // namespace jcdf
 
@@ -92,6 +94,9 @@ struct jcdf_handle {
     int64_t opt_coulomb_overlap = 0;  // two-pass sweeps on a second stream, concurrent with the tensor-core kernels
     int64_t opt_exchange_slices = 0;
     jcdf::ScfState* scf = nullptr;    // on-device SCF driver state (jcdf_scf_*), owned
+    jcdf::IntegralsState* ints = nullptr;  // basis sets + integral scratch (jcdf_set_basis / jcdf_compute_*), owned
+    bool metric_on_device = false;    // shards[0].Metric holds (P|Q) (jcdf_compute_two_center) — consumed by the factorisation
+    double max_PP = 0.0;              // max_P |(P|P)| of the last metric seen (get_max_P_P, SchwarzScreening.jl:86-95)
 };
 
 namespace jcdf {
@@ -105,13 +110,16 @@ bool launch_coulomb_fused(const Layout& L, Shard& s, int sm_count, cudaStream_t 
 void launch_epilogue(const Layout& L, Shard& s, bool add_H);
 void launch_scatter_pairs(const Layout& L, Shard& s, const double* T_dev, int64_t ld, int64_t col_begin,
                           int64_t col_count);
+void launch_gather_pairs(const Layout& L, Shard& s, double* T_dev, int64_t ld, int64_t col_begin, int64_t col_count,
+                         const int64_t* d_src_of_col);
 void launch_fill_synthetic(const Layout& L, Shard& s, uint64_t seed, double decay_length);
 size_t half_transform_smem_bytes(int bm);
 size_t exchange_smem_bytes();
 int kernels_per_build();
 
 void set_error(const std::string& msg);
-void scf_destroy(jcdf_handle* h);  // scf.cu
+void scf_destroy(jcdf_handle* h);        // scf.cu
+void integrals_destroy(jcdf_handle* h);  // integrals.cu
 
 }  // namespace jcdf
 

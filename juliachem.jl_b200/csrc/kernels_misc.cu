@@ -30,6 +30,23 @@ void launch_scatter_pairs(const Layout& L, Shard& s, const double* T_dev, int64_
                                                   L.row_len);
 }
 
+// inverse of k_scatter_pairs for introspection (jcdf_get_B): T_dev[q + ld * c] = Bp[q][src_of_col[col_begin + c]]
+__global__ void k_gather_pairs(double* __restrict__ T_dev, int64_t ld, int64_t col_begin, int64_t col_count, int q_len,
+                               const int64_t* __restrict__ src_of_col, const double* __restrict__ Bp, int64_t row_len) {
+    const int q = blockIdx.x * blockDim.x + threadIdx.x;
+    if (q >= q_len) return;
+    for (int64_t c = blockIdx.y; c < col_count; c += gridDim.y)
+        T_dev[q + ld * c] = Bp[(int64_t)q * row_len + src_of_col[col_begin + c]];
+}
+
+void launch_gather_pairs(const Layout& L, Shard& s, double* T_dev, int64_t ld, int64_t col_begin, int64_t col_count,
+                         const int64_t* d_src_of_col) {
+    if (col_count <= 0 || s.q_len <= 0) return;
+    dim3 block(128);
+    dim3 grid((unsigned)((s.q_len + 127) / 128), (unsigned)std::min<int64_t>(col_count, 32768));
+    k_gather_pairs<<<grid, block, 0, s.stream>>>(T_dev, ld, col_begin, col_count, (int)s.q_len, d_src_of_col, s.Bp, L.row_len);
+}
+
 // ---------------------------------------------------------------------------------------------------------------------
 // synthetic shard: integer-hash "Gaussian" (sum of four 16-bit uniforms) times a host-tabulated decay, so the host
 // twin jcdf_synthetic_value reproduces every element bit for bit (one int->double conversion, one multiply).

@@ -177,6 +177,12 @@ class B200Data:
         B = _f64_colmajor(B)
         check(self._lib.jcdf_set_B(self._h, dev, _ptr(B), B.shape[0]))
 
+    def get_B(self, dev: int, q_len: int, P: int) -> np.ndarray:
+        """Packed shard of device `dev` back in the reference (q_len x P) layout (jcdf_get_B)."""
+        out = np.zeros((q_len, P), dtype=np.float64, order="F")
+        check(self._lib.jcdf_get_B(self._h, dev, _ptr(out), max(q_len, 1)))
+        return out
+
     def get_metric_inverse(self) -> np.ndarray:
         out = np.zeros((self.Q, self.Q), dtype=np.float64, order="F")
         check(self._lib.jcdf_get_metric_inverse(self._h, _ptr(out)))
@@ -225,6 +231,36 @@ class B200Data:
         Cm = np.zeros((N, N), dtype=np.float64, order="F")
         check(self._lib.jcdf_eigh(self._h, _ptr(Fc), _ptr(Xc), _ptr(ev), _ptr(Cm)))
         return ev, Cm
+
+    # -- integral front-end on the GPU --------------------------------------------------------------
+    def set_basis(self, which: int, am, nprim, centers, exponents, coefficients) -> None:
+        """which = 0 primary / 1 auxiliary; centers (nshell, 3) in bohr; exponents/coefficients concatenated, raw
+        basis-set-exchange values (the library applies libint's renorm + JuliaChem's axial factors)."""
+        am = np.ascontiguousarray(am, dtype=np.int32)
+        npr = np.ascontiguousarray(nprim, dtype=np.int32)
+        cen = np.ascontiguousarray(np.asarray(centers, dtype=np.float64).reshape(len(am), 3))
+        ex = np.ascontiguousarray(exponents, dtype=np.float64)
+        co = np.ascontiguousarray(coefficients, dtype=np.float64)
+        if len(ex) != int(npr.sum()) or len(co) != len(ex):
+            raise ValueError("exponents/coefficients must hold sum(nprim) entries")
+        check(self._lib.jcdf_set_basis(self._h, which, len(am), _ptr(am), _ptr(npr), _ptr(cen), _ptr(ex), _ptr(co)))
+
+    def compute_two_center(self, want_host_copy: bool = True):
+        """calculate_two_center_intgrals (TwoCenterIntegrals.jl:7) on the device; the metric stays there."""
+        out = np.zeros((self.Q, self.Q), dtype=np.float64, order="F") if want_host_copy else None
+        check(self._lib.jcdf_compute_two_center(self._h, _ptr(out)))
+        return out
+
+    def compute_schwarz_mask(self, sigma: float):
+        """schwarz_screen_itegrals_df (SchwarzScreening.jl:9) on the device + jcdf_set_mask.  Returns (fn_mask, P)."""
+        m = np.zeros((self.N, self.N), dtype=np.uint8, order="F")
+        kept = C.c_int64()
+        check(self._lib.jcdf_compute_schwarz_mask(self._h, float(sigma), _ptr(m), C.byref(kept)))
+        return m.astype(bool), int(kept.value)
+
+    def compute_three_center(self) -> None:
+        """calculate_three_center_integrals (ThreeCenterIntegrals.jl:9) straight into the packed Q shards."""
+        check(self._lib.jcdf_compute_three_center(self._h))
 
     # -- on-device SCF step (SURVEY §8f-2) -------------------------------------------------------------------------
     def scf_init(self, S: np.ndarray, H: np.ndarray, E_nuc: float, ndiis: int = 10) -> float:

@@ -344,3 +344,37 @@ def two_center_integrals(aux_shells) -> np.ndarray:
                     n = aux_shells[si].nbas
                     out[apos[i]:apos[i] + sa.nbas, apos[si]:apos[si] + n] += val[k].T
     return out
+
+
+def schwarz_block(sa: Shell, sb: Shell) -> np.ndarray:
+    """Full (ab|ab) block of one shell pair, shape (nA, nB, nA, nB) = (mu, nu | mu', nu'), with the axial normalisation
+    on all four indices — what compute_eri_block(ish, jsh, ish, jsh) + axial_normalization_factor hand to
+    schwarz_screen_itegrals_df (SchwarzScreening.jl:41-44).  flatten_schwarz_block() gives the reference's 1-D order."""
+    Lab = sa.l + sb.l
+    T = Lab + 1
+    prims = [(cc, p, P, _pair_tensor(sa, sb, Ex, Ey, Ez)) for cc, a, b, p, P, Ex, Ey, Ez in _pair_primitives(sa, sb)]
+    sign = (-1.0) ** np.add.outer(np.add.outer(np.arange(T), np.arange(T)), np.arange(T))
+    out = np.zeros((sa.nbas, sb.nbas, sa.nbas, sb.nbas))
+    for cc1, p1, P1, E1 in prims:
+        for cc2, p2, P2, E2 in prims:
+            alpha = p1 * p2 / (p1 + p2)
+            R = hermite_R(2 * Lab, np.array(alpha), (P1 - P2))
+            E2s = E2 * sign[None, None]
+            G = np.zeros((sa.nbas, sb.nbas, T, T, T))
+            for ta in range(T):
+                for nu in range(T - ta):
+                    for ph in range(T - ta - nu):
+                        G += E2s[:, :, ta, nu, ph][:, :, None, None, None] * R[None, None, ta:ta + T, nu:nu + T, ph:ph + T]
+            pref = cc1 * cc2 * 2.0 * pi ** 2.5 / (p1 * p2 * sqrt(p1 + p2))
+            out += pref * np.einsum("ABtuv,CDtuv->ABCD", E1, G)
+    return out
+
+
+def flatten_schwarz_block(blk: np.ndarray) -> np.ndarray:
+    """Index [nu + n_nu*mu + n_nu*n_mu*nu' + n_nu*n_mu*n_nu*mu'] (SchwarzScreening.jl:62)."""
+    return np.ascontiguousarray(blk.transpose(2, 3, 0, 1)).ravel()
+
+
+def schwarz_blocks(shells) -> dict:
+    """{(ish, jsh): flattened (ab|ab) block} for every shell pair ish >= jsh (input of df_oracle.schwarz_function_mask)."""
+    return {(i, j): flatten_schwarz_block(schwarz_block(shells[i], shells[j])) for i in range(len(shells)) for j in range(i + 1)}
