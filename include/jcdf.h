@@ -154,6 +154,12 @@ int32_t jcdf_compute_schwarz_mask(jcdf_handle* h, double sigma, uint8_t* fn_mask
  * Schwarz test dropped are never computed).  Follow with jcdf_factor_and_form_B.                                   */
 int32_t jcdf_compute_three_center(jcdf_handle* h);
 
+/* One-electron matrices S, T, V = -sum_C Z_C (m| 1/|r - C| |n) over the primary basis and the nuclear repulsion — what
+ * rhf_kernel hands the SCF loop (SCF.jl:100-135; libint one-body engines, deps/src/jeri-oei.hpp).  centers: 3 x natoms
+ * column-major, bohr.  Outputs are N x N column-major host buffers (NULL = not wanted); H = T + V.                   */
+int32_t jcdf_compute_one_electron(jcdf_handle* h, int32_t natoms, const double* charges, const double* centers,
+                                  double* S_out, double* T_out, double* V_out, double* E_nuc_out);
+
 /* ---- on-device SCF step: F, C, D and the DIIS history never leave the GPU between builds ------------
  * jcdf_scf_init replaces the set-up part of rhf_kernel (src/rhf/energy/SCF.jl:141-183): uploads S and H (N x N
  * column-major, host), builds the symmetric orthogonaliser X = U_good diag(s_good^-1/2) U_good^T on the device

@@ -720,3 +720,162 @@ int32_t jcdf_compute_three_center(jcdf_handle* h) {
 }
 
 }  // extern "C"
+
+// ---------------------------------------------------------------------------------------------------------------------
+// One-electron integrals S, T, V (what rhf_kernel feeds the SCF with, src/rhf/energy/SCF.jl:100-135; libint one-body
+// engines behind deps/src/jeri-oei.hpp): thread = primary shell pair (a >= b).  Needed by the resident SCF loop so a
+// whole DF-RHF run can start from (geometry, basis sets) without any host integral code.
+// ---------------------------------------------------------------------------------------------------------------------
+namespace jcdf {
+
+struct OneElectronArgs {
+    BasisDev prim;
+    const double* boys_table;
+    const double* charges;  // [natoms]
+    const double* nuclei;   // [3 * natoms]
+    int natoms;
+    double *S, *T, *V;      // N x N column-major, both triangles written
+    int N;
+};
+
+template <int LAB_MAX>
+__global__ void __launch_bounds__(INT_THREADS) k_one_electron(OneElectronArgs g) {
+    const int64_t idx = blockIdx.x * (int64_t)INT_THREADS + threadIdx.x;
+    const int ns = g.prim.nshell;
+    if (idx >= (int64_t)ns * (ns + 1) / 2) return;
+    int sa = (int)((sqrt(8.0 * (double)idx + 1.0) - 1.0) * 0.5);
+    while ((int64_t)(sa + 1) * (sa + 2) / 2 <= idx) sa++;
+    while ((int64_t)sa * (sa + 1) / 2 > idx) sa--;
+    const int sb = (int)(idx - (int64_t)sa * (sa + 1) / 2);
+    const int la = g.prim.l[sa], lb = g.prim.l[sb], Lab = la + lb;
+    if (Lab > LAB_MAX) return;
+    const int nA = ncart(la), nB = ncart(lb), nAB = nA * nB;
+    const double Ax = g.prim.xyz[3 * sa], Ay = g.prim.xyz[3 * sa + 1], Az = g.prim.xyz[3 * sa + 2];
+    const double Bx = g.prim.xyz[3 * sb], By = g.prim.xyz[3 * sb + 1], Bz = g.prim.xyz[3 * sb + 2];
+    constexpr int EDIM = edim(LAB_MAX + 2);
+    double Ex[EDIM], Ey[EDIM], Ez[EDIM];
+    double R[(LAB_MAX + 1) * (LAB_MAX + 2) * (LAB_MAX + 3) / 6], Rz[(LAB_MAX + 1) * (LAB_MAX + 2) * (LAB_MAX + 3) / 6];
+    double accS[max_nab(LAB_MAX)], accT[max_nab(LAB_MAX)], accV[max_nab(LAB_MAX)];
+    HermIndex ix;
+    ix.init(Lab);
+    const int lb2 = lb + 2, T = la + lb2 + 1, sj = T, si = (lb2 + 1) * T;
+    const int nh = nherm(Lab);
+    for (int k = 0; k < nAB; k++) accS[k] = accT[k] = accV[k] = 0.0;
+    const int npa = g.prim.nprim[sa], npb = g.prim.nprim[sb];
+    const int oa = g.prim.prim_off[sa], ob = g.prim.prim_off[sb];
+    const double r2 = (Ax - Bx) * (Ax - Bx) + (Ay - By) * (Ay - By) + (Az - Bz) * (Az - Bz);
+    for (int ka = 0; ka < npa; ka++)
+        for (int kb = 0; kb < npb; kb++) {
+            const double a = g.prim.exps[oa + ka], b = g.prim.exps[ob + kb];
+            const double cc = g.prim.coefs[oa + ka] * g.prim.coefs[ob + kb];
+            const double p = a + b;
+            if (fabs(cc) * exp(-(a * b / p) * r2) < PRIM_SCREEN) continue;
+            hermite_E(la, lb2, a, b, Ax, Bx, Ex);
+            hermite_E(la, lb2, a, b, Ay, By, Ey);
+            hermite_E(la, lb2, a, b, Az, Bz, Ez);
+            const double Px = (a * Ax + b * Bx) / p, Py = (a * Ay + b * By) / p, Pz = (a * Az + b * Bz) / p;
+            for (int k = 0; k < nh; k++) Rz[k] = 0.0;
+            for (int c = 0; c < g.natoms; c++) {
+                hermite_R(Lab, p, Px - g.nuclei[3 * c], Py - g.nuclei[3 * c + 1], Pz - g.nuclei[3 * c + 2], g.boys_table, ix, R);
+                const double z = g.charges[c];
+                for (int k = 0; k < nh; k++) Rz[k] = fma(z, R[k], Rz[k]);
+            }
+            const double rt = sqrt(3.14159265358979323846 / p), rt3 = rt * rt * rt;
+            const double vpref = -cc * 2.0 * 3.14159265358979323846 / p;
+            for (int A = 0; A < nA; A++) {
+                int ax, ay, az;
+                cart_comp(la, A, ax, ay, az);
+                for (int B = 0; B < nB; B++) {
+                    int bx, by, bz;
+                    cart_comp(lb, B, bx, by, bz);
+                    const double* ex = Ex + ax * si;
+                    const double* ey = Ey + ay * si;
+                    const double* ez = Ez + az * si;
+                    // overlap factors s(j) = E[i, j, 0] and the second derivative on the ket, one direction each
+                    const double sx = ex[bx * sj], sy = ey[by * sj], sz = ez[bz * sj];
+                    auto d2 = [&](const double* e, int j) {
+                        double v = -2.0 * b * (2 * j + 1) * e[j * sj] + 4.0 * b * b * e[(j + 2) * sj];
+                        if (j >= 2) v += (double)(j * (j - 1)) * e[(j - 2) * sj];
+                        return v;
+                    };
+                    const double dx = d2(ex, bx), dy = d2(ey, by), dz = d2(ez, bz);
+                    accS[A * nB + B] = fma(cc * rt3, sx * sy * sz, accS[A * nB + B]);
+                    accT[A * nB + B] = fma(-0.5 * cc * rt3, dx * sy * sz + sx * dy * sz + sx * sy * dz, accT[A * nB + B]);
+                    double s = 0.0;
+                    for (int t = 0; t <= ax + bx; t++) {
+                        double su = 0.0;
+                        for (int u = 0; u <= ay + by; u++) {
+                            double sv = 0.0;
+                            for (int v = 0; v <= az + bz; v++) sv = fma(ez[bz * sj + v], Rz[ix(t, u, v)], sv);
+                            su = fma(ey[by * sj + u], sv, su);
+                        }
+                        s = fma(ex[bx * sj + t], su, s);
+                    }
+                    accV[A * nB + B] = fma(vpref, s, accV[A * nB + B]);
+                }
+            }
+        }
+    const int fa0 = g.prim.fn_off[sa], fb0 = g.prim.fn_off[sb];
+    for (int A = 0; A < nA; A++) {
+        int ax, ay, az;
+        cart_comp(la, A, ax, ay, az);
+        const double fA = comp_factor(la, ax, ay, az);
+        for (int B = 0; B < nB; B++) {
+            int bx, by, bz;
+            cart_comp(lb, B, bx, by, bz);
+            const double f = fA * comp_factor(lb, bx, by, bz);
+            const int64_t i1 = (fa0 + A) + (int64_t)g.N * (fb0 + B), i2 = (fb0 + B) + (int64_t)g.N * (fa0 + A);
+            g.S[i1] = g.S[i2] = f * accS[A * nB + B];
+            g.T[i1] = g.T[i2] = f * accT[A * nB + B];
+            g.V[i1] = g.V[i2] = f * accV[A * nB + B];
+        }
+    }
+}
+
+}  // namespace jcdf
+
+extern "C" int32_t jcdf_compute_one_electron(jcdf_handle* h, int32_t natoms, const double* charges, const double* centers,
+                                             double* S_out, double* T_out, double* V_out, double* E_nuc_out) {
+    JC_REQUIRE(h && charges && centers && natoms >= 1, "jcdf_compute_one_electron: bad argument");
+    IntegralsState* st = h->ints;
+    JC_REQUIRE(st && st->have[0], "jcdf_compute_one_electron: call jcdf_set_basis(which = 0) first");
+    Shard& s0 = h->shards[0];
+    const int64_t N = h->lay.N, nn = N * N;
+    JC_CUDA(cudaSetDevice(s0.dev));
+    double *dS = nullptr, *dZ = nullptr, *dC = nullptr;
+    JC_CUDA(cudaMalloc(reinterpret_cast<void**>(&dS), sizeof(double) * 3 * nn));
+    JC_CUDA(cudaMalloc(reinterpret_cast<void**>(&dZ), sizeof(double) * natoms));
+    JC_CUDA(cudaMalloc(reinterpret_cast<void**>(&dC), sizeof(double) * 3 * natoms));
+    JC_CUDA(cudaMemcpyAsync(dZ, charges, sizeof(double) * natoms, cudaMemcpyHostToDevice, s0.stream));
+    JC_CUDA(cudaMemcpyAsync(dC, centers, sizeof(double) * 3 * natoms, cudaMemcpyHostToDevice, s0.stream));
+    OneElectronArgs a;
+    a.prim = st->devs[0].basis[0];
+    a.boys_table = st->devs[0].boys_table;
+    a.charges = dZ; a.nuclei = dC; a.natoms = natoms;
+    a.S = dS; a.T = dS + nn; a.V = dS + 2 * nn;
+    a.N = (int)N;
+    const int ns = a.prim.nshell;
+    const int64_t npairs = (int64_t)ns * (ns + 1) / 2;
+    int lmax = 0;
+    for (int l : st->host[0].l) lmax = std::max(lmax, l);
+    const unsigned grid = (unsigned)((npairs + INT_THREADS - 1) / INT_THREADS);
+    if (2 * lmax <= 4) k_one_electron<4><<<grid, INT_THREADS, 0, s0.stream>>>(a);
+    else k_one_electron<6><<<grid, INT_THREADS, 0, s0.stream>>>(a);
+    JC_CUDA(cudaGetLastError());
+    if (S_out) JC_CUDA(cudaMemcpyAsync(S_out, a.S, sizeof(double) * nn, cudaMemcpyDeviceToHost, s0.stream));
+    if (T_out) JC_CUDA(cudaMemcpyAsync(T_out, a.T, sizeof(double) * nn, cudaMemcpyDeviceToHost, s0.stream));
+    if (V_out) JC_CUDA(cudaMemcpyAsync(V_out, a.V, sizeof(double) * nn, cudaMemcpyDeviceToHost, s0.stream));
+    JC_CUDA(cudaStreamSynchronize(s0.stream));
+    cudaFree(dS); cudaFree(dZ); cudaFree(dC);
+    if (E_nuc_out) {  // nuclear repulsion, pairs in a fixed order
+        double e = 0.0;
+        for (int i = 0; i < natoms; i++)
+            for (int j = 0; j < i; j++) {
+                const double dx = centers[3 * i] - centers[3 * j], dy = centers[3 * i + 1] - centers[3 * j + 1],
+                             dz = centers[3 * i + 2] - centers[3 * j + 2];
+                e += charges[i] * charges[j] / std::sqrt(dx * dx + dy * dy + dz * dz);
+            }
+        *E_nuc_out = e;
+    }
+    return JCDF_OK;
+}

@@ -262,6 +262,16 @@ class B200Data:
         """calculate_three_center_integrals (ThreeCenterIntegrals.jl:9) straight into the packed Q shards."""
         check(self._lib.jcdf_compute_three_center(self._h))
 
+    def compute_one_electron(self, charges, centers):
+        """S, T, V and E_nuc on the device (rhf_kernel's one-electron set-up, SCF.jl:100-135).  centers (natoms, 3) bohr."""
+        Z = np.ascontiguousarray(charges, dtype=np.float64)
+        cen = np.ascontiguousarray(np.asarray(centers, dtype=np.float64).reshape(len(Z), 3))
+        N = self.N
+        S, T, V = (np.zeros((N, N), dtype=np.float64, order="F") for _ in range(3))
+        e = C.c_double()
+        check(self._lib.jcdf_compute_one_electron(self._h, len(Z), _ptr(Z), _ptr(cen), _ptr(S), _ptr(T), _ptr(V), C.byref(e)))
+        return S, T, V, e.value
+
     # -- on-device SCF step (SURVEY §8f-2) -------------------------------------------------------------------------
     def scf_init(self, S: np.ndarray, H: np.ndarray, E_nuc: float, ndiis: int = 10) -> float:
         """rhf_kernel's set-up (SCF.jl:141-183) on the device: X = S^-1/2, hcore guess.  Returns the guess energy."""

@@ -1,0 +1,146 @@
+"""Host-side mirror of the reference's entry sequence for a DF-RHF energy, with every numerical step behind libjcdf:
+
+    mol, basis_sets = JCBasis.run(molecule, model)          src/basis/JCBasis.jl:47-170
+    rhf_energy      = JCRHF.Energy.run(mol, basis_sets, scf_flags)   src/rhf/energy/Energy.jl:35-85 -> SCF.jl:69-262
+
+`run_basis` turns the JSON contract's `molecule` / `model` objects (JCInput.jl:67-92) into flat shell arrays the way
+JCBasis does (Angstrom -> bohr with 1/0.52917724924, shift to the centre of mass with the masses of BasisHelpers.jl:61-119,
+shells in atom order, n_electrons = sum Z - charge).  `run_energy` is the body of rhf_kernel / scf_cycles_kernel for
+`contraction_mode == "B200"`: one-electron integrals, (P|Q), Schwarz mask, (P|mn), B, orthogonaliser, hcore guess and
+the SCF loop all run on the GPU(s); the host only sees the scalars of every iteration and the final matrices.
+
+The reference reads its basis sets from records/bsed.h5, a binary that is not part of the checkout; the only sets
+recoverable from the snapshot are the ones its logs print (data/basis_ccpvdz_OH.json: cc-pVDZ + cc-pVDZ-RIFIT for O, H).
+"""
+from __future__ import annotations
+
+import json
+import os
+import time
+
+import numpy as np
+
+from .df import B200Data, JCTiming, balanced_function_shards, static_load_rank_indicies
+
+ANGSTROM_TO_BOHR = 1.0 / 0.52917724924  # JCBasis.jl:61
+ATOMIC_MASS = {"H": 1.00794, "C": 12.0107, "N": 14.0067, "O": 15.9994}  # BasisHelpers.jl:61-119 (subset in use)
+_DATA = os.path.join(os.path.dirname(os.path.abspath(__file__)), "data")
+
+
+def load_basis_library(name: str = "cc-pVDZ") -> dict:
+    """{symbol: {"Z", "basis": [shell], "auxiliary_basis": [shell]}}; shell = {"l", "exps", "coefs"} (raw values)."""
+    if name.lower() not in ("cc-pvdz", "cc-pvdz/cc-pvdz-rifit"):
+        raise KeyError("basis set %r is not available here: the reference's records/bsed.h5 is not part of the checkout; "
+                       "only cc-pVDZ / cc-pVDZ-RIFIT for O and H could be recovered from its logs" % name)
+    return json.load(open(os.path.join(_DATA, "basis_ccpvdz_OH.json")))["atoms"]
+
+
+class FlatBasis:
+    """One basis set as jcdf_set_basis takes it."""
+
+    def __init__(self):
+        self.am, self.nprim, self.centers, self.exps, self.coefs, self.atom = [], [], [], [], [], []
+
+    def add(self, shell: dict, center, atom: int):
+        self.am.append(int(shell["l"]))
+        self.nprim.append(len(shell["exps"]))
+        self.centers.append(np.asarray(center, dtype=np.float64))
+        self.exps.extend(float(x) for x in shell["exps"])
+        self.coefs.extend(float(x) for x in shell["coefs"])
+        self.atom.append(atom)
+
+    @property
+    def nbas(self):
+        return [(l + 1) * (l + 2) // 2 for l in self.am]
+
+    @property
+    def n_functions(self) -> int:
+        return int(sum(self.nbas))
+
+    def args(self):
+        return self.am, self.nprim, np.array(self.centers), self.exps, self.coefs
+
+
+def run_basis(molecule: dict, model: dict, library: dict | None = None) -> dict:
+    """JCBasis.run: returns {"symbols", "centers" (natoms,3 bohr, COM at origin), "charges", "n_electrons", "primary",
+    "auxiliary"}.  molecule = {"geometry": flat Angstrom xyz, "symbols", "molecular_charge"}."""
+    library = library or load_basis_library(model.get("basis", "cc-pVDZ"))
+    symbols = list(molecule["symbols"])
+    geo = np.asarray(molecule["geometry"], dtype=np.float64).reshape(len(symbols), 3) * ANGSTROM_TO_BOHR
+    masses = np.array([ATOMIC_MASS[s] for s in symbols])
+    geo = geo - (masses[:, None] * geo).sum(axis=0) / masses.sum()  # JCBasis.jl:86-101
+    prim, aux = FlatBasis(), FlatBasis()
+    nels = -int(molecule.get("molecular_charge", 0))
+    charges = []
+    for ia, s in enumerate(symbols):
+        entry = library[s]
+        nels += entry["Z"]
+        charges.append(float(entry["Z"]))
+        for sh in entry["basis"]:
+            prim.add(sh, geo[ia], ia)
+        for sh in entry["auxiliary_basis"]:
+            aux.add(sh, geo[ia], ia)
+    return {"symbols": symbols, "centers": geo, "charges": np.array(charges), "n_electrons": nels, "primary": prim,
+            "auxiliary": aux}
+
+
+def run_energy(mol: dict, scf_flags: dict | None = None, num_devices: int = 1, keep_handle: bool = False) -> dict:
+    """JCRHF.Energy.run for scf_type = "df", contraction_mode = "B200".  scf_flags: niter, ndiis, dele, rmsd, df_sigma
+    (Constants.jl defaults).  Returns the reference's result Dict (SCF.jl:251-259) plus "Timings" and "Iterations"."""
+    f = {"niter": 50, "ndiis": 10, "dele": 1e-6, "rmsd": 1e-6, "df_sigma": 1e-5}
+    f.update(scf_flags or {})
+    prim, aux = mol["primary"], mol["auxiliary"]
+    N, Q, occ = prim.n_functions, aux.n_functions, mol["n_electrons"] // 2
+    timing = JCTiming()
+    t = {}
+
+    def clock(name, t0):
+        t[name] = time.perf_counter() - t0
+
+    t0 = time.perf_counter()
+    gd = B200Data(N, Q, occ, num_devices)
+    # Q shards: contiguous auxiliary shells per device (static_load_rank_indicies, DynamicLoad.jl:160-203)
+    if num_devices > 1:
+        gd.set_shards([static_load_rank_indicies(d, num_devices, aux.nbas)[1] for d in range(num_devices)])
+    gd.set_basis(0, *prim.args())
+    gd.set_basis(1, *aux.args())
+    clock("setup", t0)
+    t0 = time.perf_counter()
+    S, T, V, E_nuc = gd.compute_one_electron(mol["charges"], mol["centers"])
+    H = np.asfortranarray(T + V)
+    clock("one_electron", t0)
+    t0 = time.perf_counter()
+    gd.compute_two_center(False)
+    clock("two_center", t0)
+    t0 = time.perf_counter()
+    mask, P = gd.compute_schwarz_mask(f["df_sigma"])
+    clock("schwarz", t0)
+    t0 = time.perf_counter()
+    gd.compute_three_center()
+    clock("three_center", t0)
+    t0 = time.perf_counter()
+    gd.factor_and_form_B()
+    clock("form_B", t0)
+    t0 = time.perf_counter()
+    gd.scf_init(S, H, E_nuc, f["ndiis"])
+    clock("scf_init", t0)
+    iters, converged = [], False
+    t0 = time.perf_counter()
+    for it in range(1, int(f["niter"]) + 1):
+        r = gd.scf_step()
+        iters.append((it, r["E"], r["dE"], r["D_rms"]))
+        timing.timings[JCTiming.key("fock_time", it)] = r["t_fock"]
+        timing.timings[JCTiming.key("iteration_time", it)] = r["t_total"]
+        if abs(r["dE"]) <= f["dele"] and r["D_rms"] <= f["rmsd"]:  # SCF.jl:527-530
+            converged = True
+            break
+    clock("scf_loop", t0)
+    out = {"Energy": iters[-1][1], "Converged?": converged, "Iterations": iters, "Timings": dict(t, jc=timing.timings),
+           "Fock": gd.scf_get("F"), "Density": gd.scf_get("D"), "MO Coeff": gd.scf_get("C"), "Overlap": S,
+           "Orbital Energies": gd.scf_get("evals"), "N": N, "Q": Q, "occ": occ, "pairs_kept": P, "E_nuc": E_nuc,
+           "layout": gd.layout()}
+    if keep_handle:
+        out["handle"] = gd
+    else:
+        gd.close()
+    return out

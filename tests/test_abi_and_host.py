@@ -113,3 +113,22 @@ def test_balanced_shards_cover_Q():
     for Q, n in [(4800, 8), (131, 3), (7, 8)]:
         r = jc.balanced_function_shards(Q, n)
         assert r[0].start == 0 and r[-1].stop == Q and all(r[i].stop == r[i + 1].start for i in range(n - 1))
+
+
+def test_run_basis_mirrors_jcbasis():
+    """JCBasis.run (JCBasis.jl:47-170): Angstrom -> bohr, centre of mass at the origin, shells in atom order,
+    n_electrons = sum Z - charge; shard ranges by auxiliary shells (DynamicLoad.jl:160-203)."""
+    import json
+    import os
+    from juliachem_jl_b200 import rhf
+    geo = json.load(open(os.path.join(os.path.dirname(os.path.abspath(__file__)), "golden", "w50_geometry.json")))
+    mol = rhf.run_basis({"geometry": geo["geometry"], "symbols": geo["symbols"], "molecular_charge": 0}, {"basis": "cc-pVDZ"})
+    assert mol["primary"].n_functions == 1250 and mol["auxiliary"].n_functions == 4800 and mol["n_electrons"] == 500
+    m = np.array([rhf.ATOMIC_MASS[s] for s in mol["symbols"]])
+    assert np.abs((m[:, None] * mol["centers"]).sum(axis=0)).max() < 1e-9
+    d01 = np.linalg.norm(mol["centers"][0] - mol["centers"][1]) / rhf.ANGSTROM_TO_BOHR
+    raw = np.array(geo["geometry"]).reshape(-1, 3)
+    assert abs(d01 - np.linalg.norm(raw[0] - raw[1])) < 1e-12
+    assert len(mol["primary"].am) == 50 * 12 and len(mol["auxiliary"].am) == 50 * 30
+    with pytest.raises(KeyError):
+        rhf.load_basis_library("cc-pVTZ")

@@ -178,3 +178,84 @@ def test_basis_errors(water):
         gd2.compute_two_center()  # no basis yet
     gd.close()
     gd2.close()
+
+
+def test_one_electron_integrals(water):
+    g, prim, aux, p = water
+    for shells, charges, centers in [(prim, g["charges"], [a["xyz_bohr"] for a in g["geometry"]]),
+                                     (high_l_shells()[0], [3.0, 1.0, 8.0], [[0.0, 0.0, 0.0], [1.1, -0.4, 0.7], [0.2, 0.9, -1.5]])]:
+        N = sum(s.nbas for s in shells)
+        gd = jc.B200Data(N, 1, 1, 1)
+        gd.set_basis(0, *flat_basis(shells))
+        S, T, V, E_nuc = gd.compute_one_electron(charges, centers)
+        S_ref, T_ref = gi.overlap_kinetic(shells)
+        V_ref = gi.nuclear_attraction(shells, charges, centers)
+        assert np.abs(S - S_ref).max() < TOL
+        assert np.abs(T - T_ref).max() < 1e-11
+        assert np.abs(V - V_ref).max() < 1e-11
+        assert abs(E_nuc - gi.nuclear_repulsion(charges, centers)) < 1e-12
+        assert np.abs(np.diag(S) - 1.0).max() < 1e-12  # every Cartesian component is unit-normalised
+        gd.close()
+
+
+def test_energy_run_water_json_contract(water):
+    """The public entry of the B200 path: molecule/model objects of the JSON contract in, energy Dict out
+    (JCBasis.run + JCRHF.Energy.run).  Logged reference energy -75.9911548795."""
+    from juliachem_jl_b200 import rhf
+    g, prim, aux, p = water
+    geo_ang = (np.array([a["xyz_bohr"] for a in g["geometry"]]) / rhf.ANGSTROM_TO_BOHR).ravel().tolist()
+    molecule = {"geometry": geo_ang, "symbols": ["O", "H", "H"], "molecular_charge": 0}
+    model = {"method": "RHF", "basis": "cc-pVDZ", "auxiliary_basis": "cc-pVDZ-RIFIT"}
+    mol = rhf.run_basis(molecule, model)
+    assert mol["n_electrons"] == 10 and mol["primary"].n_functions == 25 and mol["auxiliary"].n_functions == 96
+    res = rhf.run_energy(mol, {"niter": 50, "ndiis": 10, "dele": 1e-6, "rmsd": 1e-6})
+    assert res["Converged?"] and len(res["Iterations"]) == 12
+    assert abs(res["Energy"] - g["E_converged"]) < 1e-8
+    assert np.abs(res["Overlap"] - p["S"]).max() < 1e-9  # same molecule up to the rigid shift to the centre of mass
+
+
+@pytest.fixture(scope="module")
+def tetramer():
+    """First four molecules of the w50 cluster, cc-pVDZ / cc-pVDZ-RIFIT (N = 100, Q = 384): the oracle's whole run on the
+    CPU (own integrals, Schwarz rule, reference screened algorithm, SCF replay)."""
+    import json
+    import os
+    from juliachem_jl_b200 import rhf
+    geo = json.load(open(os.path.join(os.path.dirname(os.path.abspath(__file__)), "golden", "w50_geometry.json")))
+    molecule = {"geometry": geo["geometry"][:36], "symbols": geo["symbols"][:12], "molecular_charge": 0}
+    mol = rhf.run_basis(molecule, {"basis": "cc-pVDZ"})
+    lib = rhf.load_basis_library()
+    prim, aux = [], []
+    for ia, s in enumerate(mol["symbols"]):
+        prim += [gi.Shell(sh["l"], np.array(sh["exps"]), np.array(sh["coefs"]), mol["centers"][ia], ia) for sh in lib[s]["basis"]]
+        aux += [gi.Shell(sh["l"], np.array(sh["exps"]), np.array(sh["coefs"]), mol["centers"][ia], ia) for sh in lib[s]["auxiliary_basis"]]
+    S, T = gi.overlap_kinetic(prim)
+    H = np.asfortranarray(T + gi.nuclear_attraction(prim, mol["charges"], mol["centers"]))
+    E_nuc = gi.nuclear_repulsion(mol["charges"], mol["centers"])
+    J = gi.two_center_integrals(aux)
+    T3 = gi.three_center_integrals(aux, prim)
+    Q, N = T3.shape[0], T3.shape[1]
+    thr = orc.schwarz_threshold(1e-5, float(np.abs(np.diag(J)).max()))
+    pos, _ = gi.shell_offsets(prim)
+    _, fn_mask = orc.schwarz_function_mask(gi.schwarz_blocks(prim), pos, [s.nbas for s in prim], thr)
+    sd = orc.ScreeningData(fn_mask)
+    Bs = orc.calculate_B(np.tril(J), np.asfortranarray(T3.reshape(Q, N * N))[:, fn_mask.ravel(order="F")])
+    nocc = mol["n_electrons"] // 2
+    ref = sr.run_scf(S, H, E_nuc, nocc, lambda C, it: orc.df_rhf_fock_build([Bs], C, nocc, H, sd, "screened"))
+    return mol, fn_mask, ref
+
+
+@pytest.mark.parametrize("ndev", [1, 2])
+def test_water_tetramer_from_w50_geometry(tetramer, ndev):
+    """Everything on the GPU from the geometry on (one-electron integrals, metric, Schwarz mask, (P|mn), B, SCF loop)
+    against the oracle doing the same run on the CPU: same mask, same iteration count, energy within 1e-8 Eh."""
+    from juliachem_jl_b200 import rhf
+    if jc.device_count() < ndev:
+        pytest.skip("needs %d GPUs" % ndev)
+    mol, fn_mask, ref = tetramer
+    res = rhf.run_energy(mol, {"df_sigma": 1e-5}, num_devices=ndev)
+    assert res["pairs_kept"] == int(fn_mask.sum()) and res["pairs_kept"] < fn_mask.size
+    assert res["Converged?"] and ref["converged"]
+    assert len(res["Iterations"]) == len(ref["iterations"])
+    assert abs(res["Energy"] - ref["E"]) < 1e-8, (res["Energy"], ref["E"])
+    assert np.abs(res["Density"] - ref["D"]).max() < 1e-6
