@@ -34,7 +34,7 @@ static int dev_alloc(T** p, size_t count) {
 static void free_shard_buffers(Shard& s, bool keep_metric = false) {
     cudaSetDevice(s.dev);
     void* ptrs[] = {s.Vpart, s.Vready, s.Bp, s.W, s.Cs, s.Craw, s.dt, s.Jt, s.V, s.Kpart, s.F, s.Hdev, s.Traw, s.d_tile_index, s.d_tile_a,
-                    s.d_tile_b, s.d_dest_of_col, s.d_fn_mask};
+                    s.d_tile_b, s.d_dest_of_col, s.d_fn_mask, s.d_kb_list, s.d_kb_count};
     for (void* p : ptrs)
         if (p) cudaFree(p);
     if (!keep_metric) {
@@ -43,7 +43,7 @@ static void free_shard_buffers(Shard& s, bool keep_metric = false) {
         s.Linv = s.Metric = nullptr;
     }
     s.Bp = s.W = s.Cs = s.Craw = s.dt = s.Jt = s.V = s.Kpart = s.F = s.Hdev = s.Traw = nullptr;
-    s.d_tile_index = s.d_tile_a = s.d_tile_b = nullptr;
+    s.d_tile_index = s.d_tile_a = s.d_tile_b = s.d_kb_list = s.d_kb_count = nullptr;
     s.Vpart = nullptr;
     s.Vready = nullptr;
     s.d_dest_of_col = nullptr;
@@ -98,6 +98,10 @@ static int alloc_shard_buffers(jcdf_handle* h, Shard& s) {
     if ((rc = dev_alloc(&s.d_tile_a, (size_t)L.tiles_kept))) return rc;
     if ((rc = dev_alloc(&s.d_tile_b, (size_t)L.tiles_kept))) return rc;
     if ((rc = dev_alloc(&s.d_dest_of_col, (size_t)L.pairs_kept))) return rc;
+    if ((rc = dev_alloc(&s.d_kb_list, (size_t)L.nb * L.nb))) return rc;
+    if ((rc = dev_alloc(&s.d_kb_count, (size_t)L.nb))) return rc;
+    JC_CUDA(cudaMemcpyAsync(s.d_kb_list, L.kb_list.data(), sizeof(int32_t) * L.kb_list.size(), cudaMemcpyHostToDevice, s.stream));
+    JC_CUDA(cudaMemcpyAsync(s.d_kb_count, L.kb_count.data(), sizeof(int32_t) * L.kb_count.size(), cudaMemcpyHostToDevice, s.stream));
     JC_CUDA(cudaMemcpyAsync(s.d_tile_index, L.tile_index.data(), sizeof(int32_t) * L.tile_index.size(),
                             cudaMemcpyHostToDevice, s.stream));
     JC_CUDA(cudaMemcpyAsync(s.d_tile_a, L.tile_a.data(), sizeof(int32_t) * L.tile_a.size(), cudaMemcpyHostToDevice,
@@ -273,6 +277,11 @@ int32_t jcdf_set_mask(jcdf_handle* h, const uint8_t* fn_mask, const int64_t* map
             }
         }
     L.tiles_kept = (int64_t)L.tile_a.size();
+    L.kb_list.assign((size_t)nb * nb, 0);
+    L.kb_count.assign((size_t)nb, 0);
+    for (int pb = 0; pb < nb; pb++)
+        for (int kb = 0; kb < nb; kb++)
+            if (L.tile_index[(size_t)std::max(pb, kb) * nb + std::min(pb, kb)] >= 0) L.kb_list[(size_t)pb * nb + L.kb_count[pb]++] = kb;
     L.row_len = L.tiles_kept * 1024;
     for (int64_t c = 0; c < N; c++)
         for (int64_t r = 0; r < N; r++)

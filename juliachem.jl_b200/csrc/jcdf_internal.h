@@ -26,6 +26,7 @@ struct Layout {
     bool mask_set = false;
     std::vector<int32_t> tile_index;  // [a * nb + b], a >= b: index of the stored tile or -1
     std::vector<int32_t> tile_a, tile_b;
+    std::vector<int32_t> kb_list, kb_count;  // per 32-wide block pb: the blocks kb with a stored tile (either order)
     std::vector<int64_t> dest_of_col;  // reference pair column -> offset inside a packed row, or -1
     std::vector<int64_t> src_of_col;   // reference pair column -> packed offset holding its value (mirror columns included)
 };
@@ -63,6 +64,8 @@ struct Shard {
     int32_t* d_tile_index = nullptr;
     int32_t* d_tile_a = nullptr;
     int32_t* d_tile_b = nullptr;
+    int32_t* d_kb_list = nullptr;   // [nb][nb]
+    int32_t* d_kb_count = nullptr;  // [nb]
     int64_t* d_dest_of_col = nullptr;
     uint8_t* d_fn_mask = nullptr;   // N x N or nullptr when unscreened
     double* Linv = nullptr;    // Q x Q on the first device only

@@ -94,18 +94,22 @@ struct HTParams {
     const double* Bp;
     int64_t row_len;
     const int32_t* tile_index;
+    const int32_t* kb_list;   // [nb][nb]: the q blocks kb for which tile (max(pb,kb), min(pb,kb)) is stored, ascending
+    const int32_t* kb_count;  // [nb]
     const double* Cs;
     double* W;
-    int q_len, nb, n_mt, n_pt128, npt64, occ_pad, n_valid_last;
+    int q_len, nb, n_mt, npt64, occ_pad, n_valid_last;
     int64_t n_items;
 };
 
-// One work item = (auxiliary row Q, 128-wide p tile, M tile of BM = 8*MT occupied orbitals):
-//   out[i, p] = sum_q Cs[q][i] * Bsym_Q[q][p]      (M = i, N = p, K = q)
-// The k loop walks the 32-wide q blocks; for p block pb and q block kb the stored tile is (max, min): read as
-// [k][n] when kb >= pb and transposed as [n][k] when kb < pb, so each stored tile serves both triangles.
-// Each consumer warp owns a (BM/2) x 32 block of the item: wm = warp >> 2 selects the M half, j = warp & 3 the 32-wide
-// p block (= one stored B tile per k slab), so a k-step of 4 costs MH + 4 fragment loads for MH * 4 DMMAs.
+// One work item = (quad of auxiliary rows Q0..Q0+3, 32-wide p block pb, M tile of BM = 8*MT occupied orbitals):
+//   out[Qj][i, p] = sum_q Cs[q][i] * Bsym_Qj[q][p]      (M = i, N = p, K = q)
+// The k loop walks only the q blocks kb whose tile (max(pb,kb), min(pb,kb)) the mask kept — the same list for every
+// auxiliary row, so the four rows of a quad do exactly the same work and a stage (one C slab + the four rows' copies
+// of one tile) never idles a warp: the cost of the half-transform is proportional to the number of stored tiles.
+// A stored tile is read as [k][n] when kb >= pb and transposed as [n][k] when kb < pb, so it serves both triangles.
+// Each consumer warp owns a (BM/2) x 32 block: wm = warp >> 2 selects the M half, j = warp & 3 the auxiliary row of
+// the quad, so a k-step of 4 costs MH + 4 fragment loads for MH * 4 DMMAs.
 template <int MT, bool TRANSPOSED>
 __device__ __forceinline__ void ht_slab(double (&acc)[MT / 2][4][2], const double* __restrict__ sA,
                                         const double* __restrict__ sB, int m0, int g, int t, int ksteps) {
@@ -129,11 +133,9 @@ __device__ __forceinline__ void ht_slab(double (&acc)[MT / 2][4][2], const doubl
     }
 }
 
-// DEDICATED (launched with HT_THREADS = 288): warp 8 is a dedicated copy producer (its lane 0 runs the whole produce() sequence, as
-// far ahead as the ring allows) and warps 0-7 only compute — measured 4 % faster here than thread 0 doubling as the
-// producer, because the tile-table lookups and the empty-barrier wait no longer sit on a DMMA warp's critical path.
-// DEDICATED = false (CTA_THREADS = 256) is the merged scheme of k_exchange; not instantiated.
-template <int MT, bool DEDICATED>
+// Launched with HT_THREADS = 288: warp 8 is a dedicated copy producer (its lane 0 runs the whole produce() sequence, as
+// far ahead as the ring allows) and warps 0-7 only compute.
+template <int MT>
 __global__ void __launch_bounds__(HT_THREADS, 1) k_half_transform(HTParams prm) {
     constexpr int BM = 8 * MT;
     constexpr int MH = MT / 2;
@@ -142,7 +144,7 @@ __global__ void __launch_bounds__(HT_THREADS, 1) k_half_transform(HTParams prm) 
     double* stages = reinterpret_cast<double*>(smem_raw);
     uint64_t* full = reinterpret_cast<uint64_t*>(stages + (size_t)NSTAGE * STAGE_DOUBLES);
     uint64_t* empty = full + NSTAGE;
-    int* present = reinterpret_cast<int*>(empty + NSTAGE);
+    int* stage_kb = reinterpret_cast<int*>(empty + NSTAGE);
 
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
     if (threadIdx.x == 0) {
@@ -155,112 +157,85 @@ __global__ void __launch_bounds__(HT_THREADS, 1) k_half_transform(HTParams prm) 
     }
     __syncthreads();
 
-    const int nb = prm.nb, n_mt = prm.n_mt, n_pt = prm.n_pt128;
-    constexpr bool dedicated = DEDICATED;
-    const bool is_producer = !dedicated && (threadIdx.x == 0);
+    const int nb = prm.nb, n_mt = prm.n_mt;
 
-    // ---- copy issue: walks the same (item, kb) sequence ahead of the consumers ----
-    PipeState pp;
-    int64_t p_item = blockIdx.x;
-    int p_kb = 0;
-    auto produce = [&]() {
-        if (p_item >= prm.n_items) return;
-        const int mt = (int)(p_item % n_mt);
-        const int64_t r1 = p_item / n_mt;
-        const int pt = (int)(r1 % n_pt);
-        const int64_t qrow = r1 / n_pt;
-        const double* Brow = prm.Bp + qrow * prm.row_len;
-        const int kb = p_kb;
-        mbar_wait(&empty[pp.stage], pp.phase ^ 1u);
-        int mask = 0;
-        int tix[4];
-#pragma unroll
-        for (int j = 0; j < 4; j++) {
-            const int pb = 4 * pt + j;
-            tix[j] = -1;
-            if (pb < nb) {
-                const int a = max(pb, kb), b = min(pb, kb);
-                tix[j] = prm.tile_index[a * nb + b];
-                if (tix[j] >= 0) mask |= 1 << j;
+    // ---- producer warp: walks the same (item, stored tile) sequence ahead of the consumers ----
+    if (warp == CONSUMER_WARPS) {
+        if (lane != 0) return;
+        PipeState pp;
+        for (int64_t item = blockIdx.x; item < prm.n_items; item += gridDim.x) {
+            const int mt = (int)(item % n_mt);
+            const int64_t r1 = item / n_mt;
+            const int pb = (int)(r1 % nb);
+            const int64_t q0 = (r1 / nb) * 4;
+            const int nq = (int)min((int64_t)4, (int64_t)prm.q_len - q0);
+            const double* Brow = prm.Bp + q0 * prm.row_len;
+            const int nk = prm.kb_count[pb];
+            const int32_t* kl = prm.kb_list + (int64_t)pb * nb;
+            for (int s = 0; s < nk; s++) {
+                const int kb = kl[s];
+                const int32_t tix = prm.tile_index[max(pb, kb) * nb + min(pb, kb)];
+                mbar_wait(&empty[pp.stage], pp.phase ^ 1u);
+                stage_kb[pp.stage] = kb;
+                double* st = stages + (size_t)pp.stage * STAGE_DOUBLES;
+                mbar_arrive_expect_tx(&full[pp.stage], 32u * BM * 8u + (uint32_t)nq * (TILE_ELEMS * 8u));
+                bulk_g2s(st, prm.Cs + ((int64_t)kb * n_mt + mt) * (32 * BM), 32u * BM * 8u, &full[pp.stage]);
+                for (int j = 0; j < nq; j++)
+                    bulk_g2s(st + 32 * BM + j * TILE_ELEMS, Brow + j * prm.row_len + (int64_t)tix * TILE_ELEMS, TILE_ELEMS * 8u,
+                             &full[pp.stage]);
+                pp.advance<NSTAGE>();
             }
         }
-        present[pp.stage] = mask;
-        double* st = stages + (size_t)pp.stage * STAGE_DOUBLES;
-        if (mask) {
-            const uint32_t bytes = 32u * BM * 8u + (uint32_t)__popc(mask) * (TILE_ELEMS * 8u);
-            mbar_arrive_expect_tx(&full[pp.stage], bytes);
-            bulk_g2s(st, prm.Cs + ((int64_t)kb * n_mt + mt) * (32 * BM), 32u * BM * 8u, &full[pp.stage]);
-#pragma unroll
-            for (int j = 0; j < 4; j++)
-                if (tix[j] >= 0)
-                    bulk_g2s(st + 32 * BM + j * TILE_ELEMS, Brow + (int64_t)tix[j] * TILE_ELEMS, TILE_ELEMS * 8u,
-                             &full[pp.stage]);
-        } else {
-            mbar_arrive(&full[pp.stage]);
-        }
-        pp.advance<NSTAGE>();
-        if (++p_kb == nb) {
-            p_kb = 0;
-            p_item += gridDim.x;
-        }
-    };
-    if (dedicated && warp == CONSUMER_WARPS) {
-        if (lane == 0)
-            while (p_item < prm.n_items) produce();
         return;
     }
-    if (is_producer)
-        for (int s = 0; s < NSTAGE - 1; s++) produce();
 
     // ---------------------------------------------------- consumers ----------------------------------------------------
     PipeState ps;
     const int g = lane >> 2, t = lane & 3;
-    const int j = warp & 3;                 // p block inside the 128-wide tile
+    const int j = warp & 3;                 // auxiliary row inside the quad
     const int m0 = (warp >> 2) * (BM / 2);  // first occupied-orbital row of this warp's half
     // the last q block holds N - 32 (nb - 1) valid rows: trim its k loop to whole DMMA k-steps (the rest is zero padding)
     const int last_ksteps = (prm.n_valid_last + 3) >> 2;
     for (int64_t item = blockIdx.x; item < prm.n_items; item += gridDim.x) {
         const int mt = (int)(item % n_mt);
         const int64_t r1 = item / n_mt;
-        const int pt = (int)(r1 % n_pt);
-        const int64_t qrow = r1 / n_pt;
-        const int pbg = 4 * pt + j;
+        const int pb = (int)(r1 % nb);
+        const int64_t qrow = (r1 / nb) * 4 + j;
+        const bool valid = qrow < prm.q_len;
+        const int nk = prm.kb_count[pb];
         double acc[MH][4][2];
 #pragma unroll
         for (int jm = 0; jm < MH; jm++)
 #pragma unroll
             for (int jn = 0; jn < 4; jn++) acc[jm][jn][0] = acc[jm][jn][1] = 0.0;
 
-        for (int kb = 0; kb < nb; kb++) {
+        for (int s = 0; s < nk; s++) {
             mbar_wait(&full[ps.stage], ps.phase);
-            const int mask = present[ps.stage];
-            if ((mask >> j) & 1) {
+            if (valid) {
+                const int kb = stage_kb[ps.stage];
                 const double* sA = stages + (size_t)ps.stage * STAGE_DOUBLES;
                 const double* sB = sA + 32 * BM + j * TILE_ELEMS;
                 const int ksteps = (kb == nb - 1) ? last_ksteps : KSLAB / 4;
-                if (kb < pbg) ht_slab<MT, true>(acc, sA, sB, m0, g, t, ksteps);
+                if (kb < pb) ht_slab<MT, true>(acc, sA, sB, m0, g, t, ksteps);
                 else ht_slab<MT, false>(acc, sA, sB, m0, g, t, ksteps);
             }
             __syncwarp();
             if (lane == 0) mbar_arrive(&empty[ps.stage]);
             ps.advance<NSTAGE>();
-            // refill the slab released one iteration ago (every warp is past it by now) with the slab NSTAGE - 1 ahead
-            if (is_producer) produce();
-            __syncwarp();
         }
         // epilogue: W[(Q,i)][p], 16-byte stores into the swizzled [32 x 64] W tiles
+        if (valid) {
 #pragma unroll
-        for (int jm = 0; jm < MH; jm++) {
-            const int i = mt * BM + m0 + 8 * jm + g;
-            if (i < prm.occ_pad) {
-                const int64_t krow = qrow * prm.occ_pad + i;
-                const int64_t kc = krow >> 5;
-                const int kr = (int)(krow & 31);
+            for (int jm = 0; jm < MH; jm++) {
+                const int i = mt * BM + m0 + 8 * jm + g;
+                if (i < prm.occ_pad) {
+                    const int64_t krow = qrow * prm.occ_pad + i;
+                    const int64_t kc = krow >> 5;
+                    const int kr = (int)(krow & 31);
 #pragma unroll
-                for (int jn = 0; jn < 4; jn++) {
-                    const int p = 128 * pt + 32 * j + 8 * jn + 2 * t;
-                    const int p64 = p >> 6, pc = p & 63;
-                    if (p64 < prm.npt64) {
+                    for (int jn = 0; jn < 4; jn++) {
+                        const int p = 32 * pb + 8 * jn + 2 * t;
+                        const int p64 = p >> 6, pc = p & 63;
                         double2 v = make_double2(acc[jm][jn][0], acc[jm][jn][1]);
                         *reinterpret_cast<double2*>(prm.W + ((kc * prm.npt64 + p64) * 32 + kr) * 64 + swz(kr, pc)) = v;
                     }
@@ -277,8 +252,8 @@ size_t half_transform_smem_bytes(int bm) {
 template <int MT>
 static void launch_ht_t(const HTParams& prm, int grid, cudaStream_t st) {
     size_t smem = half_transform_smem_bytes(8 * MT);
-    cudaFuncSetAttribute(k_half_transform<MT, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
-    k_half_transform<MT, true><<<grid, HT_THREADS, smem, st>>>(prm);
+    cudaFuncSetAttribute(k_half_transform<MT>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+    k_half_transform<MT><<<grid, HT_THREADS, smem, st>>>(prm);
 }
 
 void launch_half_transform(const Layout& L, Shard& s, int sm_count) {
@@ -286,16 +261,17 @@ void launch_half_transform(const Layout& L, Shard& s, int sm_count) {
     prm.Bp = s.Bp;
     prm.row_len = L.row_len;
     prm.tile_index = s.d_tile_index;
+    prm.kb_list = s.d_kb_list;
+    prm.kb_count = s.d_kb_count;
     prm.Cs = s.Cs;
     prm.W = s.W;
     prm.q_len = (int)s.q_len;
     prm.nb = L.nb;
     prm.n_mt = L.n_mt;
-    prm.n_pt128 = L.n_pt128;
     prm.npt64 = L.npt64;
     prm.occ_pad = L.occ_pad;
     prm.n_valid_last = (int)(L.N - 32 * (L.nb - 1));
-    prm.n_items = (int64_t)s.q_len * L.n_pt128 * L.n_mt;
+    prm.n_items = ((int64_t)s.q_len + 3) / 4 * L.nb * L.n_mt;
     int grid = (int)std::min<int64_t>(prm.n_items, sm_count);
     if (grid <= 0) return;
     switch (L.bm / 8) {
