@@ -34,7 +34,7 @@ static int dev_alloc(T** p, size_t count) {
 static void free_shard_buffers(Shard& s, bool keep_metric = false) {
     cudaSetDevice(s.dev);
     void* ptrs[] = {s.Vpart, s.Vready, s.Bp, s.W, s.Cs, s.Craw, s.dt, s.Jt, s.V, s.Kpart, s.F, s.Hdev, s.Traw, s.d_tile_index, s.d_tile_a,
-                    s.d_tile_b, s.d_dest_of_col, s.d_fn_mask, s.d_kb_list, s.d_kb_count};
+                    s.d_tile_b, s.d_dest_of_col, s.d_fn_mask, s.d_kb_list, s.d_kb_count, s.d_perm, s.d_inv, s.d_tile_strips};
     for (void* p : ptrs)
         if (p) cudaFree(p);
     if (!keep_metric) {
@@ -43,7 +43,7 @@ static void free_shard_buffers(Shard& s, bool keep_metric = false) {
         s.Linv = s.Metric = nullptr;
     }
     s.Bp = s.W = s.Cs = s.Craw = s.dt = s.Jt = s.V = s.Kpart = s.F = s.Hdev = s.Traw = nullptr;
-    s.d_tile_index = s.d_tile_a = s.d_tile_b = s.d_kb_list = s.d_kb_count = nullptr;
+    s.d_tile_index = s.d_tile_a = s.d_tile_b = s.d_kb_list = s.d_kb_count = s.d_perm = s.d_inv = s.d_tile_strips = nullptr;
     s.Vpart = nullptr;
     s.Vready = nullptr;
     s.d_dest_of_col = nullptr;
@@ -98,6 +98,12 @@ static int alloc_shard_buffers(jcdf_handle* h, Shard& s) {
     if ((rc = dev_alloc(&s.d_tile_a, (size_t)L.tiles_kept))) return rc;
     if ((rc = dev_alloc(&s.d_tile_b, (size_t)L.tiles_kept))) return rc;
     if ((rc = dev_alloc(&s.d_dest_of_col, (size_t)L.pairs_kept))) return rc;
+    if ((rc = dev_alloc(&s.d_perm, (size_t)L.n_pad))) return rc;
+    if ((rc = dev_alloc(&s.d_inv, (size_t)L.n_pad))) return rc;
+    if ((rc = dev_alloc(&s.d_tile_strips, (size_t)L.tiles_kept))) return rc;
+    JC_CUDA(cudaMemcpyAsync(s.d_perm, L.perm.data(), sizeof(int32_t) * L.perm.size(), cudaMemcpyHostToDevice, s.stream));
+    JC_CUDA(cudaMemcpyAsync(s.d_inv, L.inv.data(), sizeof(int32_t) * L.inv.size(), cudaMemcpyHostToDevice, s.stream));
+    JC_CUDA(cudaMemcpyAsync(s.d_tile_strips, L.tile_strips.data(), sizeof(int32_t) * L.tile_strips.size(), cudaMemcpyHostToDevice, s.stream));
     if ((rc = dev_alloc(&s.d_kb_list, (size_t)L.nb * L.nb))) return rc;
     if ((rc = dev_alloc(&s.d_kb_count, (size_t)L.nb))) return rc;
     JC_CUDA(cudaMemcpyAsync(s.d_kb_list, L.kb_list.data(), sizeof(int32_t) * L.kb_list.size(), cudaMemcpyHostToDevice, s.stream));
@@ -141,6 +147,56 @@ static int ensure_comm(jcdf_handle* h) {
     }
     set_error("multi-rank communicator not initialised: call jcdf_comm_init_rank first");
     return JCDF_ERR_INVALID;
+}
+
+// Mask-driven regrouping of the basis functions into 32-wide blocks (internal order only; every C-ABI argument stays
+// in the caller's order).  The Schwarz mask of a real molecule is sparse at the function-pair level, but in the input
+// order (atoms in file order, tight and diffuse shells interleaved) nearly every 32 x 32 tile holds some surviving pair.
+// Functions with similar partner sets — the same neighbourhood and a similar extent — are put in the same block:
+// a block is grown from the unassigned function of smallest degree by repeatedly adding the function that enlarges the
+// union of the block's partner set least (ties: largest overlap).  Rows are bitsets; O(N^3 / 64) word operations.
+static void regroup_functions(const uint8_t* fn_mask, int64_t N, std::vector<int32_t>& inv_out) {
+    const int64_t nw = (N + 63) / 64;
+    std::vector<uint64_t> rows((size_t)(N * nw), 0);
+    std::vector<int32_t> deg((size_t)N, 0);
+    for (int64_t c = 0; c < N; c++)
+        for (int64_t r = 0; r < N; r++)
+            if (fn_mask[r + N * c]) {
+                rows[(size_t)(r * nw + (c >> 6))] |= 1ull << (c & 63);
+                deg[(size_t)r]++;
+            }
+    std::vector<uint8_t> used((size_t)N, 0);
+    std::vector<uint64_t> uni((size_t)nw);
+    inv_out.clear();
+    inv_out.reserve((size_t)N);
+    int64_t remaining = N;
+    while (remaining > 0) {
+        int64_t seed = -1;
+        for (int64_t i = 0; i < N; i++)
+            if (!used[(size_t)i] && (seed < 0 || deg[(size_t)i] < deg[(size_t)seed])) seed = i;
+        used[(size_t)seed] = 1;
+        remaining--;
+        inv_out.push_back((int32_t)seed);
+        for (int64_t w = 0; w < nw; w++) uni[(size_t)w] = rows[(size_t)(seed * nw + w)];
+        for (int k = 1; k < 32 && remaining > 0; k++) {
+            int64_t best = -1;
+            int best_add = 0, best_ov = 0;
+            for (int64_t i = 0; i < N; i++) {
+                if (used[(size_t)i]) continue;
+                int add = 0, ov = 0;
+                const uint64_t* ri = &rows[(size_t)(i * nw)];
+                for (int64_t w = 0; w < nw; w++) {
+                    add += __builtin_popcountll(ri[w] & ~uni[(size_t)w]);
+                    ov += __builtin_popcountll(ri[w] & uni[(size_t)w]);
+                }
+                if (best < 0 || add < best_add || (add == best_add && ov > best_ov)) { best = i; best_add = add; best_ov = ov; }
+            }
+            used[(size_t)best] = 1;
+            remaining--;
+            inv_out.push_back((int32_t)best);
+            for (int64_t w = 0; w < nw; w++) uni[(size_t)w] |= rows[(size_t)(best * nw + w)];
+        }
+    }
 }
 
 }  // namespace jcdf
@@ -256,13 +312,54 @@ int32_t jcdf_set_mask(jcdf_handle* h, const uint8_t* fn_mask, const int64_t* map
     const int64_t N = L.N;
     const int nb = L.nb;
     for (Shard& s : h->shards) free_shard_buffers(s, true);
-    auto kept = [&](int64_t r, int64_t c) -> bool { return fn_mask ? fn_mask[r + N * c] != 0 : true; };
+    auto kept_ref = [&](int64_t r, int64_t c) -> bool { return fn_mask ? fn_mask[r + N * c] != 0 : true; };
+    int64_t P = 0, Ptri = 0;
+    for (int64_t c = 0; c < N; c++)
+        for (int64_t r = 0; r < N; r++)
+            if (kept_ref(r, c)) {
+                P++;
+                if (r >= c) Ptri++;
+                if (fn_mask && !fn_mask[c + N * r]) {
+                    set_error("jcdf_set_mask: basis_function_screen_matrix is not symmetric");
+                    return JCDF_ERR_INVALID;
+                }
+            }
+    for (int64_t r = 0; r < N; r++) JC_REQUIRE(kept_ref(r, r), "jcdf_set_mask: a diagonal pair (p,p) is screened");
+    // internal function order: identity, or the mask-driven regrouping when it stores fewer tiles
+    L.perm.resize((size_t)L.n_pad);
+    L.inv.resize((size_t)L.n_pad);
+    for (int i = 0; i < L.n_pad; i++) L.perm[i] = L.inv[i] = i;
+    auto count_tiles = [&](const std::vector<int32_t>& inv) {
+        int64_t n = 0;
+        for (int a = 0; a < nb; a++)
+            for (int b = 0; b <= a; b++) {
+                bool any = false;
+                const int r1 = (int)std::min<int64_t>(N, 32 * (a + 1)), c1 = (int)std::min<int64_t>(N, 32 * (b + 1));
+                for (int c = 32 * b; c < c1 && !any; c++)
+                    for (int r = 32 * a; r < r1; r++)
+                        if (kept_ref(inv[r], inv[c])) { any = true; break; }
+                n += any;
+            }
+        return n;
+    };
+    L.regrouped = false;
+    if (fn_mask && P < N * N && h->opt_regroup) {
+        std::vector<int32_t> inv2;
+        regroup_functions(fn_mask, N, inv2);
+        inv2.resize((size_t)L.n_pad);
+        for (int i = (int)N; i < L.n_pad; i++) inv2[i] = i;
+        if (count_tiles(inv2) < count_tiles(L.inv)) {
+            L.inv = inv2;
+            for (int i = 0; i < L.n_pad; i++) L.perm[L.inv[i]] = i;
+            L.regrouped = true;
+        }
+    }
+    auto kept = [&](int64_t ri, int64_t ci) -> bool { return kept_ref(L.inv[ri], L.inv[ci]); };  // internal coordinates
     // tile table: a tile is stored iff it holds at least one unscreened pair
     L.tile_index.assign((size_t)nb * nb, -1);
     L.tile_a.clear();
     L.tile_b.clear();
     L.tiles_total = (int64_t)nb * (nb + 1) / 2;
-    int64_t P = 0, Ptri = 0;
     for (int a = 0; a < nb; a++)
         for (int b = 0; b <= a; b++) {
             bool any = false;
@@ -282,18 +379,20 @@ int32_t jcdf_set_mask(jcdf_handle* h, const uint8_t* fn_mask, const int64_t* map
     for (int pb = 0; pb < nb; pb++)
         for (int kb = 0; kb < nb; kb++)
             if (L.tile_index[(size_t)std::max(pb, kb) * nb + std::min(pb, kb)] >= 0) L.kb_list[(size_t)pb * nb + L.kb_count[pb]++] = kb;
-    L.row_len = L.tiles_kept * 1024;
-    for (int64_t c = 0; c < N; c++)
-        for (int64_t r = 0; r < N; r++)
-            if (kept(r, c)) {
-                P++;
-                if (r >= c) Ptri++;
-                if (fn_mask && !fn_mask[c + N * r]) {
-                    set_error("jcdf_set_mask: basis_function_screen_matrix is not symmetric");
-                    return JCDF_ERR_INVALID;
-                }
+    // strips of four rows / four columns of every stored tile that hold an unscreened pair: bits 0-7 row strips,
+    // bits 8-15 column strips (the half-transform skips the k-steps of empty strips)
+    L.tile_strips.assign((size_t)L.tiles_kept, 0);
+    for (int64_t ti = 0; ti < L.tiles_kept; ti++) {
+        const int a = L.tile_a[(size_t)ti], b = L.tile_b[(size_t)ti];
+        uint32_t bits = 0;
+        for (int r = 0; r < 32; r++)
+            for (int c = 0; c < 32; c++) {
+                const int64_t ri = 32 * a + r, ci = 32 * b + c;
+                if (ri < N && ci < N && kept(ri, ci)) bits |= (1u << (r >> 2)) | (1u << (8 + (c >> 2)));
             }
-    for (int64_t r = 0; r < N; r++) JC_REQUIRE(kept(r, r), "jcdf_set_mask: a diagonal pair (p,p) is screened");
+        L.tile_strips[(size_t)ti] = (int32_t)bits;
+    }
+    L.row_len = L.tiles_kept * 1024;
     L.pairs_kept = P;
     L.pairs_tri = Ptri;
     // reference column -> packed offset.  Column of pair (row r, col c) is map[r + N*c] - 1 (SchwarzScreening.jl:72-81).
@@ -301,21 +400,22 @@ int32_t jcdf_set_mask(jcdf_handle* h, const uint8_t* fn_mask, const int64_t* map
     L.src_of_col.assign((size_t)P, 0);
     for (int64_t c = 0; c < N; c++)
         for (int64_t r = 0; r < N; r++) {
-            if (!kept(r, c)) {
+            if (!kept_ref(r, c)) {
                 if (map) JC_REQUIRE(map[r + N * c] == 0, "jcdf_set_mask: index map non-zero on a screened pair");
                 continue;
             }
             const int64_t col = map ? map[r + N * c] - 1 : r + N * c;
             JC_REQUIRE(col >= 0 && col < P, "jcdf_set_mask: sparse_pq_index_map entry out of range");
-            const int a = (int)(r / 32), b = (int)(c / 32);
+            const int ri = L.perm[r], ci = L.perm[c];
+            const int a = ri / 32, b = ci / 32;
             if (a < b) {  // mirror copy; the (c, r) column fills tile (b, a)
                 const int32_t tm = L.tile_index[(size_t)b * nb + a];
-                const int rm = (int)(c % 32), cm = (int)(r % 32);
+                const int rm = ci % 32, cm = ri % 32;
                 L.src_of_col[(size_t)col] = (int64_t)tm * 1024 + rm * 32 + (cm ^ ((rm & 3) << 2));
                 continue;
             }
             const int32_t ti = L.tile_index[(size_t)a * nb + b];
-            const int rr = (int)(r % 32), cc = (int)(c % 32);
+            const int rr = ri % 32, cc = ci % 32;
             L.dest_of_col[(size_t)col] = (int64_t)ti * 1024 + rr * 32 + (cc ^ ((rr & 3) << 2));
             L.src_of_col[(size_t)col] = L.dest_of_col[(size_t)col];
         }
@@ -829,7 +929,10 @@ int32_t jcdf_set_option(jcdf_handle* h, const char* name, int64_t value) {
     const std::string n(name);
     if (n == "coulomb_fused") h->opt_coulomb_fused = value;
     else if (n == "coulomb_overlap") h->opt_coulomb_overlap = value;
-    else if (n == "exchange_slices") {
+    else if (n == "regroup") {
+        h->opt_regroup = value;
+        for (Shard& s : h->shards) JC_REQUIRE(s.Bp == nullptr, "regroup must be set before jcdf_set_mask");
+    } else if (n == "exchange_slices") {
         h->opt_exchange_slices = value;
         for (Shard& s : h->shards) JC_REQUIRE(s.Bp == nullptr, "exchange_slices must be set before jcdf_set_mask");
     } else {

@@ -106,6 +106,7 @@ struct ThreeCenterArgs {
     int64_t q_begin, q_len;
     const int32_t* tile_index;
     const uint8_t* fn_mask;  // N x N or nullptr
+    const int32_t* perm;     // caller's function index -> internal (regrouped) index
     int N, nb;
 };
 
@@ -221,14 +222,16 @@ __global__ void __launch_bounds__(INT_THREADS) k_three_center(ThreeCenterArgs g)
                     const int n = fb0 + B;
                     if (n > m) continue;  // same shell: the block is symmetric, (m, n) with m >= n covers it
                     if (g.fn_mask && !g.fn_mask[m + (int64_t)g.N * n]) continue;
-                    const int32_t ti = g.tile_index[(m >> 5) * g.nb + (n >> 5)];
+                    const int mi = g.perm[m], ni = g.perm[n];
+                    const int hi = max(mi, ni), lo = min(mi, ni);
+                    const int32_t ti = g.tile_index[(hi >> 5) * g.nb + (lo >> 5)];
                     if (ti < 0) continue;
                     int bx, by, bz;
                     cart_comp(lb, B, bx, by, bz);
                     const double val = fA * comp_factor(lb, bx, by, bz) * acc[(C - c0) * nAB + A * nB + B];
-                    const int rm = m & 31, rn = n & 31;
+                    const int rm = hi & 31, rn = lo & 31;
                     row[(int64_t)ti * TILE_ELEMS + rm * 32 + swz(rm, rn)] = val;
-                    if ((m >> 5) == (n >> 5) && m != n) row[(int64_t)ti * TILE_ELEMS + rn * 32 + swz(rn, rm)] = val;
+                    if ((hi >> 5) == (lo >> 5) && hi != lo) row[(int64_t)ti * TILE_ELEMS + rn * 32 + swz(rn, rm)] = val;
                 }
             }
         }
@@ -702,6 +705,7 @@ int32_t jcdf_compute_three_center(jcdf_handle* h) {
                     a.q_len = s.q_len;
                     a.tile_index = s.d_tile_index;
                     a.fn_mask = s.d_fn_mask;
+                    a.perm = s.d_perm;
                     a.N = (int)L.N;
                     a.nb = L.nb;
                     const int Lab = la + lb, Lt = Lab + lc;

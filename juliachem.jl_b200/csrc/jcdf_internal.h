@@ -26,6 +26,9 @@ struct Layout {
     bool mask_set = false;
     std::vector<int32_t> tile_index;  // [a * nb + b], a >= b: index of the stored tile or -1
     std::vector<int32_t> tile_a, tile_b;
+    std::vector<int32_t> perm, inv;           // caller's function index -> internal index and back (n_pad entries)
+    std::vector<int32_t> tile_strips;         // per stored tile: bits 0-7 non-empty 4-row strips, bits 8-15 4-column strips
+    bool regrouped = false;
     std::vector<int32_t> kb_list, kb_count;  // per 32-wide block pb: the blocks kb with a stored tile (either order)
     std::vector<int64_t> dest_of_col;  // reference pair column -> offset inside a packed row, or -1
     std::vector<int64_t> src_of_col;   // reference pair column -> packed offset holding its value (mirror columns included)
@@ -64,6 +67,9 @@ struct Shard {
     int32_t* d_tile_index = nullptr;
     int32_t* d_tile_a = nullptr;
     int32_t* d_tile_b = nullptr;
+    int32_t* d_perm = nullptr;      // [n_pad]
+    int32_t* d_inv = nullptr;       // [n_pad]
+    int32_t* d_tile_strips = nullptr;  // [tiles_kept]
     int32_t* d_kb_list = nullptr;   // [nb][nb]
     int32_t* d_kb_count = nullptr;  // [nb]
     int64_t* d_dest_of_col = nullptr;
@@ -96,6 +102,7 @@ struct jcdf_handle {
     int64_t opt_coulomb_fused = 1;    // single-pass cooperative Coulomb kernel whenever the row segment fits in smem
     int64_t opt_coulomb_overlap = 0;  // two-pass sweeps on a second stream, concurrent with the tensor-core kernels
     int64_t opt_exchange_slices = 0;
+    int64_t opt_regroup = 1;          // mask-driven regrouping of the basis functions into 32-wide blocks
     jcdf::ScfState* scf = nullptr;    // on-device SCF driver state (jcdf_scf_*), owned
     jcdf::IntegralsState* ints = nullptr;  // basis sets + integral scratch (jcdf_set_basis / jcdf_compute_*), owned
     bool metric_on_device = false;    // shards[0].Metric holds (P|Q) (jcdf_compute_two_center) — consumed by the factorisation

@@ -26,9 +26,9 @@ constexpr int MAX_REGS = 208;  // leaves (16384 - 2*32*208) = 3072 registers per
 // =====================================================================================================================
 // C_occ re-layout and packed density
 // =====================================================================================================================
-// Cs[kb][mt][kr][swz(kr, m)] = C_occ[q = 32 kb + kr, i = mt*bm + m]   (zero beyond N / occ)
+// Cs[kb][mt][kr][swz(kr, m)] = C_occ[inv[q = 32 kb + kr], i = mt*bm + m]   (zero beyond N / occ)
 __global__ void k_prep_cs(const double* __restrict__ Craw, int64_t ldc, double* __restrict__ Cs, int N, int occ, int nb,
-                          int n_mt, int bm) {
+                          int n_mt, int bm, const int32_t* __restrict__ inv) {
     int64_t total = (int64_t)nb * n_mt * 32 * bm;
     for (int64_t idx = blockIdx.x * (int64_t)blockDim.x + threadIdx.x; idx < total;
          idx += (int64_t)gridDim.x * blockDim.x) {
@@ -39,7 +39,7 @@ __global__ void k_prep_cs(const double* __restrict__ Craw, int64_t ldc, double* 
         int mt = (int)(r2 % n_mt);
         int kb = (int)(r2 / n_mt);
         int q = kb * 32 + kr, i = mt * bm + m;
-        double v = (q < N && i < occ) ? Craw[q + ldc * i] : 0.0;
+        double v = (q < N && i < occ) ? Craw[inv[q] + ldc * i] : 0.0;  // q: internal order, inv[q]: the caller's row
         Cs[(((int64_t)kb * n_mt + mt) * 32 + kr) * bm + swz(kr, m)] = v;
     }
 }
@@ -49,7 +49,8 @@ __global__ void k_prep_cs(const double* __restrict__ Craw, int64_t ldc, double* 
 // (ScreenedDF.jl:305-316) expressed in tile space.
 __global__ void __launch_bounds__(256) k_density_packed(const double* __restrict__ Craw, int64_t ldc,
                                                          double* __restrict__ dt, const int32_t* __restrict__ tile_a,
-                                                         const int32_t* __restrict__ tile_b, int N, int occ) {
+                                                         const int32_t* __restrict__ tile_b, int N, int occ,
+                                                         const int32_t* __restrict__ inv) {
     constexpr int IC = 64;                      // occupied orbitals staged per pass
     __shared__ double sa[IC][33], sb[IC][33];   // [i][p] / [i][q], padded against bank conflicts
     const int tile = blockIdx.x;
@@ -60,8 +61,8 @@ __global__ void __launch_bounds__(256) k_density_packed(const double* __restrict
     for (int i0 = 0; i0 < occ; i0 += IC) {
         for (int ii = r0; ii < IC; ii += 8) {
             const int i = i0 + ii, p = a * 32 + c, q = b * 32 + c;
-            sa[ii][c] = (i < occ && p < N) ? Craw[p + ldc * i] : 0.0;
-            sb[ii][c] = (i < occ && q < N) ? Craw[q + ldc * i] : 0.0;
+            sa[ii][c] = (i < occ && p < N) ? Craw[inv[p] + ldc * i] : 0.0;
+            sb[ii][c] = (i < occ && q < N) ? Craw[inv[q] + ldc * i] : 0.0;
         }
         __syncthreads();
 #pragma unroll 8
@@ -82,9 +83,9 @@ __global__ void __launch_bounds__(256) k_density_packed(const double* __restrict
 void launch_prep(const Layout& L, Shard& s, int64_t ldc) {
     int64_t total = (int64_t)L.nb * L.n_mt * 32 * L.bm;
     int blocks = (int)std::min<int64_t>((total + 255) / 256, 148 * 16);
-    k_prep_cs<<<blocks, 256, 0, s.stream>>>(s.Craw, ldc, s.Cs, (int)L.N, (int)L.occ, L.nb, L.n_mt, L.bm);
+    k_prep_cs<<<blocks, 256, 0, s.stream>>>(s.Craw, ldc, s.Cs, (int)L.N, (int)L.occ, L.nb, L.n_mt, L.bm, s.d_inv);
     k_density_packed<<<(int)L.tiles_kept, 256, 0, s.stream>>>(s.Craw, ldc, s.dt, s.d_tile_a, s.d_tile_b, (int)L.N,
-                                                               (int)L.occ);
+                                                               (int)L.occ, s.d_inv);
 }
 
 // =====================================================================================================================
@@ -436,19 +437,22 @@ void launch_exchange(const Layout& L, Shard& s, int sm_count) {
 // (copy_screened_coulomb_to_fock!, ScreenedDF.jl:367-378; H add DensityFitting.jl:62-65; block mirror :598-601)
 // =====================================================================================================================
 __global__ void k_fock_epilogue(double* __restrict__ F, const double* __restrict__ H, const double* __restrict__ Jt,
-                                const double* __restrict__ Kpart, const int32_t* __restrict__ tile_index, int N, int nb,
-                                int n_tiles, int n_slices) {
+                                const double* __restrict__ Kpart, const int32_t* __restrict__ tile_index,
+                                const int32_t* __restrict__ perm, int N, int nb, int n_tiles, int n_slices) {
     const int q = blockIdx.x * blockDim.x + threadIdx.x;
     const int p = blockIdx.y;
     if (q > p || p >= N) return;
-    const int ta = p >> 7, tb = q >> 7;
+    // (p, q) in the caller's order -> internal order; K and J are symmetric, so read the (hi, lo) element
+    const int pi = perm[p], qi = perm[q];
+    const int hi = max(pi, qi), lo = min(pi, qi);
+    const int ta = hi >> 7, tb = lo >> 7;
     const int tile = ta * (ta + 1) / 2 + tb;
-    const int64_t off = (int64_t)(p & 127) * 128 + (q & 127);
+    const int64_t off = (int64_t)(hi & 127) * 128 + (lo & 127);
     double k = 0.0;
     for (int s = 0; s < n_slices; s++) k += Kpart[((int64_t)s * n_tiles + tile) * (128 * 128) + off];
     double v = -k;
-    const int ti = tile_index[(p >> 5) * nb + (q >> 5)];
-    if (ti >= 0) v += Jt[(int64_t)ti * TILE_ELEMS + (p & 31) * 32 + swz(p & 31, q & 31)];
+    const int ti = tile_index[(hi >> 5) * nb + (lo >> 5)];
+    if (ti >= 0) v += Jt[(int64_t)ti * TILE_ELEMS + (hi & 31) * 32 + swz(hi & 31, lo & 31)];
     double vpq = v, vqp = v;
     if (H != nullptr) {
         vpq += H[p + (int64_t)N * q];
@@ -461,8 +465,8 @@ __global__ void k_fock_epilogue(double* __restrict__ F, const double* __restrict
 void launch_epilogue(const Layout& L, Shard& s, bool add_H) {
     dim3 block(128);
     dim3 grid((unsigned)((L.N + 127) / 128), (unsigned)L.N);
-    k_fock_epilogue<<<grid, block, 0, s.stream>>>(s.F, add_H ? s.Hdev : nullptr, s.Jt, s.Kpart, s.d_tile_index, (int)L.N,
-                                                  L.nb, s.xplan.n_tiles, s.xplan.n_slices);
+    k_fock_epilogue<<<grid, block, 0, s.stream>>>(s.F, add_H ? s.Hdev : nullptr, s.Jt, s.Kpart, s.d_tile_index, s.d_perm,
+                                                  (int)L.N, L.nb, s.xplan.n_tiles, s.xplan.n_slices);
 }
 
 }  // namespace jcdf

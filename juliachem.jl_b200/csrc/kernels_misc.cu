@@ -67,18 +67,19 @@ __host__ __device__ inline int synth_isum(uint64_t seed, int64_t q_aux, int64_t 
 __global__ void k_fill_synthetic(double* __restrict__ Bp, int64_t row_len, int q_len, int64_t q_begin,
                                  const int32_t* __restrict__ tile_a, const int32_t* __restrict__ tile_b,
                                  const uint8_t* __restrict__ fn_mask, const double* __restrict__ cdec, int N,
-                                 uint64_t seed, int64_t n_tiles) {
+                                 uint64_t seed, int64_t n_tiles, const int32_t* __restrict__ inv) {
     const int c = threadIdx.x & 31;
     const int r0 = threadIdx.x >> 5;
     for (int64_t blk = blockIdx.x; blk < (int64_t)q_len * n_tiles; blk += gridDim.x) {
         const int64_t row = blk / n_tiles;
         const int tile = (int)(blk % n_tiles);
         const int a = tile_a[tile], b = tile_b[tile];
-        const int q = b * 32 + c;
+        const int qi = b * 32 + c;
         for (int r = r0; r < 32; r += blockDim.x >> 5) {
-            const int p = a * 32 + r;
+            const int pi = a * 32 + r;
             double v = 0.0;
-            if (p < N && q < N && (fn_mask == nullptr || fn_mask[p + (int64_t)N * q])) {
+            const int p = pi < N ? inv[pi] : pi, q = qi < N ? inv[qi] : qi;  // the caller's function indices
+            if (pi < N && qi < N && (fn_mask == nullptr || fn_mask[p + (int64_t)N * q])) {
                 const int lo = min(p, q), hi = max(p, q);
                 v = (double)synth_isum(seed, q_begin + row, lo, hi) * cdec[hi - lo];
             }
@@ -106,7 +107,7 @@ void launch_fill_synthetic(const Layout& L, Shard& s, uint64_t seed, double deca
     int grid = (int)std::min<int64_t>(blocks, 148 * 32);
     if (grid > 0)
         k_fill_synthetic<<<grid, 256, 0, s.stream>>>(s.Bp, L.row_len, (int)s.q_len, s.q_begin, s.d_tile_a, s.d_tile_b,
-                                                     s.d_fn_mask, d_cdec, (int)L.N, seed, L.tiles_kept);
+                                                     s.d_fn_mask, d_cdec, (int)L.N, seed, L.tiles_kept, s.d_inv);
     cudaStreamSynchronize(s.stream);
     cudaFree(d_cdec);
 }
