@@ -97,6 +97,7 @@ struct HTParams {
     const int32_t* tile_index;
     const int32_t* kb_list;   // [nb][nb]: the q blocks kb for which tile (max(pb,kb), min(pb,kb)) is stored, ascending
     const int32_t* kb_count;  // [nb]
+    const int32_t* tile_strips;  // [tiles_kept]: bits 0-7 non-empty 4-row strips, bits 8-15 non-empty 4-column strips
     const double* Cs;
     double* W;
     int q_len, nb, n_mt, npt64, occ_pad, n_valid_last;
@@ -112,25 +113,35 @@ struct HTParams {
 // Each consumer warp owns a (BM/2) x 32 block: wm = warp >> 2 selects the M half, j = warp & 3 the auxiliary row of
 // the quad, so a k-step of 4 costs MH + 4 fragment loads for MH * 4 DMMAs.
 template <int MT, bool TRANSPOSED>
-__device__ __forceinline__ void ht_slab(double (&acc)[MT / 2][4][2], const double* __restrict__ sA,
-                                        const double* __restrict__ sB, int m0, int g, int t, int ksteps) {
+__device__ __forceinline__ void ht_kstep(double (&acc)[MT / 2][4][2], const double* __restrict__ sA,
+                                         const double* __restrict__ sB, int m0, int g, int t, int ks) {
     constexpr int BM = 8 * MT;
     constexpr int MH = MT / 2;
+    const int kr = 4 * ks + t;
+    double a[MH], b[4];
+#pragma unroll
+    for (int jm = 0; jm < MH; jm++) a[jm] = sA[kr * BM + ((m0 + 8 * jm + g) ^ (t << 2))];
+#pragma unroll
+    for (int jn = 0; jn < 4; jn++) {
+        const int n = 8 * jn + g;
+        b[jn] = TRANSPOSED ? sB[n * 32 + (kr ^ ((n & 3) << 2))] : sB[kr * 32 + (n ^ (t << 2))];
+    }
+#pragma unroll
+    for (int jm = 0; jm < MH; jm++)
+#pragma unroll
+        for (int jn = 0; jn < 4; jn++) dmma(acc[jm][jn][0], acc[jm][jn][1], a[jm], b[jn]);
+}
+
+// strips: bit ks set = the four k rows 4 ks .. 4 ks + 3 of the tile hold an unscreened pair (empty strips are exact
+// zeros in HBM, so skipping their k-steps changes nothing); 0xFF takes the unrolled path
+template <int MT, bool TRANSPOSED>
+__device__ __forceinline__ void ht_slab(double (&acc)[MT / 2][4][2], const double* __restrict__ sA,
+                                        const double* __restrict__ sB, int m0, int g, int t, uint32_t strips) {
+    if (strips == 0xFFu) {
 #pragma unroll 2
-    for (int ks = 0; ks < ksteps; ks++) {
-        const int kr = 4 * ks + t;
-        double a[MH], b[4];
-#pragma unroll
-        for (int jm = 0; jm < MH; jm++) a[jm] = sA[kr * BM + ((m0 + 8 * jm + g) ^ (t << 2))];
-#pragma unroll
-        for (int jn = 0; jn < 4; jn++) {
-            const int n = 8 * jn + g;
-            b[jn] = TRANSPOSED ? sB[n * 32 + (kr ^ ((n & 3) << 2))] : sB[kr * 32 + (n ^ (t << 2))];
-        }
-#pragma unroll
-        for (int jm = 0; jm < MH; jm++)
-#pragma unroll
-            for (int jn = 0; jn < 4; jn++) dmma(acc[jm][jn][0], acc[jm][jn][1], a[jm], b[jn]);
+        for (int ks = 0; ks < KSLAB / 4; ks++) ht_kstep<MT, TRANSPOSED>(acc, sA, sB, m0, g, t, ks);
+    } else {
+        for (uint32_t m = strips; m; m &= m - 1) ht_kstep<MT, TRANSPOSED>(acc, sA, sB, m0, g, t, __ffs(m) - 1);
     }
 }
 
@@ -177,7 +188,9 @@ __global__ void __launch_bounds__(HT_THREADS, 1) k_half_transform(HTParams prm) 
                 const int kb = kl[s];
                 const int32_t tix = prm.tile_index[max(pb, kb) * nb + min(pb, kb)];
                 mbar_wait(&empty[pp.stage], pp.phase ^ 1u);
-                stage_kb[pp.stage] = kb;
+                // k runs over the tile's rows when kb >= pb (tile (kb, pb) read straight), over its columns otherwise
+                const uint32_t sm = (uint32_t)prm.tile_strips[tix];
+                stage_kb[pp.stage] = kb | (int)(((kb >= pb) ? (sm & 0xFFu) : ((sm >> 8) & 0xFFu)) << 16);
                 double* st = stages + (size_t)pp.stage * STAGE_DOUBLES;
                 mbar_arrive_expect_tx(&full[pp.stage], 32u * BM * 8u + (uint32_t)nq * (TILE_ELEMS * 8u));
                 bulk_g2s(st, prm.Cs + ((int64_t)kb * n_mt + mt) * (32 * BM), 32u * BM * 8u, &full[pp.stage]);
@@ -195,8 +208,6 @@ __global__ void __launch_bounds__(HT_THREADS, 1) k_half_transform(HTParams prm) 
     const int g = lane >> 2, t = lane & 3;
     const int j = warp & 3;                 // auxiliary row inside the quad
     const int m0 = (warp >> 2) * (BM / 2);  // first occupied-orbital row of this warp's half
-    // the last q block holds N - 32 (nb - 1) valid rows: trim its k loop to whole DMMA k-steps (the rest is zero padding)
-    const int last_ksteps = (prm.n_valid_last + 3) >> 2;
     for (int64_t item = blockIdx.x; item < prm.n_items; item += gridDim.x) {
         const int mt = (int)(item % n_mt);
         const int64_t r1 = item / n_mt;
@@ -213,12 +224,13 @@ __global__ void __launch_bounds__(HT_THREADS, 1) k_half_transform(HTParams prm) 
         for (int s = 0; s < nk; s++) {
             mbar_wait(&full[ps.stage], ps.phase);
             if (valid) {
-                const int kb = stage_kb[ps.stage];
+                const int info = stage_kb[ps.stage];
+                const int kb = info & 0xFFFF;
+                const uint32_t strips = (uint32_t)info >> 16;
                 const double* sA = stages + (size_t)ps.stage * STAGE_DOUBLES;
                 const double* sB = sA + 32 * BM + j * TILE_ELEMS;
-                const int ksteps = (kb == nb - 1) ? last_ksteps : KSLAB / 4;
-                if (kb < pb) ht_slab<MT, true>(acc, sA, sB, m0, g, t, ksteps);
-                else ht_slab<MT, false>(acc, sA, sB, m0, g, t, ksteps);
+                if (kb < pb) ht_slab<MT, true>(acc, sA, sB, m0, g, t, strips);
+                else ht_slab<MT, false>(acc, sA, sB, m0, g, t, strips);
             }
             __syncwarp();
             if (lane == 0) mbar_arrive(&empty[ps.stage]);
@@ -264,6 +276,7 @@ void launch_half_transform(const Layout& L, Shard& s, int sm_count) {
     prm.tile_index = s.d_tile_index;
     prm.kb_list = s.d_kb_list;
     prm.kb_count = s.d_kb_count;
+    prm.tile_strips = s.d_tile_strips;
     prm.Cs = s.Cs;
     prm.W = s.W;
     prm.q_len = (int)s.q_len;
