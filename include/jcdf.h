@@ -154,6 +154,12 @@ int32_t jcdf_compute_schwarz_mask(jcdf_handle* h, double sigma, uint8_t* fn_mask
  * Schwarz test dropped are never computed).  Follow with jcdf_factor_and_form_B.                                   */
 int32_t jcdf_compute_three_center(jcdf_handle* h);
 
+/* B = L^-1 (P|mn) for every device of this process with NO exchange between devices or ranks (replaces
+ * the host-staged block exchange of calculate_B_GPU!, GPUDF.jl:918-997, and of the multi-rank CPU path,
+ * ScreenedDF.jl:134-190): each device factors its own copy of the metric and recomputes the raw integrals of the
+ * auxiliary rows h <= its shard in chunks, B_g = sum_h Linv[Q_g, Q_h] T_h.  Works for one process per GPU (torchrun / MPI
+ * ranks), where jcdf_factor_and_form_B cannot reach the other ranks' integrals.  Needs both basis sets and the mask.  */
+int32_t jcdf_compute_B(jcdf_handle* h);
 /* One-electron matrices S, T, V = -sum_C Z_C (m| 1/|r - C| |n) over the primary basis and the nuclear repulsion — what
  * rhf_kernel hands the SCF loop (SCF.jl:100-135; libint one-body engines, deps/src/jeri-oei.hpp).  centers: 3 x natoms
  * column-major, bohr.  Outputs are N x N column-major host buffers (NULL = not wanted); H = T + V.                   */

@@ -61,6 +61,7 @@ SIGNATURES = {
     "jcdf_compute_two_center": (_i32, [_p, _p]),
     "jcdf_compute_schwarz_mask": (_i32, [_p, _f64, _p, C.POINTER(_i64)]),
     "jcdf_compute_three_center": (_i32, [_p]),
+    "jcdf_compute_B": (_i32, [_p]),
     "jcdf_compute_one_electron": (_i32, [_p, _i32, _p, _p, _p, _p, _p, C.POINTER(_f64)]),
     "jcdf_scf_init": (_i32, [_p, _p, _p, _f64, _i32, C.POINTER(_f64)]),
     "jcdf_scf_step": (_i32, [_p, _p]),

@@ -149,6 +149,43 @@ static int ensure_comm(jcdf_handle* h) {
     return JCDF_ERR_INVALID;
 }
 
+// potrf!('L') of s.Metric (Q x Q, lower triangle read) in place and s.Linv = L^-1 by a triangular solve against the
+// identity (same result as trtri!('L','N'), DensityFitting.jl:138-139) on the shard's device and stream.
+int factor_metric_on_device(Shard& s, int64_t Q) {
+    cusolverDnHandle_t sol = nullptr;
+    cublasHandle_t blas = nullptr;
+    JC_CUSOLVER(cusolverDnCreate(&sol));
+    JC_CUSOLVER(cusolverDnSetStream(sol, s.stream));
+    JC_CUBLAS(cublasCreate(&blas));
+    JC_CUBLAS(cublasSetStream(blas, s.stream));
+    int lwork = 0, rc;
+    JC_CUSOLVER(cusolverDnDpotrf_bufferSize(sol, CUBLAS_FILL_MODE_LOWER, (int)Q, s.Metric, (int)Q, &lwork));
+    double* work = nullptr;
+    int* dinfo = nullptr;
+    if ((rc = dev_alloc(&work, (size_t)lwork))) return rc;
+    if ((rc = dev_alloc(&dinfo, 1))) return rc;
+    JC_CUSOLVER(cusolverDnDpotrf(sol, CUBLAS_FILL_MODE_LOWER, (int)Q, s.Metric, (int)Q, work, lwork, dinfo));
+    int info = 0;
+    JC_CUDA(cudaMemcpyAsync(&info, dinfo, sizeof(int), cudaMemcpyDeviceToHost, s.stream));
+    JC_CUDA(cudaStreamSynchronize(s.stream));
+    cudaFree(work);
+    cudaFree(dinfo);
+    if (info != 0) {
+        cusolverDnDestroy(sol);
+        cublasDestroy(blas);
+        set_error("two-centre metric is not positive definite (potrf info = " + std::to_string(info) + ")");
+        return JCDF_ERR_NUMERIC;
+    }
+    launch_set_identity(s.Linv, Q, s.stream);
+    const double one = 1.0;
+    JC_CUBLAS(cublasDtrsm(blas, CUBLAS_SIDE_LEFT, CUBLAS_FILL_MODE_LOWER, CUBLAS_OP_N, CUBLAS_DIAG_NON_UNIT, (int)Q, (int)Q,
+                          &one, s.Metric, (int)Q, s.Linv, (int)Q));
+    JC_CUDA(cudaStreamSynchronize(s.stream));
+    cusolverDnDestroy(sol);
+    cublasDestroy(blas);
+    return JCDF_OK;
+}
+
 // Mask-driven regrouping of the basis functions into 32-wide blocks (internal order only; every C-ABI argument stays
 // in the caller's order).  The Schwarz mask of a real molecule is sparse at the function-pair level, but in the input
 // order (atoms in file order, tight and diffuse shells interleaved) nearly every 32 x 32 tile holds some surviving pair.
@@ -420,6 +457,7 @@ int32_t jcdf_set_mask(jcdf_handle* h, const uint8_t* fn_mask, const int64_t* map
             L.src_of_col[(size_t)col] = L.dest_of_col[(size_t)col];
         }
     L.mask_set = true;
+    integrals_on_set_mask(h);
     for (Shard& s : h->shards) {
         int rc = alloc_shard_buffers(h, s);
         if (rc) return rc;
@@ -577,43 +615,8 @@ int32_t jcdf_factor_and_form_B(jcdf_handle* h) {
     if (!h->metric_on_device)
         JC_CUDA(cudaMemcpyAsync(s0.Metric, h->host_metric.data(), sizeof(double) * Q * Q, cudaMemcpyHostToDevice, s0.stream));
     h->metric_on_device = false;  // potrf overwrites it with L
-    cusolverDnHandle_t sol = nullptr;
-    cublasHandle_t blas = nullptr;
-    JC_CUSOLVER(cusolverDnCreate(&sol));
-    JC_CUSOLVER(cusolverDnSetStream(sol, s0.stream));
-    JC_CUBLAS(cublasCreate(&blas));
-    JC_CUBLAS(cublasSetStream(blas, s0.stream));
-    int lwork = 0;
-    JC_CUSOLVER(cusolverDnDpotrf_bufferSize(sol, CUBLAS_FILL_MODE_LOWER, (int)Q, s0.Metric, (int)Q, &lwork));
-    double* work = nullptr;
-    int* dinfo = nullptr;
-    if ((rc = dev_alloc(&work, (size_t)lwork))) return rc;
-    if ((rc = dev_alloc(&dinfo, 1))) return rc;
-    JC_CUSOLVER(cusolverDnDpotrf(sol, CUBLAS_FILL_MODE_LOWER, (int)Q, s0.Metric, (int)Q, work, lwork, dinfo));
-    int info = 0;
-    JC_CUDA(cudaMemcpyAsync(&info, dinfo, sizeof(int), cudaMemcpyDeviceToHost, s0.stream));
-    JC_CUDA(cudaStreamSynchronize(s0.stream));
-    cudaFree(work);
-    cudaFree(dinfo);
-    if (info != 0) {
-        cusolverDnDestroy(sol);
-        cublasDestroy(blas);
-        set_error("two-centre metric is not positive definite (potrf info = " + std::to_string(info) + ")");
-        return JCDF_ERR_NUMERIC;
-    }
-    // Linv = L^-1: triangular solve against the identity (same result as trtri!('L','N'))
-    {
-        std::vector<double> eye((size_t)Q * Q, 0.0);
-        for (int64_t i = 0; i < Q; i++) eye[(size_t)(i + Q * i)] = 1.0;
-        JC_CUDA(cudaMemcpyAsync(s0.Linv, eye.data(), sizeof(double) * Q * Q, cudaMemcpyHostToDevice, s0.stream));
-        JC_CUDA(cudaStreamSynchronize(s0.stream));
-    }
+    if ((rc = factor_metric_on_device(s0, Q))) return rc;
     const double one = 1.0, zero = 0.0;
-    JC_CUBLAS(cublasDtrsm(blas, CUBLAS_SIDE_LEFT, CUBLAS_FILL_MODE_LOWER, CUBLAS_OP_N, CUBLAS_DIAG_NON_UNIT, (int)Q, (int)Q,
-                          &one, s0.Metric, (int)Q, s0.Linv, (int)Q));
-    JC_CUDA(cudaStreamSynchronize(s0.stream));
-    cusolverDnDestroy(sol);
-    cublasDestroy(blas);
 
     // --- B formation, packed column windows ---------------------------------------------------------------------------
     // Row-major packed rows [q][row_len] viewed column-major are (row_len x q) with ld = row_len, so

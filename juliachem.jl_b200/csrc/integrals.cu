@@ -15,6 +15,8 @@
 #include <cstring>
 #include <vector>
 
+#include <cublas_v2.h>
+
 #include "dmma_common.cuh"
 #include "integrals.cuh"
 #include "jcdf_internal.h"
@@ -46,9 +48,13 @@ struct IntegralsState {
         BasisDev basis[2];
         std::vector<void*> owned;
         double* boys_table = nullptr;
+        int2* d_pairs[4][4] = {};  // primary shell pairs kept by the Schwarz test, by (la, lb) class
+        int n_pairs[4][4] = {};
+        bool pair_lists_stale = true;
     };
     std::vector<Dev> devs;
     std::vector<uint8_t> shell_mask;  // primary shell pairs kept by the Schwarz test (nshell x nshell), empty = all
+    bool in_schwarz = false;          // jcdf_set_mask is being called by jcdf_compute_schwarz_mask (keeps shell_mask)
 };
 
 template <typename T>
@@ -61,12 +67,23 @@ static int ints_upload(IntegralsState::Dev& d, const std::vector<T>& v, const T*
     return JCDF_OK;
 }
 
+// jcdf_set_mask hook: a mask that did not come from jcdf_compute_schwarz_mask invalidates the shell-pair list
+void integrals_on_set_mask(jcdf_handle* h) {
+    IntegralsState* st = h->ints;
+    if (!st) return;
+    if (!st->in_schwarz) st->shell_mask.clear();
+    for (auto& D : st->devs) D.pair_lists_stale = true;
+}
+
 void integrals_destroy(jcdf_handle* h) {
     IntegralsState* st = h->ints;
     if (!st) return;
     for (auto& d : st->devs) {
         cudaSetDevice(d.dev);
         for (void* p : d.owned) cudaFree(p);
+        for (int la = 0; la < 4; la++)
+            for (int lb = 0; lb < 4; lb++)
+                if (d.d_pairs[la][lb]) cudaFree(d.d_pairs[la][lb]);
     }
     delete st;
     h->ints = nullptr;
@@ -549,6 +566,7 @@ int32_t jcdf_set_basis(jcdf_handle* h, int32_t which, int64_t nshell, const int3
     }
     st->host[which] = b;
     st->have[which] = true;
+    for (auto& D : st->devs) D.pair_lists_stale = true;
     int rc = ensure_devices(h, st);
     if (rc) return rc;
     return upload_basis(st, which);
@@ -589,10 +607,14 @@ int32_t jcdf_compute_schwarz_mask(jcdf_handle* h, double sigma, uint8_t* fn_mask
     const int64_t N = h->lay.N, Q = h->lay.Q;
     const int ns = (int)st->host[0].l.size();
     st->shell_mask.clear();
+    for (auto& D : st->devs) D.pair_lists_stale = true;
     if (!(sigma > 0.0)) {  // unscreened: setup_unscreened_screening_matricies (SchwarzScreening.jl:97-111)
         if (fn_mask_out) memset(fn_mask_out, 1, (size_t)N * N);
         if (pairs_kept_out) *pairs_kept_out = N * N;
-        return jcdf_set_mask(h, nullptr, nullptr);
+        st->in_schwarz = true;
+        const int rc0 = jcdf_set_mask(h, nullptr, nullptr);
+        st->in_schwarz = false;
+        return rc0;
     }
     JC_REQUIRE(h->max_PP > 0.0, "jcdf_compute_schwarz_mask: the two-centre metric is needed first (max_P (P|P))");
     Shard& s0 = h->shards[0];
@@ -644,81 +666,168 @@ int32_t jcdf_compute_schwarz_mask(jcdf_handle* h, double sigma, uint8_t* fn_mask
             if (mask[(size_t)q + N * p]) map[(size_t)q + N * p] = idx++;
     if (fn_mask_out) memcpy(fn_mask_out, mask.data(), (size_t)N * N);
     if (pairs_kept_out) *pairs_kept_out = idx - 1;
-    return jcdf_set_mask(h, mask.data(), map.data());
+    st->in_schwarz = true;
+    const int rc1 = jcdf_set_mask(h, mask.data(), map.data());
+    st->in_schwarz = false;
+    return rc1;
+}
+
+// (P|mn) for the auxiliary functions [q_begin, q_begin + q_len) into `dst` ([q_len][row_len], packed layout, zeroed
+// here) on device slot d of the handle; all launches go to the shard's stream, which is synchronised before returning.
+static int three_center_rows(jcdf_handle* h, size_t d, int64_t q_begin, int64_t q_len, double* dst) {
+    IntegralsState* st = h->ints;
+    const Layout& L = h->lay;
+    const IntegralsState::Basis& pb = st->host[0];
+    const IntegralsState::Basis& ab = st->host[1];
+    const int ns = (int)pb.l.size();
+    Shard& s = h->shards[d];
+    IntegralsState::Dev& D = st->devs[d];
+    JC_CUDA(cudaSetDevice(s.dev));
+    JC_CUDA(cudaMemsetAsync(dst, 0, sizeof(double) * (size_t)q_len * (size_t)L.row_len, s.stream));
+    if (q_len == 0) return JCDF_OK;
+    // primary shell pairs by (la, lb) class; pairs the Schwarz test dropped as a whole are never computed
+    if (D.pair_lists_stale) {
+        for (int la = 0; la < 4; la++)
+            for (int lb = 0; lb < 4; lb++) {
+                if (D.d_pairs[la][lb]) cudaFree(D.d_pairs[la][lb]);
+                D.d_pairs[la][lb] = nullptr;
+                D.n_pairs[la][lb] = 0;
+            }
+        std::vector<int2> cls[4][4];
+        for (int i = 0; i < ns; i++)
+            for (int j = 0; j <= i; j++) {
+                if (!st->shell_mask.empty() && !st->shell_mask[(size_t)i * ns + j]) continue;
+                cls[pb.l[i]][pb.l[j]].push_back(make_int2(i, j));
+            }
+        for (int la = 0; la < 4; la++)
+            for (int lb = 0; lb < 4; lb++) {
+                const std::vector<int2>& pr = cls[la][lb];
+                if (pr.empty()) continue;
+                JC_CUDA(cudaMalloc(reinterpret_cast<void**>(&D.d_pairs[la][lb]), sizeof(int2) * pr.size()));
+                JC_CUDA(cudaMemcpy(D.d_pairs[la][lb], pr.data(), sizeof(int2) * pr.size(), cudaMemcpyHostToDevice));
+                D.n_pairs[la][lb] = (int)pr.size();
+            }
+        D.pair_lists_stale = false;
+    }
+    std::vector<int> aux_by_l[5];
+    for (size_t c = 0; c < ab.l.size(); c++) {
+        const int64_t f0 = ab.fn_off[c], f1 = f0 + ncart(ab.l[c]);
+        if (f1 > q_begin && f0 < q_begin + q_len) aux_by_l[ab.l[c]].push_back((int)c);
+    }
+    std::vector<void*> tmp;
+    for (int lc = 0; lc < 5; lc++) {
+        const std::vector<int>& ax = aux_by_l[lc];
+        if (ax.empty()) continue;
+        int* d_aux = nullptr;
+        JC_CUDA(cudaMalloc(reinterpret_cast<void**>(&d_aux), sizeof(int) * ax.size()));
+        tmp.push_back(d_aux);
+        JC_CUDA(cudaMemcpyAsync(d_aux, ax.data(), sizeof(int) * ax.size(), cudaMemcpyHostToDevice, s.stream));
+        for (int la = 0; la < 4; la++)
+            for (int lb = 0; lb < 4; lb++) {
+                if (D.n_pairs[la][lb] == 0) continue;
+                ThreeCenterArgs a;
+                a.prim = D.basis[0];
+                a.aux = D.basis[1];
+                a.pairs = D.d_pairs[la][lb];
+                a.npairs = D.n_pairs[la][lb];
+                a.aux_shells = d_aux;
+                a.naux = (int)ax.size();
+                a.la = la; a.lb = lb; a.lc = lc;
+                a.boys_table = D.boys_table;
+                a.Bp = dst;
+                a.row_len = L.row_len;
+                a.q_begin = q_begin;
+                a.q_len = q_len;
+                a.tile_index = s.d_tile_index;
+                a.fn_mask = s.d_fn_mask;
+                a.perm = s.d_perm;
+                a.N = (int)L.N;
+                a.nb = L.nb;
+                const int Lab = la + lb, Lt = Lab + lc;
+                if (Lab <= 2 && Lt <= 6) launch_three_center_t<2, 6, 128>(a, s.stream);
+                else if (Lab <= 4 && Lt <= 8) launch_three_center_t<4, 8, 384>(a, s.stream);
+                else launch_three_center_t<6, 10, 400>(a, s.stream);
+                JC_CUDA(cudaGetLastError());
+            }
+    }
+    JC_CUDA(cudaStreamSynchronize(s.stream));
+    for (void* p : tmp) cudaFree(p);
+    return JCDF_OK;
 }
 
 int32_t jcdf_compute_three_center(jcdf_handle* h) {
     JC_REQUIRE(h != nullptr, "jcdf_compute_three_center: NULL handle");
     IntegralsState* st = h->ints;
     JC_REQUIRE(st && st->have[0] && st->have[1], "jcdf_compute_three_center: call jcdf_set_basis for both basis sets first");
-    const Layout& L = h->lay;
-    JC_REQUIRE(L.mask_set, "jcdf_compute_three_center: call jcdf_set_mask or jcdf_compute_schwarz_mask first");
-    const IntegralsState::Basis& pb = st->host[0];
-    const IntegralsState::Basis& ab = st->host[1];
-    const int ns = (int)pb.l.size();
-    // primary shell pairs by (la, lb) class; pairs the Schwarz test dropped as a whole are never computed
-    std::vector<int2> cls[4][4];
-    for (int i = 0; i < ns; i++)
-        for (int j = 0; j <= i; j++) {
-            if (!st->shell_mask.empty() && !st->shell_mask[(size_t)i * ns + j]) continue;
-            cls[pb.l[i]][pb.l[j]].push_back(make_int2(i, j));
-        }
+    JC_REQUIRE(h->lay.mask_set, "jcdf_compute_three_center: call jcdf_set_mask or jcdf_compute_schwarz_mask first");
     for (size_t d = 0; d < h->shards.size(); d++) {
         Shard& s = h->shards[d];
-        IntegralsState::Dev& D = st->devs[d];
-        JC_CUDA(cudaSetDevice(s.dev));
-        JC_CUDA(cudaMemsetAsync(s.Bp, 0, sizeof(double) * (size_t)s.q_len * (size_t)L.row_len, s.stream));
-        if (s.q_len == 0) { s.t_uploaded = true; s.b_ready = false; continue; }
-        std::vector<int> aux_by_l[5];
-        for (size_t c = 0; c < ab.l.size(); c++) {
-            const int64_t f0 = ab.fn_off[c], f1 = f0 + ncart(ab.l[c]);
-            if (f1 > s.q_begin && f0 < s.q_begin + s.q_len) aux_by_l[ab.l[c]].push_back((int)c);
-        }
-        std::vector<void*> tmp;
-        for (int la = 0; la < 4; la++)
-            for (int lb = 0; lb < 4; lb++) {
-                const std::vector<int2>& pr = cls[la][lb];
-                if (pr.empty()) continue;
-                int2* d_pairs = nullptr;
-                JC_CUDA(cudaMalloc(reinterpret_cast<void**>(&d_pairs), sizeof(int2) * pr.size()));
-                tmp.push_back(d_pairs);
-                JC_CUDA(cudaMemcpyAsync(d_pairs, pr.data(), sizeof(int2) * pr.size(), cudaMemcpyHostToDevice, s.stream));
-                for (int lc = 0; lc < 5; lc++) {
-                    const std::vector<int>& ax = aux_by_l[lc];
-                    if (ax.empty()) continue;
-                    int* d_aux = nullptr;
-                    JC_CUDA(cudaMalloc(reinterpret_cast<void**>(&d_aux), sizeof(int) * ax.size()));
-                    tmp.push_back(d_aux);
-                    JC_CUDA(cudaMemcpyAsync(d_aux, ax.data(), sizeof(int) * ax.size(), cudaMemcpyHostToDevice, s.stream));
-                    ThreeCenterArgs a;
-                    a.prim = D.basis[0];
-                    a.aux = D.basis[1];
-                    a.pairs = d_pairs;
-                    a.npairs = (int)pr.size();
-                    a.aux_shells = d_aux;
-                    a.naux = (int)ax.size();
-                    a.la = la; a.lb = lb; a.lc = lc;
-                    a.boys_table = D.boys_table;
-                    a.Bp = s.Bp;
-                    a.row_len = L.row_len;
-                    a.q_begin = s.q_begin;
-                    a.q_len = s.q_len;
-                    a.tile_index = s.d_tile_index;
-                    a.fn_mask = s.d_fn_mask;
-                    a.perm = s.d_perm;
-                    a.N = (int)L.N;
-                    a.nb = L.nb;
-                    const int Lab = la + lb, Lt = Lab + lc;
-                    if (Lab <= 2 && Lt <= 6) launch_three_center_t<2, 6, 128>(a, s.stream);
-                    else if (Lab <= 4 && Lt <= 8) launch_three_center_t<4, 8, 384>(a, s.stream);
-                    else launch_three_center_t<6, 10, 400>(a, s.stream);
-                    JC_CUDA(cudaGetLastError());
-                }
-            }
-        JC_CUDA(cudaStreamSynchronize(s.stream));
-        for (void* p : tmp) cudaFree(p);
+        int rc = three_center_rows(h, d, s.q_begin, s.q_len, s.Bp);
+        if (rc) return rc;
         s.t_uploaded = true;
         s.b_ready = false;
+    }
+    return JCDF_OK;
+}
+
+// B = L^-1 (P|mn) per device without any exchange between devices or ranks: every device factors its
+// own copy of the (cheap) metric and RECOMPUTES the raw integrals of the auxiliary rows h <= its shard in chunks,
+//     B_g = sum_h Linv[Q_g, Q_h] T_h ,
+// instead of staging T blocks through host memory (calculate_B_GPU!, GPUDF.jl:918-997; ScreenedDF.jl:134-190).  The
+// three-centre integrals of all of w50 cost 0.25 s on one B200 — far less than moving them — so this also covers
+// one-process-per-GPU runs, where jcdf_factor_and_form_B cannot see the other ranks' T.
+int32_t jcdf_compute_B(jcdf_handle* h) {
+    JC_REQUIRE(h != nullptr, "jcdf_compute_B: NULL handle");
+    IntegralsState* st = h->ints;
+    JC_REQUIRE(st && st->have[0] && st->have[1], "jcdf_compute_B: call jcdf_set_basis for both basis sets first");
+    const Layout& L = h->lay;
+    JC_REQUIRE(L.mask_set, "jcdf_compute_B: call jcdf_set_mask or jcdf_compute_schwarz_mask first");
+    const int64_t Q = L.Q;
+    const double one = 1.0, zero = 0.0;
+    for (size_t d = 0; d < h->shards.size(); d++) {
+        Shard& s = h->shards[d];
+        JC_CUDA(cudaSetDevice(s.dev));
+        if (s.q_len == 0) { s.b_ready = true; continue; }
+        // ---- metric, potrf('L'), Linv on this device ----
+        if (!s.Metric) JC_CUDA(cudaMalloc(reinterpret_cast<void**>(&s.Metric), sizeof(double) * Q * Q));
+        if (!s.Linv) JC_CUDA(cudaMalloc(reinterpret_cast<void**>(&s.Linv), sizeof(double) * Q * Q));
+        TwoCenterArgs ta;
+        ta.aux = st->devs[d].basis[1];
+        ta.boys_table = st->devs[d].boys_table;
+        ta.J = s.Metric;
+        ta.Q = (int)Q;
+        const int64_t npairs = (int64_t)ta.aux.nshell * (ta.aux.nshell + 1) / 2;
+        k_two_center<<<(unsigned)((npairs + INT_THREADS - 1) / INT_THREADS), INT_THREADS, 0, s.stream>>>(ta);
+        JC_CUDA(cudaGetLastError());
+        if (d == 0) h->metric_on_device = false;  // consumed below
+        int rc = factor_metric_on_device(s, Q);
+        if (rc) return rc;
+        // ---- B_g += Linv[Q_g, chunk] T_chunk over the rows h < q_begin + q_len ----
+        const int64_t q_end = s.q_begin + s.q_len;
+        int64_t R = std::max<int64_t>(32, std::min<int64_t>(q_end, ((int64_t)3 << 27) / std::max<int64_t>(L.row_len, 1)));  // <= 3 GiB
+        double* T = nullptr;
+        JC_CUDA(cudaMalloc(reinterpret_cast<void**>(&T), sizeof(double) * (size_t)R * (size_t)L.row_len));
+        cublasHandle_t blas = nullptr;
+        JC_CUBLAS(cublasCreate(&blas));
+        JC_CUBLAS(cublasSetStream(blas, s.stream));
+        bool first = true;
+        for (int64_t h0 = 0; h0 < q_end; h0 += R) {
+            const int64_t rows = std::min(R, q_end - h0);
+            if ((rc = three_center_rows(h, d, h0, rows, T))) return rc;
+            // packed rows [q][row_len] viewed column-major are (row_len x q): Bp^T += T^T Linv[Q_g, chunk]^T, in column
+            // windows so that every GEMM dimension fits cuBLAS' 32-bit interface
+            for (int64_t c0 = 0; c0 < L.row_len; c0 += (int64_t)1 << 30) {
+                const int64_t w = std::min<int64_t>((int64_t)1 << 30, L.row_len - c0);
+                JC_CUBLAS(cublasDgemm(blas, CUBLAS_OP_N, CUBLAS_OP_T, (int)w, (int)s.q_len, (int)rows, &one, T + c0, (int)L.row_len,
+                                      s.Linv + s.q_begin + Q * h0, (int)Q, first ? &zero : &one, s.Bp + c0, (int)L.row_len));
+            }
+            first = false;
+        }
+        JC_CUDA(cudaStreamSynchronize(s.stream));
+        cublasDestroy(blas);
+        cudaFree(T);
+        s.t_uploaded = false;
+        s.b_ready = true;
     }
     return JCDF_OK;
 }

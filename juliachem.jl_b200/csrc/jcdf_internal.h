@@ -130,6 +130,9 @@ int kernels_per_build();
 void set_error(const std::string& msg);
 void scf_destroy(jcdf_handle* h);        // scf.cu
 void integrals_destroy(jcdf_handle* h);  // integrals.cu
+void integrals_on_set_mask(jcdf_handle* h);
+int factor_metric_on_device(Shard& s, int64_t Q);  // api.cu
+void launch_set_identity(double* A, int64_t n, cudaStream_t st);  // kernels_misc.cu
 
 }  // namespace jcdf
 

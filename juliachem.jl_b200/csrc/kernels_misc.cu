@@ -30,6 +30,14 @@ void launch_scatter_pairs(const Layout& L, Shard& s, const double* T_dev, int64_
                                                   L.row_len);
 }
 
+__global__ void k_set_identity(double* __restrict__ A, int64_t n) {
+    const int64_t idx = blockIdx.x * (int64_t)blockDim.x + threadIdx.x;
+    if (idx < n * n) A[idx] = (idx / n == idx % n) ? 1.0 : 0.0;
+}
+void launch_set_identity(double* A, int64_t n, cudaStream_t st) {
+    k_set_identity<<<(unsigned)((n * n + 255) / 256), 256, 0, st>>>(A, n);
+}
+
 // inverse of k_scatter_pairs for introspection (jcdf_get_B): T_dev[q + ld * c] = Bp[q][src_of_col[col_begin + c]]
 __global__ void k_gather_pairs(double* __restrict__ T_dev, int64_t ld, int64_t col_begin, int64_t col_count, int q_len,
                                const int64_t* __restrict__ src_of_col, const double* __restrict__ Bp, int64_t row_len) {

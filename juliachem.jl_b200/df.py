@@ -262,6 +262,10 @@ class B200Data:
         """calculate_three_center_integrals (ThreeCenterIntegrals.jl:9) straight into the packed Q shards."""
         check(self._lib.jcdf_compute_three_center(self._h))
 
+    def compute_B(self) -> None:
+        """B = L^-1 (P|mn) per device by recomputing integrals instead of exchanging them (jcdf_compute_B)."""
+        check(self._lib.jcdf_compute_B(self._h))
+
     def compute_one_electron(self, charges, centers):
         """S, T, V and E_nuc on the device (rhf_kernel's one-electron set-up, SCF.jl:100-135).  centers (natoms, 3) bohr."""
         Z = np.ascontiguousarray(charges, dtype=np.float64)

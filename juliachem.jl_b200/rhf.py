@@ -115,12 +115,17 @@ def run_energy(mol: dict, scf_flags: dict | None = None, num_devices: int = 1, k
     t0 = time.perf_counter()
     mask, P = gd.compute_schwarz_mask(f["df_sigma"])
     clock("schwarz", t0)
-    t0 = time.perf_counter()
-    gd.compute_three_center()
-    clock("three_center", t0)
-    t0 = time.perf_counter()
-    gd.factor_and_form_B()
-    clock("form_B", t0)
+    if f.get("b_formation", "exchange") == "recompute":
+        t0 = time.perf_counter()
+        gd.compute_B()
+        clock("form_B", t0)
+    else:
+        t0 = time.perf_counter()
+        gd.compute_three_center()
+        clock("three_center", t0)
+        t0 = time.perf_counter()
+        gd.factor_and_form_B()
+        clock("form_B", t0)
     t0 = time.perf_counter()
     gd.scf_init(S, H, E_nuc, f["ndiis"])
     clock("scf_init", t0)

@@ -19,7 +19,8 @@ def main():
     geo = json.load(open(os.path.join(ROOT, "tests", "golden", "w50_geometry.json")))
     mol = rhf.run_basis({"geometry": geo["geometry"][:9 * n], "symbols": geo["symbols"][:3 * n], "molecular_charge": 0},
                         {"basis": "cc-pVDZ"})
-    res = rhf.run_energy(mol, {"df_sigma": sigma}, num_devices=ndev)
+    mode = sys.argv[4] if len(sys.argv) > 4 else "exchange"
+    res = rhf.run_energy(mol, {"df_sigma": sigma, "b_formation": mode}, num_devices=ndev)
     li = res["layout"]
     t = res["Timings"]
     fock = [v for k, v in t["jc"].items() if k.startswith("fock_time")]
