@@ -23,14 +23,20 @@ class Workload:
     cutoff: float        # kept iff centre distance <= cutoff (in units of the nearest-neighbour spacing); 0 = keep all
     decay_length: float  # index-distance decay of the synthetic B values (0 = none)
     seed: int
+    real_molecules: int = 0  # > 0: the first n molecules of tests/golden/w50_geometry.json with REAL cc-pVDZ/cc-pVDZ-RIFIT
+                             # integrals computed on the device (mask from the reference's Schwarz rule, df_sigma = 1e-5)
 
 
 WORKLOADS = {
     "water": Workload("water", "water DF-RHF cc-pVDZ / cc-pVDZ-RI single SCF", 25, 96, 5, "none", 1, 0.0, 0.0, 1001),
     "benzene_dimer": Workload("benzene_dimer", "S22 benzene dimer DF-RHF cc-pVTZ / cc-pVTZ-RI on 1 B200", 600, 1632, 42,
                               "none", 12, 0.0, 0.0, 1002),
-    "w50": Workload("w50", "w50 water cluster DF-RHF cc-pVDZ Q-sharded at 1/2/4/8 B200", 1250, 4800, 250, "none", 50,
-                    0.0, 400.0, 1003),
+    # the configuration BASELINE.json's metric is quoted on, with its real integrals and real Schwarz mask
+    "w50": Workload("w50", "w50 water cluster DF-RHF cc-pVDZ Q-sharded at 1/2/4/8 B200", 1250, 4800, 250, "real", 50,
+                    0.0, 0.0, 1003, real_molecules=50),
+    # same shape, synthetic B with no screening at all (upper bound of the work: every pair kept)
+    "w50_dense": Workload("w50_dense", "w50 water cluster DF-RHF cc-pVDZ shape, synthetic unscreened B", 1250, 4800, 250,
+                          "none", 50, 0.0, 400.0, 1003),
     "w50_screened": Workload("w50_screened", "w50 water cluster DF-RHF cc-pVDZ, Schwarz mask", 1250, 4800, 250,
                              "cluster", 50, 2.6, 400.0, 1013),
     # one rank's share of w50 when Q is sharded over 8 GPUs (profiling stand-in for the 8-GPU per-device work)
@@ -69,6 +75,8 @@ def screening_mask(w: Workload):
     """Symmetric Bool (N, N) column-major mask with the diagonal kept, or None for unscreened workloads.
     Kept iff the two functions' sites are within `cutoff`; pairs in the outer 15 % shell of the cutoff are thinned by
     a symmetric hash (the speckle at the band edge seen in the reference's C20H42_screening_matrix.png)."""
+    if w.real_molecules:
+        return real_mask(w)
     if w.geometry == "none" or w.cutoff <= 0:
         return None
     x = function_centres(w)
@@ -81,6 +89,28 @@ def screening_mask(w: Workload):
     keep &= ~(edge & ((h & np.uint64(3)) == 0))
     np.fill_diagonal(keep, True)
     return np.asfortranarray(keep)
+
+
+def real_molecule(w: Workload) -> dict:
+    """JSON-contract molecule object of a real workload (first n waters of the reference's w50 input)."""
+    import json
+    import os
+    root = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+    geo = json.load(open(os.path.join(root, "tests", "golden", "w50_geometry.json")))
+    n = w.real_molecules
+    return {"geometry": geo["geometry"][:9 * n], "symbols": geo["symbols"][:3 * n], "molecular_charge": 0}
+
+
+def real_mask(w: Workload):
+    """The Schwarz mask libjcdf computes for the real w50 (df_sigma = 1e-5), committed as a fixture so the CPU legs of
+    bench.py can run without a GPU (tests/golden/w50_mask_sigma1e-5.npy, made by tools/dump_w50_mask.py)."""
+    import os
+    root = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+    if w.real_molecules != 50:
+        raise ValueError("only the 50-molecule mask is committed")
+    bits = np.load(os.path.join(root, "tests", "golden", "w50_mask_sigma1e-5.npy"))
+    m = np.unpackbits(bits)[:w.N * w.N].reshape(w.N, w.N).astype(bool)
+    return np.asfortranarray(m)
 
 
 def occupied_coefficients(w: Workload, seed_offset: int = 0) -> np.ndarray:
