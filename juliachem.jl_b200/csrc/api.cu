@@ -768,6 +768,10 @@ int fock_build_impl(jcdf_handle* h, const double* C_occ, int64_t ldc, const doub
             JC_NCCL(n.AllReduce(s.F, s.F, nn, NCCL_DOUBLE, NCCL_SUM, s.nccl_comm, s.stream));
         }
         JC_NCCL(n.GroupEnd());
+        for (int d = 0; d < nd; d++) {
+            JC_CUDA(cudaSetDevice(h->shards[d].dev));
+            launch_mirror_lower(L, h->shards[d]);
+        }
     }
     for (int d = 0; d < nd; d++) {
         Shard& s = h->shards[d];
@@ -911,7 +915,8 @@ int32_t jcdf_get_layout(jcdf_handle* h, jcdf_layout_info* o) {
         o->bytes_W += (int64_t)s.xplan.chunks * L.npt64 * 2048 * 8;
     }
     // prep_cs, density, half_transform, exchange, coulomb (fused: 1, two-pass: 2), epilogue
-    o->kernel_launches_per_build = (!h->shards.empty() && h->shards[0].last_coulomb_fused) ? 6 : 7;
+    o->kernel_launches_per_build = ((!h->shards.empty() && h->shards[0].last_coulomb_fused) ? 6 : 7) +
+                                   ((h->n_ranks * (int)h->shards.size() > 1) ? 1 : 0);  // + mirror after the all-reduce
     return JCDF_OK;
 }
 

@@ -118,6 +118,7 @@ void launch_exchange(const Layout& L, Shard& s, int sm_count);
 void launch_coulomb(const Layout& L, Shard& s, int sm_count, cudaStream_t st);
 bool launch_coulomb_fused(const Layout& L, Shard& s, int sm_count, cudaStream_t st);
 void launch_epilogue(const Layout& L, Shard& s, bool add_H);
+void launch_mirror_lower(const Layout& L, Shard& s);
 void launch_scatter_pairs(const Layout& L, Shard& s, const double* T_dev, int64_t ld, int64_t col_begin,
                           int64_t col_count);
 void launch_gather_pairs(const Layout& L, Shard& s, double* T_dev, int64_t ld, int64_t col_begin, int64_t col_count,

@@ -475,6 +475,21 @@ __global__ void k_fock_epilogue(double* __restrict__ F, const double* __restrict
     F[q + (int64_t)N * p] = vqp;
 }
 
+// After the all-reduce: NCCL may sum F[p,q] and F[q,p] over the ranks in different orders (ring chunks), so the two can
+// differ in the last bit; copy the lower triangle over the upper one to keep F exactly symmetric on every rank
+// (the reference mirrors explicitly too: ScreenedDF.jl:375, :596-601).
+__global__ void k_mirror_lower(double* __restrict__ F, int N) {
+    const int q = blockIdx.x * blockDim.x + threadIdx.x;
+    const int p = blockIdx.y;
+    if (q < p && p < N) F[q + (int64_t)N * p] = F[p + (int64_t)N * q];
+}
+
+void launch_mirror_lower(const Layout& L, Shard& s) {
+    dim3 block(128);
+    dim3 grid((unsigned)((L.N + 127) / 128), (unsigned)L.N);
+    k_mirror_lower<<<grid, block, 0, s.stream>>>(s.F, (int)L.N);
+}
+
 void launch_epilogue(const Layout& L, Shard& s, bool add_H) {
     dim3 block(128);
     dim3 grid((unsigned)((L.N + 127) / 128), (unsigned)L.N);
