@@ -260,3 +260,58 @@ def test_multi_device_B_formation():
     F, _ = gd.fock_build(C_occ, H)
     assert np.abs(F - F_ref).max() < TOL
     gd.close()
+
+
+def _scattered_mask(N, n_sites, reach, seed):
+    """Functions dealt to sites in an interleaved order (like atoms in file order with tight and diffuse shells mixed):
+    sparse at the pair level, but in the input order nearly every 32 x 32 tile holds a kept pair."""
+    rng = np.random.default_rng(seed)
+    site = rng.integers(0, n_sites, size=N)
+    extent = rng.choice([0, 1, 3], size=N, p=[0.5, 0.35, 0.15])  # tight / medium / diffuse functions
+    d = np.abs(site[:, None] - site[None, :])
+    m = d <= np.minimum(extent[:, None], extent[None, :]) * reach + (extent[:, None] + extent[None, :] > 2)
+    np.fill_diagonal(m, True)
+    return np.asfortranarray(m | m.T)
+
+
+@pytest.mark.parametrize("regroup", [1, 0])
+@pytest.mark.parametrize("N,Q,occ", [(200, 48, 21), (333, 37, 40)])
+def test_regrouped_layout_is_exact(N, Q, occ, regroup):
+    """Mask-driven regrouping of the basis functions (internal order only): same Fock matrix to 1e-10, fewer stored
+    tiles; uploads, the packed round trip (jcdf_get_B) and the epilogue all go through the permutation."""
+    mask = _scattered_mask(N, 23, 1, seed=N)
+    B, C_occ, H = random_inputs(N, Q, occ, seed=N + 3, mask=mask)
+    F_ref = oracle_fock(B, C_occ, H, mask)
+    gd = jc.B200Data(N, Q, occ, 1)
+    gd.set_option("regroup", regroup)
+    gd.set_mask(jc.ScreeningData(mask, N))
+    rows = reference_layout_rows(B, range(0, Q), mask)
+    gd.set_B(0, rows)
+    li = gd.layout()
+    assert np.array_equal(gd.get_B(0, Q, li.pairs_kept), rows)  # bit-exact round trip through the packed layout
+    F, _ = gd.fock_build(C_occ, H)
+    assert np.abs(F - F_ref).max() < TOL
+    assert np.array_equal(F, F.T)
+    tiles = li.tiles_kept
+    gd.close()
+    if regroup:
+        gd0 = jc.B200Data(N, Q, occ, 1)
+        gd0.set_option("regroup", 0)
+        gd0.set_mask(jc.ScreeningData(mask, N))
+        assert tiles < gd0.layout().tiles_kept
+        gd0.close()
+
+
+def test_regrouped_synthetic_fill_matches_host_twin():
+    """jcdf_fill_synthetic_B writes through the permutation: the packed shard read back in reference order equals the
+    host twin value for value."""
+    w = wl.WORKLOADS["small"]
+    mask = _scattered_mask(w.N, 17, 1, seed=4)
+    gd = jc.B200Data(w.N, w.Q, w.occ, 1)
+    gd.set_mask(jc.ScreeningData(mask, w.N))
+    gd.fill_synthetic_B(w.seed, w.decay_length)
+    P = int(mask.sum())
+    got = gd.get_B(0, w.Q, P)
+    ref = reference_layout_rows(wl.synthetic_B_rows(w, range(0, w.Q), mask), range(0, w.Q), mask)
+    assert np.array_equal(got, ref)
+    gd.close()
