@@ -33,7 +33,7 @@ static int dev_alloc(T** p, size_t count) {
 // keep_metric: the two-centre metric / its inverse factor do not depend on the mask (jcdf_set_mask keeps them)
 static void free_shard_buffers(Shard& s, bool keep_metric = false) {
     cudaSetDevice(s.dev);
-    void* ptrs[] = {s.Vpart, s.Vready, s.Bp, s.W, s.Cs, s.Craw, s.dt, s.Jt, s.V, s.Kpart, s.F, s.Hdev, s.Traw, s.d_tile_index, s.d_tile_a,
+    void* ptrs[] = {s.Bc, s.Ci, s.d_pp_off, s.d_pp_q, s.d_pp_src, s.Vpart, s.Vready, s.Bp, s.W, s.Cs, s.Craw, s.dt, s.Jt, s.V, s.Kpart, s.F, s.Hdev, s.Traw, s.d_tile_index, s.d_tile_a,
                     s.d_tile_b, s.d_dest_of_col, s.d_fn_mask, s.d_kb_list, s.d_kb_count, s.d_perm, s.d_inv, s.d_tile_strips};
     for (void* p : ptrs)
         if (p) cudaFree(p);
@@ -46,6 +46,10 @@ static void free_shard_buffers(Shard& s, bool keep_metric = false) {
     s.d_tile_index = s.d_tile_a = s.d_tile_b = s.d_kb_list = s.d_kb_count = s.d_perm = s.d_inv = s.d_tile_strips = nullptr;
     s.Vpart = nullptr;
     s.Vready = nullptr;
+    s.Bc = s.Ci = nullptr;
+    s.d_pp_off = s.d_pp_q = s.d_pp_src = nullptr;
+    s.pp_chunks = 0;
+    s.bc_valid = false;
     s.d_dest_of_col = nullptr;
     s.d_fn_mask = nullptr;
     s.traw_capacity = 0;
@@ -74,7 +78,7 @@ static void plan_exchange(const Layout& L, Shard& s, int sm_count) {
 }
 
 static int alloc_shard_buffers(jcdf_handle* h, Shard& s) {
-    const Layout& L = h->lay;
+    Layout& L = h->lay;
     JC_CUDA(cudaSetDevice(s.dev));
     plan_exchange(L, s, h->sm_count);
     int rc;
@@ -116,6 +120,31 @@ static int alloc_shard_buffers(jcdf_handle* h, Shard& s) {
                             s.stream));
     JC_CUDA(cudaMemcpyAsync(s.d_dest_of_col, L.dest_of_col.data(), sizeof(int64_t) * L.dest_of_col.size(),
                             cudaMemcpyHostToDevice, s.stream));
+    if (L.pp_enabled) {
+        // partner-compacted copy of the shard for the per-function half-transform (kernels_pp.cu)
+        s.pp_chunks = (int)((s.q_len + 127) / 128);
+        const size_t nBc = (size_t)s.pp_chunks * (size_t)L.pp_rows * 128;
+        cudaError_t e = cudaMalloc(reinterpret_cast<void**>(&s.Bc), std::max<size_t>(nBc, 1) * sizeof(double));
+        if (e != cudaSuccess) {
+            cudaGetLastError();
+            s.Bc = nullptr;
+            if (h->opt_ht_mode == 2) {
+                set_error("out of device memory for the partner-compacted copy of B (ht_mode = 2)");
+                return JCDF_ERR_CUDA;
+            }
+            L.pp_enabled = false;  // automatic choice: fall back to the tile kernel on every shard
+        } else {
+            const int ldci = L.pp_n_nt * 32 * L.pp_nt;
+            if ((rc = dev_alloc(&s.Ci, (size_t)(L.n_pad + 1) * ldci))) return rc;
+            if ((rc = dev_alloc(&s.d_pp_off, L.pp_off.size()))) return rc;
+            if ((rc = dev_alloc(&s.d_pp_q, L.pp_q.size()))) return rc;
+            if ((rc = dev_alloc(&s.d_pp_src, L.pp_src.size()))) return rc;
+            JC_CUDA(cudaMemcpyAsync(s.d_pp_off, L.pp_off.data(), sizeof(int32_t) * L.pp_off.size(), cudaMemcpyHostToDevice, s.stream));
+            JC_CUDA(cudaMemcpyAsync(s.d_pp_q, L.pp_q.data(), sizeof(int32_t) * L.pp_q.size(), cudaMemcpyHostToDevice, s.stream));
+            JC_CUDA(cudaMemcpyAsync(s.d_pp_src, L.pp_src.data(), sizeof(int32_t) * L.pp_src.size(), cudaMemcpyHostToDevice, s.stream));
+        }
+    }
+    s.bc_valid = false;
     JC_CUDA(cudaStreamSynchronize(s.stream));
     return JCDF_OK;
 }
@@ -234,6 +263,74 @@ static void regroup_functions(const uint8_t* fn_mask, int64_t N, std::vector<int
             for (int64_t w = 0; w < nw; w++) uni[(size_t)w] |= rows[(size_t)(best * nw + w)];
         }
     }
+}
+
+// Partner lists of the per-function half-transform (kernels_pp.cu): for every function p, in internal order, the kept
+// partners q ascending, padded to a multiple of four rows, with the offset of B[Q, p, q] inside a tile-packed row.
+// Chooses between the two half-transform kernels from the DMMA k-steps each would execute on this mask.
+template <typename Kept>
+static void build_partner_lists(jcdf_handle* h, Kept kept) {
+    Layout& L = h->lay;
+    const int64_t N = L.N;
+    const int nb = L.nb;
+    L.pp_enabled = false;
+    L.pp_off.clear(); L.pp_q.clear(); L.pp_src.clear(); L.pp_tri.clear();
+    L.pp_rows = 0;
+    // occupied-orbital tiling: 4 consumer warps across n, each 8 * pp_nt wide, pp_nt <= 4
+    const int n8 = L.occ_pad / 8;
+    L.pp_n_nt = (n8 + 15) / 16;
+    L.pp_nt = ((n8 + L.pp_n_nt - 1) / L.pp_n_nt + 3) / 4;
+    if (h->opt_ht_mode == 1 || L.row_len >= ((int64_t)1 << 31)) return;
+    // executed multiply-adds per auxiliary row of either kernel
+    double cost_tiles = 0.0;
+    for (int pb = 0; pb < nb; pb++)
+        for (int x = 0; x < L.kb_count[pb]; x++) {
+            const int kb = L.kb_list[(size_t)pb * nb + x];
+            const uint32_t sm = (uint32_t)L.tile_strips[(size_t)L.tile_index[(size_t)std::max(pb, kb) * nb + std::min(pb, kb)]];
+            cost_tiles += __builtin_popcount(kb >= pb ? (sm & 0xFFu) : ((sm >> 8) & 0xFFu));
+        }
+    cost_tiles *= 4.0 * 32.0 * (double)L.bm * L.n_mt;
+    int64_t rows = 0;
+    std::vector<int32_t> cnt((size_t)N, 0);
+    for (int64_t p = 0; p < N; p++) {
+        int c = 0;
+        for (int64_t q = 0; q < N; q++) c += kept(p, q) ? 1 : 0;
+        cnt[(size_t)p] = c;
+        rows += (c + 3) / 4 * 4;
+    }
+    const double cost_pp = (double)rows * L.pp_n_nt * 32.0 * L.pp_nt;
+    if (rows >= ((int64_t)1 << 31)) return;
+    if (h->opt_ht_mode != 2 && !(cost_pp < 0.85 * cost_tiles)) return;
+    L.pp_rows = rows;
+    L.pp_off.resize((size_t)N + 1);
+    L.pp_q.reserve((size_t)rows);
+    L.pp_src.reserve((size_t)rows);
+    L.pp_tri.reserve((size_t)rows);
+    for (int64_t p = 0; p < N; p++) {
+        L.pp_off[(size_t)p] = (int32_t)L.pp_q.size();
+        for (int64_t q = 0; q < N; q++) {
+            if (!kept(p, q)) continue;
+            const int ap = (int)(p / 32), aq = (int)(q / 32);
+            int64_t off;
+            if (ap >= aq) {
+                const int rr = (int)(p % 32), cc = (int)(q % 32);
+                off = (int64_t)L.tile_index[(size_t)ap * nb + aq] * 1024 + rr * 32 + (cc ^ ((rr & 3) << 2));
+            } else {
+                const int rr = (int)(q % 32), cc = (int)(p % 32);
+                off = (int64_t)L.tile_index[(size_t)aq * nb + ap] * 1024 + rr * 32 + (cc ^ ((rr & 3) << 2));
+            }
+            L.pp_q.push_back((int32_t)q);
+            L.pp_src.push_back((int32_t)off);
+            L.pp_tri.push_back(q >= p ? 1 : 0);
+        }
+        while (L.pp_q.size() % 4) {
+            L.pp_q.push_back((int32_t)L.n_pad);
+            L.pp_src.push_back(-1);
+            L.pp_tri.push_back(0);
+        }
+    }
+    L.pp_off[(size_t)N] = (int32_t)L.pp_q.size();
+    L.pp_enabled = true;
 }
 
 }  // namespace jcdf
@@ -456,6 +553,7 @@ int32_t jcdf_set_mask(jcdf_handle* h, const uint8_t* fn_mask, const int64_t* map
             L.dest_of_col[(size_t)col] = (int64_t)ti * 1024 + rr * 32 + (cc ^ ((rr & 3) << 2));
             L.src_of_col[(size_t)col] = L.dest_of_col[(size_t)col];
         }
+    build_partner_lists(h, [&](int64_t ri, int64_t ci) { return kept(ri, ci); });
     L.mask_set = true;
     integrals_on_set_mask(h);
     for (Shard& s : h->shards) {
@@ -515,6 +613,7 @@ int32_t jcdf_upload_three_center(jcdf_handle* h, int32_t dev, const double* T, i
     if (rc) return rc;
     h->shards[dev].t_uploaded = true;
     h->shards[dev].b_ready = false;
+    h->shards[dev].bc_valid = false;
     return JCDF_OK;
 }
 
@@ -530,6 +629,7 @@ int32_t jcdf_upload_three_center_device(jcdf_handle* h, int32_t dev, const doubl
     if (rc) return rc;
     h->shards[dev].t_uploaded = true;
     h->shards[dev].b_ready = false;
+    h->shards[dev].bc_valid = false;
     return JCDF_OK;
 }
 
@@ -537,6 +637,7 @@ int32_t jcdf_set_B(jcdf_handle* h, int32_t dev, const double* B, int64_t ld) {
     int rc = upload_host(h, dev, B, ld);
     if (rc) return rc;
     h->shards[dev].b_ready = true;
+    h->shards[dev].bc_valid = false;
     return JCDF_OK;
 }
 
@@ -545,6 +646,7 @@ int32_t jcdf_set_B_device(jcdf_handle* h, int32_t dev, const double* B_dev, int6
     int rc = jcdf_upload_three_center_device(h, dev, B_dev, ld, col_begin, col_count);
     if (rc) return rc;
     h->shards[dev].b_ready = true;
+    h->shards[dev].bc_valid = false;
     return JCDF_OK;
 }
 
@@ -679,6 +781,7 @@ int32_t jcdf_factor_and_form_B(jcdf_handle* h) {
         if (R[d]) cudaFree(R[d]);
         if (bl[d]) cublasDestroy(bl[d]);
         h->shards[d].b_ready = true;
+        h->shards[d].bc_valid = false;
     }
     return JCDF_OK;
 }
@@ -738,9 +841,16 @@ int fock_build_impl(jcdf_handle* h, const double* C_occ, int64_t ldc, const doub
             add_H = s.has_H;
         }
         JC_CUDA(cudaEventRecord(s.ev[EV_H2D], s.stream));
+        const bool use_pp = L.pp_enabled && s.Bc != nullptr;
+        if (use_pp && !s.bc_valid) {  // first build after B changed: refresh the partner-compacted copy
+            launch_pp_pack(L, s);
+            s.bc_valid = true;
+        }
         launch_prep(L, s, L.N);
+        if (use_pp) launch_pp_prep(L, s, L.N);
         JC_CUDA(cudaEventRecord(s.ev[EV_PREP], s.stream));
-        launch_half_transform(L, s, h->sm_count);
+        if (use_pp) launch_pp_half_transform(L, s, h->sm_count);
+        else launch_half_transform(L, s, h->sm_count);
         JC_CUDA(cudaEventRecord(s.ev[EV_W], s.stream));
         launch_exchange(L, s, h->sm_count);
         JC_CUDA(cudaEventRecord(s.ev[EV_K], s.stream));
@@ -912,6 +1022,7 @@ int32_t jcdf_get_layout(jcdf_handle* h, jcdf_layout_info* o) {
     for (const Shard& s : h->shards) {
         o->q_local += s.q_len;
         o->bytes_B += s.q_len * L.row_len * 8;
+        if (L.pp_enabled && s.Bc) o->bytes_B += (int64_t)s.pp_chunks * L.pp_rows * 128 * 8;
         o->bytes_W += (int64_t)s.xplan.chunks * L.npt64 * 2048 * 8;
     }
     // prep_cs, density, half_transform, exchange, coulomb (fused: 1, two-pass: 2), epilogue
@@ -928,6 +1039,7 @@ int32_t jcdf_fill_synthetic_B(jcdf_handle* h, uint64_t seed, double decay_length
         launch_fill_synthetic(h->lay, s, seed, decay_length);
         JC_CUDA(cudaGetLastError());
         s.b_ready = true;
+        s.bc_valid = false;
     }
     return JCDF_OK;
 }
@@ -937,7 +1049,11 @@ int32_t jcdf_set_option(jcdf_handle* h, const char* name, int64_t value) {
     const std::string n(name);
     if (n == "coulomb_fused") h->opt_coulomb_fused = value;
     else if (n == "coulomb_overlap") h->opt_coulomb_overlap = value;
-    else if (n == "regroup") {
+    else if (n == "ht_mode") {
+        JC_REQUIRE(value >= 0 && value <= 2, "ht_mode must be 0 (automatic), 1 (tile kernel) or 2 (per-function kernel)");
+        h->opt_ht_mode = value;
+        for (Shard& s : h->shards) JC_REQUIRE(s.Bp == nullptr, "ht_mode must be set before jcdf_set_mask");
+    } else if (n == "regroup") {
         h->opt_regroup = value;
         for (Shard& s : h->shards) JC_REQUIRE(s.Bp == nullptr, "regroup must be set before jcdf_set_mask");
     } else if (n == "exchange_slices") {

@@ -766,6 +766,7 @@ int32_t jcdf_compute_three_center(jcdf_handle* h) {
         if (rc) return rc;
         s.t_uploaded = true;
         s.b_ready = false;
+        s.bc_valid = false;
     }
     return JCDF_OK;
 }
@@ -787,7 +788,7 @@ int32_t jcdf_compute_B(jcdf_handle* h) {
     for (size_t d = 0; d < h->shards.size(); d++) {
         Shard& s = h->shards[d];
         JC_CUDA(cudaSetDevice(s.dev));
-        if (s.q_len == 0) { s.b_ready = true; continue; }
+        if (s.q_len == 0) { s.b_ready = true; s.bc_valid = false; continue; }
         // ---- metric, potrf('L'), Linv on this device ----
         if (!s.Metric) JC_CUDA(cudaMalloc(reinterpret_cast<void**>(&s.Metric), sizeof(double) * Q * Q));
         if (!s.Linv) JC_CUDA(cudaMalloc(reinterpret_cast<void**>(&s.Linv), sizeof(double) * Q * Q));
@@ -828,6 +829,7 @@ int32_t jcdf_compute_B(jcdf_handle* h) {
         cudaFree(T);
         s.t_uploaded = false;
         s.b_ready = true;
+        s.bc_valid = false;
     }
     return JCDF_OK;
 }

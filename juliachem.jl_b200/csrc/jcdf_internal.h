@@ -32,6 +32,16 @@ struct Layout {
     std::vector<int32_t> kb_list, kb_count;  // per 32-wide block pb: the blocks kb with a stored tile (either order)
     std::vector<int64_t> dest_of_col;  // reference pair column -> offset inside a packed row, or -1
     std::vector<int64_t> src_of_col;   // reference pair column -> packed offset holding its value (mirror columns included)
+    // ---- partner-compacted layout of the per-function half-transform (kernels_pp.cu) ----
+    // For every function p (internal order) the kept partners q, ascending, padded to a multiple of 4 rows.
+    bool pp_enabled = false;           // the per-function path is selected for this mask
+    int pp_nt = 0;                     // 8-wide occupied-orbital tiles per consumer warp (NI = 32 * pp_nt columns per item)
+    int pp_n_nt = 0;                   // occupied-orbital tiles: pp_n_nt * 32 * pp_nt >= occ_pad
+    int64_t pp_rows = 0;               // sum over p of the padded partner counts
+    std::vector<int32_t> pp_off;       // [N + 1] first row of p
+    std::vector<int32_t> pp_q;         // [pp_rows] partner (internal index), n_pad on padding rows
+    std::vector<int32_t> pp_src;       // [pp_rows] offset of B[Q, p, q] inside a packed row of Bp, -1 on padding rows
+    std::vector<int32_t> pp_tri;       // [pp_rows] 1 where q >= p on a real row (the Coulomb half)
 };
 
 // event points recorded on the shard's stream during one build, in launch order
@@ -51,7 +61,14 @@ struct Shard {
     cudaStream_t stream_j = nullptr;  // Coulomb sweeps, concurrent with the tensor-core kernels when coulomb_overlap = 1
     // HBM-resident operands
     double* Bp = nullptr;      // [q_len][row_len] packed, swizzled tiles
-    double* W = nullptr;       // [chunks][npt64][32][64] half-transformed tensor
+    double* Bc = nullptr;      // [pp_chunks][pp_rows][128] partner-compacted copy of Bp (128 auxiliary rows fastest)
+    double* Ci = nullptr;      // [n_pad + 1][ldci] C_occ rows in internal order, row-major, zero padded (last row = 0)
+    int32_t* d_pp_off = nullptr;
+    int32_t* d_pp_q = nullptr;
+    int32_t* d_pp_src = nullptr;
+    int pp_chunks = 0;         // ceil(q_len / 128)
+    bool bc_valid = false;     // Bc mirrors the current Bp
+    double* W = nullptr;       // [chunks][npt64][64 p][32 k] half-transformed tensor, k = (Q_local, i) flattened
     double* Cs = nullptr;      // [nb][n_mt][32][bm] C_occ slabs for the half-transform
     double* Craw = nullptr;    // N x occ column-major upload
     double* dt = nullptr;      // [row_len] packed, weighted density
@@ -103,6 +120,7 @@ struct jcdf_handle {
     int64_t opt_coulomb_overlap = 0;  // two-pass sweeps on a second stream, concurrent with the tensor-core kernels
     int64_t opt_exchange_slices = 0;
     int64_t opt_regroup = 1;          // mask-driven regrouping of the basis functions into 32-wide blocks
+    int64_t opt_ht_mode = 0;          // half-transform: 0 = choose from the mask, 1 = tile kernel, 2 = per-function kernel
     jcdf::ScfState* scf = nullptr;    // on-device SCF driver state (jcdf_scf_*), owned
     jcdf::IntegralsState* ints = nullptr;  // basis sets + integral scratch (jcdf_set_basis / jcdf_compute_*), owned
     bool metric_on_device = false;    // shards[0].Metric holds (P|Q) (jcdf_compute_two_center) — consumed by the factorisation
@@ -114,6 +132,9 @@ namespace jcdf {
 // ---- kernel launchers (kernels_k.cu / kernels_j.cu / kernels_misc.cu) ----------------------------------------------
 void launch_prep(const Layout& L, Shard& s, int64_t ldc);
 void launch_half_transform(const Layout& L, Shard& s, int sm_count);
+void launch_pp_pack(const Layout& L, Shard& s);                        // kernels_pp.cu: Bp -> Bc
+void launch_pp_prep(const Layout& L, Shard& s, int64_t ldc);           // C_occ -> Ci
+void launch_pp_half_transform(const Layout& L, Shard& s, int sm_count);
 void launch_exchange(const Layout& L, Shard& s, int sm_count);
 void launch_coulomb(const Layout& L, Shard& s, int sm_count, cudaStream_t st);
 bool launch_coulomb_fused(const Layout& L, Shard& s, int sm_count, cudaStream_t st);

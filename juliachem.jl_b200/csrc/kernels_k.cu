@@ -83,7 +83,8 @@ __global__ void __launch_bounds__(256) k_density_packed(const double* __restrict
 void launch_prep(const Layout& L, Shard& s, int64_t ldc) {
     int64_t total = (int64_t)L.nb * L.n_mt * 32 * L.bm;
     int blocks = (int)std::min<int64_t>((total + 255) / 256, 148 * 16);
-    k_prep_cs<<<blocks, 256, 0, s.stream>>>(s.Craw, ldc, s.Cs, (int)L.N, (int)L.occ, L.nb, L.n_mt, L.bm, s.d_inv);
+    if (!(L.pp_enabled && s.Bc != nullptr))  // the per-function half-transform reads Ci (launch_pp_prep) instead
+        k_prep_cs<<<blocks, 256, 0, s.stream>>>(s.Craw, ldc, s.Cs, (int)L.N, (int)L.occ, L.nb, L.n_mt, L.bm, s.d_inv);
     k_density_packed<<<(int)L.tiles_kept, 256, 0, s.stream>>>(s.Craw, ldc, s.dt, s.d_tile_a, s.d_tile_b, (int)L.N,
                                                                (int)L.occ, s.d_inv);
 }
@@ -236,7 +237,7 @@ __global__ void __launch_bounds__(HT_THREADS, 1) k_half_transform(HTParams prm) 
             if (lane == 0) mbar_arrive(&empty[ps.stage]);
             ps.advance<NSTAGE>();
         }
-        // epilogue: W[(Q,i)][p], 16-byte stores into the swizzled [32 x 64] W tiles
+        // epilogue: W tile [64 p][32 k] (k = (Q,i) fastest, swizzled); 8 lanes of equal t fill 64 contiguous bytes
         if (valid) {
 #pragma unroll
             for (int jm = 0; jm < MH; jm++) {
@@ -247,10 +248,11 @@ __global__ void __launch_bounds__(HT_THREADS, 1) k_half_transform(HTParams prm) 
                     const int kr = (int)(krow & 31);
 #pragma unroll
                     for (int jn = 0; jn < 4; jn++) {
-                        const int p = 32 * pb + 8 * jn + 2 * t;
-                        const int p64 = p >> 6, pc = p & 63;
-                        double2 v = make_double2(acc[jm][jn][0], acc[jm][jn][1]);
-                        *reinterpret_cast<double2*>(prm.W + ((kc * prm.npt64 + p64) * 32 + kr) * 64 + swz(kr, pc)) = v;
+                        const int p = 32 * pb + 8 * jn + 2 * t;  // even: p and p + 1 share the 64-wide tile
+                        const int p64 = p >> 6, pr = p & 63;
+                        double* w = prm.W + ((kc * prm.npt64 + p64) * 64 + pr) * 32;
+                        w[swz(pr, kr)] = acc[jm][jn][0];
+                        w[32 + swz(pr + 1, kr)] = acc[jm][jn][1];
                     }
                 }
             }
@@ -311,7 +313,7 @@ struct XParams {
     int64_t n_items;
 };
 
-constexpr int X_STAGE_DOUBLES = 4 * 32 * 64;  // A0 A1 B0 B1, each a [32 x 64] W tile
+constexpr int X_STAGE_DOUBLES = 4 * 32 * 64;  // A0 A1 B0 B1, each a [64 p][32 k] W tile
 
 __global__ void __maxnreg__(MAX_REGS) k_exchange(XParams prm) {
     extern __shared__ __align__(128) unsigned char smem_raw[];
@@ -398,9 +400,9 @@ __global__ void __maxnreg__(MAX_REGS) k_exchange(XParams prm) {
                     const int kr = k0 + t;
                     double a[8], b[4];
 #pragma unroll
-                    for (int jm = 0; jm < 8; jm++) a[jm] = sA[kr * 64 + ((8 * jm + g) ^ (t << 2))];
+                    for (int jm = 0; jm < 8; jm++) a[jm] = sA[(8 * jm + g) * 32 + (kr ^ ((g & 3) << 2))];
 #pragma unroll
-                    for (int jn = 0; jn < 4; jn++) b[jn] = sB[kr * 64 + ((nl0 + 8 * jn + g) ^ (t << 2))];
+                    for (int jn = 0; jn < 4; jn++) b[jn] = sB[(nl0 + 8 * jn + g) * 32 + (kr ^ ((g & 3) << 2))];
 #pragma unroll
                     for (int jm = 0; jm < 8; jm++)
 #pragma unroll

@@ -8,6 +8,8 @@ from __future__ import annotations
 
 from dataclasses import dataclass
 
+import math
+
 import numpy as np
 
 
@@ -148,7 +150,8 @@ def synthetic_B_rows(w: Workload, q_range: range, mask) -> np.ndarray:
     base = (lo << np.uint64(21)) | hi
     sigma = 65536.0 / 1.7320508075688772
     dist = np.arange(N, dtype=np.float64)
-    dec = np.exp(-dist / w.decay_length) if w.decay_length > 0 else np.ones(N)
+    # math.exp is libm's exp, the function synth_table (kernels_misc.cu) calls; numpy's SIMD exp can differ in the last bit
+    dec = np.array([math.exp(-d / w.decay_length) for d in dist]) if w.decay_length > 0 else np.ones(N)
     cdec = dec / (sigma * np.sqrt(float(w.Q)))
     scale = cdec[(hi - lo).astype(np.int64)]
     if mask is not None:

@@ -9,10 +9,11 @@ pytestmark = pytest.mark.gpu
 TOL = 1e-10
 
 
-def _build(N, Q, occ, B, C_occ, H, mask, ndev=1, shards=None, fused=1, overlap=0):
+def _build(N, Q, occ, B, C_occ, H, mask, ndev=1, shards=None, fused=1, overlap=0, ht_mode=0):
     gd = jc.B200Data(N, Q, occ, ndev)
     if shards is not None:
         gd.set_shards(shards)
+    gd.set_option("ht_mode", ht_mode)  # 0 = chosen from the mask, 1 = tile kernel, 2 = per-function kernel
     gd.set_option("coulomb_fused", fused)
     gd.set_option("coulomb_overlap", overlap)
     gd.set_mask(jc.ScreeningData(mask, N))
@@ -24,24 +25,25 @@ def _build(N, Q, occ, B, C_occ, H, mask, ndev=1, shards=None, fused=1, overlap=0
 
 
 @pytest.mark.parametrize("N,Q,occ", [(25, 96, 5), (64, 32, 8), (70, 40, 9), (33, 7, 1), (129, 50, 17), (203, 131, 27)])
-@pytest.mark.parametrize("fused", [1, 0])
-def test_dense_parity(N, Q, occ, fused):
+@pytest.mark.parametrize("fused,ht_mode", [(1, 1), (0, 1), (1, 2)])
+def test_dense_parity(N, Q, occ, fused, ht_mode):
     B, C_occ, H = random_inputs(N, Q, occ, seed=N * 1000 + Q)
     F_ref = oracle_fock(B, C_occ, H, None)
-    gd, F, st = _build(N, Q, occ, B, C_occ, H, None, fused=fused)
+    gd, F, st = _build(N, Q, occ, B, C_occ, H, None, fused=fused, ht_mode=ht_mode)
     assert np.abs(F - F_ref).max() < TOL
     assert np.array_equal(F, F.T)
     gd.close()
 
 
-@pytest.mark.parametrize("fused,overlap", [(1, 0), (0, 0), (0, 1)])
+@pytest.mark.parametrize("fused,overlap,ht_mode", [(1, 0, 1), (0, 0, 1), (0, 1, 1), (1, 0, 2), (0, 0, 2)])
 @pytest.mark.parametrize("N,Q,occ,hw", [(70, 40, 9, 20), (203, 131, 27, 60), (160, 64, 16, 33), (300, 90, 40, 70)])
-def test_screened_parity(N, Q, occ, hw, fused, overlap):
-    """All three Coulomb schedules: single-pass cooperative kernel, two-pass sweeps, two-pass on the second stream."""
+def test_screened_parity(N, Q, occ, hw, fused, overlap, ht_mode):
+    """All three Coulomb schedules (single-pass cooperative kernel, two-pass sweeps, two-pass on the second stream) and
+    both half-transform kernels (32 x 32 tiles with strip skipping / per-function partner lists)."""
     mask = banded_mask(N, hw, seed=N)
     B, C_occ, H = random_inputs(N, Q, occ, seed=N + 17, mask=mask, decay=hw / 2.0)
     F_ref = oracle_fock(B, C_occ, H, mask)
-    gd, F, st = _build(N, Q, occ, B, C_occ, H, mask, fused=fused, overlap=overlap)
+    gd, F, st = _build(N, Q, occ, B, C_occ, H, mask, fused=fused, overlap=overlap, ht_mode=ht_mode)
     assert gd.layout().kernel_launches_per_build == (6 if fused else 7)
     li = gd.layout()
     assert li.pairs_kept == int(mask.sum())
@@ -272,6 +274,47 @@ def _scattered_mask(N, n_sites, reach, seed):
     m = d <= np.minimum(extent[:, None], extent[None, :]) * reach + (extent[:, None] + extent[None, :] > 2)
     np.fill_diagonal(m, True)
     return np.asfortranarray(m | m.T)
+
+
+@pytest.mark.parametrize("N,Q,occ,ht_mode", [(180, 300, 130, 2), (333, 257, 40, 2), (333, 257, 40, 0), (96, 129, 81, 2)])
+def test_per_function_half_transform(N, Q, occ, ht_mode):
+    """The partner-compacted path (calculate_W_screened restated per function, kernels_pp.cu) on a scattered mask that
+    gets regrouped: several 128-row chunks with a ragged last one, more than one occupied-orbital tile (occ = 130),
+    partner counts that are not multiples of 4, and a refresh of the compact copy when B is replaced."""
+    mask = _scattered_mask(N, 19, 1, seed=N + 1)
+    B, C_occ, H = random_inputs(N, Q, occ, seed=N + 5, mask=mask)
+    F_ref = oracle_fock(B, C_occ, H, mask)
+    gd, F, _ = _build(N, Q, occ, B, C_occ, H, mask, ht_mode=ht_mode)
+    assert np.abs(F - F_ref).max() < TOL
+    assert np.array_equal(F, F.T)
+    F2, _ = gd.fock_build(C_occ, H)  # second build reuses the compact copy
+    assert np.array_equal(F2, F)
+    B2, C2, H2 = random_inputs(N, Q, occ, seed=N + 6, mask=mask)
+    gd.set_B(0, reference_layout_rows(B2, range(0, Q), mask))  # B replaced: the compact copy must follow
+    F3, _ = gd.fock_build(C2, H2)
+    assert np.abs(F3 - oracle_fock(B2, C2, H2, mask)).max() < TOL
+    gd.close()
+
+
+def test_half_transform_kernels_agree_on_sharded_run():
+    """Two shards on one device, per-function kernel on each, against the tile kernel: same Fock matrix to 1e-10."""
+    N, Q, occ = 150, 200, 33
+    mask = _scattered_mask(N, 13, 1, seed=9)
+    B, C_occ, H = random_inputs(N, Q, occ, seed=10, mask=mask)
+    F_ref = oracle_fock(B, C_occ, H, mask)
+    out = {}
+    for mode in (1, 2):
+        acc = np.zeros((N, N))
+        for r, Hr in ((range(0, 135), H), (range(135, 200), None)):
+            gd = jc.B200Data(N, len(r), occ, 1)
+            gd.set_option("ht_mode", mode)
+            gd.set_mask(jc.ScreeningData(mask, N))
+            gd.set_B(0, reference_layout_rows(B, r, mask))
+            acc += gd.fock_build(C_occ, Hr)[0]
+            gd.close()
+        out[mode] = acc
+        assert np.abs(acc - F_ref).max() < TOL
+    assert np.abs(out[1] - out[2]).max() < TOL
 
 
 @pytest.mark.parametrize("regroup", [1, 0])
