@@ -33,7 +33,7 @@ static int dev_alloc(T** p, size_t count) {
 // keep_metric: the two-centre metric / its inverse factor do not depend on the mask (jcdf_set_mask keeps them)
 static void free_shard_buffers(Shard& s, bool keep_metric = false) {
     cudaSetDevice(s.dev);
-    void* ptrs[] = {s.Bc, s.Ci, s.d_pp_off, s.d_pp_q, s.d_pp_src, s.Vpart, s.Vready, s.Bp, s.W, s.Cs, s.Craw, s.dt, s.Jt, s.V, s.Kpart, s.F, s.Hdev, s.Traw, s.d_tile_index, s.d_tile_a,
+    void* ptrs[] = {s.d_xitems, s.d_xoff, s.Bc, s.Ci, s.d_pp_off, s.d_pp_q, s.d_pp_src, s.d_pp_p, s.d_pp_jdst, s.dvec, s.VpartP, s.Jpart, s.Vpart, s.Vready, s.Bp, s.W, s.Cs, s.Craw, s.dt, s.Jt, s.V, s.Kpart, s.F, s.Hdev, s.Traw, s.d_tile_index, s.d_tile_a,
                     s.d_tile_b, s.d_dest_of_col, s.d_fn_mask, s.d_kb_list, s.d_kb_count, s.d_perm, s.d_inv, s.d_tile_strips};
     for (void* p : ptrs)
         if (p) cudaFree(p);
@@ -47,7 +47,9 @@ static void free_shard_buffers(Shard& s, bool keep_metric = false) {
     s.Vpart = nullptr;
     s.Vready = nullptr;
     s.Bc = s.Ci = nullptr;
-    s.d_pp_off = s.d_pp_q = s.d_pp_src = nullptr;
+    s.d_pp_off = s.d_pp_q = s.d_pp_src = s.d_pp_p = s.d_pp_jdst = nullptr;
+    s.dvec = s.VpartP = s.Jpart = nullptr;
+    s.d_xitems = s.d_xoff = nullptr;
     s.pp_chunks = 0;
     s.bc_valid = false;
     s.d_dest_of_col = nullptr;
@@ -57,9 +59,9 @@ static void free_shard_buffers(Shard& s, bool keep_metric = false) {
 }
 
 // Split of the exchange contraction index: items = tiles x slices dealt round-robin to one CTA per SM.
-static void plan_exchange(const Layout& L, Shard& s, int sm_count) {
+static void plan_exchange(const Layout& L, Shard& s, int sm_count, bool balance) {
     ExchangePlan& x = s.xplan;
-    x.chunks = (int)((s.q_len * L.occ_pad + 31) / 32);
+    x.chunks = (int)((s.q_len * L.occ_w + 31) / 32);
     x.n_tiles = L.n128 * (L.n128 + 1) / 2;
     int max_slices = std::max(1, x.chunks / 8);
     int want = std::max(1, (12 * sm_count + x.n_tiles - 1) / x.n_tiles);
@@ -75,12 +77,49 @@ static void plan_exchange(const Layout& L, Shard& s, int sm_count) {
     x.chunks_per_slice = (x.chunks + best - 1) / best;
     if (x.chunks_per_slice < 1) x.chunks_per_slice = 1;
     x.n_slices = std::max(1, (x.chunks + x.chunks_per_slice - 1) / x.chunks_per_slice);
+    // Items cost differently (diagonal tiles issue 10/16 of a full tile's DMMAs, the last tile row is clipped to N, the
+    // last slice may be short): deal them to the persistent CTAs longest-first onto the least-loaded CTA.
+    const int n_items = x.n_tiles * x.n_slices;
+    x.n_ctas = std::max(1, std::min(n_items, sm_count));
+    std::vector<int64_t> cost((size_t)n_items);
+    std::vector<int> tile_cost((size_t)x.n_tiles);
+    for (int t = 0; t < x.n_tiles; t++) tile_cost[(size_t)t] = exchange_tile_cost(t, (int)L.N);
+    for (int it = 0; it < n_items; it++) {
+        const int slice = it / x.n_tiles;
+        const int kc0 = slice * x.chunks_per_slice, kc1 = std::min(x.chunks, kc0 + x.chunks_per_slice);
+        cost[(size_t)it] = (int64_t)tile_cost[(size_t)(it % x.n_tiles)] * std::max(0, kc1 - kc0) + 6 * 32;  // + epilogue
+    }
+    std::vector<int32_t> order((size_t)n_items);
+    for (int it = 0; it < n_items; it++) order[(size_t)it] = it;
+    std::stable_sort(order.begin(), order.end(), [&](int32_t a, int32_t b) { return cost[(size_t)a] > cost[(size_t)b]; });
+    std::vector<int64_t> load((size_t)x.n_ctas, 0);
+    std::vector<std::vector<int32_t>> bins((size_t)x.n_ctas);
+    if (!balance) {  // plain round-robin in item order
+        for (int it = 0; it < n_items; it++) bins[(size_t)(it % x.n_ctas)].push_back(it);
+        order.clear();
+    }
+    for (int32_t it : order) {
+        int best_c = 0;
+        for (int c = 1; c < x.n_ctas; c++)
+            if (load[(size_t)c] < load[(size_t)best_c]) best_c = c;
+        load[(size_t)best_c] += cost[(size_t)it];
+        bins[(size_t)best_c].push_back(it);
+    }
+    x.item_list.clear();
+    x.item_off.assign((size_t)x.n_ctas + 1, 0);
+    for (int c = 0; c < x.n_ctas; c++) {
+        // ascending item id inside a CTA: consecutive slices of a tile keep its W columns warm in L2
+        std::sort(bins[(size_t)c].begin(), bins[(size_t)c].end());
+        x.item_off[(size_t)c] = (int32_t)x.item_list.size();
+        x.item_list.insert(x.item_list.end(), bins[(size_t)c].begin(), bins[(size_t)c].end());
+    }
+    x.item_off[(size_t)x.n_ctas] = (int32_t)x.item_list.size();
 }
 
 static int alloc_shard_buffers(jcdf_handle* h, Shard& s) {
     Layout& L = h->lay;
     JC_CUDA(cudaSetDevice(s.dev));
-    plan_exchange(L, s, h->sm_count);
+    plan_exchange(L, s, h->sm_count, h->opt_exchange_balance != 0);
     int rc;
     const size_t nB = (size_t)s.q_len * (size_t)L.row_len;
     if ((rc = dev_alloc(&s.Bp, nB))) return rc;
@@ -92,10 +131,15 @@ static int alloc_shard_buffers(jcdf_handle* h, Shard& s) {
     if ((rc = dev_alloc(&s.Craw, (size_t)L.N * L.occ))) return rc;
     if ((rc = dev_alloc(&s.dt, (size_t)L.row_len))) return rc;
     if ((rc = dev_alloc(&s.Jt, (size_t)L.row_len))) return rc;
+    JC_CUDA(cudaMemsetAsync(s.Jt, 0, std::max<size_t>((size_t)L.row_len, 1) * sizeof(double), s.stream));
     if ((rc = dev_alloc(&s.V, (size_t)std::max<int64_t>(s.q_len, 1)))) return rc;
     if ((rc = dev_alloc(&s.Vpart, (size_t)std::max<int64_t>(s.q_len, 1) * h->sm_count))) return rc;
     if ((rc = dev_alloc(&s.Vready, (size_t)std::max<int64_t>(s.q_len, 1)))) return rc;
     if ((rc = dev_alloc(&s.Kpart, (size_t)s.xplan.n_tiles * s.xplan.n_slices * 128 * 128))) return rc;
+    if ((rc = dev_alloc(&s.d_xitems, s.xplan.item_list.size()))) return rc;
+    if ((rc = dev_alloc(&s.d_xoff, s.xplan.item_off.size()))) return rc;
+    JC_CUDA(cudaMemcpyAsync(s.d_xitems, s.xplan.item_list.data(), sizeof(int32_t) * s.xplan.item_list.size(), cudaMemcpyHostToDevice, s.stream));
+    JC_CUDA(cudaMemcpyAsync(s.d_xoff, s.xplan.item_off.data(), sizeof(int32_t) * s.xplan.item_off.size(), cudaMemcpyHostToDevice, s.stream));
     if ((rc = dev_alloc(&s.F, (size_t)L.N * L.N))) return rc;
     if ((rc = dev_alloc(&s.Hdev, (size_t)L.N * L.N))) return rc;
     if ((rc = dev_alloc(&s.d_tile_index, (size_t)L.nb * L.nb))) return rc;
@@ -142,6 +186,13 @@ static int alloc_shard_buffers(jcdf_handle* h, Shard& s) {
             JC_CUDA(cudaMemcpyAsync(s.d_pp_off, L.pp_off.data(), sizeof(int32_t) * L.pp_off.size(), cudaMemcpyHostToDevice, s.stream));
             JC_CUDA(cudaMemcpyAsync(s.d_pp_q, L.pp_q.data(), sizeof(int32_t) * L.pp_q.size(), cudaMemcpyHostToDevice, s.stream));
             JC_CUDA(cudaMemcpyAsync(s.d_pp_src, L.pp_src.data(), sizeof(int32_t) * L.pp_src.size(), cudaMemcpyHostToDevice, s.stream));
+            if ((rc = dev_alloc(&s.d_pp_p, L.pp_p.size()))) return rc;
+            if ((rc = dev_alloc(&s.d_pp_jdst, L.pp_jdst.size()))) return rc;
+            JC_CUDA(cudaMemcpyAsync(s.d_pp_p, L.pp_p.data(), sizeof(int32_t) * L.pp_p.size(), cudaMemcpyHostToDevice, s.stream));
+            JC_CUDA(cudaMemcpyAsync(s.d_pp_jdst, L.pp_jdst.data(), sizeof(int32_t) * L.pp_jdst.size(), cudaMemcpyHostToDevice, s.stream));
+            if ((rc = dev_alloc(&s.dvec, (size_t)L.pp_rows))) return rc;
+            if ((rc = dev_alloc(&s.VpartP, (size_t)pp_coulomb_slabs(L) * s.pp_chunks * 128))) return rc;
+            if ((rc = dev_alloc(&s.Jpart, (size_t)s.pp_chunks * L.pp_rows))) return rc;
         }
     }
     s.bc_valid = false;
@@ -274,7 +325,7 @@ static void build_partner_lists(jcdf_handle* h, Kept kept) {
     const int64_t N = L.N;
     const int nb = L.nb;
     L.pp_enabled = false;
-    L.pp_off.clear(); L.pp_q.clear(); L.pp_src.clear(); L.pp_tri.clear();
+    L.pp_off.clear(); L.pp_q.clear(); L.pp_src.clear(); L.pp_p.clear(); L.pp_jdst.clear();
     L.pp_rows = 0;
     // occupied-orbital tiling: 4 consumer warps across n, each 8 * pp_nt wide, pp_nt <= 4
     const int n8 = L.occ_pad / 8;
@@ -305,7 +356,8 @@ static void build_partner_lists(jcdf_handle* h, Kept kept) {
     L.pp_off.resize((size_t)N + 1);
     L.pp_q.reserve((size_t)rows);
     L.pp_src.reserve((size_t)rows);
-    L.pp_tri.reserve((size_t)rows);
+    L.pp_p.reserve((size_t)rows);
+    L.pp_jdst.reserve((size_t)rows);
     for (int64_t p = 0; p < N; p++) {
         L.pp_off[(size_t)p] = (int32_t)L.pp_q.size();
         for (int64_t q = 0; q < N; q++) {
@@ -321,12 +373,20 @@ static void build_partner_lists(jcdf_handle* h, Kept kept) {
             }
             L.pp_q.push_back((int32_t)q);
             L.pp_src.push_back((int32_t)off);
-            L.pp_tri.push_back(q >= p ? 1 : 0);
+            L.pp_p.push_back((int32_t)p);
+            // Coulomb half: rows with q >= p; the epilogue reads J at (row hi = q, column lo = p) of tile (aq, ap)
+            int64_t jd = -1;
+            if (q >= p) {
+                const int rr = (int)(q % 32), cc = (int)(p % 32);
+                jd = (int64_t)L.tile_index[(size_t)aq * nb + ap] * 1024 + rr * 32 + (cc ^ ((rr & 3) << 2));
+            }
+            L.pp_jdst.push_back((int32_t)jd);
         }
         while (L.pp_q.size() % 4) {
             L.pp_q.push_back((int32_t)L.n_pad);
             L.pp_src.push_back(-1);
-            L.pp_tri.push_back(0);
+            L.pp_p.push_back((int32_t)p);
+            L.pp_jdst.push_back(-1);
         }
     }
     L.pp_off[(size_t)N] = (int32_t)L.pp_q.size();
@@ -368,6 +428,7 @@ int32_t jcdf_create(int64_t N, int64_t Q, int64_t occ, int32_t ndev, const int32
     L.nb = (int)((N + 31) / 32);
     L.n_pad = 32 * L.nb;
     L.occ_pad = (int)round_up(occ, 8);
+    L.occ_w = (int)round_up(occ, 2);
     L.n_mt = (L.occ_pad + 127) / 128;
     L.bm = (int)round_up((L.occ_pad + L.n_mt - 1) / L.n_mt, 16);
     L.npt64 = (L.n_pad + 63) / 64;
@@ -846,8 +907,10 @@ int fock_build_impl(jcdf_handle* h, const double* C_occ, int64_t ldc, const doub
             launch_pp_pack(L, s);
             s.bc_valid = true;
         }
-        launch_prep(L, s, L.N);
+        const bool pp_j = use_pp && h->opt_coulomb_pp;  // Coulomb over the compact copy as well
+        if (!pp_j) launch_prep(L, s, L.N);
         if (use_pp) launch_pp_prep(L, s, L.N);
+        if (pp_j) launch_pp_density(L, s);
         JC_CUDA(cudaEventRecord(s.ev[EV_PREP], s.stream));
         if (use_pp) launch_pp_half_transform(L, s, h->sm_count);
         else launch_half_transform(L, s, h->sm_count);
@@ -857,13 +920,19 @@ int fock_build_impl(jcdf_handle* h, const double* C_occ, int64_t ldc, const doub
         // Coulomb sweeps (HBM-bound, 32-40 registers, no dynamic smem).  With coulomb_overlap they go to a second,
         // lower-priority stream: their CTAs co-reside with the persistent tensor-core CTAs (one per SM, compute-bound,
         // issue slots ~16 % busy) and soak up the idle HBM bandwidth instead of queueing behind them.
-        const bool overlap = h->opt_coulomb_overlap && !h->opt_coulomb_fused;
+        const bool overlap = h->opt_coulomb_overlap && !h->opt_coulomb_fused && !pp_j;
         cudaStream_t sj = overlap ? s.stream_j : s.stream;
         if (overlap) JC_CUDA(cudaStreamWaitEvent(sj, s.ev[EV_PREP], 0));
         JC_CUDA(cudaEventRecord(s.ev[EV_JBEGIN], sj));
         JC_CUDA(cudaEventRecord(s.ev[EV_V], sj));  // two-pass: overwritten at the V | J boundary; fused: V time reads 0
-        s.last_coulomb_fused = h->opt_coulomb_fused && launch_coulomb_fused(L, s, h->sm_count, sj);
-        if (!s.last_coulomb_fused) launch_coulomb(L, s, h->sm_count, sj);
+        if (pp_j) {
+            s.last_coulomb_fused = false;
+            launch_pp_coulomb(L, s, sj, s.ev[EV_V]);
+        } else {
+            s.last_coulomb_fused = h->opt_coulomb_fused && launch_coulomb_fused(L, s, h->sm_count, sj);
+            if (!s.last_coulomb_fused) launch_coulomb(L, s, h->sm_count, sj);
+        }
+        s.last_pp_j = pp_j;
         JC_CUDA(cudaEventRecord(s.ev[EV_J], sj));
         if (overlap) JC_CUDA(cudaStreamWaitEvent(s.stream, s.ev[EV_J], 0));
         launch_epilogue(L, s, add_H);
@@ -912,7 +981,7 @@ int fock_build_impl(jcdf_handle* h, const double* C_occ, int64_t ldc, const doub
         s.last_ms[JCDF_T_K] = el(EV_W, EV_K);
         s.last_ms[JCDF_T_V] = el(EV_JBEGIN, EV_V);
         s.last_ms[JCDF_T_J] = el(EV_V, EV_J);
-        s.last_ms[JCDF_T_EPILOGUE] = (h->opt_coulomb_overlap && !h->opt_coulomb_fused) ? el(EV_K, EV_EPI) : el(EV_J, EV_EPI);
+        s.last_ms[JCDF_T_EPILOGUE] = (h->opt_coulomb_overlap && !h->opt_coulomb_fused && !s.last_pp_j) ? el(EV_K, EV_EPI) : el(EV_J, EV_EPI);
         s.last_ms[JCDF_T_ALLREDUCE] = el(EV_EPI, EV_AR);
         s.last_ms[JCDF_T_D2H] = d == 0 ? el(EV_AR, EV_D2H) : 0.0;
         s.last_ms[JCDF_T_TOTAL] = std::chrono::duration<double, std::milli>(t1 - t0).count();
@@ -1026,7 +1095,9 @@ int32_t jcdf_get_layout(jcdf_handle* h, jcdf_layout_info* o) {
         o->bytes_W += (int64_t)s.xplan.chunks * L.npt64 * 2048 * 8;
     }
     // prep_cs, density, half_transform, exchange, coulomb (fused: 1, two-pass: 2), epilogue
-    o->kernel_launches_per_build = ((!h->shards.empty() && h->shards[0].last_coulomb_fused) ? 6 : 7) +
+    // per-function path with its own Coulomb: prep, density, half_transform, exchange, V, V reduce, J, J reduce, epilogue
+    const bool ppj = !h->shards.empty() && L.pp_enabled && h->shards[0].Bc != nullptr && h->opt_coulomb_pp;
+    o->kernel_launches_per_build = (ppj ? 9 : ((!h->shards.empty() && h->shards[0].last_coulomb_fused) ? 6 : 7)) +
                                    ((h->n_ranks * (int)h->shards.size() > 1) ? 1 : 0);  // + mirror after the all-reduce
     return JCDF_OK;
 }
@@ -1049,6 +1120,11 @@ int32_t jcdf_set_option(jcdf_handle* h, const char* name, int64_t value) {
     const std::string n(name);
     if (n == "coulomb_fused") h->opt_coulomb_fused = value;
     else if (n == "coulomb_overlap") h->opt_coulomb_overlap = value;
+    else if (n == "coulomb_pp") h->opt_coulomb_pp = value;
+    else if (n == "exchange_balance") {
+        h->opt_exchange_balance = value;
+        for (Shard& s : h->shards) JC_REQUIRE(s.Bp == nullptr, "exchange_balance must be set before jcdf_set_mask");
+    }
     else if (n == "ht_mode") {
         JC_REQUIRE(value >= 0 && value <= 2, "ht_mode must be 0 (automatic), 1 (tile kernel) or 2 (per-function kernel)");
         h->opt_ht_mode = value;

@@ -15,6 +15,7 @@ struct Layout {
     int nb = 0;         // 32-wide blocks per dimension
     int n_pad = 0;      // 32 * nb
     int occ_pad = 0;    // occ rounded up to 8
+    int occ_w = 0;      // occ rounded up to 2: row stride of the flattened contraction index k = Q_local * occ_w + i of W
     int bm = 0;         // half-transform M tile (rows i per work item), multiple of 16, <= 128
     int n_mt = 0;       // M tiles: bm * n_mt >= occ_pad
     int npt64 = 0;      // 64-wide W column tiles
@@ -41,7 +42,8 @@ struct Layout {
     std::vector<int32_t> pp_off;       // [N + 1] first row of p
     std::vector<int32_t> pp_q;         // [pp_rows] partner (internal index), n_pad on padding rows
     std::vector<int32_t> pp_src;       // [pp_rows] offset of B[Q, p, q] inside a packed row of Bp, -1 on padding rows
-    std::vector<int32_t> pp_tri;       // [pp_rows] 1 where q >= p on a real row (the Coulomb half)
+    std::vector<int32_t> pp_p;         // [pp_rows] the function p of the row
+    std::vector<int32_t> pp_jdst;      // [pp_rows] q >= p rows (the Coulomb half): offset of (q, p) inside Jt; -1 elsewhere
 };
 
 // event points recorded on the shard's stream during one build, in launch order
@@ -52,6 +54,8 @@ struct ExchangePlan {
     int n_slices = 0;    // split of the contraction index per tile
     int chunks = 0;      // 32-row k chunks held by the shard
     int chunks_per_slice = 0;
+    int n_ctas = 0;      // persistent CTAs (<= SM count)
+    std::vector<int32_t> item_list, item_off;  // cost-balanced item lists per CTA (longest-processing-time first)
 };
 
 struct Shard {
@@ -66,6 +70,11 @@ struct Shard {
     int32_t* d_pp_off = nullptr;
     int32_t* d_pp_q = nullptr;
     int32_t* d_pp_src = nullptr;
+    int32_t* d_pp_p = nullptr;
+    int32_t* d_pp_jdst = nullptr;
+    double* dvec = nullptr;    // [pp_rows] weighted density in partner-row space
+    double* VpartP = nullptr;  // [slabs][pp_chunks * 128] partial V of the compact Coulomb pass
+    double* Jpart = nullptr;   // [pp_chunks][pp_rows] partial J per chunk
     int pp_chunks = 0;         // ceil(q_len / 128)
     bool bc_valid = false;     // Bc mirrors the current Bp
     double* W = nullptr;       // [chunks][npt64][64 p][32 k] half-transformed tensor, k = (Q_local, i) flattened
@@ -77,6 +86,8 @@ struct Shard {
     double* Vpart = nullptr;   // [q_len][sm_count] per-CTA partial V of the fused Coulomb kernel
     unsigned int* Vready = nullptr;  // [q_len] chunk flags of the fused Coulomb kernel
     double* Kpart = nullptr;   // [n_tiles * n_slices][128*128]
+    int32_t* d_xitems = nullptr;  // exchange item lists (ExchangePlan)
+    int32_t* d_xoff = nullptr;
     double* F = nullptr;       // N x N column-major partial / reduced Fock
     double* Hdev = nullptr;    // N x N (only where H is added)
     double* Traw = nullptr;    // staging window for uploads
@@ -95,6 +106,7 @@ struct Shard {
     double* Metric = nullptr;
     bool has_H = false;
     bool last_coulomb_fused = false;
+    bool last_pp_j = false;    // the last build ran the Coulomb passes over the partner-compacted copy
     bool b_ready = false;
     bool t_uploaded = false;
     ExchangePlan xplan;
@@ -119,7 +131,9 @@ struct jcdf_handle {
     int64_t opt_coulomb_fused = 1;    // single-pass cooperative Coulomb kernel whenever the row segment fits in smem
     int64_t opt_coulomb_overlap = 0;  // two-pass sweeps on a second stream, concurrent with the tensor-core kernels
     int64_t opt_exchange_slices = 0;
+    int64_t opt_exchange_balance = 1;  // cost-balanced exchange item lists (0: round-robin in item order)
     int64_t opt_regroup = 1;          // mask-driven regrouping of the basis functions into 32-wide blocks
+    int64_t opt_coulomb_pp = 1;       // Coulomb over the partner-compacted copy whenever the per-function path is active
     int64_t opt_ht_mode = 0;          // half-transform: 0 = choose from the mask, 1 = tile kernel, 2 = per-function kernel
     jcdf::ScfState* scf = nullptr;    // on-device SCF driver state (jcdf_scf_*), owned
     jcdf::IntegralsState* ints = nullptr;  // basis sets + integral scratch (jcdf_set_basis / jcdf_compute_*), owned
@@ -135,6 +149,9 @@ void launch_half_transform(const Layout& L, Shard& s, int sm_count);
 void launch_pp_pack(const Layout& L, Shard& s);                        // kernels_pp.cu: Bp -> Bc
 void launch_pp_prep(const Layout& L, Shard& s, int64_t ldc);           // C_occ -> Ci
 void launch_pp_half_transform(const Layout& L, Shard& s, int sm_count);
+void launch_pp_density(const Layout& L, Shard& s);
+void launch_pp_coulomb(const Layout& L, Shard& s, cudaStream_t st, cudaEvent_t ev_v);
+int64_t pp_coulomb_slabs(const Layout& L);
 void launch_exchange(const Layout& L, Shard& s, int sm_count);
 void launch_coulomb(const Layout& L, Shard& s, int sm_count, cudaStream_t st);
 bool launch_coulomb_fused(const Layout& L, Shard& s, int sm_count, cudaStream_t st);
@@ -147,6 +164,7 @@ void launch_gather_pairs(const Layout& L, Shard& s, double* T_dev, int64_t ld, i
 void launch_fill_synthetic(const Layout& L, Shard& s, uint64_t seed, double decay_length);
 size_t half_transform_smem_bytes(int bm);
 size_t exchange_smem_bytes();
+int exchange_tile_cost(int tile, int N);  // kernels_k.cu: DMMA row units per k-step on the busiest sub-partition
 int kernels_per_build();
 
 void set_error(const std::string& msg);

@@ -9,6 +9,8 @@
 // Both kernels are persistent (one CTA per SM, static round-robin over work items); 8 warps issue DMMA and thread 0 is
 // also the copy producer, running NSTAGE - 1 slabs ahead through a full/empty mbarrier ring.  All operands are stored
 // in HBM pre-swizzled (dmma_common.cuh: swz) so a dense bulk copy lands bank-conflict-free in shared memory.
+#include <algorithm>
+
 #include "dmma_common.cuh"
 #include "jcdf_internal.h"
 
@@ -101,7 +103,7 @@ struct HTParams {
     const int32_t* tile_strips;  // [tiles_kept]: bits 0-7 non-empty 4-row strips, bits 8-15 non-empty 4-column strips
     const double* Cs;
     double* W;
-    int q_len, nb, n_mt, npt64, occ_pad, n_valid_last;
+    int q_len, nb, n_mt, npt64, occ_w, n_valid_last;
     int64_t n_items;
 };
 
@@ -242,8 +244,8 @@ __global__ void __launch_bounds__(HT_THREADS, 1) k_half_transform(HTParams prm) 
 #pragma unroll
             for (int jm = 0; jm < MH; jm++) {
                 const int i = mt * BM + m0 + 8 * jm + g;
-                if (i < prm.occ_pad) {
-                    const int64_t krow = qrow * prm.occ_pad + i;
+                if (i < prm.occ_w) {
+                    const int64_t krow = qrow * prm.occ_w + i;
                     const int64_t kc = krow >> 5;
                     const int kr = (int)(krow & 31);
 #pragma unroll
@@ -285,7 +287,7 @@ void launch_half_transform(const Layout& L, Shard& s, int sm_count) {
     prm.nb = L.nb;
     prm.n_mt = L.n_mt;
     prm.npt64 = L.npt64;
-    prm.occ_pad = L.occ_pad;
+    prm.occ_w = L.occ_w;
     prm.n_valid_last = (int)(L.N - 32 * (L.nb - 1));
     prm.n_items = ((int64_t)s.q_len + 3) / 4 * L.nb * L.n_mt;
     int grid = (int)std::min<int64_t>(prm.n_items, sm_count);
@@ -309,11 +311,98 @@ void launch_half_transform(const Layout& L, Shard& s, int sm_count) {
 struct XParams {
     const double* W;
     double* Kpart;
-    int npt64, n_tiles, n_slices, chunks, chunks_per_slice;
-    int64_t n_items;
+    const int32_t* item_list;  // items of CTA c: item_list[item_off[c] .. item_off[c + 1])  (cost-balanced on the host)
+    const int32_t* item_off;
+    int npt64, n_tiles, n_slices, chunks, chunks_per_slice, N;
 };
 
 constexpr int X_STAGE_DOUBLES = 4 * 32 * 64;  // A0 A1 B0 B1, each a [64 p][32 k] W tile
+
+// Which block of the 128 x 128 output tile (ta, tb) a warp owns, in units of 8 rows / columns: rows 8 r0 .. 8 (r0 + mt),
+// columns 8 c0 .. 8 (c0 + nt), mt <= 8, nt <= 4.
+//   * off-diagonal tiles: the plain 2 x 4 arrangement of 64 x 32 blocks;
+//   * diagonal tiles: only the lower triangle is needed (the reference computes its diagonal blocks whole,
+//     ScreenedDF.jl:596-601) — it is covered by eight rectangles chosen so that the two warps of every SM sub-partition
+//     (w and w + 4) together issue 10 of the 16 row units a full tile costs;
+//   * rows / columns beyond N (the last tile row) are clipped.
+// Shared by the kernel and the host-side cost model of plan_exchange.
+__host__ __device__ inline void exchange_warp_block(int ta, int tb, int warp, int N, int& r0, int& c0, int& mt, int& nt) {
+    if (ta == tb) {
+        // warp:  0 = T1  1 = T2  2 = A1a  3 = A2a  4 = A1b  5 = A2b  6 = t1  7 = t2   (one nibble per warp)
+        //   r0 = {0, 8, 8, 8, 14, 14, 4, 12}   c0 = {0, 8, 0, 4, 0, 4, 4, 12}   mt = {8, 8, 6, 6, 2, 2, 4, 4}
+        r0 = (int)((0xC4EE8880u >> (4 * warp)) & 15u);
+        c0 = (int)((0xC4404080u >> (4 * warp)) & 15u);
+        mt = (int)((0x44226688u >> (4 * warp)) & 15u);
+        nt = 4;
+    } else {
+        r0 = 8 * (warp >> 2); c0 = 4 * (warp & 3); mt = 8; nt = 4;
+    }
+    const int rows8 = (N - 128 * ta + 7) >> 3, cols8 = (N - 128 * tb + 7) >> 3;
+    mt = max(0, min(mt, rows8 - r0));
+    nt = max(0, min(nt, cols8 - c0));
+    if (mt == 0 || nt == 0) mt = nt = 0;
+}
+
+__host__ __device__ inline void exchange_decode_tile(int tile, int& ta, int& tb) {
+    int a = 0;
+    while ((a + 1) * (a + 2) / 2 <= tile) a++;
+    ta = a;
+    tb = tile - a * (a + 1) / 2;
+}
+
+// DMMA row units (x 4 column tiles) the busiest sub-partition issues per k-step of 4 for this tile: the cost model
+int exchange_tile_cost(int tile, int N) {
+    int ta, tb, best = 0;
+    exchange_decode_tile(tile, ta, tb);
+    for (int j = 0; j < 4; j++) {
+        int c = 0;
+        for (int w = j; w < 8; w += 4) {
+            int r0, c0, mt, nt;
+            exchange_warp_block(ta, tb, w, N, r0, c0, mt, nt);
+            c += mt * nt;
+        }
+        best = std::max(best, c);
+    }
+    return best;
+}
+
+// One pipeline stage (32 k rows) of a warp block of MT x NT DMMA tiles.  MT and NT are compile-time so a clipped or
+// diagonal block issues exactly MT * NT DMMAs per k-step (a predicated-off DMMA still takes its slot in the tensor pipe:
+// measured — the predicated version of this loop left the pipe cycles of the diagonal tiles unchanged).
+template <int MT, int NT>
+__device__ __forceinline__ void x_slab(double (&acc)[8][4][2], const double* __restrict__ sA, const double* __restrict__ sB,
+                                       int g, int t) {
+    const int sw = (g & 3) << 2;
+#pragma unroll 2
+    for (int k0 = 0; k0 < KSLAB; k0 += 4) {
+        const int kr = (k0 + t) ^ sw;
+        double a[MT], b[NT];
+#pragma unroll
+        for (int jm = 0; jm < MT; jm++) a[jm] = sA[(8 * jm + g) * 32 + kr];
+#pragma unroll
+        for (int jn = 0; jn < NT; jn++) b[jn] = sB[(8 * jn + g) * 32 + kr];
+#pragma unroll
+        for (int jm = 0; jm < MT; jm++)
+#pragma unroll
+            for (int jn = 0; jn < NT; jn++) dmma(acc[jm][jn][0], acc[jm][jn][1], a[jm], b[jn]);
+    }
+}
+
+template <int NT>
+__device__ __forceinline__ void x_slab_mt(double (&acc)[8][4][2], const double* __restrict__ sA,
+                                          const double* __restrict__ sB, int g, int t, int mt) {
+    switch (mt) {
+        case 1: x_slab<1, NT>(acc, sA, sB, g, t); break;
+        case 2: x_slab<2, NT>(acc, sA, sB, g, t); break;
+        case 3: x_slab<3, NT>(acc, sA, sB, g, t); break;
+        case 4: x_slab<4, NT>(acc, sA, sB, g, t); break;
+        case 5: x_slab<5, NT>(acc, sA, sB, g, t); break;
+        case 6: x_slab<6, NT>(acc, sA, sB, g, t); break;
+        case 7: x_slab<7, NT>(acc, sA, sB, g, t); break;
+        case 8: x_slab<8, NT>(acc, sA, sB, g, t); break;
+        default: break;
+    }
+}
 
 __global__ void __maxnreg__(MAX_REGS) k_exchange(XParams prm) {
     extern __shared__ __align__(128) unsigned char smem_raw[];
@@ -334,28 +423,25 @@ __global__ void __maxnreg__(MAX_REGS) k_exchange(XParams prm) {
 
     const int npt64 = prm.npt64;
     const bool is_producer = (threadIdx.x == 0);
+    const int j_begin = prm.item_off[blockIdx.x], j_end = prm.item_off[blockIdx.x + 1];
 
-    auto decode = [&](int64_t item, int& ta, int& tb, int& kc0, int& kc1) {
-        const int tile = (int)(item % prm.n_tiles);
-        const int slice = (int)(item / prm.n_tiles);
-        int a = 0;
-        while ((a + 1) * (a + 2) / 2 <= tile) a++;
-        ta = a;
-        tb = tile - a * (a + 1) / 2;
+    auto decode = [&](int item, int& ta, int& tb, int& kc0, int& kc1) {
+        exchange_decode_tile(item % prm.n_tiles, ta, tb);
+        const int slice = item / prm.n_tiles;
         kc0 = slice * prm.chunks_per_slice;
         kc1 = min(prm.chunks, kc0 + prm.chunks_per_slice);
     };
 
     // ---- copy issue (thread 0 only), NSTAGE - 1 chunks ahead of the consumers ----
     PipeState pp;
-    int64_t p_item = blockIdx.x;
+    int p_j = j_begin;
     int p_kc = -1, p_kc1 = 0, p_col[4] = {0, 0, 0, 0}, p_nvalid = 0;
     auto produce = [&]() {
         while (p_kc < 0 || p_kc >= p_kc1) {  // next item (skips empty slices)
-            if (p_kc >= 0) p_item += gridDim.x;
-            if (p_item >= prm.n_items) return;
+            if (p_kc >= 0) p_j++;
+            if (p_j >= j_end) return;
             int ta, tb, kc0, kc1;
-            decode(p_item, ta, tb, kc0, kc1);
+            decode(prm.item_list[p_j], ta, tb, kc0, kc1);
             p_col[0] = 2 * ta; p_col[1] = 2 * ta + 1; p_col[2] = 2 * tb; p_col[3] = 2 * tb + 1;
             p_nvalid = 0;
 #pragma unroll
@@ -378,12 +464,17 @@ __global__ void __maxnreg__(MAX_REGS) k_exchange(XParams prm) {
 
     PipeState ps;
     const int g = lane >> 2, t = lane & 3;
-    const int wm = warp >> 2, wn = warp & 3;
-    const int nl0 = (wn & 1) * 32;
-    for (int64_t item = blockIdx.x; item < prm.n_items; item += gridDim.x) {
+    for (int j = j_begin; j < j_end; j++) {
+        const int item = prm.item_list[j];
         int ta, tb, kc0, kc1;
         decode(item, ta, tb, kc0, kc1);
-        const bool active = (2 * ta + wm < npt64) && (2 * tb + (wn >> 1) < npt64);
+        int r0, c0, mt, nt;
+        exchange_warp_block(ta, tb, warp, prm.N, r0, c0, mt, nt);
+        const bool active = mt > 0;
+        const bool whole = (mt == 8) && (nt == 4);
+        // operand tiles: rows 8 r0 .. live in A0 (r0 < 8) or A1, columns 8 c0 .. in B0 (c0 < 8) or B1; no block straddles
+        const int a_off = (r0 >> 3) * 2048 + (r0 & 7) * 8 * 32;
+        const int b_off = (2 + (c0 >> 3)) * 2048 + (c0 & 7) * 8 * 32;
         double acc[8][4][2];
 #pragma unroll
         for (int jm = 0; jm < 8; jm++)
@@ -392,36 +483,29 @@ __global__ void __maxnreg__(MAX_REGS) k_exchange(XParams prm) {
 
         for (int kc = kc0; kc < kc1; kc++) {
             mbar_wait(&full[ps.stage], ps.phase);
-            if (active) {
-                const double* sA = stages + (size_t)ps.stage * X_STAGE_DOUBLES + wm * 2048;
-                const double* sB = stages + (size_t)ps.stage * X_STAGE_DOUBLES + (2 + (wn >> 1)) * 2048;
-#pragma unroll 2
-                for (int k0 = 0; k0 < KSLAB; k0 += 4) {
-                    const int kr = k0 + t;
-                    double a[8], b[4];
-#pragma unroll
-                    for (int jm = 0; jm < 8; jm++) a[jm] = sA[(8 * jm + g) * 32 + (kr ^ ((g & 3) << 2))];
-#pragma unroll
-                    for (int jn = 0; jn < 4; jn++) b[jn] = sB[(nl0 + 8 * jn + g) * 32 + (kr ^ ((g & 3) << 2))];
-#pragma unroll
-                    for (int jm = 0; jm < 8; jm++)
-#pragma unroll
-                        for (int jn = 0; jn < 4; jn++) dmma(acc[jm][jn][0], acc[jm][jn][1], a[jm], b[jn]);
-                }
-            }
+            const double* sA = stages + (size_t)ps.stage * X_STAGE_DOUBLES + a_off;
+            const double* sB = stages + (size_t)ps.stage * X_STAGE_DOUBLES + b_off;
+            if (whole) x_slab<8, 4>(acc, sA, sB, g, t);
+            else if (nt == 4) x_slab_mt<4>(acc, sA, sB, g, t, mt);
+            else if (nt == 3) x_slab_mt<3>(acc, sA, sB, g, t, mt);
+            else if (nt == 2) x_slab_mt<2>(acc, sA, sB, g, t, mt);
+            else if (nt == 1) x_slab_mt<1>(acc, sA, sB, g, t, mt);
             __syncwarp();
             if (lane == 0) mbar_arrive(&empty[ps.stage]);
             ps.advance<NSTAGE>();
             if (is_producer) produce();
             __syncwarp();
         }
-        double* out = prm.Kpart + item * (128 * 128);
+        if (!active) continue;
+        double* out = prm.Kpart + (int64_t)item * (128 * 128);
 #pragma unroll
         for (int jm = 0; jm < 8; jm++) {
-            const int m = 64 * wm + 8 * jm + g;
+            if (jm >= mt) continue;
+            const int m = 8 * (r0 + jm) + g;
 #pragma unroll
             for (int jn = 0; jn < 4; jn++) {
-                const int n = 32 * wn + 8 * jn + 2 * t;
+                if (jn >= nt) continue;
+                const int n = 8 * (c0 + jn) + 2 * t;
                 *reinterpret_cast<double2*>(out + m * 128 + n) = make_double2(acc[jm][jn][0], acc[jm][jn][1]);
             }
         }
@@ -434,13 +518,15 @@ void launch_exchange(const Layout& L, Shard& s, int sm_count) {
     XParams prm;
     prm.W = s.W;
     prm.Kpart = s.Kpart;
+    prm.item_list = s.d_xitems;
+    prm.item_off = s.d_xoff;
     prm.npt64 = L.npt64;
     prm.n_tiles = s.xplan.n_tiles;
     prm.n_slices = s.xplan.n_slices;
     prm.chunks = s.xplan.chunks;
     prm.chunks_per_slice = s.xplan.chunks_per_slice;
-    prm.n_items = (int64_t)s.xplan.n_tiles * s.xplan.n_slices;
-    int grid = (int)std::min<int64_t>(prm.n_items, sm_count);
+    prm.N = (int)L.N;
+    const int grid = s.xplan.n_ctas;
     if (grid <= 0) return;
     size_t smem = exchange_smem_bytes();
     cudaFuncSetAttribute(k_exchange, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);

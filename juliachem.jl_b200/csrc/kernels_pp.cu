@@ -71,7 +71,7 @@ struct PPParams {
     const int32_t* off;
     const int32_t* q;
     int64_t rows;
-    int ldci, n_fn, n_nt, chunks, q_len, npt64, occ_pad;
+    int ldci, n_fn, n_nt, chunks, q_len, npt64, occ_w;
     int64_t n_items;
 };
 
@@ -158,15 +158,24 @@ __global__ void __launch_bounds__(PP_THREADS, 1) k_pp_half_transform(PPParams pr
     const int g = lane >> 2, t = lane & 3;
     const int m0 = (warp >> 2) * 64;
     const int n0 = (warp & 3) * 8 * NT;
+    // the partner count of the NEXT item is fetched while the current one computes (the k loop bound would otherwise
+    // wait on two dependent global loads at every item start)
+    auto count_of = [&](int64_t it) -> int {
+        if (it >= prm.n_items) return 0;
+        const int pf = (int)(it / chunks / n_nt);
+        return prm.off[pf + 1] - prm.off[pf];
+    };
+    int k4_next = count_of(blockIdx.x);
     for (int64_t item = blockIdx.x; item < prm.n_items; item += gridDim.x) {
         const int ch = (int)(item % chunks);
         const int64_t r1 = item / chunks;
         const int nt = (int)(r1 % n_nt);
         const int p = (int)(r1 / n_nt);
-        const int k4 = prm.off[p + 1] - prm.off[p];
+        const int k4 = k4_next;
+        k4_next = count_of(item + gridDim.x);
         const int rows_valid = min(PP_QC, prm.q_len - ch * PP_QC);
         const int mt_valid = max(0, min(8, (rows_valid - m0 + 7) >> 3));
-        const int nt_valid = max(0, min(NT, (prm.occ_pad - nt * NI - n0 + 7) >> 3));
+        const int nt_valid = max(0, min(NT, (prm.occ_w - nt * NI - n0 + 7) >> 3));
         const bool any = mt_valid > 0 && nt_valid > 0;
         const bool whole = mt_valid == 8 && nt_valid == NT;
         double acc[8][NT][2];
@@ -205,8 +214,8 @@ __global__ void __launch_bounds__(PP_THREADS, 1) k_pp_half_transform(PPParams pr
 #pragma unroll
             for (int jn = 0; jn < NT; jn++) {
                 const int i = nt * NI + n0 + 8 * jn + 2 * t;
-                if (i >= prm.occ_pad) continue;
-                const int64_t krow = Qrow * prm.occ_pad + i;
+                if (i >= prm.occ_w) continue;  // i and occ_w are even: the pair (i, i + 1) is in or out together
+                const int64_t krow = Qrow * prm.occ_w + i;
                 const int64_t kc = krow >> 5;
                 const int kr = (int)(krow & 31);
                 *reinterpret_cast<double2*>(prm.W + ((kc * prm.npt64 + p64) * 64 + pr) * 32 + (kr ^ sw)) =
@@ -215,6 +224,168 @@ __global__ void __launch_bounds__(PP_THREADS, 1) k_pp_half_transform(PPParams pr
         }
     }
 }
+
+// =====================================================================================================================
+// Coulomb over the partner-compacted copy: the rows with q >= p (a contiguous tail of every partner list, like the column
+// tails calculate_coulomb_screened walks, ScreenedDF.jl:326-358) are streamed twice, 1 KiB per row and chunk:
+//     V[Q]  = sum_rows Bc[chunk][row][Q] * dvec[row]          dvec = D[p,q] (x 2 off the diagonal, :305-316)
+//     J[row] = 2 * sum_Q Bc[chunk][row][Q] * V[Q]
+// Every partial sum is written to its own slot and reduced in a fixed order (no atomics: bit-reproducible).
+// =====================================================================================================================
+constexpr int PPJ_SLAB = 512;  // rows per block
+
+__device__ __forceinline__ double2 ld_stream2(const double* p) {
+    double2 v;
+    asm volatile("ld.global.nc.L1::no_allocate.v2.f64 {%0,%1}, [%2];" : "=d"(v.x), "=d"(v.y) : "l"(p));
+    return v;
+}
+
+// one warp per row: dvec[row] = w * sum_i Ci[p][i] * Ci[q][i]
+__global__ void __launch_bounds__(256) k_pp_density(const double* __restrict__ Ci, int ldci, int occ,
+                                                     const int32_t* __restrict__ rp, const int32_t* __restrict__ rq,
+                                                     const int32_t* __restrict__ jdst, double* __restrict__ dvec,
+                                                     int64_t rows) {
+    const int lane = threadIdx.x & 31;
+    const int64_t warp0 = (blockIdx.x * (int64_t)blockDim.x + threadIdx.x) >> 5;
+    const int64_t nwarps = ((int64_t)gridDim.x * blockDim.x) >> 5;
+    for (int64_t r = warp0; r < rows; r += nwarps) {
+        if (jdst[r] < 0) {
+            if (lane == 0) dvec[r] = 0.0;
+            continue;
+        }
+        const int p = rp[r], q = rq[r];
+        const double* cp = Ci + (int64_t)p * ldci;
+        const double* cq = Ci + (int64_t)q * ldci;
+        double acc = 0.0;
+        for (int i = lane; i < occ; i += 32) acc = fma(cp[i], cq[i], acc);
+        acc = warp_sum(acc);
+        if (lane == 0) dvec[r] = (p == q) ? acc : 2.0 * acc;
+    }
+}
+
+__global__ void __launch_bounds__(256) k_pp_coulomb_v(const double* __restrict__ Bc, const double* __restrict__ dvec,
+                                                       double* __restrict__ Vpart, int64_t rows, int qpad) {
+    __shared__ double part[8][PP_QC];
+    const int ch = blockIdx.y;
+    const int64_t r0 = (int64_t)blockIdx.x * PPJ_SLAB;
+    const int64_t r1 = min(rows, r0 + PPJ_SLAB);
+    const int w = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    const double* base = Bc + (int64_t)ch * rows * PP_QC + lane * 4;
+    double acc[4] = {0.0, 0.0, 0.0, 0.0};
+    for (int64_t r = r0 + w; r < r1; r += 32) {  // rows r, r+8, r+16, r+24: all = w (mod 8), so (row & 3) = w & 3
+        double d[4];
+        double2 x[4], y[4];
+#pragma unroll
+        for (int u = 0; u < 4; u++) d[u] = (r + 8 * u < r1) ? dvec[r + 8 * u] : 0.0;
+#pragma unroll
+        for (int u = 0; u < 4; u++) {
+            x[u] = y[u] = make_double2(0.0, 0.0);
+            if (d[u] != 0.0) {
+                const double* src = base + (r + 8 * u) * PP_QC;
+                x[u] = ld_stream2(src);
+                y[u] = ld_stream2(src + 2);
+            }
+        }
+#pragma unroll
+        for (int u = 0; u < 4; u++) {
+            acc[0] = fma(d[u], x[u].x, acc[0]);
+            acc[1] = fma(d[u], x[u].y, acc[1]);
+            acc[2] = fma(d[u], y[u].x, acc[2]);
+            acc[3] = fma(d[u], y[u].y, acc[3]);
+        }
+    }
+    const int lg = (lane * 4) ^ ((w & 3) << 2);  // un-swizzle: the auxiliary rows this thread's four columns hold
+#pragma unroll
+    for (int j = 0; j < 4; j++) part[w][lg + j] = acc[j];
+    __syncthreads();
+    if (threadIdx.x < PP_QC) {
+        double v = 0.0;
+#pragma unroll
+        for (int k = 0; k < 8; k++) v += part[k][threadIdx.x];
+        Vpart[(int64_t)blockIdx.x * qpad + ch * PP_QC + threadIdx.x] = v;
+    }
+}
+
+__global__ void k_pp_vreduce(const double* __restrict__ Vpart, double* __restrict__ V, int n_slab, int qpad, int q_len) {
+    const int Q = blockIdx.x * blockDim.x + threadIdx.x;
+    if (Q >= qpad) return;
+    double v = 0.0;
+    for (int s = 0; s < n_slab; s++) v += Vpart[(int64_t)s * qpad + Q];
+    if (Q < q_len) V[Q] = v;
+}
+
+__global__ void __launch_bounds__(256) k_pp_coulomb_j(const double* __restrict__ Bc, const double* __restrict__ V,
+                                                       const int32_t* __restrict__ jdst, double* __restrict__ Jpart,
+                                                       int64_t rows, int q_len) {
+    const int ch = blockIdx.y;
+    const int64_t r0 = (int64_t)blockIdx.x * PPJ_SLAB;
+    const int64_t r1 = min(rows, r0 + PPJ_SLAB);
+    const int w = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    const int lg = (lane * 4) ^ ((w & 3) << 2);
+    double v[4];
+#pragma unroll
+    for (int j = 0; j < 4; j++) {
+        const int Q = ch * PP_QC + lg + j;
+        v[j] = Q < q_len ? V[Q] : 0.0;
+    }
+    const double* base = Bc + (int64_t)ch * rows * PP_QC + lane * 4;
+    double* out = Jpart + (int64_t)ch * rows;
+    for (int64_t r = r0 + w; r < r1; r += 32) {
+        bool on[4];
+        double2 x[4], y[4];
+#pragma unroll
+        for (int u = 0; u < 4; u++) on[u] = (r + 8 * u < r1) && jdst[r + 8 * u] >= 0;
+#pragma unroll
+        for (int u = 0; u < 4; u++) {
+            x[u] = y[u] = make_double2(0.0, 0.0);
+            if (on[u]) {
+                const double* src = base + (r + 8 * u) * PP_QC;
+                x[u] = ld_stream2(src);
+                y[u] = ld_stream2(src + 2);
+            }
+        }
+#pragma unroll
+        for (int u = 0; u < 4; u++) {
+            if (!on[u]) continue;  // warp-uniform
+            double dot = fma(x[u].x, v[0], fma(x[u].y, v[1], fma(y[u].x, v[2], y[u].y * v[3])));
+            dot = warp_sum(dot);
+            if (lane == 0) out[r + 8 * u] = dot;
+        }
+    }
+}
+
+// Jt[tile-space offset of (hi, lo)] = 2 * sum_chunks Jpart[chunk][row]   (the epilogue reads Jt as before)
+__global__ void k_pp_jreduce(const double* __restrict__ Jpart, const int32_t* __restrict__ jdst, double* __restrict__ Jt,
+                             int64_t rows, int chunks) {
+    const int64_t r = blockIdx.x * (int64_t)blockDim.x + threadIdx.x;
+    if (r >= rows) return;
+    const int32_t dst = jdst[r];
+    if (dst < 0) return;
+    double s = 0.0;
+    for (int c = 0; c < chunks; c++) s += Jpart[(int64_t)c * rows + r];
+    Jt[dst] = 2.0 * s;
+}
+
+void launch_pp_density(const Layout& L, Shard& s) {
+    const int ldci = L.pp_n_nt * 32 * L.pp_nt;
+    const int blocks = (int)std::min<int64_t>((L.pp_rows + 7) / 8, 148 * 16);
+    if (blocks <= 0) return;
+    k_pp_density<<<blocks, 256, 0, s.stream>>>(s.Ci, ldci, (int)L.occ, s.d_pp_p, s.d_pp_q, s.d_pp_jdst, s.dvec, L.pp_rows);
+}
+
+void launch_pp_coulomb(const Layout& L, Shard& s, cudaStream_t st, cudaEvent_t ev_v) {
+    if (s.pp_chunks <= 0 || L.pp_rows <= 0) return;
+    const int n_slab = (int)((L.pp_rows + PPJ_SLAB - 1) / PPJ_SLAB);
+    const int qpad = s.pp_chunks * PP_QC;
+    dim3 grid((unsigned)n_slab, (unsigned)s.pp_chunks);
+    k_pp_coulomb_v<<<grid, 256, 0, st>>>(s.Bc, s.dvec, s.VpartP, L.pp_rows, qpad);
+    k_pp_vreduce<<<(qpad + 127) / 128, 128, 0, st>>>(s.VpartP, s.V, n_slab, qpad, (int)s.q_len);
+    if (ev_v) cudaEventRecord(ev_v, st);
+    k_pp_coulomb_j<<<grid, 256, 0, st>>>(s.Bc, s.V, s.d_pp_jdst, s.Jpart, L.pp_rows, (int)s.q_len);
+    k_pp_jreduce<<<(unsigned)((L.pp_rows + 255) / 256), 256, 0, st>>>(s.Jpart, s.d_pp_jdst, s.Jt, L.pp_rows, s.pp_chunks);
+}
+
+int64_t pp_coulomb_slabs(const Layout& L) { return (L.pp_rows + PPJ_SLAB - 1) / PPJ_SLAB; }
 
 static size_t pp_smem_bytes(int nt) {
     return (size_t)PP_NSTAGE * (PP_KS * PP_QC + PP_KS * (32 * nt + 4)) * 8 + 2 * PP_NSTAGE * 8 + 16;
@@ -254,7 +425,7 @@ void launch_pp_half_transform(const Layout& L, Shard& s, int sm_count) {
     prm.chunks = s.pp_chunks;
     prm.q_len = (int)s.q_len;
     prm.npt64 = L.npt64;
-    prm.occ_pad = L.occ_pad;
+    prm.occ_w = L.occ_w;
     prm.n_items = (int64_t)L.N * L.pp_n_nt * s.pp_chunks;
     const int grid = (int)std::min<int64_t>(prm.n_items, sm_count);
     if (grid <= 0) return;
