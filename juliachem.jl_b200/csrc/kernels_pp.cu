@@ -75,26 +75,54 @@ struct PPParams {
     int64_t n_items;
 };
 
-template <int NT, bool PARTIAL>
-__device__ __forceinline__ void pp_kstep(double (&acc)[8][NT][2], const double* __restrict__ sA,
-                                         const double* __restrict__ sC, int m0, int n0, int g, int t, int ks, int mt_valid,
-                                         int nt_valid) {
+// One pipeline stage (nks k-steps of 4 partner rows) of a warp block of MTV x NTV DMMA tiles inside the warp's 8 x NT
+// accumulator block.  MTV / NTV are compile-time: a predicated-off DMMA still takes its slot in the tensor pipe, so the
+// ragged last chunk and the ragged last orbital tile get their own instantiations instead of predicates.
+template <int NT, int MTV, int NTV>
+__device__ __forceinline__ void pp_slab(double (&acc)[8][NT][2], const double* __restrict__ sA,
+                                        const double* __restrict__ sC, int m0, int n0, int g, int t, int nks) {
     constexpr int LDC = 32 * NT + 4;
-    const int kr = 4 * ks + t;
-    double a[8], b[NT];
+    // (m0 + 8 jm + g) ^ (t << 2): the swizzle touches bits 2-3, 8 jm bit 3 and up -> one base for even jm, one for odd jm
+    const double* pa0 = sA + t * PP_QC + ((m0 + g) ^ (t << 2));
+    const double* pa1 = sA + t * PP_QC + ((m0 + 8 + g) ^ (t << 2)) - 8;
+    const double* pc = sC + t * LDC + n0 + g;
+#pragma unroll 2
+    for (int ks = 0; ks < nks; ks++) {
+        double a[MTV], b[NTV];
 #pragma unroll
-    for (int jm = 0; jm < 8; jm++) a[jm] = sA[kr * PP_QC + ((m0 + 8 * jm + g) ^ (t << 2))];
+        for (int jm = 0; jm < MTV; jm++) a[jm] = ((jm & 1) ? pa1 : pa0)[ks * 4 * PP_QC + 8 * jm];
 #pragma unroll
-    for (int jn = 0; jn < NT; jn++) b[jn] = sC[kr * LDC + n0 + 8 * jn + g];
+        for (int jn = 0; jn < NTV; jn++) b[jn] = pc[ks * 4 * LDC + 8 * jn];
 #pragma unroll
-    for (int jm = 0; jm < 8; jm++) {
-        if (PARTIAL && jm >= mt_valid) continue;
+        for (int jm = 0; jm < MTV; jm++)
 #pragma unroll
-        for (int jn = 0; jn < NT; jn++) {
-            if (PARTIAL && jn >= nt_valid) continue;
-            dmma(acc[jm][jn][0], acc[jm][jn][1], a[jm], b[jn]);
-        }
+            for (int jn = 0; jn < NTV; jn++) dmma(acc[jm][jn][0], acc[jm][jn][1], a[jm], b[jn]);
     }
+}
+
+template <int NT, int NTV>
+__device__ __forceinline__ void pp_slab_m(double (&acc)[8][NT][2], const double* sA, const double* sC, int m0, int n0,
+                                          int g, int t, int nks, int mtv) {
+    switch (mtv) {
+        case 1: pp_slab<NT, 1, NTV>(acc, sA, sC, m0, n0, g, t, nks); break;
+        case 2: pp_slab<NT, 2, NTV>(acc, sA, sC, m0, n0, g, t, nks); break;
+        case 3: pp_slab<NT, 3, NTV>(acc, sA, sC, m0, n0, g, t, nks); break;
+        case 4: pp_slab<NT, 4, NTV>(acc, sA, sC, m0, n0, g, t, nks); break;
+        case 5: pp_slab<NT, 5, NTV>(acc, sA, sC, m0, n0, g, t, nks); break;
+        case 6: pp_slab<NT, 6, NTV>(acc, sA, sC, m0, n0, g, t, nks); break;
+        case 7: pp_slab<NT, 7, NTV>(acc, sA, sC, m0, n0, g, t, nks); break;
+        case 8: pp_slab<NT, 8, NTV>(acc, sA, sC, m0, n0, g, t, nks); break;
+        default: break;
+    }
+}
+
+template <int NT>
+__device__ __forceinline__ void pp_slab_mn(double (&acc)[8][NT][2], const double* sA, const double* sC, int m0, int n0,
+                                           int g, int t, int nks, int mtv, int ntv) {
+    if (ntv == NT) pp_slab_m<NT, NT>(acc, sA, sC, m0, n0, g, t, nks, mtv);
+    else if (NT > 1 && ntv == 1) pp_slab_m<NT, 1>(acc, sA, sC, m0, n0, g, t, nks, mtv);
+    else if (NT > 2 && ntv == 2) pp_slab_m<NT, (NT > 2 ? 2 : 1)>(acc, sA, sC, m0, n0, g, t, nks, mtv);
+    else if (NT > 3 && ntv == 3) pp_slab_m<NT, (NT > 3 ? 3 : 1)>(acc, sA, sC, m0, n0, g, t, nks, mtv);
 }
 
 // One work item = (function p, chunk of 128 auxiliary rows, tile of NI = 32 NT occupied orbitals):
@@ -189,16 +217,8 @@ __global__ void __launch_bounds__(PP_THREADS, 1) k_pp_half_transform(PPParams pr
             mbar_wait(&full[ps.stage], ps.phase);
             const double* sA = stages + (size_t)ps.stage * STAGE_DOUBLES;
             const double* sC = sA + PP_KS * PP_QC;
-            if (whole) {
-                if (nks == PP_KS / 4) {
-#pragma unroll 2
-                    for (int ks = 0; ks < PP_KS / 4; ks++) pp_kstep<NT, false>(acc, sA, sC, m0, n0, g, t, ks, 8, NT);
-                } else {
-                    for (int ks = 0; ks < nks; ks++) pp_kstep<NT, false>(acc, sA, sC, m0, n0, g, t, ks, 8, NT);
-                }
-            } else if (any) {
-                for (int ks = 0; ks < nks; ks++) pp_kstep<NT, true>(acc, sA, sC, m0, n0, g, t, ks, mt_valid, nt_valid);
-            }
+            if (whole) pp_slab<NT, 8, NT>(acc, sA, sC, m0, n0, g, t, nks);
+            else if (any) pp_slab_mn<NT>(acc, sA, sC, m0, n0, g, t, nks, mt_valid, nt_valid);
             __syncwarp();
             if (lane == 0) mbar_arrive(&empty[ps.stage]);
             ps.advance<PP_NSTAGE>();
