@@ -37,6 +37,11 @@ if ROOT not in sys.path:
 
 METRIC = "DF-RHF Fock builds/sec"
 UNIT = "builds/s"
+# dram__bytes_read.sum + dram__bytes_write.sum per launch from the committed `ncu --set full` capture (not measured live:
+# a number taken under a profiler is never a bench value, and DRAM counters need the profiler)
+NCU_TRAFFIC_SOURCE = "profiles/r01_ncu_w50_full_f.txt (ncu --set full --clock-control none, per launch, bytes)"
+NCU_TRAFFIC = {("w50", 1, "exchange"): 54.181312e9 + 0.500081e9,
+               ("w50", 1, "half_transform"): 10.454650e9 + 12.052038e9}
 FP64_MICROBENCH_PEAK = 37.1  # TFLOP/s, DMMA issue peak measured by tools/microbench_fp64 (profiles/r01_microbench_fp64.log)
 
 
@@ -379,7 +384,8 @@ def run_b200(args):
             kern[k]["frac"] = kern[k]["achieved"] / peak_tf
         d = kern[dom]
         roofline = {"kernel": dom, "bound": d["bound"], "achieved": d["achieved"], "peak": d["peak"], "unit": d["unit"],
-                    "frac": d["frac"], "traffic": None,
+                    "frac": d["frac"], "traffic": NCU_TRAFFIC.get((args.workload, n_total, dom)),
+                    "traffic_source": NCU_TRAFFIC_SOURCE if (args.workload, n_total, dom) in NCU_TRAFFIC else None,
                     "peak_source": peak_src if d["bound"] == "tensor" else hbm_src,
                     "fp64_dmma_issue_peak_tflops": FP64_MICROBENCH_PEAK,
                     "jk_tensor_frac": tf(work["w_flops"] + work["k_flops"],

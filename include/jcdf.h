@@ -218,7 +218,12 @@ double jcdf_synthetic_value(uint64_t seed, int64_t Q_total, int64_t q_aux, int64
 /* Tuning knobs (tests, bench).  Names: "coulomb_fused" (1 = default: single-pass cooperative J kernel whenever a
  * row segment fits the shared-memory ring, 0 = two-pass sweeps), "coulomb_overlap" (two-pass sweeps on a second
  * stream, concurrent with the tensor-core kernels; default 0), "exchange_slices" (0 = automatic split of the K
- * contraction index).  Unknown names -> JCDF_ERR_INVALID.                                                       */
+ * contraction index), "regroup" (1 = default: mask-driven internal function order), "ht_mode" (half-transform kernel:
+ * 0 = default, chosen from the mask by executed DMMA count; 1 = 32 x 32 tiles with strip skipping; 2 = per-function
+ * partner lists over a partner-compacted copy of B = calculate_W_screened's own blocking, ScreenedDF.jl:242-289),
+ * "coulomb_pp" (1 = default: with the per-function kernel the Coulomb passes stream the compact copy too),
+ * "exchange_balance" (1 = default: cost-balanced exchange work lists; 0 = round-robin).  "regroup", "ht_mode",
+ * "exchange_slices" and "exchange_balance" must be set before jcdf_set_mask.  Unknown names -> JCDF_ERR_INVALID.   */
 int32_t jcdf_set_option(jcdf_handle* h, const char* name, int64_t value);
 
 /* Per-kernel device time of the last build of device `dev` in ms (CUDA events on the launching stream):

@@ -33,7 +33,7 @@ static int dev_alloc(T** p, size_t count) {
 // keep_metric: the two-centre metric / its inverse factor do not depend on the mask (jcdf_set_mask keeps them)
 static void free_shard_buffers(Shard& s, bool keep_metric = false) {
     cudaSetDevice(s.dev);
-    void* ptrs[] = {s.d_xitems, s.d_xoff, s.Bc, s.Ci, s.d_pp_off, s.d_pp_q, s.d_pp_src, s.d_pp_p, s.d_pp_jdst, s.dvec, s.VpartP, s.Jpart, s.Vpart, s.Vready, s.Bp, s.W, s.Cs, s.Craw, s.dt, s.Jt, s.V, s.Kpart, s.F, s.Hdev, s.Traw, s.d_tile_index, s.d_tile_a,
+    void* ptrs[] = {s.Ksum, s.d_xitems, s.d_xoff, s.Bc, s.Ci, s.d_pp_off, s.d_pp_q, s.d_pp_src, s.d_pp_p, s.d_pp_jdst, s.dvec, s.VpartP, s.Jpart, s.Vpart, s.Vready, s.Bp, s.W, s.Cs, s.Craw, s.dt, s.Jt, s.V, s.Kpart, s.F, s.Hdev, s.Traw, s.d_tile_index, s.d_tile_a,
                     s.d_tile_b, s.d_dest_of_col, s.d_fn_mask, s.d_kb_list, s.d_kb_count, s.d_perm, s.d_inv, s.d_tile_strips};
     for (void* p : ptrs)
         if (p) cudaFree(p);
@@ -50,6 +50,7 @@ static void free_shard_buffers(Shard& s, bool keep_metric = false) {
     s.d_pp_off = s.d_pp_q = s.d_pp_src = s.d_pp_p = s.d_pp_jdst = nullptr;
     s.dvec = s.VpartP = s.Jpart = nullptr;
     s.d_xitems = s.d_xoff = nullptr;
+    s.Ksum = nullptr;
     s.pp_chunks = 0;
     s.bc_valid = false;
     s.d_dest_of_col = nullptr;
@@ -136,6 +137,10 @@ static int alloc_shard_buffers(jcdf_handle* h, Shard& s) {
     if ((rc = dev_alloc(&s.Vpart, (size_t)std::max<int64_t>(s.q_len, 1) * h->sm_count))) return rc;
     if ((rc = dev_alloc(&s.Vready, (size_t)std::max<int64_t>(s.q_len, 1)))) return rc;
     if ((rc = dev_alloc(&s.Kpart, (size_t)s.xplan.n_tiles * s.xplan.n_slices * 128 * 128))) return rc;
+    // Kpart is zeroed once: blocks no warp owns (above the diagonal, beyond N) are never written but are summed by
+    // k_exchange_reduce, and uninitialised memory could hold NaN patterns
+    JC_CUDA(cudaMemsetAsync(s.Kpart, 0, (size_t)s.xplan.n_tiles * s.xplan.n_slices * 128 * 128 * sizeof(double), s.stream));
+    if ((rc = dev_alloc(&s.Ksum, (size_t)s.xplan.n_tiles * 128 * 128))) return rc;
     if ((rc = dev_alloc(&s.d_xitems, s.xplan.item_list.size()))) return rc;
     if ((rc = dev_alloc(&s.d_xoff, s.xplan.item_off.size()))) return rc;
     JC_CUDA(cudaMemcpyAsync(s.d_xitems, s.xplan.item_list.data(), sizeof(int32_t) * s.xplan.item_list.size(), cudaMemcpyHostToDevice, s.stream));
@@ -1097,7 +1102,8 @@ int32_t jcdf_get_layout(jcdf_handle* h, jcdf_layout_info* o) {
     // prep_cs, density, half_transform, exchange, coulomb (fused: 1, two-pass: 2), epilogue
     // per-function path with its own Coulomb: prep, density, half_transform, exchange, V, V reduce, J, J reduce, epilogue
     const bool ppj = !h->shards.empty() && L.pp_enabled && h->shards[0].Bc != nullptr && h->opt_coulomb_pp;
-    o->kernel_launches_per_build = (ppj ? 9 : ((!h->shards.empty() && h->shards[0].last_coulomb_fused) ? 6 : 7)) +
+    const int kred = (!h->shards.empty() && h->shards[0].xplan.n_slices > 1) ? 1 : 0;  // k_exchange_reduce
+    o->kernel_launches_per_build = kred + (ppj ? 9 : ((!h->shards.empty() && h->shards[0].last_coulomb_fused) ? 6 : 7)) +
                                    ((h->n_ranks * (int)h->shards.size() > 1) ? 1 : 0);  // + mirror after the all-reduce
     return JCDF_OK;
 }

@@ -86,6 +86,7 @@ struct Shard {
     double* Vpart = nullptr;   // [q_len][sm_count] per-CTA partial V of the fused Coulomb kernel
     unsigned int* Vready = nullptr;  // [q_len] chunk flags of the fused Coulomb kernel
     double* Kpart = nullptr;   // [n_tiles * n_slices][128*128]
+    double* Ksum = nullptr;    // [n_tiles][128*128] slices of Kpart summed (k_exchange_reduce)
     int32_t* d_xitems = nullptr;  // exchange item lists (ExchangePlan)
     int32_t* d_xoff = nullptr;
     double* F = nullptr;       // N x N column-major partial / reduced Fock

@@ -578,11 +578,34 @@ void launch_mirror_lower(const Layout& L, Shard& s) {
     k_mirror_lower<<<grid, block, 0, s.stream>>>(s.F, (int)L.N);
 }
 
+// Ksum[tile][m][n] = sum_slices Kpart[slice][tile][m][n], slices in ascending order (deterministic).  The slices are
+// read as coalesced streams here, so the permuted gather of the epilogue touches one L2-resident copy only.
+__global__ void k_exchange_reduce(const double* __restrict__ Kpart, double* __restrict__ Ksum, int64_t tile_elems_total,
+                                  int n_slices) {
+    const int64_t i = (blockIdx.x * (int64_t)blockDim.x + threadIdx.x) * 2;
+    if (i >= tile_elems_total) return;
+    double2 acc = make_double2(0.0, 0.0);
+    for (int s = 0; s < n_slices; s++) {
+        const double2 v = *reinterpret_cast<const double2*>(Kpart + (int64_t)s * tile_elems_total + i);
+        acc.x += v.x;
+        acc.y += v.y;
+    }
+    *reinterpret_cast<double2*>(Ksum + i) = acc;
+}
+
 void launch_epilogue(const Layout& L, Shard& s, bool add_H) {
+    const double* K = s.Kpart;
+    int n_slices = s.xplan.n_slices;
+    if (n_slices > 1) {
+        const int64_t total = (int64_t)s.xplan.n_tiles * 128 * 128;
+        k_exchange_reduce<<<(unsigned)((total / 2 + 255) / 256), 256, 0, s.stream>>>(s.Kpart, s.Ksum, total, n_slices);
+        K = s.Ksum;
+        n_slices = 1;
+    }
     dim3 block(128);
     dim3 grid((unsigned)((L.N + 127) / 128), (unsigned)L.N);
-    k_fock_epilogue<<<grid, block, 0, s.stream>>>(s.F, add_H ? s.Hdev : nullptr, s.Jt, s.Kpart, s.d_tile_index, s.d_perm,
-                                                  (int)L.N, L.nb, s.xplan.n_tiles, s.xplan.n_slices);
+    k_fock_epilogue<<<grid, block, 0, s.stream>>>(s.F, add_H ? s.Hdev : nullptr, s.Jt, K, s.d_tile_index, s.d_perm,
+                                                  (int)L.N, L.nb, s.xplan.n_tiles, n_slices);
 }
 
 }  // namespace jcdf

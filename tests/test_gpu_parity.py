@@ -46,7 +46,8 @@ def test_screened_parity(N, Q, occ, hw, fused, overlap, ht_mode, coulomb_pp):
     B, C_occ, H = random_inputs(N, Q, occ, seed=N + 17, mask=mask, decay=hw / 2.0)
     F_ref = oracle_fock(B, C_occ, H, mask)
     gd, F, st = _build(N, Q, occ, B, C_occ, H, mask, fused=fused, overlap=overlap, ht_mode=ht_mode, coulomb_pp=coulomb_pp)
-    assert gd.layout().kernel_launches_per_build == (9 if (ht_mode == 2 and coulomb_pp) else 6 if fused else 7)
+    base = 9 if (ht_mode == 2 and coulomb_pp) else 6 if fused else 7
+    assert gd.layout().kernel_launches_per_build in (base, base + 1)  # + k_exchange_reduce when the contraction is sliced
     li = gd.layout()
     assert li.pairs_kept == int(mask.sum())
     assert li.pairs_tri == int(np.tril(mask).sum())
