@@ -483,6 +483,10 @@ __global__ void __maxnreg__(MAX_REGS) k_exchange(XParams prm) {
 
         for (int kc = kc0; kc < kc1; kc++) {
             mbar_wait(&full[ps.stage], ps.phase);
+            // refill the slot every warp released one stage ago BEFORE computing this one: the copy then has two full
+            // stage times to land (issued after the compute it had one, and the wait on `full` showed up in the profile)
+            if (is_producer) produce();
+            __syncwarp();
             const double* sA = stages + (size_t)ps.stage * X_STAGE_DOUBLES + a_off;
             const double* sB = stages + (size_t)ps.stage * X_STAGE_DOUBLES + b_off;
             if (whole) x_slab<8, 4>(acc, sA, sB, g, t);
@@ -493,8 +497,6 @@ __global__ void __maxnreg__(MAX_REGS) k_exchange(XParams prm) {
             __syncwarp();
             if (lane == 0) mbar_arrive(&empty[ps.stage]);
             ps.advance<NSTAGE>();
-            if (is_producer) produce();
-            __syncwarp();
         }
         if (!active) continue;
         double* out = prm.Kpart + (int64_t)item * (128 * 128);
