@@ -230,6 +230,11 @@ int32_t jcdf_set_option(jcdf_handle* h, const char* name, int64_t value);
  * out[0..JCDF_N_STAGES) in the stage order above.                                                                */
 int32_t jcdf_last_kernel_ms(jcdf_handle* h, int32_t dev, double* out);
 
+/* Per-CTA busy time of the last exchange launch of device `dev`, in SM clock cycles (clock64 around the CTA's whole work
+ * list): out[0..n) for the first n persistent CTAs; returns the number of CTAs launched.  Profiling aid for the
+ * cost-balanced work lists (no reference counterpart).                                                            */
+int32_t jcdf_exchange_cta_cycles(jcdf_handle* h, int32_t dev, int64_t* out, int32_t n);
+
 /* The CUDA stream (cudaStream_t, returned as void*) every kernel, copy and all-reduce of device `dev` is issued on —
  * so a caller can bracket builds with its own CUDA events or order its own work against them (the fork's CUDA.jl
  * path uses the task-local default stream and CUDA.synchronize() instead, GPUDF.jl:206-263).                     */

@@ -33,7 +33,7 @@ static int dev_alloc(T** p, size_t count) {
 // keep_metric: the two-centre metric / its inverse factor do not depend on the mask (jcdf_set_mask keeps them)
 static void free_shard_buffers(Shard& s, bool keep_metric = false) {
     cudaSetDevice(s.dev);
-    void* ptrs[] = {s.Ksum, s.d_xitems, s.d_xoff, s.Bc, s.Ci, s.d_pp_off, s.d_pp_q, s.d_pp_src, s.d_pp_p, s.d_pp_jdst, s.dvec, s.VpartP, s.Jpart, s.Vpart, s.Vready, s.Bp, s.W, s.Cs, s.Craw, s.dt, s.Jt, s.V, s.Kpart, s.F, s.Hdev, s.Traw, s.d_tile_index, s.d_tile_a,
+    void* ptrs[] = {s.d_xcycles, s.Ksum, s.d_xitems, s.d_xoff, s.Bc, s.Ci, s.d_pp_off, s.d_pp_q, s.d_pp_src, s.d_pp_p, s.d_pp_jdst, s.dvec, s.VpartP, s.Jpart, s.Vpart, s.Vready, s.Bp, s.W, s.Cs, s.Craw, s.dt, s.Jt, s.V, s.Kpart, s.F, s.Hdev, s.Traw, s.d_tile_index, s.d_tile_a,
                     s.d_tile_b, s.d_dest_of_col, s.d_fn_mask, s.d_kb_list, s.d_kb_count, s.d_perm, s.d_inv, s.d_tile_strips};
     for (void* p : ptrs)
         if (p) cudaFree(p);
@@ -50,6 +50,7 @@ static void free_shard_buffers(Shard& s, bool keep_metric = false) {
     s.d_pp_off = s.d_pp_q = s.d_pp_src = s.d_pp_p = s.d_pp_jdst = nullptr;
     s.dvec = s.VpartP = s.Jpart = nullptr;
     s.d_xitems = s.d_xoff = nullptr;
+    s.d_xcycles = nullptr;
     s.Ksum = nullptr;
     s.pp_chunks = 0;
     s.bc_valid = false;
@@ -143,6 +144,7 @@ static int alloc_shard_buffers(jcdf_handle* h, Shard& s) {
     if ((rc = dev_alloc(&s.Ksum, (size_t)s.xplan.n_tiles * 128 * 128))) return rc;
     if ((rc = dev_alloc(&s.d_xitems, s.xplan.item_list.size()))) return rc;
     if ((rc = dev_alloc(&s.d_xoff, s.xplan.item_off.size()))) return rc;
+    if ((rc = dev_alloc(&s.d_xcycles, (size_t)std::max(1, s.xplan.n_ctas)))) return rc;
     JC_CUDA(cudaMemcpyAsync(s.d_xitems, s.xplan.item_list.data(), sizeof(int32_t) * s.xplan.item_list.size(), cudaMemcpyHostToDevice, s.stream));
     JC_CUDA(cudaMemcpyAsync(s.d_xoff, s.xplan.item_off.data(), sizeof(int32_t) * s.xplan.item_off.size(), cudaMemcpyHostToDevice, s.stream));
     if ((rc = dev_alloc(&s.F, (size_t)L.N * L.N))) return rc;
@@ -1153,6 +1155,19 @@ int32_t jcdf_last_kernel_ms(jcdf_handle* h, int32_t dev, double* out) {
     JC_REQUIRE(dev >= 0 && dev < (int)h->shards.size(), "jcdf_last_kernel_ms: device index out of range");
     for (int i = 0; i < JCDF_N_STAGES; i++) out[i] = h->shards[dev].last_ms[i];
     return JCDF_OK;
+}
+
+int32_t jcdf_exchange_cta_cycles(jcdf_handle* h, int32_t dev, int64_t* out, int32_t n) {
+    JC_REQUIRE(h && out, "jcdf_exchange_cta_cycles: NULL argument");
+    JC_REQUIRE(dev >= 0 && dev < (int)h->shards.size(), "jcdf_exchange_cta_cycles: device index out of range");
+    Shard& s = h->shards[dev];
+    JC_REQUIRE(s.d_xcycles != nullptr, "jcdf_exchange_cta_cycles: call jcdf_set_mask first");
+    const int m = std::min<int>(n, s.xplan.n_ctas);
+    JC_CUDA(cudaSetDevice(s.dev));
+    JC_CUDA(cudaStreamSynchronize(s.stream));
+    static_assert(sizeof(long long) == sizeof(int64_t), "clock64 width");
+    JC_CUDA(cudaMemcpy(out, s.d_xcycles, sizeof(int64_t) * (size_t)std::max(m, 0), cudaMemcpyDeviceToHost));
+    return s.xplan.n_ctas;
 }
 
 int32_t jcdf_get_stream(jcdf_handle* h, int32_t dev, void** stream_out) {

@@ -89,6 +89,7 @@ struct Shard {
     double* Ksum = nullptr;    // [n_tiles][128*128] slices of Kpart summed (k_exchange_reduce)
     int32_t* d_xitems = nullptr;  // exchange item lists (ExchangePlan)
     int32_t* d_xoff = nullptr;
+    long long* d_xcycles = nullptr;  // [n_ctas] busy cycles of the last exchange launch
     double* F = nullptr;       // N x N column-major partial / reduced Fock
     double* Hdev = nullptr;    // N x N (only where H is added)
     double* Traw = nullptr;    // staging window for uploads

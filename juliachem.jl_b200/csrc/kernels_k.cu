@@ -23,7 +23,7 @@ constexpr int CONSUMER_WARPS = 8;
 // fills that sub-partition's register file, so no Coulomb CTA could co-reside.)
 constexpr int CTA_THREADS = CONSUMER_WARPS * 32;
 constexpr int HT_THREADS = CTA_THREADS + 32;  // half-transform: plus one dedicated producer warp (168 registers/thread)
-constexpr int MAX_REGS = 208;  // leaves (16384 - 2*32*208) = 3072 registers per sub-partition for the Coulomb sweeps
+constexpr int MAX_REGS = 208;
 
 // =====================================================================================================================
 // C_occ re-layout and packed density
@@ -313,6 +313,7 @@ struct XParams {
     double* Kpart;
     const int32_t* item_list;  // items of CTA c: item_list[item_off[c] .. item_off[c + 1])  (cost-balanced on the host)
     const int32_t* item_off;
+    long long* cta_cycles;     // [gridDim.x] busy cycles of this launch (profiling aid)
     int npt64, n_tiles, n_slices, chunks, chunks_per_slice, N;
 };
 
@@ -323,19 +324,28 @@ constexpr int X_STAGE_DOUBLES = 4 * 32 * 64;  // A0 A1 B0 B1, each a [64 p][32 k
 //   * off-diagonal tiles: the plain 2 x 4 arrangement of 64 x 32 blocks;
 //   * diagonal tiles: only the lower triangle is needed (the reference computes its diagonal blocks whole,
 //     ScreenedDF.jl:596-601) — it is covered by eight rectangles chosen so that the two warps of every SM sub-partition
-//     (w and w + 4) together issue 10 of the 16 row units a full tile costs;
+//     (w and w + 4) together issue 6 + 4 = 10 of the 16 row units a full tile costs;
 //   * rows / columns beyond N (the last tile row) are clipped.
 // Shared by the kernel and the host-side cost model of plan_exchange.
 __host__ __device__ inline void exchange_warp_block(int ta, int tb, int warp, int N, int& r0, int& c0, int& mt, int& nt) {
     if (ta == tb) {
-        // warp:  0 = T1  1 = T2  2 = A1a  3 = A2a  4 = A1b  5 = A2b  6 = t1  7 = t2   (one nibble per warp)
-        //   r0 = {0, 8, 8, 8, 14, 14, 4, 12}   c0 = {0, 8, 0, 4, 0, 4, 4, 12}   mt = {8, 8, 6, 6, 2, 2, 4, 4}
-        r0 = (int)((0xC4EE8880u >> (4 * warp)) & 15u);
-        c0 = (int)((0xC4404080u >> (4 * warp)) & 15u);
-        mt = (int)((0x44226688u >> (4 * warp)) & 15u);
+        // Eight rectangles over the lower triangle of the 16 x 16 grid of 8 x 8 DMMA tiles, column strips of 4:
+        //   cols 0-3: rows 0-5, 6-11, 12-15   cols 4-7: rows 4-9, 10-15   cols 8-11: rows 8-11, 12-15   cols 12-15: rows 12-15
+        // paired (w, w + 4) as 6 + 4 row units on every sub-partition (an 8 + 2 pairing of the same cover measured the
+        // same to 0.3 %: the pipe total per sub-partition is what counts).
+        //   r0 = {0, 6, 4, 10, 12, 8, 12, 12}   c0 = {0, 0, 4, 4, 0, 8, 8, 12}   mt = {6, 6, 6, 6, 4, 4, 4, 4}
+        r0 = (int)((0xCC8CA460u >> (4 * warp)) & 15u);
+        c0 = (int)((0xC8804400u >> (4 * warp)) & 15u);
+        mt = (int)((0x44446666u >> (4 * warp)) & 15u);
         nt = 4;
     } else {
-        r0 = 8 * (warp >> 2); c0 = 4 * (warp & 3); mt = 8; nt = 4;
+        // column strip warp & 3; the valid rows of the tile (16 units, fewer in the last tile row) split evenly between
+        // the two warps of the sub-partition
+        const int rows16 = min(16, (N - 128 * ta + 7) >> 3);
+        const int half = (rows16 + 1) >> 1;
+        r0 = (warp >> 2) ? half : 0;
+        mt = (warp >> 2) ? rows16 - half : half;
+        c0 = 4 * (warp & 3); nt = 4;
     }
     const int rows8 = (N - 128 * ta + 7) >> 3, cols8 = (N - 128 * tb + 7) >> 3;
     mt = max(0, min(mt, rows8 - r0));
@@ -421,6 +431,7 @@ __global__ void __maxnreg__(MAX_REGS) k_exchange(XParams prm) {
     }
     __syncthreads();
 
+    const long long t_begin = clock64();
     const int npt64 = prm.npt64;
     const bool is_producer = (threadIdx.x == 0);
     const int j_begin = prm.item_off[blockIdx.x], j_end = prm.item_off[blockIdx.x + 1];
@@ -472,9 +483,9 @@ __global__ void __maxnreg__(MAX_REGS) k_exchange(XParams prm) {
         exchange_warp_block(ta, tb, warp, prm.N, r0, c0, mt, nt);
         const bool active = mt > 0;
         const bool whole = (mt == 8) && (nt == 4);
-        // operand tiles: rows 8 r0 .. live in A0 (r0 < 8) or A1, columns 8 c0 .. in B0 (c0 < 8) or B1; no block straddles
-        const int a_off = (r0 >> 3) * 2048 + (r0 & 7) * 8 * 32;
-        const int b_off = (2 + (c0 >> 3)) * 2048 + (c0 & 7) * 8 * 32;
+        // A0 | A1 and B0 | B1 are adjacent [64][32] tiles: 128 rows of one stride, so a block may straddle the pair
+        const int a_off = r0 * 8 * 32;
+        const int b_off = 2 * 2048 + c0 * 8 * 32;
         double acc[8][4][2];
 #pragma unroll
         for (int jm = 0; jm < 8; jm++)
@@ -484,7 +495,8 @@ __global__ void __maxnreg__(MAX_REGS) k_exchange(XParams prm) {
         for (int kc = kc0; kc < kc1; kc++) {
             mbar_wait(&full[ps.stage], ps.phase);
             // refill the slot every warp released one stage ago BEFORE computing this one: the copy then has two full
-            // stage times to land (issued after the compute it had one, and the wait on `full` showed up in the profile)
+            // stage times to land.  (Also tried: register double-buffering of the fragments across k-steps and stage
+            // boundaries — 244 registers, 3 % slower; the two warps per sub-partition already cover each other's bubbles.)
             if (is_producer) produce();
             __syncwarp();
             const double* sA = stages + (size_t)ps.stage * X_STAGE_DOUBLES + a_off;
@@ -512,6 +524,7 @@ __global__ void __maxnreg__(MAX_REGS) k_exchange(XParams prm) {
             }
         }
     }
+    if (threadIdx.x == 0) prm.cta_cycles[blockIdx.x] = clock64() - t_begin;
 }
 
 size_t exchange_smem_bytes() { return (size_t)NSTAGE * X_STAGE_DOUBLES * 8 + 2 * NSTAGE * 8 + 16; }
@@ -522,6 +535,7 @@ void launch_exchange(const Layout& L, Shard& s, int sm_count) {
     prm.Kpart = s.Kpart;
     prm.item_list = s.d_xitems;
     prm.item_off = s.d_xoff;
+    prm.cta_cycles = s.d_xcycles;
     prm.npt64 = L.npt64;
     prm.n_tiles = s.xplan.n_tiles;
     prm.n_slices = s.xplan.n_slices;

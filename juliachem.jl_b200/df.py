@@ -316,6 +316,15 @@ class B200Data:
         check(self._lib.jcdf_last_kernel_ms(self._h, dev, _ptr(out)))
         return dict(zip(STAGE_NAMES, out.tolist()))
 
+
+    def exchange_cta_cycles(self, dev: int = 0) -> np.ndarray:
+        """Busy cycles of every persistent CTA of the last exchange launch (profiling aid)."""
+        out = np.zeros(1024, dtype=np.int64)
+        n = self._lib.jcdf_exchange_cta_cycles(self._h, dev, _ptr(out), 1024)
+        if n < 0:
+            check(n)
+        return out[:n]
+
     def stream(self, dev: int = 0) -> int:
         """cudaStream_t (as an integer) the builds of device `dev` run on — wrap with torch.cuda.ExternalStream."""
         out = C.c_void_p()
