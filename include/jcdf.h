@@ -215,8 +215,9 @@ int32_t jcdf_get_layout(jcdf_handle* h, jcdf_layout_info* out);
 int32_t jcdf_fill_synthetic_B(jcdf_handle* h, uint64_t seed, double decay_length);
 double jcdf_synthetic_value(uint64_t seed, int64_t Q_total, int64_t q_aux, int64_t p, int64_t q, double decay_length);
 
-/* Tuning knobs (tests, bench).  Names: "coulomb_fused" (1 = default: single-pass cooperative J kernel whenever a
- * row segment fits the shared-memory ring, 0 = two-pass sweeps), "coulomb_overlap" (two-pass sweeps on a second
+/* Tuning knobs (tests, bench).  Names: "coulomb_fused" (tile-family Coulomb: 2 = default, single-pass cooperative J
+ * kernel on long column segments and two-pass sweeps on short ones; 1 = single pass whenever a row segment fits the
+ * shared-memory ring; 0 = two-pass sweeps), "coulomb_overlap" (two-pass sweeps on a second
  * stream, concurrent with the tensor-core kernels; default 0), "exchange_slices" (0 = automatic split of the K
  * contraction index), "regroup" (1 = default: mask-driven internal function order), "ht_mode" (half-transform kernel:
  * 0 = default, chosen from the mask by executed DMMA count; 1 = 32 x 32 tiles with strip skipping; 2 = per-function

@@ -358,7 +358,9 @@ static void build_partner_lists(jcdf_handle* h, Kept kept) {
     }
     const double cost_pp = (double)rows * L.pp_n_nt * 32.0 * L.pp_nt;
     if (rows >= ((int64_t)1 << 31)) return;
-    if (h->opt_ht_mode != 2 && !(cost_pp < 0.85 * cost_tiles)) return;
+    // measured on the C20H42 shape (52.8 % of the pairs kept, cost ratio 0.93): per-function 18.2 ms + compact Coulomb
+    // 4.4 ms against tiles 19.3 ms + 5.3 ms — the compact family wins as soon as it executes fewer DMMAs at all
+    if (h->opt_ht_mode != 2 && !(cost_pp < 0.97 * cost_tiles)) return;
     L.pp_rows = rows;
     L.pp_off.resize((size_t)N + 1);
     L.pp_q.reserve((size_t)rows);
@@ -936,7 +938,12 @@ int fock_build_impl(jcdf_handle* h, const double* C_occ, int64_t ldc, const doub
             s.last_coulomb_fused = false;
             launch_pp_coulomb(L, s, sj, s.ev[EV_V]);
         } else {
-            s.last_coulomb_fused = h->opt_coulomb_fused && launch_coulomb_fused(L, s, h->sm_count, sj);
+            // fused single pass pays off on long column segments (w50 dense: 3.8 TB/s effective against <= 3.05 for two
+            // passes at the copy bandwidth); on short ones its per-chunk grid-wide flags dominate and two streaming
+            // passes are faster (measured: benzene dimer 1.01 -> 0.91 ms, C20H42 5.54 -> 5.26 ms)
+            const bool want_fused = h->opt_coulomb_fused == 1 ||
+                                    (h->opt_coulomb_fused == 2 && L.row_len / std::max(1, h->sm_count) >= 4500);
+            s.last_coulomb_fused = want_fused && launch_coulomb_fused(L, s, h->sm_count, sj);
             if (!s.last_coulomb_fused) launch_coulomb(L, s, h->sm_count, sj);
         }
         s.last_pp_j = pp_j;

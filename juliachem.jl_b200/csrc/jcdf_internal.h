@@ -130,7 +130,8 @@ struct jcdf_handle {
     bool shards_set = false;
     int sm_count = 148;
     std::vector<double> host_metric;
-    int64_t opt_coulomb_fused = 1;    // single-pass cooperative Coulomb kernel whenever the row segment fits in smem
+    int64_t opt_coulomb_fused = 2;    // tile-family Coulomb: 2 = single-pass cooperative kernel on long column segments,
+                                      // two streaming passes on short ones; 1 = single pass whenever it fits; 0 = two passes
     int64_t opt_coulomb_overlap = 0;  // two-pass sweeps on a second stream, concurrent with the tensor-core kernels
     int64_t opt_exchange_slices = 0;
     int64_t opt_exchange_balance = 1;  // cost-balanced exchange item lists (0: round-robin in item order)

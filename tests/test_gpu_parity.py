@@ -301,6 +301,47 @@ def test_per_function_half_transform(N, Q, occ, ht_mode, coulomb_pp):
     gd.close()
 
 
+@pytest.mark.parametrize("N,Q,occ", [(128, 40, 12), (256, 130, 30), (40, 5, 3), (130, 128, 64)])
+@pytest.mark.parametrize("ht_mode", [1, 2])
+def test_tile_edge_sizes(N, Q, occ, ht_mode):
+    """Sizes on the edges of the blockings: N an exact multiple of the 128-wide exchange tile (no clipping), one tile only
+    (diagonal rectangles alone), Q below / exactly one 128-row chunk, occ = 64 (two full orbital tiles of 32)."""
+    mask = _scattered_mask(N, 7, 1, seed=N + Q)
+    B, C_occ, H = random_inputs(N, Q, occ, seed=N + Q + 1, mask=mask)
+    F_ref = oracle_fock(B, C_occ, H, mask)
+    gd, F, _ = _build(N, Q, occ, B, C_occ, H, mask, ht_mode=ht_mode)
+    assert np.abs(F - F_ref).max() < TOL
+    assert np.array_equal(F, F.T)
+    gd.close()
+
+
+def test_isolated_functions_and_empty_shard():
+    """Functions whose only kept partner is themselves (partner list of 1, padded to 4 rows) and a device-less corner:
+    a shard of zero auxiliary rows next to a full one on the same handle layout (q_len = 0 must launch nothing)."""
+    N, Q, occ = 97, 33, 11
+    mask = _scattered_mask(N, 11, 1, seed=2)
+    iso = [3, 50, 96]
+    mask[iso, :] = False
+    mask[:, iso] = False
+    mask[iso, iso] = True
+    mask = np.asfortranarray(mask)
+    B, C_occ, H = random_inputs(N, Q, occ, seed=77, mask=mask)
+    F_ref = oracle_fock(B, C_occ, H, mask)
+    for mode in (1, 2):
+        gd, F, _ = _build(N, Q, occ, B, C_occ, H, mask, ht_mode=mode)
+        assert np.abs(F - F_ref).max() < TOL
+        gd.close()
+    # empty shard: H only
+    gd = jc.B200Data(N, Q, occ, 1)
+    gd.set_shards([range(0, 0)])
+    gd.set_option("ht_mode", 2)
+    gd.set_mask(jc.ScreeningData(mask, N))
+    gd.set_B(0, np.zeros((0, int(mask.sum())), order="F"))
+    F, _ = gd.fock_build(C_occ, H)
+    assert np.abs(F - H).max() == 0.0
+    gd.close()
+
+
 def test_half_transform_kernels_agree_on_sharded_run():
     """Two shards on one device, per-function kernel on each, against the tile kernel: same Fock matrix to 1e-10."""
     N, Q, occ = 150, 200, 33
