@@ -224,22 +224,26 @@ __global__ void __launch_bounds__(PP_THREADS, 1) k_pp_half_transform(PPParams pr
             ps.advance<PP_NSTAGE>();
         }
         if (!any) continue;
-        // epilogue: the thread's (i, i + 1) pair is adjacent in the k-fastest W tile -> 16-byte stores, 4 lanes = 64 bytes
-        const int p64 = p >> 6, pr = p & 63;
+        // epilogue: the thread's (i, i + 1) pair is adjacent in the k-fastest W tile -> 16-byte stores, 4 lanes = 64 bytes.
+        // 32-bit index arithmetic up to the tile number (k rows and tiles are far below 2^31), one wide multiply per store.
+        const int pr = p & 63;
         const int sw = (pr & 3) << 2;
+        double* const wbase = prm.W + ((int64_t)(p >> 6) * 64 + pr) * 32;
+        const int tile_stride = prm.npt64;  // W tiles per k chunk
+        const int i0 = nt * NI + n0 + 2 * t;
+        const int q0 = ch * PP_QC + m0 + g;
+        const bool all_in = (mt_valid == 8) && (nt * NI + n0 + 8 * NT <= prm.occ_w);
 #pragma unroll
         for (int jm = 0; jm < 8; jm++) {
-            const int64_t Qrow = (int64_t)ch * PP_QC + m0 + 8 * jm + g;
-            if (Qrow >= prm.q_len) continue;
+            const int Qrow = q0 + 8 * jm;
+            if (!all_in && Qrow >= prm.q_len) continue;
+            const int krow0 = Qrow * prm.occ_w + i0;
 #pragma unroll
             for (int jn = 0; jn < NT; jn++) {
-                const int i = nt * NI + n0 + 8 * jn + 2 * t;
-                if (i >= prm.occ_w) continue;  // i and occ_w are even: the pair (i, i + 1) is in or out together
-                const int64_t krow = Qrow * prm.occ_w + i;
-                const int64_t kc = krow >> 5;
-                const int kr = (int)(krow & 31);
-                *reinterpret_cast<double2*>(prm.W + ((kc * prm.npt64 + p64) * 64 + pr) * 32 + (kr ^ sw)) =
-                    make_double2(acc[jm][jn][0], acc[jm][jn][1]);
+                if (!all_in && i0 + 8 * jn >= prm.occ_w) continue;  // i and occ_w are even: the pair is in or out together
+                const int krow = krow0 + 8 * jn;
+                double* dst = wbase + (int64_t)((krow >> 5) * tile_stride) * 2048 + ((krow & 31) ^ sw);
+                *reinterpret_cast<double2*>(dst) = make_double2(acc[jm][jn][0], acc[jm][jn][1]);
             }
         }
     }
