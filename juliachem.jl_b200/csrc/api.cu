@@ -929,7 +929,7 @@ int fock_build_impl(jcdf_handle* h, const double* C_occ, int64_t ldc, const doub
         // Coulomb sweeps (HBM-bound, 32-40 registers, no dynamic smem).  With coulomb_overlap they go to a second,
         // lower-priority stream: their CTAs co-reside with the persistent tensor-core CTAs (one per SM, compute-bound,
         // issue slots ~16 % busy) and soak up the idle HBM bandwidth instead of queueing behind them.
-        const bool overlap = h->opt_coulomb_overlap && !h->opt_coulomb_fused && !pp_j;
+        const bool overlap = h->opt_coulomb_overlap && (pp_j || !h->opt_coulomb_fused);
         cudaStream_t sj = overlap ? s.stream_j : s.stream;
         if (overlap) JC_CUDA(cudaStreamWaitEvent(sj, s.ev[EV_PREP], 0));
         JC_CUDA(cudaEventRecord(s.ev[EV_JBEGIN], sj));
@@ -995,7 +995,7 @@ int fock_build_impl(jcdf_handle* h, const double* C_occ, int64_t ldc, const doub
         s.last_ms[JCDF_T_K] = el(EV_W, EV_K);
         s.last_ms[JCDF_T_V] = el(EV_JBEGIN, EV_V);
         s.last_ms[JCDF_T_J] = el(EV_V, EV_J);
-        s.last_ms[JCDF_T_EPILOGUE] = (h->opt_coulomb_overlap && !h->opt_coulomb_fused && !s.last_pp_j) ? el(EV_K, EV_EPI) : el(EV_J, EV_EPI);
+        s.last_ms[JCDF_T_EPILOGUE] = (h->opt_coulomb_overlap && (s.last_pp_j || !h->opt_coulomb_fused)) ? el(EV_K, EV_EPI) : el(EV_J, EV_EPI);
         s.last_ms[JCDF_T_ALLREDUCE] = el(EV_EPI, EV_AR);
         s.last_ms[JCDF_T_D2H] = d == 0 ? el(EV_AR, EV_D2H) : 0.0;
         s.last_ms[JCDF_T_TOTAL] = std::chrono::duration<double, std::milli>(t1 - t0).count();
