@@ -454,6 +454,7 @@ __global__ void __maxnreg__(MAX_REGS) k_exchange(XParams prm) {
             int ta, tb, kc0, kc1;
             decode(prm.item_list[p_j], ta, tb, kc0, kc1);
             p_col[0] = 2 * ta; p_col[1] = 2 * ta + 1; p_col[2] = 2 * tb; p_col[3] = 2 * tb + 1;
+            if (ta == tb) p_col[2] = p_col[3] = npt64;  // diagonal tile: B0 B1 = A0 A1, read from the A slots
             p_nvalid = 0;
 #pragma unroll
             for (int x = 0; x < 4; x++) p_nvalid += (p_col[x] < npt64);
@@ -485,7 +486,7 @@ __global__ void __maxnreg__(MAX_REGS) k_exchange(XParams prm) {
         const bool whole = (mt == 8) && (nt == 4);
         // A0 | A1 and B0 | B1 are adjacent [64][32] tiles: 128 rows of one stride, so a block may straddle the pair
         const int a_off = r0 * 8 * 32;
-        const int b_off = 2 * 2048 + c0 * 8 * 32;
+        const int b_off = (ta == tb ? 0 : 2 * 2048) + c0 * 8 * 32;
         double acc[8][4][2];
 #pragma unroll
         for (int jm = 0; jm < 8; jm++)
