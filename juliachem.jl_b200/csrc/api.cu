@@ -33,7 +33,7 @@ static int dev_alloc(T** p, size_t count) {
 // keep_metric: the two-centre metric / its inverse factor do not depend on the mask (jcdf_set_mask keeps them)
 static void free_shard_buffers(Shard& s, bool keep_metric = false) {
     cudaSetDevice(s.dev);
-    void* ptrs[] = {s.d_xcycles, s.Ksum, s.d_xitems, s.d_xoff, s.Bc, s.Ci, s.d_pp_off, s.d_pp_q, s.d_pp_src, s.d_pp_p, s.d_pp_jdst, s.dvec, s.VpartP, s.Jpart, s.Vpart, s.Vready, s.Bp, s.W, s.Cs, s.Craw, s.dt, s.Jt, s.V, s.Kpart, s.F, s.Hdev, s.Traw, s.d_tile_index, s.d_tile_a,
+    void* ptrs[] = {s.d_ppitems, s.d_ppoff, s.d_xcycles, s.Ksum, s.d_xitems, s.d_xoff, s.Bc, s.Ci, s.d_pp_off, s.d_pp_q, s.d_pp_src, s.d_pp_p, s.d_pp_jdst, s.dvec, s.VpartP, s.Jpart, s.Vpart, s.Vready, s.Bp, s.W, s.Cs, s.Craw, s.dt, s.Jt, s.V, s.Kpart, s.F, s.Hdev, s.Traw, s.d_tile_index, s.d_tile_a,
                     s.d_tile_b, s.d_dest_of_col, s.d_fn_mask, s.d_kb_list, s.d_kb_count, s.d_perm, s.d_inv, s.d_tile_strips};
     for (void* p : ptrs)
         if (p) cudaFree(p);
@@ -51,6 +51,8 @@ static void free_shard_buffers(Shard& s, bool keep_metric = false) {
     s.dvec = s.VpartP = s.Jpart = nullptr;
     s.d_xitems = s.d_xoff = nullptr;
     s.d_xcycles = nullptr;
+    s.d_ppitems = s.d_ppoff = nullptr;
+    s.pp_ctas = 0;
     s.Ksum = nullptr;
     s.pp_chunks = 0;
     s.bc_valid = false;
@@ -197,6 +199,14 @@ static int alloc_shard_buffers(jcdf_handle* h, Shard& s) {
             if ((rc = dev_alloc(&s.d_pp_jdst, L.pp_jdst.size()))) return rc;
             JC_CUDA(cudaMemcpyAsync(s.d_pp_p, L.pp_p.data(), sizeof(int32_t) * L.pp_p.size(), cudaMemcpyHostToDevice, s.stream));
             JC_CUDA(cudaMemcpyAsync(s.d_pp_jdst, L.pp_jdst.data(), sizeof(int32_t) * L.pp_jdst.size(), cudaMemcpyHostToDevice, s.stream));
+            {
+                std::vector<int32_t> list, off;
+                plan_pp_items(L, s, h->sm_count, list, off);
+                if ((rc = dev_alloc(&s.d_ppitems, list.size()))) return rc;
+                if ((rc = dev_alloc(&s.d_ppoff, off.size()))) return rc;
+                JC_CUDA(cudaMemcpy(s.d_ppitems, list.data(), sizeof(int32_t) * list.size(), cudaMemcpyHostToDevice));
+                JC_CUDA(cudaMemcpy(s.d_ppoff, off.data(), sizeof(int32_t) * off.size(), cudaMemcpyHostToDevice));
+            }
             if ((rc = dev_alloc(&s.dvec, (size_t)L.pp_rows))) return rc;
             if ((rc = dev_alloc(&s.VpartP, (size_t)pp_coulomb_slabs(L) * s.pp_chunks * 128))) return rc;
             if ((rc = dev_alloc(&s.Jpart, (size_t)s.pp_chunks * L.pp_rows))) return rc;

@@ -72,6 +72,9 @@ struct Shard {
     int32_t* d_pp_src = nullptr;
     int32_t* d_pp_p = nullptr;
     int32_t* d_pp_jdst = nullptr;
+    int32_t* d_ppitems = nullptr;  // cost-balanced work lists of the per-function half-transform
+    int32_t* d_ppoff = nullptr;
+    int pp_ctas = 0;
     double* dvec = nullptr;    // [pp_rows] weighted density in partner-row space
     double* VpartP = nullptr;  // [slabs][pp_chunks * 128] partial V of the compact Coulomb pass
     double* Jpart = nullptr;   // [pp_chunks][pp_rows] partial J per chunk
@@ -153,6 +156,7 @@ void launch_pp_pack(const Layout& L, Shard& s);                        // kernel
 void launch_pp_prep(const Layout& L, Shard& s, int64_t ldc);           // C_occ -> Ci
 void launch_pp_half_transform(const Layout& L, Shard& s, int sm_count);
 void launch_pp_density(const Layout& L, Shard& s);
+void plan_pp_items(const Layout& L, Shard& s, int sm_count, std::vector<int32_t>& list, std::vector<int32_t>& off);
 void launch_pp_coulomb(const Layout& L, Shard& s, cudaStream_t st, cudaEvent_t ev_v);
 int64_t pp_coulomb_slabs(const Layout& L);
 void launch_exchange(const Layout& L, Shard& s, int sm_count);

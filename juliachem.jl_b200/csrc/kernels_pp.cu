@@ -16,6 +16,8 @@
 //
 // Executed flops = 2 Q occ_tile sum_p ceil4(K_p): 1.02 x the algorithmic count at w50.
 #include <algorithm>
+#include <utility>
+#include <vector>
 
 #include "dmma_common.cuh"
 #include "jcdf_internal.h"
@@ -72,7 +74,8 @@ struct PPParams {
     const int32_t* q;
     int64_t rows;
     int ldci, n_fn, n_nt, chunks, q_len, npt64, occ_w;
-    int64_t n_items;
+    const int32_t* item_list;  // items of CTA c: item_list[item_off[c] .. item_off[c + 1])  (cost-balanced on the host)
+    const int32_t* item_off;
 };
 
 // One pipeline stage (nks k-steps of 4 partner rows) of a warp block of MTV x NTV DMMA tiles inside the warp's 8 x NT
@@ -154,7 +157,8 @@ __global__ void __launch_bounds__(PP_THREADS, 1) k_pp_half_transform(PPParams pr
     if (warp == PP_CONSUMERS) {
         // ------------------------------------------------ producer warp ------------------------------------------------
         PipeState pp;
-        for (int64_t item = blockIdx.x; item < prm.n_items; item += gridDim.x) {
+        for (int j = prm.item_off[blockIdx.x]; j < prm.item_off[blockIdx.x + 1]; j++) {
+            const int item = prm.item_list[j];
             const int ch = (int)(item % chunks);
             const int64_t r1 = item / chunks;
             const int nt = (int)(r1 % n_nt);
@@ -188,19 +192,21 @@ __global__ void __launch_bounds__(PP_THREADS, 1) k_pp_half_transform(PPParams pr
     const int n0 = (warp & 3) * 8 * NT;
     // the partner count of the NEXT item is fetched while the current one computes (the k loop bound would otherwise
     // wait on two dependent global loads at every item start)
-    auto count_of = [&](int64_t it) -> int {
-        if (it >= prm.n_items) return 0;
-        const int pf = (int)(it / chunks / n_nt);
+    const int j_end = prm.item_off[blockIdx.x + 1];
+    auto count_of = [&](int jj) -> int {
+        if (jj >= j_end) return 0;
+        const int pf = prm.item_list[jj] / chunks / n_nt;
         return prm.off[pf + 1] - prm.off[pf];
     };
-    int k4_next = count_of(blockIdx.x);
-    for (int64_t item = blockIdx.x; item < prm.n_items; item += gridDim.x) {
+    int k4_next = count_of(prm.item_off[blockIdx.x]);
+    for (int j = prm.item_off[blockIdx.x]; j < j_end; j++) {
+        const int item = prm.item_list[j];
         const int ch = (int)(item % chunks);
         const int64_t r1 = item / chunks;
         const int nt = (int)(r1 % n_nt);
         const int p = (int)(r1 / n_nt);
         const int k4 = k4_next;
-        k4_next = count_of(item + gridDim.x);
+        k4_next = count_of(j + 1);
         const int rows_valid = min(PP_QC, prm.q_len - ch * PP_QC);
         const int mt_valid = max(0, min(8, (rows_valid - m0 + 7) >> 3));
         const int nt_valid = max(0, min(NT, (prm.occ_w - nt * NI - n0 + 7) >> 3));
@@ -422,6 +428,61 @@ static void launch_pp_t(const PPParams& prm, int grid, cudaStream_t st) {
     k_pp_half_transform<NT><<<grid, PP_THREADS, smem, st>>>(prm);
 }
 
+// Work lists of the per-function half-transform.  Items differ in cost — the partner count of p, the ragged last
+// 128-row chunk, the ragged last orbital tile — and a static round-robin aliases with the chunk count (gly18 shard,
+// 10 chunks of which the last holds 15 rows: CTAs of one parity got all the cheap items and the others 11 % more than
+// the mean).  Items are dealt longest-first onto the least-loaded CTA from the DMMA count the busiest sub-partition
+// issues; each CTA then walks its list in ascending (p-major) order so co-running CTAs share C rows in L2.
+void plan_pp_items(const Layout& L, Shard& s, int sm_count, std::vector<int32_t>& list, std::vector<int32_t>& off) {
+    const int chunks = s.pp_chunks, n_nt = L.pp_n_nt, NT = L.pp_nt;
+    const int64_t n_items = (int64_t)L.N * n_nt * chunks;
+    const int n_ctas = (int)std::max<int64_t>(1, std::min<int64_t>(n_items, sm_count));
+    s.pp_ctas = n_items > 0 ? n_ctas : 0;
+    list.clear();
+    off.assign((size_t)n_ctas + 1, 0);
+    if (n_items <= 0 || n_items >= ((int64_t)1 << 31)) { s.pp_ctas = 0; return; }
+    // row units of a chunk (both 64-row halves of the CTA tile) and orbital tiles of the busiest warp column
+    std::vector<int> m_units((size_t)chunks), n_units((size_t)n_nt);
+    for (int ch = 0; ch < chunks; ch++) {
+        const int rows = (int)std::min<int64_t>(PP_QC, s.q_len - (int64_t)ch * PP_QC);
+        const int m0 = std::max(0, std::min(8, (rows + 7) >> 3)), m1 = std::max(0, std::min(8, (rows - 64 + 7) >> 3));
+        m_units[(size_t)ch] = m0 + m1;
+    }
+    for (int nt = 0; nt < n_nt; nt++)
+        n_units[(size_t)nt] = std::max(0, std::min(NT, (L.occ_w - nt * 32 * NT + 7) >> 3));
+    std::vector<int64_t> cost((size_t)n_items);
+    std::vector<int32_t> order((size_t)n_items);
+    for (int64_t it = 0; it < n_items; it++) {
+        const int ch = (int)(it % chunks);
+        const int nt = (int)((it / chunks) % n_nt);
+        const int p = (int)(it / chunks / n_nt);
+        const int ksteps = (L.pp_off[(size_t)p + 1] - L.pp_off[(size_t)p]) / 4;
+        // 16 pipe cycles per DMMA; ~1500 cycles of epilogue and ramp per item
+        cost[(size_t)it] = (int64_t)ksteps * m_units[(size_t)ch] * n_units[(size_t)nt] * 16 + 1500;
+        order[(size_t)it] = (int32_t)it;
+    }
+    std::stable_sort(order.begin(), order.end(), [&](int32_t a, int32_t b) { return cost[(size_t)a] > cost[(size_t)b]; });
+    // least-loaded CTA through a binary heap of (load, cta)
+    std::vector<std::pair<int64_t, int>> heap;
+    for (int c = 0; c < n_ctas; c++) heap.emplace_back(0, c);
+    auto cmp = [](const std::pair<int64_t, int>& a, const std::pair<int64_t, int>& b) { return a > b; };
+    std::make_heap(heap.begin(), heap.end(), cmp);
+    std::vector<std::vector<int32_t>> bins((size_t)n_ctas);
+    for (int32_t it : order) {
+        std::pop_heap(heap.begin(), heap.end(), cmp);
+        auto& top = heap.back();
+        top.first += cost[(size_t)it];
+        bins[(size_t)top.second].push_back(it);
+        std::push_heap(heap.begin(), heap.end(), cmp);
+    }
+    for (int c = 0; c < n_ctas; c++) {
+        std::sort(bins[(size_t)c].begin(), bins[(size_t)c].end());
+        off[(size_t)c] = (int32_t)list.size();
+        list.insert(list.end(), bins[(size_t)c].begin(), bins[(size_t)c].end());
+    }
+    off[(size_t)n_ctas] = (int32_t)list.size();
+}
+
 void launch_pp_pack(const Layout& L, Shard& s) {
     if (s.pp_chunks <= 0 || L.pp_rows <= 0) return;
     dim3 grid((unsigned)((L.pp_rows + 31) / 32), (unsigned)s.pp_chunks);
@@ -450,8 +511,10 @@ void launch_pp_half_transform(const Layout& L, Shard& s, int sm_count) {
     prm.q_len = (int)s.q_len;
     prm.npt64 = L.npt64;
     prm.occ_w = L.occ_w;
-    prm.n_items = (int64_t)L.N * L.pp_n_nt * s.pp_chunks;
-    const int grid = (int)std::min<int64_t>(prm.n_items, sm_count);
+    prm.item_list = s.d_ppitems;
+    prm.item_off = s.d_ppoff;
+    const int grid = s.pp_ctas;
+    (void)sm_count;
     if (grid <= 0) return;
     switch (L.pp_nt) {
         case 1: launch_pp_t<1>(prm, grid, s.stream); break;

@@ -48,6 +48,9 @@ WORKLOADS = {
                        "chain", 20, 6.5, 300.0, 1004),
     "gly18": Workload("gly18", "glycine oligomer DF-RHF cc-pVTZ, largest B tensor, 8 B200", 3395, 9333, 275, "chain",
                       90, 14.0, 600.0, 1005),
+    # one rank's share of gly18 when Q is sharded over 8 GPUs (profiling stand-in for the 8-GPU per-device work)
+    "gly18_q1167": Workload("gly18_q1167", "glycine oligomer DF-RHF cc-pVTZ, the 1167 auxiliary rows one of 8 GPUs owns",
+                            3395, 1167, 275, "chain", 90, 14.0, 600.0, 1005),
     # reduced shapes for parity tests the oracle finishes in seconds
     "tiny": Workload("tiny", "parity-test shape", 70, 40, 9, "chain", 7, 2.5, 20.0, 1100),
     "small": Workload("small", "parity-test shape", 203, 131, 27, "cluster", 12, 1.9, 60.0, 1101),

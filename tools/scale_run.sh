@@ -8,7 +8,7 @@ for n in 2 4 8; do
   python - <<PY
 import json
 try:
-    d = json.load(open("gpurun_out/scale_w50_n$n.json"))
+    d = json.loads([l for l in open("gpurun_out/scale_w50_n$n.json") if l.startswith("{")][-1])
     print("w50", d["n_gpus"], d["value"], d["ms_per_step"], d["e2e"]["value"], d["stage_ms"])
 except Exception as e:
     print("w50 n=$n failed", e)
@@ -20,7 +20,7 @@ timeout 900 python -m torch.distributed.run --nnodes=1 --nproc-per-node 8 --mast
 python - <<PY
 import json
 try:
-    d = json.load(open("gpurun_out/scale_gly18_n8.json"))
+    d = json.loads([l for l in open("gpurun_out/scale_gly18_n8.json") if l.startswith("{")][-1])
     print("gly18", d["n_gpus"], d["value"], d["ms_per_step"], d["e2e"]["value"], d["stage_ms"], d["config"])
 except Exception as e:
     print("gly18 failed", e)
