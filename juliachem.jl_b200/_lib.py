@@ -56,6 +56,7 @@ SIGNATURES = {
     "jcdf_synthetic_value": (_f64, [_u64, _i64, _i64, _i64, _i64, _f64]),
     "jcdf_last_kernel_ms": (_i32, [_p, _i32, _p]),
     "jcdf_exchange_cta_cycles": (_i32, [_p, _i32, _p, _i32]),
+    "jcdf_debug_exchange_block": (_i32, [_i32, _i32, _i32, _i64, _p]),
     "jcdf_set_option": (_i32, [_p, C.c_char_p, _i64]),
     "jcdf_get_stream": (_i32, [_p, _i32, C.POINTER(_p)]),
     "jcdf_set_basis": (_i32, [_p, _i32, _i64, _p, _p, _p, _p, _p]),

@@ -626,3 +626,14 @@ void launch_epilogue(const Layout& L, Shard& s, bool add_H) {
 }
 
 }  // namespace jcdf
+
+extern "C" int32_t jcdf_debug_exchange_block(int32_t ta, int32_t tb, int32_t warp, int64_t N, int32_t* out4) {
+    if (!out4 || ta < tb || tb < 0 || warp < 0 || warp > 7 || N <= 128 * (int64_t)ta) {
+        jcdf::set_error("jcdf_debug_exchange_block: need out4, 0 <= tb <= ta, 0 <= warp < 8, 128 ta < N");
+        return JCDF_ERR_INVALID;
+    }
+    int r0, c0, mt, nt;
+    jcdf::exchange_warp_block(ta, tb, warp, (int)N, r0, c0, mt, nt);
+    out4[0] = r0; out4[1] = c0; out4[2] = mt; out4[3] = nt;
+    return JCDF_OK;
+}

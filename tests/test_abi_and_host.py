@@ -132,3 +132,37 @@ def test_run_basis_mirrors_jcbasis():
     assert len(mol["primary"].am) == 50 * 12 and len(mol["auxiliary"].am) == 50 * 30
     with pytest.raises(KeyError):
         rhf.load_basis_library("cc-pVTZ")
+
+
+@pytest.mark.parametrize("N", [129, 200, 256, 600, 1250, 1279, 1280, 3395])
+def test_exchange_work_split_covers_the_lower_triangle_exactly_once(N):
+    """Host view of the exchange kernel's warp blocks (jcdf_debug_exchange_block, the function the kernel and the work-list
+    cost model share): over every lower-triangular 128 x 128 tile the eight warp rectangles cover every 8 x 8 DMMA tile
+    that holds an element (row >= col, row < N, col < N) exactly once, never reach past N rounded up to 8, and on whole
+    diagonal tiles the two warps of each SM sub-partition (w, w + 4) together own 10 of the 16 row units of a full tile."""
+    import ctypes as C
+    lib = jc.load_library()
+    n128 = (N + 127) // 128
+    out = (C.c_int32 * 4)()
+    units = (N + 7) // 8
+    for ta in range(n128):
+        for tb in range(ta + 1):
+            cover = np.zeros((16, 16), dtype=np.int32)
+            per_warp = []
+            for w in range(8):
+                assert lib.jcdf_debug_exchange_block(ta, tb, w, N, out) == 0
+                r0, c0, mt, nt = out[0], out[1], out[2], out[3]
+                assert 0 <= mt <= 8 and 0 <= nt <= 4
+                per_warp.append(mt * nt)
+                if mt:
+                    assert r0 + mt <= 16 and c0 + nt <= 16
+                    cover[r0:r0 + mt, c0:c0 + nt] += 1
+            assert cover.max() <= 1  # no 8 x 8 tile computed twice
+            rr, cc = np.meshgrid(16 * ta + np.arange(16), 16 * tb + np.arange(16), indexing="ij")
+            needed = (rr < units) & (cc < units) & (rr >= cc)
+            assert np.all(cover[needed] == 1)
+            assert not np.any(cover[(rr >= units) | (cc >= units)])  # nothing beyond N rounded up to 8
+            if ta == tb and 128 * (ta + 1) <= N:
+                assert [per_warp[j] + per_warp[j + 4] for j in range(4)] == [40, 40, 40, 40]  # 10 row units x 4
+            if ta != tb and 128 * (ta + 1) <= N:
+                assert per_warp == [32] * 8
