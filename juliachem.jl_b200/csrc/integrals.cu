@@ -817,10 +817,14 @@ int32_t jcdf_compute_B(jcdf_handle* h) {
             if ((rc = three_center_rows(h, d, h0, rows, T))) return rc;
             // packed rows [q][row_len] viewed column-major are (row_len x q): Bp^T += T^T Linv[Q_g, chunk]^T, in column
             // windows so that every GEMM dimension fits cuBLAS' 32-bit interface
-            for (int64_t c0 = 0; c0 < L.row_len; c0 += (int64_t)1 << 30) {
+            // Linv is lower triangular (exact zeros above the diagonal: trsm against the identity), so the chunk only
+            // reaches the shard rows Q >= h0 — about half of the rectangle on a single device
+            const int64_t q_lo = std::max<int64_t>(0, h0 - s.q_begin);
+            for (int64_t c0 = 0; c0 < L.row_len && q_lo < s.q_len; c0 += (int64_t)1 << 30) {
                 const int64_t w = std::min<int64_t>((int64_t)1 << 30, L.row_len - c0);
-                JC_CUBLAS(cublasDgemm(blas, CUBLAS_OP_N, CUBLAS_OP_T, (int)w, (int)s.q_len, (int)rows, &one, T + c0, (int)L.row_len,
-                                      s.Linv + s.q_begin + Q * h0, (int)Q, first ? &zero : &one, s.Bp + c0, (int)L.row_len));
+                JC_CUBLAS(cublasDgemm(blas, CUBLAS_OP_N, CUBLAS_OP_T, (int)w, (int)(s.q_len - q_lo), (int)rows, &one, T + c0,
+                                      (int)L.row_len, s.Linv + s.q_begin + q_lo + Q * h0, (int)Q, first ? &zero : &one,
+                                      s.Bp + c0 + q_lo * L.row_len, (int)L.row_len));
             }
             first = false;
         }
