@@ -33,7 +33,7 @@ static int dev_alloc(T** p, size_t count) {
 // keep_metric: the two-centre metric / its inverse factor do not depend on the mask (jcdf_set_mask keeps them)
 static void free_shard_buffers(Shard& s, bool keep_metric = false) {
     cudaSetDevice(s.dev);
-    void* ptrs[] = {s.d_ppitems, s.d_ppoff, s.d_xcycles, s.Ksum, s.d_xitems, s.d_xoff, s.Bc, s.Ci, s.d_pp_off, s.d_pp_q, s.d_pp_src, s.d_pp_p, s.d_pp_jdst, s.dvec, s.VpartP, s.Jpart, s.Vpart, s.Vready, s.Bp, s.W, s.Cs, s.Craw, s.dt, s.Jt, s.V, s.Kpart, s.F, s.Hdev, s.Traw, s.d_tile_index, s.d_tile_a,
+    void* ptrs[] = {s.d_pp_trirow, s.ppj_flag, s.ppj_vp, s.d_ppitems, s.d_ppoff, s.d_xcycles, s.Ksum, s.d_xitems, s.d_xoff, s.Bc, s.Ci, s.d_pp_off, s.d_pp_q, s.d_pp_src, s.d_pp_p, s.d_pp_jdst, s.dvec, s.VpartP, s.Jpart, s.Vpart, s.Vready, s.Bp, s.W, s.Cs, s.Craw, s.dt, s.Jt, s.V, s.Kpart, s.F, s.Hdev, s.Traw, s.d_tile_index, s.d_tile_a,
                     s.d_tile_b, s.d_dest_of_col, s.d_fn_mask, s.d_kb_list, s.d_kb_count, s.d_perm, s.d_inv, s.d_tile_strips};
     for (void* p : ptrs)
         if (p) cudaFree(p);
@@ -52,6 +52,9 @@ static void free_shard_buffers(Shard& s, bool keep_metric = false) {
     s.d_xitems = s.d_xoff = nullptr;
     s.d_xcycles = nullptr;
     s.d_ppitems = s.d_ppoff = nullptr;
+    s.d_pp_trirow = nullptr;
+    s.ppj_flag = nullptr;
+    s.ppj_vp = nullptr;
     s.pp_ctas = 0;
     s.Ksum = nullptr;
     s.pp_chunks = 0;
@@ -208,6 +211,10 @@ static int alloc_shard_buffers(jcdf_handle* h, Shard& s) {
                 JC_CUDA(cudaMemcpy(s.d_ppoff, off.data(), sizeof(int32_t) * off.size(), cudaMemcpyHostToDevice));
             }
             if ((rc = dev_alloc(&s.dvec, (size_t)L.pp_rows))) return rc;
+            if ((rc = dev_alloc(&s.d_pp_trirow, L.pp_trirow.size()))) return rc;
+            JC_CUDA(cudaMemcpyAsync(s.d_pp_trirow, L.pp_trirow.data(), sizeof(int32_t) * L.pp_trirow.size(), cudaMemcpyHostToDevice, s.stream));
+            if ((rc = dev_alloc(&s.ppj_flag, (size_t)s.pp_chunks * 4))) return rc;
+            if ((rc = dev_alloc(&s.ppj_vp, (size_t)s.pp_chunks * 4 * h->sm_count * 32))) return rc;
             if ((rc = dev_alloc(&s.VpartP, (size_t)pp_coulomb_slabs(L) * s.pp_chunks * 128))) return rc;
             if ((rc = dev_alloc(&s.Jpart, (size_t)s.pp_chunks * L.pp_rows))) return rc;
         }
@@ -342,7 +349,7 @@ static void build_partner_lists(jcdf_handle* h, Kept kept) {
     const int64_t N = L.N;
     const int nb = L.nb;
     L.pp_enabled = false;
-    L.pp_off.clear(); L.pp_q.clear(); L.pp_src.clear(); L.pp_p.clear(); L.pp_jdst.clear();
+    L.pp_off.clear(); L.pp_q.clear(); L.pp_src.clear(); L.pp_p.clear(); L.pp_jdst.clear(); L.pp_trirow.clear(); L.pp_n_tri = 0;
     L.pp_rows = 0;
     // occupied-orbital tiling: 4 consumer warps across n, each 8 * pp_nt wide, pp_nt <= 4
     const int n8 = L.occ_pad / 8;
@@ -399,6 +406,7 @@ static void build_partner_lists(jcdf_handle* h, Kept kept) {
                 const int rr = (int)(q % 32), cc = (int)(p % 32);
                 jd = (int64_t)L.tile_index[(size_t)aq * nb + ap] * 1024 + rr * 32 + (cc ^ ((rr & 3) << 2));
             }
+            if (jd >= 0) L.pp_trirow.push_back((int32_t)L.pp_jdst.size());
             L.pp_jdst.push_back((int32_t)jd);
         }
         while (L.pp_q.size() % 4) {
@@ -409,6 +417,7 @@ static void build_partner_lists(jcdf_handle* h, Kept kept) {
         }
     }
     L.pp_off[(size_t)N] = (int32_t)L.pp_q.size();
+    L.pp_n_tri = (int64_t)L.pp_trirow.size();
     L.pp_enabled = true;
 }
 
@@ -946,7 +955,8 @@ int fock_build_impl(jcdf_handle* h, const double* C_occ, int64_t ldc, const doub
         JC_CUDA(cudaEventRecord(s.ev[EV_V], sj));  // two-pass: overwritten at the V | J boundary; fused: V time reads 0
         if (pp_j) {
             s.last_coulomb_fused = false;
-            launch_pp_coulomb(L, s, sj, s.ev[EV_V]);
+            s.last_ppj_fused = h->opt_coulomb_pp_fused && launch_pp_coulomb_fused(L, s, h->sm_count, sj);
+            if (!s.last_ppj_fused) launch_pp_coulomb(L, s, sj, s.ev[EV_V]);
         } else {
             // fused single pass pays off on long column segments (w50 dense: 3.8 TB/s effective against <= 3.05 for two
             // passes at the copy bandwidth); on short ones its per-chunk grid-wide flags dominate and two streaming
@@ -1122,7 +1132,8 @@ int32_t jcdf_get_layout(jcdf_handle* h, jcdf_layout_info* o) {
     // per-function path with its own Coulomb: prep, density, half_transform, exchange, V, V reduce, J, J reduce, epilogue
     const bool ppj = !h->shards.empty() && L.pp_enabled && h->shards[0].Bc != nullptr && h->opt_coulomb_pp;
     const int kred = (!h->shards.empty() && h->shards[0].xplan.n_slices > 1) ? 1 : 0;  // k_exchange_reduce
-    o->kernel_launches_per_build = kred + (ppj ? 9 : ((!h->shards.empty() && h->shards[0].last_coulomb_fused) ? 6 : 7)) +
+    const bool ppjf = ppj && h->shards[0].last_ppj_fused;  // one cooperative Coulomb kernel instead of V, V reduce, J, J reduce
+    o->kernel_launches_per_build = kred + (ppjf ? 6 : ppj ? 9 : ((!h->shards.empty() && h->shards[0].last_coulomb_fused) ? 6 : 7)) +
                                    ((h->n_ranks * (int)h->shards.size() > 1) ? 1 : 0);  // + mirror after the all-reduce
     return JCDF_OK;
 }
@@ -1146,6 +1157,7 @@ int32_t jcdf_set_option(jcdf_handle* h, const char* name, int64_t value) {
     if (n == "coulomb_fused") h->opt_coulomb_fused = value;
     else if (n == "coulomb_overlap") h->opt_coulomb_overlap = value;
     else if (n == "coulomb_pp") h->opt_coulomb_pp = value;
+    else if (n == "coulomb_pp_fused") h->opt_coulomb_pp_fused = value;
     else if (n == "exchange_balance") {
         h->opt_exchange_balance = value;
         for (Shard& s : h->shards) JC_REQUIRE(s.Bp == nullptr, "exchange_balance must be set before jcdf_set_mask");

@@ -43,6 +43,8 @@ struct Layout {
     std::vector<int32_t> pp_q;         // [pp_rows] partner (internal index), n_pad on padding rows
     std::vector<int32_t> pp_src;       // [pp_rows] offset of B[Q, p, q] inside a packed row of Bp, -1 on padding rows
     std::vector<int32_t> pp_p;         // [pp_rows] the function p of the row
+    std::vector<int32_t> pp_trirow;    // indices of the q >= p rows (pp_jdst >= 0), ascending
+    int64_t pp_n_tri = 0;
     std::vector<int32_t> pp_jdst;      // [pp_rows] q >= p rows (the Coulomb half): offset of (q, p) inside Jt; -1 elsewhere
 };
 
@@ -72,6 +74,10 @@ struct Shard {
     int32_t* d_pp_src = nullptr;
     int32_t* d_pp_p = nullptr;
     int32_t* d_pp_jdst = nullptr;
+    int32_t* d_pp_trirow = nullptr;
+    unsigned int* ppj_flag = nullptr;  // [pp_chunks * 4] quarter flags of the single-pass compact Coulomb kernel
+    double* ppj_vp = nullptr;          // [pp_chunks * 4][sm_count][32] per-CTA partial V
+    bool last_ppj_fused = false;
     int32_t* d_ppitems = nullptr;  // cost-balanced work lists of the per-function half-transform
     int32_t* d_ppoff = nullptr;
     int pp_ctas = 0;
@@ -139,6 +145,8 @@ struct jcdf_handle {
     int64_t opt_exchange_slices = 0;
     int64_t opt_exchange_balance = 1;  // cost-balanced exchange item lists (0: round-robin in item order)
     int64_t opt_regroup = 1;          // mask-driven regrouping of the basis functions into 32-wide blocks
+    int64_t opt_coulomb_pp_fused = 0;  // compact Coulomb as ONE HBM pass (cooperative kernel): measured slower than the two
+                                       // streaming passes (2.1 vs 1.3 ms at w50: 150 grid-wide flag rounds), so off by default
     int64_t opt_coulomb_pp = 1;       // Coulomb over the partner-compacted copy whenever the per-function path is active
     int64_t opt_ht_mode = 0;          // half-transform: 0 = choose from the mask, 1 = tile kernel, 2 = per-function kernel
     jcdf::ScfState* scf = nullptr;    // on-device SCF driver state (jcdf_scf_*), owned
@@ -159,6 +167,7 @@ void launch_pp_density(const Layout& L, Shard& s);
 void plan_pp_items(const Layout& L, Shard& s, int sm_count, std::vector<int32_t>& list, std::vector<int32_t>& off);
 void launch_pp_coulomb(const Layout& L, Shard& s, cudaStream_t st, cudaEvent_t ev_v);
 int64_t pp_coulomb_slabs(const Layout& L);
+bool launch_pp_coulomb_fused(const Layout& L, Shard& s, int sm_count, cudaStream_t st);
 void launch_exchange(const Layout& L, Shard& s, int sm_count);
 void launch_coulomb(const Layout& L, Shard& s, int sm_count, cudaStream_t st);
 bool launch_coulomb_fused(const Layout& L, Shard& s, int sm_count, cudaStream_t st);

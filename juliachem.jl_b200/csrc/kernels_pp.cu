@@ -396,6 +396,197 @@ __global__ void k_pp_jreduce(const double* __restrict__ Jpart, const int32_t* __
     Jt[dst] = 2.0 * s;
 }
 
+// ---------------------------------------------------------------------------------------------------------------------
+// Single HBM pass: one cooperative persistent grid.  CTA c owns a fixed range of the q >= p rows and walks the auxiliary
+// index in quarters of a chunk (32 functions = 256 B of every row, 26 MB per quarter at w50):
+//   pass 1 of quarter s      partial V over the CTA's rows -> Vp[s][c][32] in L2, one release-increment of flag[s]
+//   pass 2 of quarter s-LAG  once all CTAs have contributed: V = sum_c Vp (fixed order), the SAME 256-byte pieces are
+//                            read again — now L2 hits, LAG + 1 quarters stay resident — and J[row] += B . V accumulates
+//                            in shared memory; J leaves the SM once, at the end.
+// HBM sees every q >= p element of Bc once; no atomics on data, every sum in a fixed order (bit-reproducible).
+// Measured (real w50, 150 quarters of 26 MB): 2.1 ms against 1.3 ms for the two streaming passes — every quarter costs a
+// grid-wide flag round plus a 148-way gather of partial V (about 14 us of serial latency for 4 us of traffic), and the
+// L2 cannot hold a larger step between the passes.  Kept as an option (coulomb_pp_fused = 1), off by default.
+// ---------------------------------------------------------------------------------------------------------------------
+constexpr int PJF_THREADS = 512;
+constexpr int PJF_LAG = 2;
+constexpr int PJF_UNROLL = 8;    // rows in flight per thread (16 bytes each)
+constexpr int PJF_MAX_ROWS = 8192;  // q >= p rows per CTA that fit the shared-memory row cache
+
+struct PJFParams {
+    const double* Bc;
+    const double* dvec;
+    const int32_t* trirow;  // [n_tri] indices of the q >= p rows, ascending
+    const int32_t* jdst;
+    double* Vp;             // [quarters][gridDim.x][32]
+    unsigned int* flag;     // [quarters], zeroed before launch
+    double* Jt;
+    double* V;
+    int64_t rows;
+    int n_tri, chunks, q_len;
+};
+
+__device__ __forceinline__ unsigned int pjf_ld_acquire(const unsigned int* p) {
+    unsigned int v;
+    asm volatile("ld.acquire.gpu.global.u32 %0, [%1];" : "=r"(v) : "l"(p) : "memory");
+    return v;
+}
+__device__ __forceinline__ void pjf_red_release(unsigned int* p) {
+    asm volatile("red.release.gpu.global.add.u32 [%0], 1;" ::"l"(p) : "memory");
+}
+__device__ __forceinline__ double2 pjf_ld2(const double* p) {  // plain (L2-allocating) 16-byte load
+    double2 v;
+    asm volatile("ld.global.v2.f64 {%0,%1}, [%2];" : "=d"(v.x), "=d"(v.y) : "l"(p));
+    return v;
+}
+
+__global__ void __launch_bounds__(PJF_THREADS, 1) k_pp_coulomb_fused(PJFParams prm) {
+    extern __shared__ __align__(16) unsigned char pjf_smem[];
+    const int G = gridDim.x, c = blockIdx.x, tid = threadIdx.x;
+    const int t0 = (int)((int64_t)prm.n_tri * c / G), t1 = (int)((int64_t)prm.n_tri * (c + 1) / G);
+    const int nloc = t1 - t0;
+    double* Jacc = reinterpret_cast<double*>(pjf_smem);             // [nloc]
+    double* sd = Jacc + nloc;                                       // [nloc] weighted density of the row
+    double* red = sd + nloc;                                        // [32][32]
+    double* sV = red + 32 * 32;                                     // [32]
+    int32_t* soff = reinterpret_cast<int32_t*>(sV + 32);            // [nloc] row index (its low 2 bits = swizzle phase)
+    for (int i = tid; i < nloc; i += PJF_THREADS) {
+        const int r = prm.trirow[t0 + i];
+        soff[i] = r;
+        sd[i] = prm.dvec[r];
+        Jacc[i] = 0.0;
+    }
+    __syncthreads();
+    // half-warp = one row piece of 16 x 16 bytes; l = logical pair of auxiliary rows; warp wp handles rows 2 wp + h (+ 32 k)
+    const int hw = tid >> 4, l = tid & 15, wp = tid >> 5, h = (tid >> 4) & 1;
+    const int nq = prm.chunks * 4;
+    for (int step = 0; step < nq + PJF_LAG; step++) {
+        if (step < nq) {
+            const double* base = prm.Bc + (int64_t)(step >> 2) * prm.rows * PP_QC + (step & 3) * 32;
+            double ax = 0.0, ay = 0.0;
+            int ib = 2 * wp;  // rows ib + h: the trip count is uniform per warp (pass 2 shuffles inside the same loops)
+            for (; ib + 32 * (PJF_UNROLL - 1) < nloc; ib += 32 * PJF_UNROLL) {  // PJF_UNROLL rows in flight per thread
+                double2 v[PJF_UNROLL];
+                double d[PJF_UNROLL];
+#pragma unroll
+                for (int u = 0; u < PJF_UNROLL; u++) {
+                    const int i = ib + 32 * u + h;
+                    const bool ok = i < nloc;
+                    const int r = ok ? soff[i] : 0;
+                    d[u] = ok ? sd[i] : 0.0;
+                    v[u] = ok ? pjf_ld2(base + (int64_t)r * PP_QC + ((l ^ ((r & 3) << 1)) << 1)) : make_double2(0.0, 0.0);
+                }
+#pragma unroll
+                for (int u = 0; u < PJF_UNROLL; u++) {
+                    ax = fma(d[u], v[u].x, ax);
+                    ay = fma(d[u], v[u].y, ay);
+                }
+            }
+            for (; ib < nloc; ib += 32) {
+                const int i = ib + h;
+                if (i < nloc) {
+                    const int r = soff[i];
+                    const double2 v = pjf_ld2(base + (int64_t)r * PP_QC + ((l ^ ((r & 3) << 1)) << 1));
+                    ax = fma(sd[i], v.x, ax);
+                    ay = fma(sd[i], v.y, ay);
+                }
+            }
+            red[hw * 32 + 2 * l] = ax;
+            red[hw * 32 + 2 * l + 1] = ay;
+            __syncthreads();
+            if (tid < 32) {
+                double v = 0.0;
+#pragma unroll 8
+                for (int k = 0; k < 32; k++) v += red[k * 32 + tid];
+                prm.Vp[((int64_t)step * G + c) * 32 + tid] = v;
+                __threadfence();
+            }
+            __syncthreads();
+            if (tid == 0) pjf_red_release(prm.flag + step);
+        }
+        const int j = step - PJF_LAG;
+        if (j >= 0) {
+            if (tid == 0)
+                while (pjf_ld_acquire(prm.flag + j) < (unsigned int)G) {}
+            __syncthreads();
+            {   // V of quarter j: 16 groups of threads sum interleaved CTAs, then one fixed-order sum of the 16 partials
+                const int k = tid >> 5, m = tid & 31;
+                double v = 0.0;
+                for (int cc = k; cc < G; cc += 16) v += __ldcg(prm.Vp + ((int64_t)j * G + cc) * 32 + m);
+                red[k * 32 + m] = v;
+            }
+            __syncthreads();
+            if (tid < 32) {
+                double v = 0.0;
+#pragma unroll
+                for (int k = 0; k < 16; k++) v += red[k * 32 + tid];
+                sV[tid] = v;
+                const int Q = (j >> 2) * PP_QC + (j & 3) * 32 + tid;
+                if (c == 0 && Q < prm.q_len) prm.V[Q] = v;
+            }
+            __syncthreads();
+            const double vx = sV[2 * l], vy = sV[2 * l + 1];
+            const double* base = prm.Bc + (int64_t)(j >> 2) * prm.rows * PP_QC + (j & 3) * 32;
+            int ib = 2 * wp;
+            for (; ib + 32 * (PJF_UNROLL - 1) < nloc; ib += 32 * PJF_UNROLL) {
+                double2 v[PJF_UNROLL];
+#pragma unroll
+                for (int u = 0; u < PJF_UNROLL; u++) {
+                    const int i = ib + 32 * u + h;
+                    const int r = i < nloc ? soff[i] : 0;
+                    v[u] = i < nloc ? pjf_ld2(base + (int64_t)r * PP_QC + ((l ^ ((r & 3) << 1)) << 1)) : make_double2(0.0, 0.0);
+                }
+#pragma unroll
+                for (int u = 0; u < PJF_UNROLL; u++) {
+                    const int i = ib + 32 * u + h;
+                    double dot = fma(v[u].x, vx, v[u].y * vy);
+#pragma unroll
+                    for (int o = 8; o > 0; o >>= 1) dot += __shfl_xor_sync(0xffffffffu, dot, o);
+                    if (l == 0 && i < nloc) Jacc[i] += dot;
+                }
+            }
+            for (; ib < nloc; ib += 32) {
+                const int i = ib + h;
+                const int r = i < nloc ? soff[i] : 0;
+                const double2 v = i < nloc ? pjf_ld2(base + (int64_t)r * PP_QC + ((l ^ ((r & 3) << 1)) << 1)) : make_double2(0.0, 0.0);
+                double dot = fma(v.x, vx, v.y * vy);
+#pragma unroll
+                for (int o = 8; o > 0; o >>= 1) dot += __shfl_xor_sync(0xffffffffu, dot, o);
+                if (l == 0 && i < nloc) Jacc[i] += dot;
+            }
+            __syncthreads();  // red / sV are reused by the next step
+        }
+    }
+    for (int i = tid; i < nloc; i += PJF_THREADS) prm.Jt[prm.jdst[soff[i]]] = 2.0 * Jacc[i];
+}
+
+static size_t pjf_smem_bytes(int nloc) { return (size_t)nloc * (8 + 8 + 4) + (32 * 32 + 32) * 8 + 64; }
+
+// false: the shard does not fit (rows per CTA) or the cooperative launch failed -> the caller runs the two passes
+bool launch_pp_coulomb_fused(const Layout& L, Shard& s, int sm_count, cudaStream_t st) {
+    if (s.pp_chunks <= 0 || L.pp_n_tri <= 0 || s.ppj_flag == nullptr) return false;
+    const int grid = sm_count;
+    const int nloc_max = (int)((L.pp_n_tri + grid - 1) / grid) + 1;
+    if (nloc_max > PJF_MAX_ROWS) return false;
+    PJFParams prm;
+    prm.Bc = s.Bc; prm.dvec = s.dvec; prm.trirow = s.d_pp_trirow; prm.jdst = s.d_pp_jdst;
+    prm.Vp = s.ppj_vp; prm.flag = s.ppj_flag; prm.Jt = s.Jt; prm.V = s.V;
+    prm.rows = L.pp_rows; prm.n_tri = (int)L.pp_n_tri; prm.chunks = s.pp_chunks; prm.q_len = (int)s.q_len;
+    const size_t smem = pjf_smem_bytes(nloc_max);
+    if (cudaFuncSetAttribute(k_pp_coulomb_fused, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem) != cudaSuccess) {
+        cudaGetLastError();
+        return false;
+    }
+    cudaMemsetAsync(s.ppj_flag, 0, sizeof(unsigned int) * (size_t)s.pp_chunks * 4, st);
+    void* args[] = {&prm};
+    if (cudaLaunchCooperativeKernel((const void*)k_pp_coulomb_fused, dim3(grid), dim3(PJF_THREADS), args, smem, st) !=
+        cudaSuccess) {
+        cudaGetLastError();
+        return false;
+    }
+    return true;
+}
+
 void launch_pp_density(const Layout& L, Shard& s) {
     const int ldci = L.pp_n_nt * 32 * L.pp_nt;
     const int blocks = (int)std::min<int64_t>((L.pp_rows + 7) / 8, 148 * 16);
@@ -403,7 +594,7 @@ void launch_pp_density(const Layout& L, Shard& s) {
     k_pp_density<<<blocks, 256, 0, s.stream>>>(s.Ci, ldci, (int)L.occ, s.d_pp_p, s.d_pp_q, s.d_pp_jdst, s.dvec, L.pp_rows);
 }
 
-void launch_pp_coulomb(const Layout& L, Shard& s, cudaStream_t st, cudaEvent_t ev_v) {
+void launch_pp_coulomb(const Layout& L, Shard& s, cudaStream_t st, cudaEvent_t ev_v) {  // two streaming passes
     if (s.pp_chunks <= 0 || L.pp_rows <= 0) return;
     const int n_slab = (int)((L.pp_rows + PPJ_SLAB - 1) / PPJ_SLAB);
     const int qpad = s.pp_chunks * PP_QC;

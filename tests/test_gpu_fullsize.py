@@ -33,8 +33,8 @@ def test_w50_kernel_families_agree_and_shards_sum():
     w = wl.WORKLOADS["w50"]
     C, H = wl.occupied_coefficients(w), wl.core_hamiltonian(w)
     _, gd = _w50(2)
-    assert gd.layout().kernel_launches_per_build == 10  # per-function path + sliced exchange reduce
     F_pp = gd.fock_build(C, H)[0].copy()
+    assert gd.layout().kernel_launches_per_build == 10  # per-function path, two-pass compact Coulomb, sliced exchange reduce
     gd.close()
     _, gd = _w50(1)
     F_tiles = gd.fock_build(C, H)[0].copy()

@@ -9,12 +9,13 @@ pytestmark = pytest.mark.gpu
 TOL = 1e-10
 
 
-def _build(N, Q, occ, B, C_occ, H, mask, ndev=1, shards=None, fused=1, overlap=0, ht_mode=0, coulomb_pp=1):
+def _build(N, Q, occ, B, C_occ, H, mask, ndev=1, shards=None, fused=1, overlap=0, ht_mode=0, coulomb_pp=1, pp_fused=1):
     gd = jc.B200Data(N, Q, occ, ndev)
     if shards is not None:
         gd.set_shards(shards)
     gd.set_option("ht_mode", ht_mode)  # 0 = chosen from the mask, 1 = tile kernel, 2 = per-function kernel
     gd.set_option("coulomb_pp", coulomb_pp)  # with the per-function kernel: Coulomb over the compact copy too
+    gd.set_option("coulomb_pp_fused", pp_fused)  # ... as one cooperative single-pass kernel (0: two streaming passes)
     gd.set_option("coulomb_fused", fused)
     gd.set_option("coulomb_overlap", overlap)
     gd.set_mask(jc.ScreeningData(mask, N))
@@ -37,7 +38,7 @@ def test_dense_parity(N, Q, occ, fused, ht_mode):
 
 
 @pytest.mark.parametrize("fused,overlap,ht_mode,coulomb_pp",
-                         [(1, 0, 1, 1), (0, 0, 1, 1), (0, 1, 1, 1), (1, 0, 2, 1), (1, 0, 2, 0), (0, 0, 2, 0)])
+                         [(1, 0, 1, 1), (0, 0, 1, 1), (0, 1, 1, 1), (1, 0, 2, 1), (1, 0, 2, 2), (1, 0, 2, 0), (0, 0, 2, 0)])
 @pytest.mark.parametrize("N,Q,occ,hw", [(70, 40, 9, 20), (203, 131, 27, 60), (160, 64, 16, 33), (300, 90, 40, 70)])
 def test_screened_parity(N, Q, occ, hw, fused, overlap, ht_mode, coulomb_pp):
     """All three Coulomb schedules (single-pass cooperative kernel, two-pass sweeps, two-pass on the second stream) and
@@ -45,8 +46,10 @@ def test_screened_parity(N, Q, occ, hw, fused, overlap, ht_mode, coulomb_pp):
     mask = banded_mask(N, hw, seed=N)
     B, C_occ, H = random_inputs(N, Q, occ, seed=N + 17, mask=mask, decay=hw / 2.0)
     F_ref = oracle_fock(B, C_occ, H, mask)
-    gd, F, st = _build(N, Q, occ, B, C_occ, H, mask, fused=fused, overlap=overlap, ht_mode=ht_mode, coulomb_pp=coulomb_pp)
-    base = 9 if (ht_mode == 2 and coulomb_pp) else 6 if fused else 7
+    # coulomb_pp: 1 = compact Coulomb as one cooperative single-pass kernel, 2 = as two streaming passes, 0 = tile space
+    gd, F, st = _build(N, Q, occ, B, C_occ, H, mask, fused=fused, overlap=overlap, ht_mode=ht_mode,
+                       coulomb_pp=min(coulomb_pp, 1), pp_fused=int(coulomb_pp == 1))
+    base = (6 if coulomb_pp == 1 else 9) if (ht_mode == 2 and coulomb_pp) else 6 if fused else 7
     assert gd.layout().kernel_launches_per_build in (base, base + 1)  # + k_exchange_reduce when the contraction is sliced
     li = gd.layout()
     assert li.pairs_kept == int(mask.sum())
@@ -280,8 +283,8 @@ def _scattered_mask(N, n_sites, reach, seed):
 
 
 @pytest.mark.parametrize("N,Q,occ,ht_mode,coulomb_pp",
-                         [(180, 300, 130, 2, 1), (180, 300, 130, 2, 0), (333, 257, 40, 2, 1), (333, 257, 40, 0, 1),
-                          (96, 129, 81, 2, 1), (700, 520, 33, 2, 1)])
+                         [(180, 300, 130, 2, 1), (180, 300, 130, 2, 2), (180, 300, 130, 2, 0), (333, 257, 40, 2, 1),
+                          (333, 257, 40, 0, 1), (96, 129, 81, 2, 1), (700, 520, 33, 2, 1), (700, 520, 33, 2, 2)])
 def test_per_function_half_transform(N, Q, occ, ht_mode, coulomb_pp):
     """The partner-compacted path (calculate_W_screened restated per function, kernels_pp.cu) on a scattered mask that
     gets regrouped: several 128-row chunks with a ragged last one, more than one occupied-orbital tile (occ = 130),
@@ -289,7 +292,8 @@ def test_per_function_half_transform(N, Q, occ, ht_mode, coulomb_pp):
     mask = _scattered_mask(N, 19, 1, seed=N + 1)
     B, C_occ, H = random_inputs(N, Q, occ, seed=N + 5, mask=mask)
     F_ref = oracle_fock(B, C_occ, H, mask)
-    gd, F, _ = _build(N, Q, occ, B, C_occ, H, mask, ht_mode=ht_mode, coulomb_pp=coulomb_pp)
+    gd, F, _ = _build(N, Q, occ, B, C_occ, H, mask, ht_mode=ht_mode, coulomb_pp=min(coulomb_pp, 1),
+                      pp_fused=int(coulomb_pp == 1))
     assert np.abs(F - F_ref).max() < TOL
     assert np.array_equal(F, F.T)
     F2, _ = gd.fock_build(C_occ, H)  # second build reuses the compact copy
