@@ -223,6 +223,8 @@ double jcdf_synthetic_value(uint64_t seed, int64_t Q_total, int64_t q_aux, int64
  * 0 = default, chosen from the mask by executed DMMA count; 1 = 32 x 32 tiles with strip skipping; 2 = per-function
  * partner lists over a partner-compacted copy of B = calculate_W_screened's own blocking, ScreenedDF.jl:242-289),
  * "coulomb_pp" (1 = default: with the per-function kernel the Coulomb passes stream the compact copy too),
+ * "pp_max_bytes" (cap on the compact copy per shard; above it — or when cudaMalloc refuses — the automatic choice falls
+ * back to the tile family, ht_mode = 2 reports JCDF_ERR_CUDA; 0 = no cap),
  * "coulomb_pp_fused" (0 = default: two streaming passes; 1 = one cooperative single-pass kernel, measured slower),
  * "exchange_balance" (1 = default: cost-balanced exchange work lists; 0 = round-robin).  "regroup", "ht_mode",
  * "exchange_slices" and "exchange_balance" must be set before jcdf_set_mask.  Unknown names -> JCDF_ERR_INVALID.   */

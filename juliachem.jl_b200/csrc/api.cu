@@ -180,7 +180,9 @@ static int alloc_shard_buffers(jcdf_handle* h, Shard& s) {
         // partner-compacted copy of the shard for the per-function half-transform (kernels_pp.cu)
         s.pp_chunks = (int)((s.q_len + 127) / 128);
         const size_t nBc = (size_t)s.pp_chunks * (size_t)L.pp_rows * 128;
-        cudaError_t e = cudaMalloc(reinterpret_cast<void**>(&s.Bc), std::max<size_t>(nBc, 1) * sizeof(double));
+        cudaError_t e = cudaErrorMemoryAllocation;
+        if (h->opt_pp_max_bytes <= 0 || (int64_t)(nBc * sizeof(double)) <= h->opt_pp_max_bytes)
+            e = cudaMalloc(reinterpret_cast<void**>(&s.Bc), std::max<size_t>(nBc, 1) * sizeof(double));
         if (e != cudaSuccess) {
             cudaGetLastError();
             s.Bc = nullptr;
@@ -1156,6 +1158,7 @@ int32_t jcdf_set_option(jcdf_handle* h, const char* name, int64_t value) {
     const std::string n(name);
     if (n == "coulomb_fused") h->opt_coulomb_fused = value;
     else if (n == "coulomb_overlap") h->opt_coulomb_overlap = value;
+    else if (n == "pp_max_bytes") h->opt_pp_max_bytes = value;
     else if (n == "coulomb_pp") h->opt_coulomb_pp = value;
     else if (n == "coulomb_pp_fused") h->opt_coulomb_pp_fused = value;
     else if (n == "exchange_balance") {

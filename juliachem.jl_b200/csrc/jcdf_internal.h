@@ -147,6 +147,7 @@ struct jcdf_handle {
     int64_t opt_regroup = 1;          // mask-driven regrouping of the basis functions into 32-wide blocks
     int64_t opt_coulomb_pp_fused = 0;  // compact Coulomb as ONE HBM pass (cooperative kernel): measured slower than the two
                                        // streaming passes (2.1 vs 1.3 ms at w50: 150 grid-wide flag rounds), so off by default
+    int64_t opt_pp_max_bytes = 0;      // cap on the partner-compacted copy per shard (0 = whatever cudaMalloc grants)
     int64_t opt_coulomb_pp = 1;       // Coulomb over the partner-compacted copy whenever the per-function path is active
     int64_t opt_ht_mode = 0;          // half-transform: 0 = choose from the mask, 1 = tile kernel, 2 = per-function kernel
     jcdf::ScfState* scf = nullptr;    // on-device SCF driver state (jcdf_scf_*), owned

@@ -346,6 +346,29 @@ def test_isolated_functions_and_empty_shard():
     gd.close()
 
 
+def test_compact_copy_that_does_not_fit_falls_back_to_tiles():
+    """The partner-compacted second copy of B is optional: when it exceeds the cap (or cudaMalloc refuses) the automatic
+    choice silently uses the tile family; forcing the per-function family is then an error, never a wrong result."""
+    N, Q, occ = 200, 150, 21
+    mask = _scattered_mask(N, 23, 1, seed=N)
+    B, C_occ, H = random_inputs(N, Q, occ, seed=N + 3, mask=mask)
+    F_ref = oracle_fock(B, C_occ, H, mask)
+    gd = jc.B200Data(N, Q, occ, 1)
+    gd.set_option("pp_max_bytes", 1024)
+    gd.set_mask(jc.ScreeningData(mask, N))
+    gd.set_B(0, reference_layout_rows(B, range(0, Q), mask))
+    F, _ = gd.fock_build(C_occ, H)
+    assert np.abs(F - F_ref).max() < TOL
+    assert gd.layout().kernel_launches_per_build in (6, 7, 8)  # tile family (fused or two-pass Coulomb, +- slice reduce)
+    gd.close()
+    gd = jc.B200Data(N, Q, occ, 1)
+    gd.set_option("pp_max_bytes", 1024)
+    gd.set_option("ht_mode", 2)
+    with pytest.raises(jc.JCDFError):
+        gd.set_mask(jc.ScreeningData(mask, N))
+    gd.close()
+
+
 def test_half_transform_kernels_agree_on_sharded_run():
     """Two shards on one device, per-function kernel on each, against the tile kernel: same Fock matrix to 1e-10."""
     N, Q, occ = 150, 200, 33
