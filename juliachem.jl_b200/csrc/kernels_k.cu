@@ -498,6 +498,7 @@ __global__ void __maxnreg__(MAX_REGS) k_exchange(XParams prm) {
             // refill the slot every warp released one stage ago BEFORE computing this one: the copy then has two full
             // stage times to land.  (Also tried: register double-buffering of the fragments across k-steps and stage
             // boundaries — 244 registers, 3 % slower; the two warps per sub-partition already cover each other's bubbles.)
+            // Also tried: cp.async.bulk.prefetch.L2 of the chunk four stages beyond the ring — 6 % slower.
             if (is_producer) produce();
             __syncwarp();
             const double* sA = stages + (size_t)ps.stage * X_STAGE_DOUBLES + a_off;
