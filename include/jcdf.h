@@ -204,7 +204,8 @@ typedef struct jcdf_layout_info {
     int64_t pairs_tri;        /* P_tri = kept pairs with q >= p                             */
     int64_t packed_row_len;   /* doubles per auxiliary row in HBM = tiles_kept * 1024       */
     int64_t q_local;          /* auxiliary functions held by this process                   */
-    int64_t bytes_B, bytes_W; /* device bytes, summed over this process's devices           */
+    int64_t bytes_B, bytes_W; /* device bytes, summed over this process's devices (bytes_B includes the
+                               * partner-compacted second copy when the per-function family is active)   */
     int64_t kernel_launches_per_build; /* launches of this library's own kernels per build  */
 } jcdf_layout_info;
 int32_t jcdf_get_layout(jcdf_handle* h, jcdf_layout_info* out);

@@ -6,7 +6,10 @@
 //   exchange         K[p,q]     = sum_(Q,i) W[(Q,i),p] * W[(Q,i),q]    replaces calculate_K_lower_diagonal_block_no_screen
 //                                                                      (ScreenedDF.jl:548-641; dense DensityFitting.jl:219)
 //
-// Both kernels are persistent (one CTA per SM, static round-robin over work items); 8 warps issue DMMA and thread 0 is
+// (the per-function half-transform used on sparse masks lives in kernels_pp.cu; W is stored as [chunk of 32 k][64-wide
+// p tile][64 p][32 k], k = Q_local * occ_w + i, so both half-transforms write and the exchange reads the same tiles)
+// Both kernels are persistent (one CTA per SM; the exchange walks cost-balanced work lists, the tile half-transform a
+// static round-robin); 8 warps issue DMMA and thread 0 is
 // also the copy producer, running NSTAGE - 1 slabs ahead through a full/empty mbarrier ring.  All operands are stored
 // in HBM pre-swizzled (dmma_common.cuh: swz) so a dense bulk copy lands bank-conflict-free in shared memory.
 #include <algorithm>
