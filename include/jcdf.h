@@ -242,9 +242,11 @@ int32_t jcdf_exchange_cta_cycles(jcdf_handle* h, int32_t dev, int64_t* out, int3
 
 /* Host-side view of the exchange kernel's work split (no device needed; used by the CPU test suite): the block of the
  * 128 x 128 output tile (ta, tb), ta >= tb, that warp `warp` (0..7) owns for a basis of N functions, in units of 8 rows /
- * columns: out4 = {first row unit, first column unit, row units, column units}; all zero when the warp has no work.
+ * columns: out5 = {first row unit, first column unit, row units, column units, staircase}; staircase = 1 when the
+ * rectangle starts on the diagonal of a diagonal tile and only its column units <= row unit are computed; row and
+ * column units are zero when the warp has no work.
  * The same function drives the kernel and the cost model of the work lists.                                        */
-int32_t jcdf_debug_exchange_block(int32_t ta, int32_t tb, int32_t warp, int64_t N, int32_t* out4);
+int32_t jcdf_debug_exchange_block(int32_t ta, int32_t tb, int32_t warp, int64_t N, int32_t* out5);
 
 /* The CUDA stream (cudaStream_t, returned as void*) every kernel, copy and all-reduce of device `dev` is issued on —
  * so a caller can bracket builds with its own CUDA events or order its own work against them (the fork's CUDA.jl

@@ -356,6 +356,18 @@ __host__ __device__ inline void exchange_warp_block(int ta, int tb, int warp, in
     if (mt == 0 || nt == 0) mt = nt = 0;
 }
 
+// A rectangle that starts ON the diagonal of a diagonal tile (r0 == c0) only needs its lower staircase: row unit jm needs
+// the column units <= jm.  All four diagonal-crossing rectangles of the cover start on it.
+__host__ __device__ inline bool exchange_block_is_stair(int ta, int tb, int r0, int c0) { return ta == tb && r0 == c0; }
+
+// DMMA tiles per k-step of a warp block
+__host__ __device__ inline int exchange_block_tiles(int ta, int tb, int r0, int c0, int mt, int nt) {
+    if (!exchange_block_is_stair(ta, tb, r0, c0)) return mt * nt;
+    int n = 0;
+    for (int jm = 0; jm < mt; jm++) n += min(nt, jm + 1);
+    return n;
+}
+
 __host__ __device__ inline void exchange_decode_tile(int tile, int& ta, int& tb) {
     int a = 0;
     while ((a + 1) * (a + 2) / 2 <= tile) a++;
@@ -372,7 +384,7 @@ int exchange_tile_cost(int tile, int N) {
         for (int w = j; w < 8; w += 4) {
             int r0, c0, mt, nt;
             exchange_warp_block(ta, tb, w, N, r0, c0, mt, nt);
-            c += mt * nt;
+            c += exchange_block_tiles(ta, tb, r0, c0, mt, nt);
         }
         best = std::max(best, c);
     }
@@ -398,6 +410,41 @@ __device__ __forceinline__ void x_slab(double (&acc)[8][4][2], const double* __r
         for (int jm = 0; jm < MT; jm++)
 #pragma unroll
             for (int jn = 0; jn < NT; jn++) dmma(acc[jm][jn][0], acc[jm][jn][1], a[jm], b[jn]);
+    }
+}
+
+// Staircase block of a rectangle that starts on the diagonal: row unit jm times column units 0 .. min(3, jm)
+template <int MT>
+__device__ __forceinline__ void x_slab_stair(double (&acc)[8][4][2], const double* __restrict__ sA,
+                                             const double* __restrict__ sB, int g, int t) {
+    const int sw = (g & 3) << 2;
+#pragma unroll 2
+    for (int k0 = 0; k0 < KSLAB; k0 += 4) {
+        const int kr = (k0 + t) ^ sw;
+        double a[MT], b[4];
+#pragma unroll
+        for (int jm = 0; jm < MT; jm++) a[jm] = sA[(8 * jm + g) * 32 + kr];
+#pragma unroll
+        for (int jn = 0; jn < 4; jn++)
+            if (jn < MT) b[jn] = sB[(8 * jn + g) * 32 + kr];
+#pragma unroll
+        for (int jm = 0; jm < MT; jm++)
+#pragma unroll
+            for (int jn = 0; jn < 4; jn++)
+                if (jn <= jm) dmma(acc[jm][jn][0], acc[jm][jn][1], a[jm], b[jn]);  // compile-time after unrolling
+    }
+}
+
+__device__ __forceinline__ void x_slab_stair_mt(double (&acc)[8][4][2], const double* sA, const double* sB, int g, int t,
+                                                int mt) {
+    switch (mt) {
+        case 1: x_slab_stair<1>(acc, sA, sB, g, t); break;
+        case 2: x_slab_stair<2>(acc, sA, sB, g, t); break;
+        case 3: x_slab_stair<3>(acc, sA, sB, g, t); break;
+        case 4: x_slab_stair<4>(acc, sA, sB, g, t); break;
+        case 5: x_slab_stair<5>(acc, sA, sB, g, t); break;
+        case 6: x_slab_stair<6>(acc, sA, sB, g, t); break;
+        default: break;
     }
 }
 
@@ -487,6 +534,7 @@ __global__ void __maxnreg__(MAX_REGS) k_exchange(XParams prm) {
         exchange_warp_block(ta, tb, warp, prm.N, r0, c0, mt, nt);
         const bool active = mt > 0;
         const bool whole = (mt == 8) && (nt == 4);
+        const bool stair = exchange_block_is_stair(ta, tb, r0, c0) && mt > 0;  // mt <= 6 on these rectangles, nt >= min(4, mt)
         // A0 | A1 and B0 | B1 are adjacent [64][32] tiles: 128 rows of one stride, so a block may straddle the pair
         const int a_off = r0 * 8 * 32;
         const int b_off = (ta == tb ? 0 : 2 * 2048) + c0 * 8 * 32;
@@ -507,6 +555,7 @@ __global__ void __maxnreg__(MAX_REGS) k_exchange(XParams prm) {
             const double* sA = stages + (size_t)ps.stage * X_STAGE_DOUBLES + a_off;
             const double* sB = stages + (size_t)ps.stage * X_STAGE_DOUBLES + b_off;
             if (whole) x_slab<8, 4>(acc, sA, sB, g, t);
+            else if (stair) x_slab_stair_mt(acc, sA, sB, g, t, mt);
             else if (nt == 4) x_slab_mt<4>(acc, sA, sB, g, t, mt);
             else if (nt == 3) x_slab_mt<3>(acc, sA, sB, g, t, mt);
             else if (nt == 2) x_slab_mt<2>(acc, sA, sB, g, t, mt);
@@ -631,7 +680,7 @@ void launch_epilogue(const Layout& L, Shard& s, bool add_H) {
 
 }  // namespace jcdf
 
-extern "C" int32_t jcdf_debug_exchange_block(int32_t ta, int32_t tb, int32_t warp, int64_t N, int32_t* out4) {
+extern "C" int32_t jcdf_debug_exchange_block(int32_t ta, int32_t tb, int32_t warp, int64_t N, int32_t* out4 /* 5 values */) {
     if (!out4 || ta < tb || tb < 0 || warp < 0 || warp > 7 || N <= 128 * (int64_t)ta) {
         jcdf::set_error("jcdf_debug_exchange_block: need out4, 0 <= tb <= ta, 0 <= warp < 8, 128 ta < N");
         return JCDF_ERR_INVALID;
@@ -639,5 +688,6 @@ extern "C" int32_t jcdf_debug_exchange_block(int32_t ta, int32_t tb, int32_t war
     int r0, c0, mt, nt;
     jcdf::exchange_warp_block(ta, tb, warp, (int)N, r0, c0, mt, nt);
     out4[0] = r0; out4[1] = c0; out4[2] = mt; out4[3] = nt;
+    out4[4] = (mt > 0 && jcdf::exchange_block_is_stair(ta, tb, r0, c0)) ? 1 : 0;
     return JCDF_OK;
 }

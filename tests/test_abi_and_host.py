@@ -139,11 +139,12 @@ def test_exchange_work_split_covers_the_lower_triangle_exactly_once(N):
     """Host view of the exchange kernel's warp blocks (jcdf_debug_exchange_block, the function the kernel and the work-list
     cost model share): over every lower-triangular 128 x 128 tile the eight warp rectangles cover every 8 x 8 DMMA tile
     that holds an element (row >= col, row < N, col < N) exactly once, never reach past N rounded up to 8, and on whole
-    diagonal tiles the two warps of each SM sub-partition (w, w + 4) together own 10 of the 16 row units of a full tile."""
+    diagonal tiles the two warps of each SM sub-partition (w, w + 4) together own 34 of the 64 DMMA tiles a full tile
+    costs per sub-partition (exactly the 136 tiles on or below the diagonal in total)."""
     import ctypes as C
     lib = jc.load_library()
     n128 = (N + 127) // 128
-    out = (C.c_int32 * 4)()
+    out = (C.c_int32 * 5)()
     units = (N + 7) // 8
     for ta in range(n128):
         for tb in range(ta + 1):
@@ -151,18 +152,25 @@ def test_exchange_work_split_covers_the_lower_triangle_exactly_once(N):
             per_warp = []
             for w in range(8):
                 assert lib.jcdf_debug_exchange_block(ta, tb, w, N, out) == 0
-                r0, c0, mt, nt = out[0], out[1], out[2], out[3]
+                r0, c0, mt, nt, stair = out[0], out[1], out[2], out[3], out[4]
                 assert 0 <= mt <= 8 and 0 <= nt <= 4
-                per_warp.append(mt * nt)
                 if mt:
                     assert r0 + mt <= 16 and c0 + nt <= 16
-                    cover[r0:r0 + mt, c0:c0 + nt] += 1
+                    block = np.ones((mt, nt), dtype=np.int32)
+                    if stair:  # a rectangle that starts on the diagonal computes its lower staircase only
+                        assert ta == tb and r0 == c0
+                        block = np.tril(block)
+                    cover[r0:r0 + mt, c0:c0 + nt] += block
+                    per_warp.append(int(block.sum()))
+                else:
+                    per_warp.append(0)
             assert cover.max() <= 1  # no 8 x 8 tile computed twice
             rr, cc = np.meshgrid(16 * ta + np.arange(16), 16 * tb + np.arange(16), indexing="ij")
             needed = (rr < units) & (cc < units) & (rr >= cc)
             assert np.all(cover[needed] == 1)
             assert not np.any(cover[(rr >= units) | (cc >= units)])  # nothing beyond N rounded up to 8
             if ta == tb and 128 * (ta + 1) <= N:
-                assert [per_warp[j] + per_warp[j + 4] for j in range(4)] == [40, 40, 40, 40]  # 10 row units x 4
+                assert [per_warp[j] + per_warp[j + 4] for j in range(4)] == [34, 34, 34, 34]  # of the 64 of a full tile
+                assert int(cover.sum()) == 136  # exactly the 8 x 8 tiles on or below the diagonal
             if ta != tb and 128 * (ta + 1) <= N:
                 assert per_warp == [32] * 8
