@@ -33,7 +33,7 @@ static int dev_alloc(T** p, size_t count) {
 // keep_metric: the two-centre metric / its inverse factor do not depend on the mask (jcdf_set_mask keeps them)
 static void free_shard_buffers(Shard& s, bool keep_metric = false) {
     cudaSetDevice(s.dev);
-    void* ptrs[] = {s.d_pp_trirow, s.ppj_flag, s.ppj_vp, s.d_ppitems, s.d_ppoff, s.d_xcycles, s.Ksum, s.d_xitems, s.d_xoff, s.Bc, s.Ci, s.d_pp_off, s.d_pp_q, s.d_pp_src, s.d_pp_p, s.d_pp_jdst, s.dvec, s.VpartP, s.Jpart, s.Vpart, s.Vready, s.Bp, s.W, s.Cs, s.Craw, s.dt, s.Jt, s.V, s.Kpart, s.F, s.Hdev, s.Traw, s.d_tile_index, s.d_tile_a,
+    void* ptrs[] = {s.d_pp_trirow, s.ppj_flag, s.ppj_vp, s.d_ppitems, s.d_ppoff, s.d_xcycles, s.Ksum, s.d_xitems, s.d_xoff, s.Bc, s.Ci, s.d_pp_off, s.d_pp_q, s.d_pp_src, s.d_pp_p, s.d_pp_jdst, s.dvec, s.VpartP, s.Vitem, s.Jpart, s.Vpart, s.Vready, s.Bp, s.W, s.Cs, s.Craw, s.dt, s.Jt, s.V, s.Kpart, s.F, s.Hdev, s.Traw, s.d_tile_index, s.d_tile_a,
                     s.d_tile_b, s.d_dest_of_col, s.d_fn_mask, s.d_kb_list, s.d_kb_count, s.d_perm, s.d_inv, s.d_tile_strips};
     for (void* p : ptrs)
         if (p) cudaFree(p);
@@ -48,7 +48,7 @@ static void free_shard_buffers(Shard& s, bool keep_metric = false) {
     s.Vready = nullptr;
     s.Bc = s.Ci = nullptr;
     s.d_pp_off = s.d_pp_q = s.d_pp_src = s.d_pp_p = s.d_pp_jdst = nullptr;
-    s.dvec = s.VpartP = s.Jpart = nullptr;
+    s.dvec = s.VpartP = s.Vitem = s.Jpart = nullptr;
     s.d_xitems = s.d_xoff = nullptr;
     s.d_xcycles = nullptr;
     s.d_ppitems = s.d_ppoff = nullptr;
@@ -192,7 +192,7 @@ static int alloc_shard_buffers(jcdf_handle* h, Shard& s) {
             }
             L.pp_enabled = false;  // automatic choice: fall back to the tile kernel on every shard
         } else {
-            const int ldci = L.pp_n_nt * 32 * L.pp_nt;
+            const int ldci = L.pp_n_nt * pp_item_orbitals(L);
             if ((rc = dev_alloc(&s.Ci, (size_t)(L.n_pad + 1) * ldci))) return rc;
             if ((rc = dev_alloc(&s.d_pp_off, L.pp_off.size()))) return rc;
             if ((rc = dev_alloc(&s.d_pp_q, L.pp_q.size()))) return rc;
@@ -219,6 +219,11 @@ static int alloc_shard_buffers(jcdf_handle* h, Shard& s) {
             if ((rc = dev_alloc(&s.ppj_vp, (size_t)s.pp_chunks * 4 * h->sm_count * 32))) return rc;
             if ((rc = dev_alloc(&s.VpartP, (size_t)pp_coulomb_slabs(L) * s.pp_chunks * 128))) return rc;
             if ((rc = dev_alloc(&s.Jpart, (size_t)s.pp_chunks * L.pp_rows))) return rc;
+            {   // partial V of every half-transform item; warps without valid rows or orbitals never write: cleared once
+                const size_t nv = (size_t)L.N * s.pp_chunks * pp_v_slots(L) * 128;
+                if ((rc = dev_alloc(&s.Vitem, nv))) return rc;
+                JC_CUDA(cudaMemsetAsync(s.Vitem, 0, nv * sizeof(double), s.stream));
+            }
         }
     }
     s.bc_valid = false;
@@ -353,10 +358,16 @@ static void build_partner_lists(jcdf_handle* h, Kept kept) {
     L.pp_enabled = false;
     L.pp_off.clear(); L.pp_q.clear(); L.pp_src.clear(); L.pp_p.clear(); L.pp_jdst.clear(); L.pp_trirow.clear(); L.pp_n_tri = 0;
     L.pp_rows = 0;
-    // occupied-orbital tiling: 4 consumer warps across n, each 8 * pp_nt wide, pp_nt <= 4
+    // occupied-orbital tiling.  Layout 0: 4 consumer warps across n, each 8 * nt wide (nt <= 4) — the orbital count of
+    // an item is padded to a multiple of 32.  Layout 1: every warp takes all 8 * nt orbitals of the item (nt <= 12) — no
+    // padding beyond the 8-wide DMMA tile; taken when it executes fewer tiles on the busiest sub-partition.
     const int n8 = L.occ_pad / 8;
-    L.pp_n_nt = (n8 + 15) / 16;
-    L.pp_nt = ((n8 + L.pp_n_nt - 1) / L.pp_n_nt + 3) / 4;
+    const int n_nt0 = (n8 + 15) / 16, nt0 = ((n8 + n_nt0 - 1) / n_nt0 + 3) / 4;
+    const int n_nt1 = (n8 + 11) / 12, nt1 = (n8 + n_nt1 - 1) / n_nt1;
+    const bool layout1 = h->opt_pp_layout == 1 || (h->opt_pp_layout < 0 && n_nt1 * nt1 * 100 < n_nt0 * 4 * nt0 * 97);
+    L.pp_layout = layout1 ? 1 : 0;
+    L.pp_n_nt = layout1 ? n_nt1 : n_nt0;
+    L.pp_nt = layout1 ? nt1 : nt0;
     if (h->opt_ht_mode == 1 || L.row_len >= ((int64_t)1 << 31)) return;
     // executed multiply-adds per auxiliary row of either kernel
     double cost_tiles = 0.0;
@@ -375,7 +386,7 @@ static void build_partner_lists(jcdf_handle* h, Kept kept) {
         cnt[(size_t)p] = c;
         rows += (c + 3) / 4 * 4;
     }
-    const double cost_pp = (double)rows * L.pp_n_nt * 32.0 * L.pp_nt;
+    const double cost_pp = (double)rows * L.pp_n_nt * (L.pp_layout ? 8.0 : 32.0) * L.pp_nt;
     if (rows >= ((int64_t)1 << 31)) return;
     // measured on the C20H42 shape (52.8 % of the pairs kept, cost ratio 0.93): per-function 18.2 ms + compact Coulomb
     // 4.4 ms against tiles 19.3 ms + 5.3 ms — the compact family wins as soon as it executes fewer DMMAs at all
@@ -940,12 +951,19 @@ int fock_build_impl(jcdf_handle* h, const double* C_occ, int64_t ldc, const doub
         const bool pp_j = use_pp && h->opt_coulomb_pp;  // Coulomb over the compact copy as well
         if (!pp_j) launch_prep(L, s, L.N);
         if (use_pp) launch_pp_prep(L, s, L.N);
-        if (pp_j) launch_pp_density(L, s);
+        // V = sum_p sum_i C[p,i] W[Q,i,p] comes out of the half-transform's accumulators: no density, no V sweep
+        // (1 = where it pays: the 2 x 4 arrangement at 4 tiles per warp has no registers to spare, the block spills
+        // inside its k loop and costs more than the sweep it saves — w50: +2.4 ms against -0.7 ms; 2 = always)
+        const bool v_fits = h->opt_coulomb_v_in_ht >= 2 || !(L.pp_layout == 0 && L.pp_nt == 4);
+        const bool v_in_ht = pp_j && h->opt_coulomb_v_in_ht && v_fits && !h->opt_coulomb_pp_fused && s.Vitem != nullptr;
+        if (pp_j && !v_in_ht) launch_pp_density(L, s);
         JC_CUDA(cudaEventRecord(s.ev[EV_PREP], s.stream));
-        if (use_pp) launch_pp_half_transform(L, s, h->sm_count);
+        if (use_pp) launch_pp_half_transform(L, s, h->sm_count, v_in_ht);
         else launch_half_transform(L, s, h->sm_count);
+        JC_CUDA(cudaPeekAtLastError());  // a launch that did not fit fails the build here, not as a wrong Fock matrix
         JC_CUDA(cudaEventRecord(s.ev[EV_W], s.stream));
         launch_exchange(L, s, h->sm_count);
+        JC_CUDA(cudaPeekAtLastError());
         JC_CUDA(cudaEventRecord(s.ev[EV_K], s.stream));
         // Coulomb sweeps (HBM-bound, 32-40 registers, no dynamic smem).  With coulomb_overlap they go to a second,
         // lower-priority stream: their CTAs co-reside with the persistent tensor-core CTAs (one per SM, compute-bound,
@@ -958,7 +976,10 @@ int fock_build_impl(jcdf_handle* h, const double* C_occ, int64_t ldc, const doub
         if (pp_j) {
             s.last_coulomb_fused = false;
             s.last_ppj_fused = h->opt_coulomb_pp_fused && launch_pp_coulomb_fused(L, s, h->sm_count, sj);
-            if (!s.last_ppj_fused) launch_pp_coulomb(L, s, sj, s.ev[EV_V]);
+            if (!s.last_ppj_fused) {
+                if (v_in_ht && overlap) JC_CUDA(cudaStreamWaitEvent(sj, s.ev[EV_W], 0));  // the partials come from the half-transform
+                launch_pp_coulomb(L, s, sj, s.ev[EV_V], v_in_ht);
+            }
         } else {
             // fused single pass pays off on long column segments (w50 dense: 3.8 TB/s effective against <= 3.05 for two
             // passes at the copy bandwidth); on short ones its per-chunk grid-wide flags dominate and two streaming
@@ -969,6 +990,7 @@ int fock_build_impl(jcdf_handle* h, const double* C_occ, int64_t ldc, const doub
             if (!s.last_coulomb_fused) launch_coulomb(L, s, h->sm_count, sj);
         }
         s.last_pp_j = pp_j;
+        s.last_v_in_ht = v_in_ht && !s.last_ppj_fused;
         JC_CUDA(cudaEventRecord(s.ev[EV_J], sj));
         if (overlap) JC_CUDA(cudaStreamWaitEvent(s.stream, s.ev[EV_J], 0));
         launch_epilogue(L, s, add_H);
@@ -1135,7 +1157,9 @@ int32_t jcdf_get_layout(jcdf_handle* h, jcdf_layout_info* o) {
     const bool ppj = !h->shards.empty() && L.pp_enabled && h->shards[0].Bc != nullptr && h->opt_coulomb_pp;
     const int kred = (!h->shards.empty() && h->shards[0].xplan.n_slices > 1) ? 1 : 0;  // k_exchange_reduce
     const bool ppjf = ppj && h->shards[0].last_ppj_fused;  // one cooperative Coulomb kernel instead of V, V reduce, J, J reduce
-    o->kernel_launches_per_build = kred + (ppjf ? 6 : ppj ? 9 : ((!h->shards.empty() && h->shards[0].last_coulomb_fused) ? 6 : 7)) +
+    const bool vht = ppj && !ppjf && h->opt_coulomb_v_in_ht && !h->opt_coulomb_pp_fused &&
+                     (h->opt_coulomb_v_in_ht >= 2 || !(L.pp_layout == 0 && L.pp_nt == 4));  // density, V pass, V reduce -> one reduce
+    o->kernel_launches_per_build = kred + (ppjf ? 6 : ppj ? (vht ? 7 : 9) : ((!h->shards.empty() && h->shards[0].last_coulomb_fused) ? 6 : 7)) +
                                    ((h->n_ranks * (int)h->shards.size() > 1) ? 1 : 0);  // + mirror after the all-reduce
     return JCDF_OK;
 }
@@ -1159,7 +1183,12 @@ int32_t jcdf_set_option(jcdf_handle* h, const char* name, int64_t value) {
     if (n == "coulomb_fused") h->opt_coulomb_fused = value;
     else if (n == "coulomb_overlap") h->opt_coulomb_overlap = value;
     else if (n == "pp_max_bytes") h->opt_pp_max_bytes = value;
+    else if (n == "pp_layout") {
+        h->opt_pp_layout = value;
+        for (Shard& s : h->shards) JC_REQUIRE(s.Bp == nullptr, "pp_layout must be set before jcdf_set_mask");
+    }
     else if (n == "coulomb_pp") h->opt_coulomb_pp = value;
+    else if (n == "coulomb_v_in_ht") h->opt_coulomb_v_in_ht = value;
     else if (n == "coulomb_pp_fused") h->opt_coulomb_pp_fused = value;
     else if (n == "exchange_balance") {
         h->opt_exchange_balance = value;

@@ -36,8 +36,9 @@ struct Layout {
     // ---- partner-compacted layout of the per-function half-transform (kernels_pp.cu) ----
     // For every function p (internal order) the kept partners q, ascending, padded to a multiple of 4 rows.
     bool pp_enabled = false;           // the per-function path is selected for this mask
-    int pp_nt = 0;                     // 8-wide occupied-orbital tiles per consumer warp (NI = 32 * pp_nt columns per item)
-    int pp_n_nt = 0;                   // occupied-orbital tiles: pp_n_nt * 32 * pp_nt >= occ_pad
+    int pp_layout = 0;                 // consumer warp arrangement: 0 = 2 x 4 (NI = 32 pp_nt orbitals per item), 1 = 8 x 1 (NI = 8 pp_nt)
+    int pp_nt = 0;                     // 8-wide occupied-orbital tiles per consumer warp
+    int pp_n_nt = 0;                   // items along the occupied orbitals: pp_n_nt * NI >= occ_w
     int64_t pp_rows = 0;               // sum over p of the padded partner counts
     std::vector<int32_t> pp_off;       // [N + 1] first row of p
     std::vector<int32_t> pp_q;         // [pp_rows] partner (internal index), n_pad on padding rows
@@ -47,6 +48,9 @@ struct Layout {
     int64_t pp_n_tri = 0;
     std::vector<int32_t> pp_jdst;      // [pp_rows] q >= p rows (the Coulomb half): offset of (q, p) inside Jt; -1 elsewhere
 };
+
+inline int pp_item_orbitals(const Layout& L) { return L.pp_layout ? 8 * L.pp_nt : 32 * L.pp_nt; }
+inline int pp_v_slots(const Layout& L) { return L.pp_n_nt * (L.pp_layout ? 1 : 4); }  // partial-V slots per (function, chunk)
 
 // event points recorded on the shard's stream during one build, in launch order
 enum EvPoint { EV_START = 0, EV_H2D, EV_PREP, EV_W, EV_K, EV_JBEGIN, EV_V, EV_J, EV_EPI, EV_AR, EV_D2H, EV_COUNT };
@@ -78,11 +82,13 @@ struct Shard {
     unsigned int* ppj_flag = nullptr;  // [pp_chunks * 4] quarter flags of the single-pass compact Coulomb kernel
     double* ppj_vp = nullptr;          // [pp_chunks * 4][sm_count][32] per-CTA partial V
     bool last_ppj_fused = false;
+    bool last_v_in_ht = false;
     int32_t* d_ppitems = nullptr;  // cost-balanced work lists of the per-function half-transform
     int32_t* d_ppoff = nullptr;
     int pp_ctas = 0;
     double* dvec = nullptr;    // [pp_rows] weighted density in partner-row space
     double* VpartP = nullptr;  // [slabs][pp_chunks * 128] partial V of the compact Coulomb pass
+    double* Vitem = nullptr;   // [N][pp_chunks][pp_v_slots][128] partial V left by the per-function half-transform
     double* Jpart = nullptr;   // [pp_chunks][pp_rows] partial J per chunk
     int pp_chunks = 0;         // ceil(q_len / 128)
     bool bc_valid = false;     // Bc mirrors the current Bp
@@ -145,8 +151,10 @@ struct jcdf_handle {
     int64_t opt_exchange_slices = 0;
     int64_t opt_exchange_balance = 1;  // cost-balanced exchange item lists (0: round-robin in item order)
     int64_t opt_regroup = 1;          // mask-driven regrouping of the basis functions into 32-wide blocks
+    int64_t opt_coulomb_v_in_ht = 1;   // compact Coulomb: V from the per-function half-transform's accumulators (no density, no V sweep)
     int64_t opt_coulomb_pp_fused = 0;  // compact Coulomb as ONE HBM pass (cooperative kernel): measured slower than the two
                                        // streaming passes (2.1 vs 1.3 ms at w50: 150 grid-wide flag rounds), so off by default
+    int64_t opt_pp_layout = -1;        // per-function half-transform warp arrangement: -1 = chosen from occ, 0 = 2 x 4, 1 = 8 x 1
     int64_t opt_pp_max_bytes = 0;      // cap on the partner-compacted copy per shard (0 = whatever cudaMalloc grants)
     int64_t opt_coulomb_pp = 1;       // Coulomb over the partner-compacted copy whenever the per-function path is active
     int64_t opt_ht_mode = 0;          // half-transform: 0 = choose from the mask, 1 = tile kernel, 2 = per-function kernel
@@ -163,10 +171,10 @@ void launch_prep(const Layout& L, Shard& s, int64_t ldc);
 void launch_half_transform(const Layout& L, Shard& s, int sm_count);
 void launch_pp_pack(const Layout& L, Shard& s);                        // kernels_pp.cu: Bp -> Bc
 void launch_pp_prep(const Layout& L, Shard& s, int64_t ldc);           // C_occ -> Ci
-void launch_pp_half_transform(const Layout& L, Shard& s, int sm_count);
+void launch_pp_half_transform(const Layout& L, Shard& s, int sm_count, bool v_in_ht);
 void launch_pp_density(const Layout& L, Shard& s);
 void plan_pp_items(const Layout& L, Shard& s, int sm_count, std::vector<int32_t>& list, std::vector<int32_t>& off);
-void launch_pp_coulomb(const Layout& L, Shard& s, cudaStream_t st, cudaEvent_t ev_v);
+void launch_pp_coulomb(const Layout& L, Shard& s, cudaStream_t st, cudaEvent_t ev_v, bool v_in_ht);
 int64_t pp_coulomb_slabs(const Layout& L);
 bool launch_pp_coulomb_fused(const Layout& L, Shard& s, int sm_count, cudaStream_t st);
 void launch_exchange(const Layout& L, Shard& s, int sm_count);

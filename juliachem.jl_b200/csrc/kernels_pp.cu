@@ -76,15 +76,15 @@ struct PPParams {
     int ldci, n_fn, n_nt, chunks, q_len, npt64, occ_w;
     const int32_t* item_list;  // items of CTA c: item_list[item_off[c] .. item_off[c + 1])  (cost-balanced on the host)
     const int32_t* item_off;
+    double* vitem;  // [function p][chunk][orbital tile][warp column][128] partial Coulomb V of the item (nullptr: not wanted)
 };
 
 // One pipeline stage (nks k-steps of 4 partner rows) of a warp block of MTV x NTV DMMA tiles inside the warp's 8 x NT
 // accumulator block.  MTV / NTV are compile-time: a predicated-off DMMA still takes its slot in the tensor pipe, so the
 // ragged last chunk and the ragged last orbital tile get their own instantiations instead of predicates.
-template <int NT, int MTV, int NTV>
-__device__ __forceinline__ void pp_slab(double (&acc)[8][NT][2], const double* __restrict__ sA,
+template <int MTW, int NT, int LDC, int MTV, int NTV>
+__device__ __forceinline__ void pp_slab(double (&acc)[MTW][NT][2], const double* __restrict__ sA,
                                         const double* __restrict__ sC, int m0, int n0, int g, int t, int nks) {
-    constexpr int LDC = 32 * NT + 4;
     // (m0 + 8 jm + g) ^ (t << 2): the swizzle touches bits 2-3, 8 jm bit 3 and up -> one base for even jm, one for odd jm
     const double* pa0 = sA + t * PP_QC + ((m0 + g) ^ (t << 2));
     const double* pa1 = sA + t * PP_QC + ((m0 + 8 + g) ^ (t << 2)) - 8;
@@ -103,38 +103,48 @@ __device__ __forceinline__ void pp_slab(double (&acc)[8][NT][2], const double* _
     }
 }
 
-template <int NT, int NTV>
-__device__ __forceinline__ void pp_slab_m(double (&acc)[8][NT][2], const double* sA, const double* sC, int m0, int n0,
+template <int MTW, int NT, int LDC, int NTV>
+__device__ __forceinline__ void pp_slab_m(double (&acc)[MTW][NT][2], const double* sA, const double* sC, int m0, int n0,
                                           int g, int t, int nks, int mtv) {
     switch (mtv) {
-        case 1: pp_slab<NT, 1, NTV>(acc, sA, sC, m0, n0, g, t, nks); break;
-        case 2: pp_slab<NT, 2, NTV>(acc, sA, sC, m0, n0, g, t, nks); break;
-        case 3: pp_slab<NT, 3, NTV>(acc, sA, sC, m0, n0, g, t, nks); break;
-        case 4: pp_slab<NT, 4, NTV>(acc, sA, sC, m0, n0, g, t, nks); break;
-        case 5: pp_slab<NT, 5, NTV>(acc, sA, sC, m0, n0, g, t, nks); break;
-        case 6: pp_slab<NT, 6, NTV>(acc, sA, sC, m0, n0, g, t, nks); break;
-        case 7: pp_slab<NT, 7, NTV>(acc, sA, sC, m0, n0, g, t, nks); break;
-        case 8: pp_slab<NT, 8, NTV>(acc, sA, sC, m0, n0, g, t, nks); break;
+        case 1: pp_slab<MTW, NT, LDC, 1, NTV>(acc, sA, sC, m0, n0, g, t, nks); break;
+        case 2: pp_slab<MTW, NT, LDC, (MTW >= 2 ? 2 : 1), NTV>(acc, sA, sC, m0, n0, g, t, nks); break;
+        case 3: if (MTW >= 3) pp_slab<MTW, NT, LDC, (MTW >= 3 ? 3 : 1), NTV>(acc, sA, sC, m0, n0, g, t, nks); break;
+        case 4: if (MTW >= 4) pp_slab<MTW, NT, LDC, (MTW >= 4 ? 4 : 1), NTV>(acc, sA, sC, m0, n0, g, t, nks); break;
+        case 5: if (MTW >= 5) pp_slab<MTW, NT, LDC, (MTW >= 5 ? 5 : 1), NTV>(acc, sA, sC, m0, n0, g, t, nks); break;
+        case 6: if (MTW >= 6) pp_slab<MTW, NT, LDC, (MTW >= 6 ? 6 : 1), NTV>(acc, sA, sC, m0, n0, g, t, nks); break;
+        case 7: if (MTW >= 7) pp_slab<MTW, NT, LDC, (MTW >= 7 ? 7 : 1), NTV>(acc, sA, sC, m0, n0, g, t, nks); break;
+        case 8: if (MTW >= 8) pp_slab<MTW, NT, LDC, (MTW >= 8 ? 8 : 1), NTV>(acc, sA, sC, m0, n0, g, t, nks); break;
         default: break;
     }
 }
 
-template <int NT>
-__device__ __forceinline__ void pp_slab_mn(double (&acc)[8][NT][2], const double* sA, const double* sC, int m0, int n0,
+template <int MTW, int NT, int LDC>
+__device__ __forceinline__ void pp_slab_mn(double (&acc)[MTW][NT][2], const double* sA, const double* sC, int m0, int n0,
                                            int g, int t, int nks, int mtv, int ntv) {
-    if (ntv == NT) pp_slab_m<NT, NT>(acc, sA, sC, m0, n0, g, t, nks, mtv);
-    else if (NT > 1 && ntv == 1) pp_slab_m<NT, 1>(acc, sA, sC, m0, n0, g, t, nks, mtv);
-    else if (NT > 2 && ntv == 2) pp_slab_m<NT, (NT > 2 ? 2 : 1)>(acc, sA, sC, m0, n0, g, t, nks, mtv);
-    else if (NT > 3 && ntv == 3) pp_slab_m<NT, (NT > 3 ? 3 : 1)>(acc, sA, sC, m0, n0, g, t, nks, mtv);
+    if (ntv == NT) pp_slab_m<MTW, NT, LDC, NT>(acc, sA, sC, m0, n0, g, t, nks, mtv);
+    else if (NT > 1 && ntv == 1) pp_slab_m<MTW, NT, LDC, 1>(acc, sA, sC, m0, n0, g, t, nks, mtv);
+    else if (NT > 2 && ntv == 2) pp_slab_m<MTW, NT, LDC, (NT > 2 ? 2 : 1)>(acc, sA, sC, m0, n0, g, t, nks, mtv);
+    else if (NT > 3 && ntv == 3) pp_slab_m<MTW, NT, LDC, (NT > 3 ? 3 : 1)>(acc, sA, sC, m0, n0, g, t, nks, mtv);
+    else if (ntv > 0) pp_slab_m<MTW, NT, LDC, NT>(acc, sA, sC, m0, n0, g, t, nks, mtv);  // layout 1 tail: whole width (zero C columns)
 }
 
 // One work item = (function p, chunk of 128 auxiliary rows, tile of NI = 32 NT occupied orbitals):
 //     out[Q, i] = sum_k Bc[chunk][off_p + k][Q] * Ci[q_k(p)][i]        (M = Q, N = i, K = padded partner count of p)
 // Warp 8 is the producer: lane 0 issues the A copy, lane j the copy of partner row j; warps 0-7 own 64 x (8 NT) blocks.
-template <int NT>
+// LAYOUT 0: consumer warps 2 (M halves of 64 rows) x 4 (N quarters of 8 NT orbitals), NI = 32 NT — the least shared
+//           memory traffic per DMMA, but the orbital count is padded to a multiple of 32 per item;
+// LAYOUT 1: consumer warps 8 x 1, every warp 16 rows x ALL NI = 8 NT orbitals (NT <= 12) — no padding beyond the 8-wide
+//           DMMA tile and the same DMMA count on every sub-partition; chosen when it executes fewer tiles (occ = 81:
+//           11 tiles instead of 12 on the busiest sub-partition).
+// WITH_V: the epilogue also leaves the item's share of the Coulomb vector V (a separate instantiation: the block costs
+//         registers the NT = 4 kernel does not have to spare).
+template <int NT, int LAYOUT, bool WITH_V>
+// 9 warps are allocated like 12 (register file granularity of 4 warps): 168 registers per thread is the cap
 __global__ void __launch_bounds__(PP_THREADS, 1) k_pp_half_transform(PPParams prm) {
-    constexpr int NI = 32 * NT;
-    constexpr int LDC = NI + 4;  // = 4 mod 16 doubles: the b fragment rows t = 0..3 fall on distinct bank quads
+    constexpr int MTW = LAYOUT ? 2 : 8;             // 8-row DMMA tiles per warp
+    constexpr int NI = LAYOUT ? 8 * NT : 32 * NT;   // orbitals per item
+    constexpr int LDC = NI + 4;  // = 4 (or 12) mod 16 doubles: the b fragment rows t = 0..3 fall on distinct bank quads
     constexpr int STAGE_DOUBLES = PP_KS * PP_QC + PP_KS * LDC;
     extern __shared__ __align__(128) unsigned char smem_raw[];
     double* stages = reinterpret_cast<double*>(smem_raw);
@@ -188,8 +198,8 @@ __global__ void __launch_bounds__(PP_THREADS, 1) k_pp_half_transform(PPParams pr
     // --------------------------------------------------- consumers ---------------------------------------------------
     PipeState ps;
     const int g = lane >> 2, t = lane & 3;
-    const int m0 = (warp >> 2) * 64;
-    const int n0 = (warp & 3) * 8 * NT;
+    const int m0 = LAYOUT ? warp * 16 : (warp >> 2) * 64;
+    const int n0 = LAYOUT ? 0 : (warp & 3) * 8 * NT;
     // the partner count of the NEXT item is fetched while the current one computes (the k loop bound would otherwise
     // wait on two dependent global loads at every item start)
     const int j_end = prm.item_off[blockIdx.x + 1];
@@ -208,13 +218,13 @@ __global__ void __launch_bounds__(PP_THREADS, 1) k_pp_half_transform(PPParams pr
         const int k4 = k4_next;
         k4_next = count_of(j + 1);
         const int rows_valid = min(PP_QC, prm.q_len - ch * PP_QC);
-        const int mt_valid = max(0, min(8, (rows_valid - m0 + 7) >> 3));
+        const int mt_valid = max(0, min(MTW, (rows_valid - m0 + 7) >> 3));
         const int nt_valid = max(0, min(NT, (prm.occ_w - nt * NI - n0 + 7) >> 3));
         const bool any = mt_valid > 0 && nt_valid > 0;
-        const bool whole = mt_valid == 8 && nt_valid == NT;
-        double acc[8][NT][2];
+        const bool whole = mt_valid == MTW && nt_valid == NT;
+        double acc[MTW][NT][2];
 #pragma unroll
-        for (int jm = 0; jm < 8; jm++)
+        for (int jm = 0; jm < MTW; jm++)
 #pragma unroll
             for (int jn = 0; jn < NT; jn++) acc[jm][jn][0] = acc[jm][jn][1] = 0.0;
 
@@ -223,13 +233,45 @@ __global__ void __launch_bounds__(PP_THREADS, 1) k_pp_half_transform(PPParams pr
             mbar_wait(&full[ps.stage], ps.phase);
             const double* sA = stages + (size_t)ps.stage * STAGE_DOUBLES;
             const double* sC = sA + PP_KS * PP_QC;
-            if (whole) pp_slab<NT, 8, NT>(acc, sA, sC, m0, n0, g, t, nks);
-            else if (any) pp_slab_mn<NT>(acc, sA, sC, m0, n0, g, t, nks, mt_valid, nt_valid);
+            if (whole) pp_slab<MTW, NT, LDC, MTW, NT>(acc, sA, sC, m0, n0, g, t, nks);
+            else if (any) pp_slab_mn<MTW, NT, LDC>(acc, sA, sC, m0, n0, g, t, nks, mt_valid, nt_valid);
             __syncwarp();
             if (lane == 0) mbar_arrive(&empty[ps.stage]);
             ps.advance<PP_NSTAGE>();
         }
         if (!any) continue;
+        // Coulomb V from the accumulators: D[p,q] = sum_i C[p,i] C[q,i], so
+        //     V[Q] = sum_pq B[Q,p,q] D[p,q] = sum_p sum_i C[p,i] W[Q,i,p]
+        // and the item's share is a dot product of each accumulator row with row p of C: MTW * NT * 2 DFMA per thread
+        // and ITEM, no density pass and no first sweep over B.  Each warp leaves its rows in its own slot; skipped
+        // warps leave the zeros the buffer was cleared to.
+        if constexpr (WITH_V) {
+            // opaque copies: nothing of this block may be hoisted above the k loop, where every register is taken
+            int pe = p, che = ch, nte = nt, lne = lane;
+            asm volatile("" : "+r"(pe), "+r"(che), "+r"(nte), "+r"(lne));
+            const int te = lne & 3, ge = lne >> 2;
+            const double* cp = prm.Ci + (int64_t)pe * prm.ldci + nte * NI + n0 + 2 * te;
+            constexpr int NW = LAYOUT ? 1 : 4;
+            double* vdst = prm.vitem + (((((int64_t)pe * chunks + che) * n_nt + nte) * NW + (LAYOUT ? 0 : (warp & 3))) * PP_QC) + m0 + ge;
+#pragma unroll
+            for (int jm = 0; jm < MTW; jm += 2) {  // two rows at a time: row p of C is re-read from L1, few registers live
+                double v0 = 0.0, v1 = 0.0;
+#pragma unroll
+                for (int jn = 0; jn < NT; jn++) {
+                    const double2 c = *reinterpret_cast<const double2*>(cp + 8 * jn);
+                    v0 = fma(acc[jm][jn][0], c.x, fma(acc[jm][jn][1], c.y, v0));
+                    v1 = fma(acc[jm + 1][jn][0], c.x, fma(acc[jm + 1][jn][1], c.y, v1));
+                }
+                v0 += __shfl_xor_sync(0xffffffffu, v0, 1);
+                v1 += __shfl_xor_sync(0xffffffffu, v1, 1);
+                v0 += __shfl_xor_sync(0xffffffffu, v0, 2);
+                v1 += __shfl_xor_sync(0xffffffffu, v1, 2);
+                if (te == 0) {
+                    vdst[8 * jm] = v0;
+                    vdst[8 * jm + 8] = v1;
+                }
+            }
+        }
         // epilogue: the thread's (i, i + 1) pair is adjacent in the k-fastest W tile -> 16-byte stores, 4 lanes = 64 bytes.
         // 32-bit index arithmetic up to the tile number (k rows and tiles are far below 2^31), one wide multiply per store.
         const int pr = p & 63;
@@ -238,9 +280,10 @@ __global__ void __launch_bounds__(PP_THREADS, 1) k_pp_half_transform(PPParams pr
         const int tile_stride = prm.npt64;  // W tiles per k chunk
         const int i0 = nt * NI + n0 + 2 * t;
         const int q0 = ch * PP_QC + m0 + g;
-        const bool all_in = (mt_valid == 8) && (nt * NI + n0 + 8 * NT <= prm.occ_w);
+        // every row and orbital of the warp's block exists (a last 8-row tile may be partly beyond q_len: guarded stores)
+        const bool all_in = (rows_valid - m0 >= 8 * MTW) && (nt * NI + n0 + 8 * NT <= prm.occ_w);
 #pragma unroll
-        for (int jm = 0; jm < 8; jm++) {
+        for (int jm = 0; jm < MTW; jm++) {
             const int Qrow = q0 + 8 * jm;
             if (!all_in && Qrow >= prm.q_len) continue;
             const int krow0 = Qrow * prm.occ_w + i0;
@@ -342,6 +385,30 @@ __global__ void k_pp_vreduce(const double* __restrict__ Vpart, double* __restric
     double v = 0.0;
     for (int s = 0; s < n_slab; s++) v += Vpart[(int64_t)s * qpad + Q];
     if (Q < q_len) V[Q] = v;
+}
+
+// V[Q] = sum of the per-item partials the half-transform left, in a fixed order.  One block per 32 auxiliary functions:
+// 32 groups of 32 threads take the functions p = k (mod 32), then one sum over the 32 groups.
+__global__ void __launch_bounds__(1024) k_pp_vitem_reduce(const double* __restrict__ vitem, double* __restrict__ V,
+                                                          int n_fn, int chunks, int slots, int q_len) {
+    __shared__ double part[32][33];
+    const int ch = blockIdx.x >> 2, c = (blockIdx.x & 3) * 32 + (threadIdx.x & 31), k = threadIdx.x >> 5;
+    double a = 0.0;
+    for (int p = k; p < n_fn; p += 32) {
+        const double* src = vitem + ((int64_t)p * chunks + ch) * slots * PP_QC + c;
+        double b = 0.0;
+        for (int sl = 0; sl < slots; sl++) b += __ldcs(src + sl * PP_QC);
+        a += b;
+    }
+    part[k][threadIdx.x & 31] = a;
+    __syncthreads();
+    if (k == 0) {
+        double v = 0.0;
+#pragma unroll
+        for (int kk = 0; kk < 32; kk++) v += part[kk][threadIdx.x];
+        const int Q = ch * PP_QC + c;
+        if (Q < q_len) V[Q] = v;
+    }
 }
 
 __global__ void __launch_bounds__(256) k_pp_coulomb_j(const double* __restrict__ Bc, const double* __restrict__ V,
@@ -588,19 +655,24 @@ bool launch_pp_coulomb_fused(const Layout& L, Shard& s, int sm_count, cudaStream
 }
 
 void launch_pp_density(const Layout& L, Shard& s) {
-    const int ldci = L.pp_n_nt * 32 * L.pp_nt;
+    const int ldci = L.pp_n_nt * pp_item_orbitals(L);
     const int blocks = (int)std::min<int64_t>((L.pp_rows + 7) / 8, 148 * 16);
     if (blocks <= 0) return;
     k_pp_density<<<blocks, 256, 0, s.stream>>>(s.Ci, ldci, (int)L.occ, s.d_pp_p, s.d_pp_q, s.d_pp_jdst, s.dvec, L.pp_rows);
 }
 
-void launch_pp_coulomb(const Layout& L, Shard& s, cudaStream_t st, cudaEvent_t ev_v) {  // two streaming passes
+// two streaming passes; v_in_ht: the half-transform already left the partial V sums, only their reduction remains
+void launch_pp_coulomb(const Layout& L, Shard& s, cudaStream_t st, cudaEvent_t ev_v, bool v_in_ht) {
     if (s.pp_chunks <= 0 || L.pp_rows <= 0) return;
     const int n_slab = (int)((L.pp_rows + PPJ_SLAB - 1) / PPJ_SLAB);
     const int qpad = s.pp_chunks * PP_QC;
     dim3 grid((unsigned)n_slab, (unsigned)s.pp_chunks);
-    k_pp_coulomb_v<<<grid, 256, 0, st>>>(s.Bc, s.dvec, s.VpartP, L.pp_rows, qpad);
-    k_pp_vreduce<<<(qpad + 127) / 128, 128, 0, st>>>(s.VpartP, s.V, n_slab, qpad, (int)s.q_len);
+    if (v_in_ht) {
+        k_pp_vitem_reduce<<<s.pp_chunks * 4, 1024, 0, st>>>(s.Vitem, s.V, (int)L.N, s.pp_chunks, pp_v_slots(L), (int)s.q_len);
+    } else {
+        k_pp_coulomb_v<<<grid, 256, 0, st>>>(s.Bc, s.dvec, s.VpartP, L.pp_rows, qpad);
+        k_pp_vreduce<<<(qpad + 127) / 128, 128, 0, st>>>(s.VpartP, s.V, n_slab, qpad, (int)s.q_len);
+    }
     if (ev_v) cudaEventRecord(ev_v, st);
     k_pp_coulomb_j<<<grid, 256, 0, st>>>(s.Bc, s.V, s.d_pp_jdst, s.Jpart, L.pp_rows, (int)s.q_len);
     k_pp_jreduce<<<(unsigned)((L.pp_rows + 255) / 256), 256, 0, st>>>(s.Jpart, s.d_pp_jdst, s.Jt, L.pp_rows, s.pp_chunks);
@@ -608,15 +680,20 @@ void launch_pp_coulomb(const Layout& L, Shard& s, cudaStream_t st, cudaEvent_t e
 
 int64_t pp_coulomb_slabs(const Layout& L) { return (L.pp_rows + PPJ_SLAB - 1) / PPJ_SLAB; }
 
-static size_t pp_smem_bytes(int nt) {
-    return (size_t)PP_NSTAGE * (PP_KS * PP_QC + PP_KS * (32 * nt + 4)) * 8 + 2 * PP_NSTAGE * 8 + 16;
+static size_t pp_smem_bytes(int ni) {
+    return (size_t)PP_NSTAGE * (PP_KS * PP_QC + PP_KS * (ni + 4)) * 8 + 2 * PP_NSTAGE * 8 + 16;
 }
 
-template <int NT>
+template <int NT, int LAYOUT>
 static void launch_pp_t(const PPParams& prm, int grid, cudaStream_t st) {
-    const size_t smem = pp_smem_bytes(NT);
-    cudaFuncSetAttribute(k_pp_half_transform<NT>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
-    k_pp_half_transform<NT><<<grid, PP_THREADS, smem, st>>>(prm);
+    const size_t smem = pp_smem_bytes(LAYOUT ? 8 * NT : 32 * NT);
+    if (prm.vitem != nullptr) {
+        cudaFuncSetAttribute(k_pp_half_transform<NT, LAYOUT, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+        k_pp_half_transform<NT, LAYOUT, true><<<grid, PP_THREADS, smem, st>>>(prm);
+    } else {
+        cudaFuncSetAttribute(k_pp_half_transform<NT, LAYOUT, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+        k_pp_half_transform<NT, LAYOUT, false><<<grid, PP_THREADS, smem, st>>>(prm);
+    }
 }
 
 // Work lists of the per-function half-transform.  Items differ in cost — the partner count of p, the ragged last
@@ -634,13 +711,27 @@ void plan_pp_items(const Layout& L, Shard& s, int sm_count, std::vector<int32_t>
     if (n_items <= 0 || n_items >= ((int64_t)1 << 31)) { s.pp_ctas = 0; return; }
     // row units of a chunk (both 64-row halves of the CTA tile) and orbital tiles of the busiest warp column
     std::vector<int> m_units((size_t)chunks), n_units((size_t)n_nt);
+    const int NI = pp_item_orbitals(L);
     for (int ch = 0; ch < chunks; ch++) {
         const int rows = (int)std::min<int64_t>(PP_QC, s.q_len - (int64_t)ch * PP_QC);
-        const int m0 = std::max(0, std::min(8, (rows + 7) >> 3)), m1 = std::max(0, std::min(8, (rows - 64 + 7) >> 3));
-        m_units[(size_t)ch] = m0 + m1;
+        if (L.pp_layout == 0) {
+            const int m0 = std::max(0, std::min(8, (rows + 7) >> 3)), m1 = std::max(0, std::min(8, (rows - 64 + 7) >> 3));
+            m_units[(size_t)ch] = m0 + m1;
+        } else {  // warps w and w + 4 share a sub-partition, 16 rows each
+            int best = 0;
+            for (int w = 0; w < 4; w++) {
+                const int a = std::max(0, std::min(2, (rows - 16 * w + 7) >> 3));
+                const int b = std::max(0, std::min(2, (rows - 16 * (w + 4) + 7) >> 3));
+                best = std::max(best, a + b);
+            }
+            m_units[(size_t)ch] = best;
+        }
     }
-    for (int nt = 0; nt < n_nt; nt++)
-        n_units[(size_t)nt] = std::max(0, std::min(NT, (L.occ_w - nt * 32 * NT + 7) >> 3));
+    for (int nt = 0; nt < n_nt; nt++) {
+        int u = std::max(0, std::min(NT, (L.occ_w - nt * NI + 7) >> 3));
+        if (L.pp_layout == 1 && u > 3 && u < NT) u = NT;  // the ragged last item of layout 1 runs the whole width
+        n_units[(size_t)nt] = u;
+    }
     std::vector<int64_t> cost((size_t)n_items);
     std::vector<int32_t> order((size_t)n_items);
     for (int64_t it = 0; it < n_items; it++) {
@@ -681,13 +772,13 @@ void launch_pp_pack(const Layout& L, Shard& s) {
 }
 
 void launch_pp_prep(const Layout& L, Shard& s, int64_t ldc) {
-    const int ldci = L.pp_n_nt * 32 * L.pp_nt;
+    const int ldci = L.pp_n_nt * pp_item_orbitals(L);
     const int64_t total = (int64_t)(L.n_pad + 1) * ldci;
     const int blocks = (int)std::min<int64_t>((total + 255) / 256, 148 * 16);
     k_pp_prep<<<blocks, 256, 0, s.stream>>>(s.Craw, ldc, s.Ci, (int)L.N, (int)L.occ, L.n_pad + 1, ldci, s.d_inv);
 }
 
-void launch_pp_half_transform(const Layout& L, Shard& s, int sm_count) {
+void launch_pp_half_transform(const Layout& L, Shard& s, int sm_count, bool v_in_ht) {
     PPParams prm;
     prm.Bc = s.Bc;
     prm.Ci = s.Ci;
@@ -695,7 +786,7 @@ void launch_pp_half_transform(const Layout& L, Shard& s, int sm_count) {
     prm.off = s.d_pp_off;
     prm.q = s.d_pp_q;
     prm.rows = L.pp_rows;
-    prm.ldci = L.pp_n_nt * 32 * L.pp_nt;
+    prm.ldci = L.pp_n_nt * pp_item_orbitals(L);
     prm.n_fn = (int)L.N;
     prm.n_nt = L.pp_n_nt;
     prm.chunks = s.pp_chunks;
@@ -704,15 +795,34 @@ void launch_pp_half_transform(const Layout& L, Shard& s, int sm_count) {
     prm.occ_w = L.occ_w;
     prm.item_list = s.d_ppitems;
     prm.item_off = s.d_ppoff;
+    prm.vitem = v_in_ht ? s.Vitem : nullptr;
     const int grid = s.pp_ctas;
     (void)sm_count;
     if (grid <= 0) return;
-    switch (L.pp_nt) {
-        case 1: launch_pp_t<1>(prm, grid, s.stream); break;
-        case 2: launch_pp_t<2>(prm, grid, s.stream); break;
-        case 3: launch_pp_t<3>(prm, grid, s.stream); break;
-        case 4: launch_pp_t<4>(prm, grid, s.stream); break;
-        default: break;
+    if (L.pp_layout == 0) {
+        switch (L.pp_nt) {
+            case 1: launch_pp_t<1, 0>(prm, grid, s.stream); break;
+            case 2: launch_pp_t<2, 0>(prm, grid, s.stream); break;
+            case 3: launch_pp_t<3, 0>(prm, grid, s.stream); break;
+            case 4: launch_pp_t<4, 0>(prm, grid, s.stream); break;
+            default: break;
+        }
+    } else {
+        switch (L.pp_nt) {
+            case 1: launch_pp_t<1, 1>(prm, grid, s.stream); break;
+            case 2: launch_pp_t<2, 1>(prm, grid, s.stream); break;
+            case 3: launch_pp_t<3, 1>(prm, grid, s.stream); break;
+            case 4: launch_pp_t<4, 1>(prm, grid, s.stream); break;
+            case 5: launch_pp_t<5, 1>(prm, grid, s.stream); break;
+            case 6: launch_pp_t<6, 1>(prm, grid, s.stream); break;
+            case 7: launch_pp_t<7, 1>(prm, grid, s.stream); break;
+            case 8: launch_pp_t<8, 1>(prm, grid, s.stream); break;
+            case 9: launch_pp_t<9, 1>(prm, grid, s.stream); break;
+            case 10: launch_pp_t<10, 1>(prm, grid, s.stream); break;
+            case 11: launch_pp_t<11, 1>(prm, grid, s.stream); break;
+            case 12: launch_pp_t<12, 1>(prm, grid, s.stream); break;
+            default: break;
+        }
     }
 }
 

@@ -9,13 +9,15 @@ pytestmark = pytest.mark.gpu
 TOL = 1e-10
 
 
-def _build(N, Q, occ, B, C_occ, H, mask, ndev=1, shards=None, fused=1, overlap=0, ht_mode=0, coulomb_pp=1, pp_fused=1):
+def _build(N, Q, occ, B, C_occ, H, mask, ndev=1, shards=None, fused=1, overlap=0, ht_mode=0, coulomb_pp=1, pp_fused=1,
+           v_in_ht=1):
     gd = jc.B200Data(N, Q, occ, ndev)
     if shards is not None:
         gd.set_shards(shards)
     gd.set_option("ht_mode", ht_mode)  # 0 = chosen from the mask, 1 = tile kernel, 2 = per-function kernel
     gd.set_option("coulomb_pp", coulomb_pp)  # with the per-function kernel: Coulomb over the compact copy too
     gd.set_option("coulomb_pp_fused", pp_fused)  # ... as one cooperative single-pass kernel (0: two streaming passes)
+    gd.set_option("coulomb_v_in_ht", v_in_ht)  # compact Coulomb: V from the half-transform's accumulators
     gd.set_option("coulomb_fused", fused)
     gd.set_option("coulomb_overlap", overlap)
     gd.set_mask(jc.ScreeningData(mask, N))
@@ -49,7 +51,7 @@ def test_screened_parity(N, Q, occ, hw, fused, overlap, ht_mode, coulomb_pp):
     # coulomb_pp: 1 = compact Coulomb as one cooperative single-pass kernel, 2 = as two streaming passes, 0 = tile space
     gd, F, st = _build(N, Q, occ, B, C_occ, H, mask, fused=fused, overlap=overlap, ht_mode=ht_mode,
                        coulomb_pp=min(coulomb_pp, 1), pp_fused=int(coulomb_pp == 1))
-    base = (6 if coulomb_pp == 1 else 9) if (ht_mode == 2 and coulomb_pp) else 6 if fused else 7
+    base = (6 if coulomb_pp == 1 else 7) if (ht_mode == 2 and coulomb_pp) else 6 if fused else 7
     assert gd.layout().kernel_launches_per_build in (base, base + 1)  # + k_exchange_reduce when the contraction is sliced
     li = gd.layout()
     assert li.pairs_kept == int(mask.sum())
@@ -81,7 +83,7 @@ def test_fused_coulomb_is_deterministic_and_long_rows_fall_back():
     gd.close()
     N, Q, occ = 1500, 3, 2
     B, C_occ, H = random_inputs(N, Q, occ, seed=10)
-    gd, F, _ = _build(N, Q, occ, B, C_occ, H, None, fused=1)
+    gd, F, _ = _build(N, Q, occ, B, C_occ, H, None, fused=1, ht_mode=1)  # tile family: its Coulomb is the one under test
     assert gd.layout().kernel_launches_per_build == 7
     assert np.abs(F - oracle_fock(B, C_occ, H, None)).max() < TOL
     gd.close()
@@ -305,11 +307,55 @@ def test_per_function_half_transform(N, Q, occ, ht_mode, coulomb_pp):
     gd.close()
 
 
-@pytest.mark.parametrize("N,Q,occ", [(128, 40, 12), (256, 130, 30), (40, 5, 3), (130, 128, 64)])
+@pytest.mark.parametrize("N,Q,occ,overlap", [(180, 300, 130, 0), (333, 257, 40, 0), (333, 257, 40, 1), (96, 129, 81, 0),
+                                             (700, 520, 33, 0), (64, 5, 3, 0)])
+def test_coulomb_v_folded_into_half_transform(N, Q, occ, overlap):
+    """Compact Coulomb with V[Q] = sum_p sum_i C[p,i] W[Q,i,p] taken from the per-function half-transform's accumulators
+    (default) against the density + separate V pass: both within tolerance of the oracle, two kernel launches fewer,
+    repeat builds bit-identical (per-item partials are reduced in a fixed order), several orbital tiles (occ = 130)."""
+    mask = _scattered_mask(N, 19, 1, seed=N + 2)
+    B, C_occ, H = random_inputs(N, Q, occ, seed=N + 8, mask=mask)
+    F_ref = oracle_fock(B, C_occ, H, mask)
+    out = []
+    for v_in_ht in (1, 0):
+        gd, F, _ = _build(N, Q, occ, B, C_occ, H, mask, ht_mode=2, coulomb_pp=1, pp_fused=0, overlap=overlap, v_in_ht=v_in_ht)
+        assert gd.layout().kernel_launches_per_build in ((7, 8) if v_in_ht else (9, 10))
+        assert np.abs(F - F_ref).max() < TOL
+        assert np.array_equal(F, F.T)
+        assert np.array_equal(gd.fock_build(C_occ, None)[0], F)
+        out.append(F)
+        gd.close()
+    assert np.abs(out[0] - out[1]).max() < 1e-12
+
+
+@pytest.mark.parametrize("occ", [1, 7, 8, 9, 24, 25, 41, 81, 96, 97, 103, 104, 130, 193])
+@pytest.mark.parametrize("pp_layout", [0, 1])
+def test_per_function_warp_layouts(occ, pp_layout):
+    """Both consumer-warp arrangements of the per-function kernel (2 x 4 warps with the orbitals of an item padded to 32,
+    8 x 1 warps with 8-wide tiles only) over occupied counts that hit every ragged case: fewer than one tile, exact
+    multiples of 8 / 32 / 96, one orbital over (97 = 13 tiles -> two items of 7 with 6 valid in the second), several
+    items (193), and a Q range with a ragged last chunk of 9 rows (one warp busy in the 8 x 1 arrangement)."""
+    N, Q = max(100, occ + 10), 137
+    mask = _scattered_mask(N, 11, 1, seed=occ)
+    B, C_occ, H = random_inputs(N, Q, occ, seed=occ + 31, mask=mask)
+    F_ref = oracle_fock(B, C_occ, H, mask)
+    gd = jc.B200Data(N, Q, occ, 1)
+    gd.set_option("ht_mode", 2)
+    gd.set_option("pp_layout", pp_layout)
+    gd.set_mask(jc.ScreeningData(mask, N))
+    gd.set_B(0, reference_layout_rows(B, range(0, Q), mask))
+    F, _ = gd.fock_build(C_occ, H)
+    assert np.abs(F - F_ref).max() < TOL
+    assert np.array_equal(F, F.T)
+    gd.close()
+
+
+@pytest.mark.parametrize("N,Q,occ", [(128, 40, 12), (256, 130, 30), (40, 5, 3), (130, 128, 64), (130, 188, 12), (90, 125, 30)])
 @pytest.mark.parametrize("ht_mode", [1, 2])
 def test_tile_edge_sizes(N, Q, occ, ht_mode):
     """Sizes on the edges of the blockings: N an exact multiple of the 128-wide exchange tile (no clipping), one tile only
-    (diagonal rectangles alone), Q below / exactly one 128-row chunk, occ = 64 (two full orbital tiles of 32)."""
+    (diagonal rectangles alone), Q below / exactly one 128-row chunk, occ = 64 (two full orbital tiles of 32), a last
+    chunk of 60 / 125 rows (the last 8-row tile of a warp partly beyond Q: stores must stay guarded)."""
     mask = _scattered_mask(N, 7, 1, seed=N + Q)
     B, C_occ, H = random_inputs(N, Q, occ, seed=N + Q + 1, mask=mask)
     F_ref = oracle_fock(B, C_occ, H, mask)
