@@ -952,10 +952,7 @@ int fock_build_impl(jcdf_handle* h, const double* C_occ, int64_t ldc, const doub
         if (!pp_j) launch_prep(L, s, L.N);
         if (use_pp) launch_pp_prep(L, s, L.N);
         // V = sum_p sum_i C[p,i] W[Q,i,p] comes out of the half-transform's accumulators: no density, no V sweep
-        // (1 = where it pays: the 2 x 4 arrangement at 4 tiles per warp has no registers to spare, the block spills
-        // inside its k loop and costs more than the sweep it saves — w50: +2.4 ms against -0.7 ms; 2 = always)
-        const bool v_fits = h->opt_coulomb_v_in_ht >= 2 || !(L.pp_layout == 0 && L.pp_nt == 4);
-        const bool v_in_ht = pp_j && h->opt_coulomb_v_in_ht && v_fits && !h->opt_coulomb_pp_fused && s.Vitem != nullptr;
+        const bool v_in_ht = pp_j && h->opt_coulomb_v_in_ht && !h->opt_coulomb_pp_fused && s.Vitem != nullptr;
         if (pp_j && !v_in_ht) launch_pp_density(L, s);
         JC_CUDA(cudaEventRecord(s.ev[EV_PREP], s.stream));
         if (use_pp) launch_pp_half_transform(L, s, h->sm_count, v_in_ht);
@@ -1157,8 +1154,7 @@ int32_t jcdf_get_layout(jcdf_handle* h, jcdf_layout_info* o) {
     const bool ppj = !h->shards.empty() && L.pp_enabled && h->shards[0].Bc != nullptr && h->opt_coulomb_pp;
     const int kred = (!h->shards.empty() && h->shards[0].xplan.n_slices > 1) ? 1 : 0;  // k_exchange_reduce
     const bool ppjf = ppj && h->shards[0].last_ppj_fused;  // one cooperative Coulomb kernel instead of V, V reduce, J, J reduce
-    const bool vht = ppj && !ppjf && h->opt_coulomb_v_in_ht && !h->opt_coulomb_pp_fused &&
-                     (h->opt_coulomb_v_in_ht >= 2 || !(L.pp_layout == 0 && L.pp_nt == 4));  // density, V pass, V reduce -> one reduce
+    const bool vht = ppj && !ppjf && h->opt_coulomb_v_in_ht && !h->opt_coulomb_pp_fused;  // density, V pass, V reduce -> one reduce
     o->kernel_launches_per_build = kred + (ppjf ? 6 : ppj ? (vht ? 7 : 9) : ((!h->shards.empty() && h->shards[0].last_coulomb_fused) ? 6 : 7)) +
                                    ((h->n_ranks * (int)h->shards.size() > 1) ? 1 : 0);  // + mirror after the all-reduce
     return JCDF_OK;

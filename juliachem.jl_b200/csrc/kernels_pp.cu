@@ -227,6 +227,9 @@ __global__ void __launch_bounds__(PP_THREADS, 1) k_pp_half_transform(PPParams pr
         for (int jm = 0; jm < MTW; jm++)
 #pragma unroll
             for (int jn = 0; jn < NT; jn++) acc[jm][jn][0] = acc[jm][jn][1] = 0.0;
+        if constexpr (WITH_V) {  // the epilogue reads the warp's 8 NT orbitals of row p of C: have them in L1 by then
+            if (lane < NT) asm volatile("prefetch.global.L1 [%0];" ::"l"(prm.Ci + (int64_t)p * prm.ldci + nt * NI + n0 + 8 * lane));
+        }
 
         for (int k0 = 0; k0 < k4; k0 += PP_KS) {
             const int nks = min(PP_KS, k4 - k0) >> 2;
@@ -240,38 +243,6 @@ __global__ void __launch_bounds__(PP_THREADS, 1) k_pp_half_transform(PPParams pr
             ps.advance<PP_NSTAGE>();
         }
         if (!any) continue;
-        // Coulomb V from the accumulators: D[p,q] = sum_i C[p,i] C[q,i], so
-        //     V[Q] = sum_pq B[Q,p,q] D[p,q] = sum_p sum_i C[p,i] W[Q,i,p]
-        // and the item's share is a dot product of each accumulator row with row p of C: MTW * NT * 2 DFMA per thread
-        // and ITEM, no density pass and no first sweep over B.  Each warp leaves its rows in its own slot; skipped
-        // warps leave the zeros the buffer was cleared to.
-        if constexpr (WITH_V) {
-            // opaque copies: nothing of this block may be hoisted above the k loop, where every register is taken
-            int pe = p, che = ch, nte = nt, lne = lane;
-            asm volatile("" : "+r"(pe), "+r"(che), "+r"(nte), "+r"(lne));
-            const int te = lne & 3, ge = lne >> 2;
-            const double* cp = prm.Ci + (int64_t)pe * prm.ldci + nte * NI + n0 + 2 * te;
-            constexpr int NW = LAYOUT ? 1 : 4;
-            double* vdst = prm.vitem + (((((int64_t)pe * chunks + che) * n_nt + nte) * NW + (LAYOUT ? 0 : (warp & 3))) * PP_QC) + m0 + ge;
-#pragma unroll
-            for (int jm = 0; jm < MTW; jm += 2) {  // two rows at a time: row p of C is re-read from L1, few registers live
-                double v0 = 0.0, v1 = 0.0;
-#pragma unroll
-                for (int jn = 0; jn < NT; jn++) {
-                    const double2 c = *reinterpret_cast<const double2*>(cp + 8 * jn);
-                    v0 = fma(acc[jm][jn][0], c.x, fma(acc[jm][jn][1], c.y, v0));
-                    v1 = fma(acc[jm + 1][jn][0], c.x, fma(acc[jm + 1][jn][1], c.y, v1));
-                }
-                v0 += __shfl_xor_sync(0xffffffffu, v0, 1);
-                v1 += __shfl_xor_sync(0xffffffffu, v1, 1);
-                v0 += __shfl_xor_sync(0xffffffffu, v0, 2);
-                v1 += __shfl_xor_sync(0xffffffffu, v1, 2);
-                if (te == 0) {
-                    vdst[8 * jm] = v0;
-                    vdst[8 * jm + 8] = v1;
-                }
-            }
-        }
         // epilogue: the thread's (i, i + 1) pair is adjacent in the k-fastest W tile -> 16-byte stores, 4 lanes = 64 bytes.
         // 32-bit index arithmetic up to the tile number (k rows and tiles are far below 2^31), one wide multiply per store.
         const int pr = p & 63;
@@ -293,6 +264,40 @@ __global__ void __launch_bounds__(PP_THREADS, 1) k_pp_half_transform(PPParams pr
                 const int krow = krow0 + 8 * jn;
                 double* dst = wbase + (int64_t)((krow >> 5) * tile_stride) * 2048 + ((krow & 31) ^ sw);
                 *reinterpret_cast<double2*>(dst) = make_double2(acc[jm][jn][0], acc[jm][jn][1]);
+            }
+        }
+        // Coulomb V from the accumulators: D[p,q] = sum_i C[p,i] C[q,i], so
+        //     V[Q] = sum_pq B[Q,p,q] D[p,q] = sum_p sum_i C[p,i] W[Q,i,p]
+        // and the item's share is a dot product of each accumulator row with row p of C: MTW * NT * 2 DFMA per thread
+        // and ITEM, no density pass and no first sweep over B.  Each warp leaves its rows in its own slot; skipped
+        // warps leave the zeros the buffer was cleared to.
+        if constexpr (WITH_V) {
+            // opaque copies: nothing of this block may be hoisted above the k loop, where every register is taken
+            int pe = p, che = ch, nte = nt, lne = lane;
+            asm volatile("" : "+r"(pe), "+r"(che), "+r"(nte), "+r"(lne));
+            const int te = lne & 3, ge = lne >> 2;
+            const double* cp = prm.Ci + (int64_t)pe * prm.ldci + nte * NI + n0 + 2 * te;
+            constexpr int NW = LAYOUT ? 1 : 4;
+            double* vdst = prm.vitem + (((((int64_t)pe * chunks + che) * n_nt + nte) * NW + (LAYOUT ? 0 : (warp & 3))) * PP_QC) + m0 + ge;
+            // after the W stores only the accumulators are live: row p of C is loaded whole (one latency), then MTW
+            // independent dot-product chains
+            double2 c[NT];
+#pragma unroll
+            for (int jn = 0; jn < NT; jn++) c[jn] = *reinterpret_cast<const double2*>(cp + 8 * jn);
+            double v[MTW];
+#pragma unroll
+            for (int jm = 0; jm < MTW; jm++) v[jm] = 0.0;
+#pragma unroll
+            for (int jn = 0; jn < NT; jn++)
+#pragma unroll
+                for (int jm = 0; jm < MTW; jm++) v[jm] = fma(acc[jm][jn][0], c[jn].x, fma(acc[jm][jn][1], c[jn].y, v[jm]));
+#pragma unroll
+            for (int jm = 0; jm < MTW; jm++) v[jm] += __shfl_xor_sync(0xffffffffu, v[jm], 1);
+#pragma unroll
+            for (int jm = 0; jm < MTW; jm++) v[jm] += __shfl_xor_sync(0xffffffffu, v[jm], 2);
+            if (te == 0) {
+#pragma unroll
+                for (int jm = 0; jm < MTW; jm++) vdst[8 * jm] = v[jm];
             }
         }
     }

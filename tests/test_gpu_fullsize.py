@@ -34,7 +34,7 @@ def test_w50_kernel_families_agree_and_shards_sum():
     C, H = wl.occupied_coefficients(w), wl.core_hamiltonian(w)
     _, gd = _w50(2)
     F_pp = gd.fock_build(C, H)[0].copy()
-    assert gd.layout().kernel_launches_per_build == 10  # per-function path (occ 250: 2 x 4 warps, 4 tiles each -> separate density + V pass), sliced exchange reduce
+    assert gd.layout().kernel_launches_per_build == 8  # per-function path, compact Coulomb with V from the half-transform, sliced exchange reduce
     gd.close()
     _, gd = _w50(1)
     F_tiles = gd.fock_build(C, H)[0].copy()
