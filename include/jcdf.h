@@ -100,6 +100,10 @@ int32_t jcdf_set_B_device(jcdf_handle* h, int32_t dev, const double* B_dev, int6
  * columns in the reference pair order): T after jcdf_upload_three_center / jcdf_compute_three_center, B after
  * jcdf_factor_and_form_B / jcdf_set_B — scf_data.D of ScreenedDF.jl:103.  For tests and debugging.                */
 int32_t jcdf_get_B(jcdf_handle* h, int32_t dev, double* out, int64_t ld);
+/* Same for the row window [row_begin, row_begin + row_count) of the shard (local row numbers): out is
+ * (row_count x P) column-major with leading dimension ld.  Lets a checker pull a shard too large for one host array
+ * slab by slab (the Fock build is a plain sum over auxiliary rows).                                                */
+int32_t jcdf_get_B_rows(jcdf_handle* h, int32_t dev, int64_t row_begin, int64_t row_count, double* out, int64_t ld);
 /* Copy the inverse Cholesky factor Linv (Q x Q, lower, column-major) back — for tests (J_AB_invt, ScreenedDF.jl:95) */
 int32_t jcdf_get_metric_inverse(jcdf_handle* h, double* Linv_out);
 /* Keep H resident on the shard-0 device so later jcdf_fock_build calls may pass H = NULL (H is constant over an SCF:

@@ -44,6 +44,7 @@ SIGNATURES = {
     "jcdf_set_B": (_i32, [_p, _i32, _p, _i64]),
     "jcdf_set_B_device": (_i32, [_p, _i32, _p, _i64, _i64, _i64]),
     "jcdf_get_B": (_i32, [_p, _i32, _p, _i64]),
+    "jcdf_get_B_rows": (_i32, [_p, _i32, _i64, _i64, _p, _i64]),
     "jcdf_get_metric_inverse": (_i32, [_p, _p]),
     "jcdf_set_core_hamiltonian": (_i32, [_p, _p]),
     "jcdf_fock_build": (_i32, [_p, _p, _i64, _p, _p, _p]),

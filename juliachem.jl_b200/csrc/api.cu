@@ -752,34 +752,44 @@ int32_t jcdf_set_B_device(jcdf_handle* h, int32_t dev, const double* B_dev, int6
     return JCDF_OK;
 }
 
-int32_t jcdf_get_B(jcdf_handle* h, int32_t dev, double* out, int64_t ld) {
-    JC_REQUIRE(h && out, "jcdf_get_B: NULL argument");
-    JC_REQUIRE(h->lay.mask_set, "jcdf_get_B: call jcdf_set_mask first");
-    JC_REQUIRE(dev >= 0 && dev < (int)h->shards.size(), "jcdf_get_B: device index out of range");
+int32_t jcdf_get_B_rows(jcdf_handle* h, int32_t dev, int64_t row_begin, int64_t row_count, double* out, int64_t ld) {
+    JC_REQUIRE(h && out, "jcdf_get_B_rows: NULL argument");
+    JC_REQUIRE(h->lay.mask_set, "jcdf_get_B_rows: call jcdf_set_mask first");
+    JC_REQUIRE(dev >= 0 && dev < (int)h->shards.size(), "jcdf_get_B_rows: device index out of range");
     Shard& s = h->shards[dev];
-    JC_REQUIRE(ld >= s.q_len, "jcdf_get_B: ld smaller than the shard's row count");
-    if (s.q_len == 0) return JCDF_OK;
+    JC_REQUIRE(row_begin >= 0 && row_count >= 0 && row_begin + row_count <= s.q_len, "jcdf_get_B_rows: rows outside the shard");
+    JC_REQUIRE(ld >= row_count, "jcdf_get_B_rows: ld smaller than the row count");
+    if (row_count == 0) return JCDF_OK;
     const Layout& L = h->lay;
     const int64_t P = L.pairs_kept;
     JC_CUDA(cudaSetDevice(s.dev));
-    int64_t* d_src = nullptr;
-    double* win_buf = nullptr;
+    // scope guard: the two scratch buffers are released on every exit path
+    struct Scratch {
+        int64_t* d_src = nullptr;
+        double* win_buf = nullptr;
+        ~Scratch() { if (d_src) cudaFree(d_src); if (win_buf) cudaFree(win_buf); }
+    } sc;
     int rc;
-    if ((rc = dev_alloc(&d_src, (size_t)P))) return rc;
-    JC_CUDA(cudaMemcpyAsync(d_src, L.src_of_col.data(), sizeof(int64_t) * P, cudaMemcpyHostToDevice, s.stream));
-    const int64_t win = std::max<int64_t>(1, std::min<int64_t>(P, ((int64_t)1 << 26) / std::max<int64_t>(s.q_len, 1)));
-    if ((rc = dev_alloc(&win_buf, (size_t)(win * s.q_len)))) return rc;
+    if ((rc = dev_alloc(&sc.d_src, (size_t)P))) return rc;
+    JC_CUDA(cudaMemcpyAsync(sc.d_src, L.src_of_col.data(), sizeof(int64_t) * P, cudaMemcpyHostToDevice, s.stream));
+    const int64_t win = std::max<int64_t>(1, std::min<int64_t>(P, ((int64_t)1 << 26) / std::max<int64_t>(row_count, 1)));
+    if ((rc = dev_alloc(&sc.win_buf, (size_t)(win * row_count)))) return rc;
     for (int64_t c0 = 0; c0 < P; c0 += win) {
         const int64_t nc = std::min(win, P - c0);
-        launch_gather_pairs(L, s, win_buf, s.q_len, c0, nc, d_src);
+        launch_gather_pairs(L, s, sc.win_buf, row_count, c0, nc, sc.d_src, row_begin, row_count);
         JC_CUDA(cudaGetLastError());
-        JC_CUDA(cudaMemcpy2DAsync(out + ld * c0, sizeof(double) * ld, win_buf, sizeof(double) * s.q_len, sizeof(double) * s.q_len,
-                                  (size_t)nc, cudaMemcpyDeviceToHost, s.stream));
+        JC_CUDA(cudaMemcpy2DAsync(out + ld * c0, sizeof(double) * ld, sc.win_buf, sizeof(double) * row_count,
+                                  sizeof(double) * row_count, (size_t)nc, cudaMemcpyDeviceToHost, s.stream));
         JC_CUDA(cudaStreamSynchronize(s.stream));
     }
-    cudaFree(d_src);
-    cudaFree(win_buf);
     return JCDF_OK;
+}
+
+int32_t jcdf_get_B(jcdf_handle* h, int32_t dev, double* out, int64_t ld) {
+    JC_REQUIRE(h && out, "jcdf_get_B: NULL argument");
+    JC_REQUIRE(dev >= 0 && dev < (int)h->shards.size(), "jcdf_get_B: device index out of range");
+    JC_REQUIRE(ld >= h->shards[dev].q_len, "jcdf_get_B: ld smaller than the shard's row count");
+    return jcdf_get_B_rows(h, dev, 0, h->shards[dev].q_len, out, ld);
 }
 
 int32_t jcdf_upload_metric(jcdf_handle* h, const double* J_PQ) {

@@ -185,7 +185,7 @@ void launch_mirror_lower(const Layout& L, Shard& s);
 void launch_scatter_pairs(const Layout& L, Shard& s, const double* T_dev, int64_t ld, int64_t col_begin,
                           int64_t col_count);
 void launch_gather_pairs(const Layout& L, Shard& s, double* T_dev, int64_t ld, int64_t col_begin, int64_t col_count,
-                         const int64_t* d_src_of_col);
+                         const int64_t* d_src_of_col, int64_t row_begin, int64_t row_count);
 void launch_fill_synthetic(const Layout& L, Shard& s, uint64_t seed, double decay_length);
 size_t half_transform_smem_bytes(int bm);
 size_t exchange_smem_bytes();

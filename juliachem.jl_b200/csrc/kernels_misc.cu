@@ -48,11 +48,12 @@ __global__ void k_gather_pairs(double* __restrict__ T_dev, int64_t ld, int64_t c
 }
 
 void launch_gather_pairs(const Layout& L, Shard& s, double* T_dev, int64_t ld, int64_t col_begin, int64_t col_count,
-                         const int64_t* d_src_of_col) {
-    if (col_count <= 0 || s.q_len <= 0) return;
+                         const int64_t* d_src_of_col, int64_t row_begin, int64_t row_count) {
+    if (col_count <= 0 || row_count <= 0) return;
     dim3 block(128);
-    dim3 grid((unsigned)((s.q_len + 127) / 128), (unsigned)std::min<int64_t>(col_count, 32768));
-    k_gather_pairs<<<grid, block, 0, s.stream>>>(T_dev, ld, col_begin, col_count, (int)s.q_len, d_src_of_col, s.Bp, L.row_len);
+    dim3 grid((unsigned)((row_count + 127) / 128), (unsigned)std::min<int64_t>(col_count, 32768));
+    k_gather_pairs<<<grid, block, 0, s.stream>>>(T_dev, ld, col_begin, col_count, (int)row_count, d_src_of_col,
+                                                 s.Bp + row_begin * L.row_len, L.row_len);
 }
 
 // ---------------------------------------------------------------------------------------------------------------------

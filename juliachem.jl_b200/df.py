@@ -183,6 +183,12 @@ class B200Data:
         check(self._lib.jcdf_get_B(self._h, dev, _ptr(out), max(q_len, 1)))
         return out
 
+    def get_B_rows(self, dev: int, row_begin: int, row_count: int, P: int) -> np.ndarray:
+        """Rows [row_begin, row_begin + row_count) of device `dev`'s shard in the reference layout (jcdf_get_B_rows)."""
+        out = np.zeros((row_count, P), dtype=np.float64, order="F")
+        check(self._lib.jcdf_get_B_rows(self._h, dev, row_begin, row_count, _ptr(out), max(row_count, 1)))
+        return out
+
     def get_metric_inverse(self) -> np.ndarray:
         out = np.zeros((self.Q, self.Q), dtype=np.float64, order="F")
         check(self._lib.jcdf_get_metric_inverse(self._h, _ptr(out)))

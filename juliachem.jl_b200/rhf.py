@@ -10,7 +10,8 @@ shells in atom order, n_electrons = sum Z - charge).  `run_energy` is the body o
 the SCF loop all run on the GPU(s); the host only sees the scalars of every iteration and the final matrices.
 
 The reference reads its basis sets from records/bsed.h5, a binary that is not part of the checkout; the only sets
-recoverable from the snapshot are the ones its logs print (data/basis_ccpvdz_OH.json: cc-pVDZ + cc-pVDZ-RIFIT for O, H).
+recoverable from the snapshot are the ones its logs print (data/basis_ccpvdz_OH.json: cc-pVDZ + cc-pVDZ-RIFIT for O, H;
+data/basis_631g2dfp_jkfit_HCO.json: 6-31G(2df,p) + cc-pVTZ-JKFIT for H, C, O).
 """
 from __future__ import annotations
 
@@ -27,12 +28,22 @@ ATOMIC_MASS = {"H": 1.00794, "C": 12.0107, "N": 14.0067, "O": 15.9994}  # BasisH
 _DATA = os.path.join(os.path.dirname(os.path.abspath(__file__)), "data")
 
 
+_BASIS_FILES = {
+    # model["basis"] (lower case) -> data file; each file holds one primary set and the auxiliary set the reference ran it with
+    "cc-pvdz": "basis_ccpvdz_OH.json",                     # + cc-pVDZ-RIFIT, O H   (water_ccpvdz_out.log:43-170)
+    "cc-pvdz/cc-pvdz-rifit": "basis_ccpvdz_OH.json",
+    "6-31g(2df,p)": "basis_631g2dfp_jkfit_HCO.json",       # + cc-pVTZ-JKFIT, H C O (test/s10_new_algo-3-20.log:43-205, 641-1560)
+    "6-31g(2df,p)/cc-pvtz-jkfit": "basis_631g2dfp_jkfit_HCO.json",
+}
+
+
 def load_basis_library(name: str = "cc-pVDZ") -> dict:
     """{symbol: {"Z", "basis": [shell], "auxiliary_basis": [shell]}}; shell = {"l", "exps", "coefs"} (raw values)."""
-    if name.lower() not in ("cc-pvdz", "cc-pvdz/cc-pvdz-rifit"):
+    f = _BASIS_FILES.get(name.lower())
+    if f is None:
         raise KeyError("basis set %r is not available here: the reference's records/bsed.h5 is not part of the checkout; "
-                       "only cc-pVDZ / cc-pVDZ-RIFIT for O and H could be recovered from its logs" % name)
-    return json.load(open(os.path.join(_DATA, "basis_ccpvdz_OH.json")))["atoms"]
+                       "only the sets its logs print could be recovered: %s" % (name, sorted(_BASIS_FILES)))
+    return json.load(open(os.path.join(_DATA, f)))["atoms"]
 
 
 class FlatBasis:

@@ -425,3 +425,21 @@ def fock_build_screened_rank_threaded(B: np.ndarray, C_occ: np.ndarray, sd: Scre
     if timings is not None:
         timings.update({"W": t1 - t0, "K": t2 - t1, "J": t3 - t2})
     return fock
+
+
+def fock_build_screened_slabs(get_rows, Q: int, C_occ: np.ndarray, sd: ScreeningData, n_threads: int, slab: int,
+                              timings: dict | None = None) -> np.ndarray:
+    """The two-electron Fock matrix of all Q auxiliary rows as the sum of fock_build_screened_rank_threaded over
+    contiguous row slabs — the way the reference's MPI ranks each contract their own Q rows and Allreduce the partials
+    (DensityFitting.jl:68-71).  get_rows(q0, q1) returns rows [q0, q1) of B as a (q1 - q0, P) column-major array, so a
+    tensor too large for one host array (real w50: 7.7 GB) is checked slab by slab."""
+    total = None
+    for q0 in range(0, Q, slab):
+        q1 = min(Q, q0 + slab)
+        tm = {}
+        f = fock_build_screened_rank_threaded(np.asfortranarray(get_rows(q0, q1)), C_occ, sd, n_threads, 0, tm)
+        total = f if total is None else total + f
+        if timings is not None:
+            for k, v in tm.items():
+                timings[k] = timings.get(k, 0.0) + v
+    return total

@@ -288,34 +288,55 @@ def _aux_groups(aux_shells):
     return [_AuxGroup(l, aux_shells, ids) for l, ids in sorted(by_l.items())]
 
 
-def three_center_integrals(aux_shells, shells) -> np.ndarray:
-    """(P|mu nu), returned as a C-ordered array T[P, mu, nu] (symmetric in mu, nu)."""
+def _three_center_row(args):
+    """All blocks (P | shell i, shell j <= i) of one primary shell i: {j: {aux shell: [C, A, B]}}."""
+    i, aux_shells, shells = args
+    groups = _aux_groups(aux_shells)
+    sa = shells[i]
+    row = {}
+    for j, sb in enumerate(shells[:i + 1]):
+        Lab = sa.l + sb.l
+        T = Lab + 1
+        blocks = {g.l: np.zeros((len(aux_shells), (g.l + 1) * (g.l + 2) // 2, sa.nbas, sb.nbas)) for g in groups}
+        for cc, a, b, p, P, Ex, Ey, Ez in _pair_primitives(sa, sb):
+            Eab = cc * _pair_tensor(sa, sb, Ex, Ey, Ez)
+            for g in groups:
+                q = g.exps
+                alpha = p * q / (p + q)
+                R = hermite_R(Lab + g.l, alpha, P[None, :] - g.centers)
+                # pad so that slices [tau:tau+T] exist for every tau <= l
+                G = g.contract_R(R, T)
+                pref = 2.0 * pi ** 2.5 / (p * q * np.sqrt(p + q))
+                val = np.einsum("k,kCtuv,ABtuv->kCAB", pref, G, Eab)
+                np.add.at(blocks[g.l], g.owner, val)
+        row[j] = {si: blocks[g.l][si] for g in groups for si in g.shell_ids}
+    return i, row
+
+
+def _pool_map(fn, jobs, workers: int):
+    """Plain loop, or a fork pool over independent jobs (the arithmetic of every job is unchanged)."""
+    if workers <= 1 or len(jobs) < 2:
+        return [fn(j) for j in jobs]
+    import multiprocessing as mp
+    with mp.get_context("fork").Pool(min(workers, len(jobs))) as pool:
+        return pool.map(fn, jobs, chunksize=1)
+
+
+def three_center_integrals(aux_shells, shells, workers: int = 1) -> np.ndarray:
+    """(P|mu nu), returned as a C-ordered array T[P, mu, nu] (symmetric in mu, nu).  workers > 1: primary shells are
+    dealt to a fork pool (same arithmetic per block)."""
     apos, Q = shell_offsets(aux_shells)
     pos, N = shell_offsets(shells)
     out = np.zeros((Q, N, N))
-    groups = _aux_groups(aux_shells)
-    for i, sa in enumerate(shells):
-        for j, sb in enumerate(shells[:i + 1]):
-            Lab = sa.l + sb.l
-            T = Lab + 1
-            blocks = {g.l: np.zeros((len(aux_shells), (g.l + 1) * (g.l + 2) // 2, sa.nbas, sb.nbas)) for g in groups}
-            for cc, a, b, p, P, Ex, Ey, Ez in _pair_primitives(sa, sb):
-                Eab = cc * _pair_tensor(sa, sb, Ex, Ey, Ez)
-                for g in groups:
-                    q = g.exps
-                    alpha = p * q / (p + q)
-                    R = hermite_R(Lab + g.l, alpha, P[None, :] - g.centers)
-                    # pad so that slices [tau:tau+T] exist for every tau <= l
-                    G = g.contract_R(R, T)
-                    pref = 2.0 * pi ** 2.5 / (p * q * np.sqrt(p + q))
-                    val = np.einsum("k,kCtuv,ABtuv->kCAB", pref, G, Eab)
-                    np.add.at(blocks[g.l], g.owner, val)
-            for g in groups:
-                for si in g.shell_ids:
-                    blk = blocks[g.l][si]  # [C, A, B]
-                    n = aux_shells[si].nbas
-                    out[apos[si]:apos[si] + n, pos[i]:pos[i] + sa.nbas, pos[j]:pos[j] + sb.nbas] = blk
-                    out[apos[si]:apos[si] + n, pos[j]:pos[j] + sb.nbas, pos[i]:pos[i] + sa.nbas] = blk.transpose(0, 2, 1)
+    order = sorted(range(len(shells)), key=lambda i: -(i + 1) * shells[i].nbas)  # heaviest rows first
+    for i, row in _pool_map(_three_center_row, [(i, aux_shells, shells) for i in order], workers):
+        sa = shells[i]
+        for j, per_aux in row.items():
+            sb = shells[j]
+            for si, blk in per_aux.items():  # [C, A, B]
+                n = aux_shells[si].nbas
+                out[apos[si]:apos[si] + n, pos[i]:pos[i] + sa.nbas, pos[j]:pos[j] + sb.nbas] = blk
+                out[apos[si]:apos[si] + n, pos[j]:pos[j] + sb.nbas, pos[i]:pos[i] + sa.nbas] = blk.transpose(0, 2, 1)
     return out
 
 
@@ -375,6 +396,16 @@ def flatten_schwarz_block(blk: np.ndarray) -> np.ndarray:
     return np.ascontiguousarray(blk.transpose(2, 3, 0, 1)).ravel()
 
 
-def schwarz_blocks(shells) -> dict:
+def _schwarz_row(args):
+    i, shells = args
+    return i, [flatten_schwarz_block(schwarz_block(shells[i], shells[j])) for j in range(i + 1)]
+
+
+def schwarz_blocks(shells, workers: int = 1) -> dict:
     """{(ish, jsh): flattened (ab|ab) block} for every shell pair ish >= jsh (input of df_oracle.schwarz_function_mask)."""
-    return {(i, j): flatten_schwarz_block(schwarz_block(shells[i], shells[j])) for i in range(len(shells)) for j in range(i + 1)}
+    order = sorted(range(len(shells)), key=lambda i: -(i + 1) * shells[i].nbas ** 2)
+    out = {}
+    for i, row in _pool_map(_schwarz_row, [(i, shells) for i in order], workers):
+        for j, blk in enumerate(row):
+            out[(i, j)] = blk
+    return out

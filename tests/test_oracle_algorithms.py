@@ -88,3 +88,18 @@ def test_iteration_energy_and_density():
     assert np.abs(F @ C - S @ C @ np.diag(ev)).max() < 1e-9
     assert abs(np.trace(D @ S) - 2 * nocc) < 1e-10
     assert abs(E - 0.5 * np.sum(D * (F + H))) < 1e-12
+
+
+def test_slab_sum_of_the_threaded_build_is_the_whole_build():
+    """fock_build_screened_slabs (used at full size, where B is read back from the device slab by slab) against the
+    one-shot threaded build and the einsum statement; ragged last slab."""
+    N, Q, occ = 130, 37, 11
+    mask = banded_mask(N, 50, seed=5)
+    B, C_occ, H = random_inputs(N, Q, occ, seed=8, mask=mask)
+    sd = orc.ScreeningData(mask)
+    Bs = orc.dense_to_screened(B, sd)
+    tm = {}
+    F = orc.fock_build_screened_slabs(lambda q0, q1: Bs[q0:q1], Q, C_occ, sd, 3, 10, tm) + H
+    assert np.abs(F - _einsum_fock(B, C_occ, H)).max() < 1e-11
+    assert np.abs(F - (orc.fock_build_screened_rank_threaded(Bs, C_occ, sd, 3) + H)).max() < 1e-11
+    assert set(tm) == {"W", "K", "J"}
