@@ -55,7 +55,8 @@ def parse_args():
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-e2e", action="store_true")
     ap.add_argument("--opt", action="append", default=[], help="library option name=value (jcdf_set_option)")
-    ap.add_argument("--cpu-seconds", type=float, default=4.0, help="target seconds per CPU sample build")
+    ap.add_argument("--cpu-budget", type=float, default=100.0,
+                    help="seconds the timed CPU builds may take in total (at least 3 builds are always timed)")
     return ap.parse_args()
 
 
@@ -116,62 +117,104 @@ class ClockSampler:
 
 
 # ----------------------------------------------------------------------------------------------------------------------
-# CPU arm: oracle port of the reference's threaded screened algorithm on a bounded Q-slab
+# CPU arm: oracle port of the reference's threaded screened algorithm, run on the WHOLE workload whenever it fits the host
 # ----------------------------------------------------------------------------------------------------------------------
-def cpu_reference_builds_per_sec(w, target_seconds: float, reps: int, warmup: int):
-    """Returns (builds/s extrapolated to the full workload, dict describing the sample).  The Fock build is a plain sum
-    over auxiliary rows (every stage is linear in Q), so a slab of Qs rows costs Qs/Q of a build."""
+def host_cores() -> int:
+    try:
+        return len(os.sched_getaffinity(0))
+    except Exception:
+        return os.cpu_count() or 1
+
+
+def random_B(rows: int, P: int, Q: int, seed: int, threads: int):
+    """(rows x P) column-major N(0, 1/Q)-like values, every element distinct, filled by `threads` generators in parallel
+    (the contraction's run time does not depend on the values)."""
     import numpy as np
-    from threadpoolctl import threadpool_limits
+    from concurrent.futures import ThreadPoolExecutor
+    B = np.empty((rows, P), dtype=np.float64, order="F")
+    flat = B.reshape(-1, order="F")
+    n = flat.shape[0]
+    cuts = [n * i // threads for i in range(threads + 1)]
+
+    def fill(i):
+        g = np.random.default_rng(seed + 7919 * i)
+        step = 1 << 24
+        for a in range(cuts[i], cuts[i + 1], step):
+            e = min(cuts[i + 1], a + step)
+            g.random(out=flat[a:e])
+            flat[a:e] -= 0.5
+            flat[a:e] *= 3.4641016151377544 / (Q ** 0.5)
+    with ThreadPoolExecutor(max_workers=threads) as pool:
+        list(pool.map(fill, range(threads)))
+    return B
+
+
+def cpu_reference_builds_per_sec(w, steps: int, warmup: int, budget_seconds: float, get_rows=None, C_occ=None):
+    """Times the oracle's restatement of the reference's threaded screened Fock build (W per function, K blocks, Coulomb
+    gemv sweeps; ScreenedDF.jl:227-378, 548-641) on this box's host cores.  The whole workload (all Q auxiliary rows, one
+    (Q x P) array like the reference's scf_data.D) is built `steps` times after `warmup` untimed builds; the value is
+    1 / median.  get_rows(q0, q1) supplies real rows of B (the B200 arm reads them back from the device); without it B is
+    filled with distinct random values.  Only when the tensor does not fit the host (or one build would exceed the time
+    budget) a Q-slab is timed instead and the value is extrapolated — the line then says "extrapolated": true.
+    Returns (value, info, F or None) — F = 2J - K of the last build when the whole workload was built."""
+    import numpy as np
+    import psutil
 
     from juliachem_jl_b200 import workloads as wl
     from oracle import df_oracle as orc  # bench.py's CPU legs are allowed to execute the oracle
 
-    cores = os.cpu_count() or 1
-    try:
-        cores = len(os.sched_getaffinity(0))
-    except Exception:
-        pass
+    cores = host_cores()
     N, Q, occ = w.N, w.Q, w.occ
     mask = wl.screening_mask(w)
     if mask is None:
         mask = np.asfortranarray(np.ones((N, N), dtype=bool))
     sd = orc.ScreeningData(mask)
     P = sd.screened_indices_count
-    # calibrate: DGEMM rate of this host
-    with threadpool_limits(limits=cores, user_api="blas"):
-        a = np.asfortranarray(np.random.default_rng(0).standard_normal((2048, 2048)))
-        (a @ a)
-        dt = 1e9
-        for _ in range(3):
-            t0 = time.perf_counter(); (a @ a); dt = min(dt, time.perf_counter() - t0)
-    gflops = 2 * 2048 ** 3 / dt / 1e9
-    flops_per_row = 2.0 * occ * P + 1.0 * occ * N * (N + 1) + 4.0 * P
-    qs = int(target_seconds * gflops * 1e9 * 0.5 / flops_per_row)
-    qs = max(16, min(Q, qs, int(6e9 / (8.0 * P))))
-    rng = np.random.default_rng(w.seed)
-    B = np.empty((qs, P), dtype=np.float64, order="F")
-    blk = rng.standard_normal((min(qs, 32), P)) / np.sqrt(Q)
-    for r0 in range(0, qs, blk.shape[0]):  # timing does not depend on the values; repeat a 32-row slab
-        n = min(blk.shape[0], qs - r0)
-        B[r0:r0 + n, :] = blk[:n]
-    C_occ = wl.occupied_coefficients(w)
-    best, stages = None, {}
-    for i in range(warmup + reps):
+    if C_occ is None:
+        C_occ = wl.occupied_coefficients(w)
+    avail = psutil.virtual_memory().available
+    bytes_per_row = 8.0 * P + 8.0 * occ * N
+    rows_fit = int(0.6 * avail / bytes_per_row)
+    qs = max(16, min(Q, rows_fit))
+    t_fill = time.perf_counter()
+    if get_rows is not None:
+        B = np.empty((qs, P), dtype=np.float64, order="F")
+        for q0 in range(0, qs, 600):
+            q1 = min(qs, q0 + 600)
+            B[q0:q1, :] = get_rows(q0, q1)
+        source = "real B rows read back from the device (jcdf_get_B_rows)"
+    else:
+        B = random_B(qs, P, Q, w.seed, cores)
+        source = "random B, all elements distinct (run time is value-independent)"
+    t_fill = time.perf_counter() - t_fill
+    times, stages, F = [], {}, None
+    W_buf = np.zeros((qs, occ, N), dtype=np.float64, order="F")  # scf_data.D_tilde: allocated once (ScreenedDF.jl:110)
+    t_begin = time.perf_counter()
+    done = 0
+    for i in range(warmup + steps):
         tm = {}
         t0 = time.perf_counter()
-        orc.fock_build_screened_rank_threaded(B, C_occ, sd, cores, 0, tm)
+        F = orc.fock_build_screened_rank_threaded(B, C_occ, sd, cores, 0, tm, W_buf)
         dt = time.perf_counter() - t0
-        if i >= warmup and (best is None or dt < best):
-            best, stages = dt, tm
-    value = 1.0 / (best * Q / qs)
-    info = {"cores": cores, "kind": "port",
-            "sample": "Q-slab of %d of %d auxiliary rows of %s (N=%d occ=%d P=%d), reference screened algorithm "
-                      "(threads over p / K blocks, OpenBLAS), best of %d after %d warm-up; %.2f s per slab, "
-                      "extrapolated linearly in Q" % (qs, Q, w.name, N, occ, P, reps, warmup, best),
-            "host_dgemm_gflops": round(gflops, 1),
+        if i >= warmup:
+            times.append(dt)
+            stages = tm
+            done += 1
+            # keep the whole run inside the budget: stop early but never below 3 timed builds
+            if done >= 3 and (time.perf_counter() - t_begin) + dt > budget_seconds:
+                break
+    med = sorted(times)[len(times) // 2]
+    extrapolated = qs < Q
+    value = 1.0 / (med * Q / qs)
+    info = {"cores": cores, "kind": "port", "extrapolated": extrapolated, "steps_timed": len(times), "warmup": warmup,
+            "seconds_per_build_median": round(med * Q / qs, 4), "seconds_per_build_all": [round(t, 4) for t in times],
+            "sample": "%s %d of %d auxiliary rows of %s (N=%d occ=%d P=%d): the reference's screened algorithm "
+                      "(threads over p / over K blocks with single-threaded BLAS inside, threaded gemv sweeps; OpenBLAS), "
+                      "median of %d builds after %d warm-up; %s" % (
+                          "ALL" if not extrapolated else "Q-slab of", qs, Q, w.name, N, occ, P, len(times), warmup, source),
+            "fill_seconds": round(t_fill, 1),
             "stage_seconds_sample": {k: round(v, 4) for k, v in stages.items()}}
-    return value, info
+    return value, info, (F if not extrapolated else None)
 
 
 def run_reference(args):
@@ -181,11 +224,14 @@ def run_reference(args):
     from juliachem_jl_b200 import workloads as wl
     w = wl.WORKLOADS[args.workload]
     t0 = time.perf_counter()
-    value, info = cpu_reference_builds_per_sec(w, args.cpu_seconds, max(1, min(args.steps, 3)), max(1, min(args.warmup, 1)))
+    value, info, _ = cpu_reference_builds_per_sec(w, max(3, args.steps), max(1, min(args.warmup, 2)), args.cpu_budget)
     line = {
-        "impl": "reference", "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": args.gpus, "steps": args.steps,
-        "warmup": args.warmup, "ms_per_step": 1e3 / value, "higher_is_better": True, "scaling": "strong",
-        "vs_baseline": None, "dtype": "f64", "data": data_label(w),
+        "impl": "reference", "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": args.gpus,
+        "steps": info["steps_timed"], "warmup": info["warmup"], "steps_requested": args.steps, "warmup_requested": args.warmup,
+        "ms_per_step": 1e3 / value, "higher_is_better": True, "scaling": "strong",
+        "vs_baseline": None, "dtype": "f64", "extrapolated": info["extrapolated"],
+        "data": "synthetic: random B of the w50 shape and its real Schwarz mask (this arm never touches the GPU library); "
+                "synthetic orthonormal C_occ" if w.real_molecules else "synthetic",
         "config": workload_config(w, args.gpus),
         "cpu_baseline": dict(info, value=value, unit=UNIT),
         "e2e": {"value": value, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
@@ -321,6 +367,20 @@ def run_b200(args):
     F_chk = F_dev.cpu().numpy()
     if not (np.isfinite(F_chk).all() and np.array_equal(F_chk, F_chk.T)):
         raise SystemExit("bench.py: Fock matrix is not finite/symmetric")
+    # ---- parity of the timed result: every rank compares its all-reduced Fock matrix with ORACLE values committed as a
+    # fixture (tests/golden/w50_fock_fixture.json, re-derived by tests/test_gpu_fullsize.py); 1e-10 per element
+    parity = None
+    fx_path = os.path.join(ROOT, "tests", "golden", "%s_fock_fixture.json" % w.name)
+    if os.path.exists(fx_path):
+        fx = json.load(open(fx_path))
+        idx = np.array(fx["index"])
+        err = float(np.abs(F_chk[idx[:, 0], idx[:, 1]] - np.array(fx["value"])).max())
+        fro = float(abs(np.linalg.norm(F_chk) - fx["frobenius"]))
+        err_all = maxreduce(err)
+        parity = {"vs": "fixture", "max_abs_err": err_all, "frobenius_abs_err": fro, "tol": 1e-10, "samples": len(idx),
+                  "fixture": "tests/golden/%s_fock_fixture.json (oracle values)" % w.name}
+        if not err_all < 1e-10:
+            raise SystemExit("bench.py: Fock matrix differs from the oracle fixture by %.3e on some rank" % err_all)
 
     # ---- end to end through the host-pointer C-ABI call ----------------------------------------------------------
     e2e = None
@@ -331,16 +391,30 @@ def run_b200(args):
         F_np = F_pin.numpy().T
         gd.fock_build(C_np, H_host, F_np)  # H uploaded once; stays resident (constant over an SCF)
 
+        host_acc = {}
+
         def step_host():
-            gd.fock_build(C_np, None, F_np)
+            _, st = gd.fock_build(C_np, None, F_np)
+            for k, v in st.items():
+                host_acc[k] = host_acc.get(k, 0.0) + v * 1e3
 
         for _ in range(2):
             step_host()
+        host_acc.clear()
         ms_e2e = timed(step_host, args.steps) / args.steps
         if not np.allclose(F_np, F_chk, rtol=0, atol=1e-9):
             raise SystemExit("bench.py: host-path Fock differs from device-path Fock")
+        hs = {k: v / args.steps for k, v in host_acc.items()}
+        dev_kernels = sum(hs.get(k, 0.0) for k in ("density", "W", "K", "V", "J", "epilogue", "allreduce"))
+        # where the e2e - device gap goes, worst rank: copies on the stream, and what is left of the blocking call's host
+        # clock once every stream stage is subtracted (launch + NCCL enqueue + stream synchronize + Python)
+        gap = {"h2d_ms": maxreduce(hs.get("h2d", 0.0)), "d2h_ms": maxreduce(hs.get("d2h", 0.0)),
+               "kernels_and_allreduce_ms": maxreduce(dev_kernels), "call_host_clock_ms": maxreduce(hs.get("total", 0.0)),
+               "call_minus_stream_stages_ms": maxreduce(hs.get("total", 0.0) - dev_kernels - hs.get("h2d", 0.0) - hs.get("d2h", 0.0)),
+               "e2e_minus_device_ms": ms_e2e - ms_per_step}
         e2e = {"value": 1e3 / ms_e2e, "unit": UNIT, "h2d_bytes_per_step": int(C_pin.numel() * 8) * n_total,
-               "d2h_bytes_per_step": int(F_pin.numel() * 8) * (world if world > 1 else 1), "ms_per_step": ms_e2e}
+               "d2h_bytes_per_step": int(F_pin.numel() * 8) * (world if world > 1 else 1), "ms_per_step": ms_e2e,
+               "gap_breakdown": {k: round(v, 4) for k, v in gap.items()}}
 
     # ---- roofline of the dominant kernels (rank 0's shard) -----------------------------------------------------------
     q_local0 = len(my_shards[0])
@@ -393,14 +467,26 @@ def run_b200(args):
                     "build_frac_of_fp64_peak": tf(work["w_flops"] + work["k_flops"] + work["j_flops"], ms_per_step) / peak_tf,
                     "kernels": kern}
 
+    graph_replays = int(gd.layout().graph_replays)
+    cpu = None
+    if rank == 0 and n_total == 1 and not args.no_cpu_baseline:
+        # the CPU leg contracts the SAME tensor: B is read back from the device in the reference's (Q x P) layout, so its
+        # Fock matrix is also the oracle check of the timed GPU result at full size
+        P = int(li.pairs_kept)
+        v, info, F_cpu = cpu_reference_builds_per_sec(w, 3, 1, args.cpu_budget,
+                                                      get_rows=lambda q0, q1: gd.get_B_rows(0, q0, q1 - q0, P), C_occ=C_host)
+        cpu = dict(info, value=v, unit=UNIT)
+        if F_cpu is not None:
+            err = float(np.abs(F_chk - (F_cpu + H_host)).max())
+            parity = dict(parity or {}, vs="oracle", max_abs_err_vs_oracle=err, tol=1e-10,
+                          oracle="oracle.fock_build_screened_rank_threaded on all %d rows of the device's B" % Q)
+            if parity.get("max_abs_err") is None:
+                parity["max_abs_err"] = err
+            if not err < 1e-10:
+                raise SystemExit("bench.py: GPU Fock matrix differs from the oracle by %.3e" % err)
     gd.close()
     del F_dev, C_dev, H_dev
     torch.cuda.empty_cache()
-
-    cpu = None
-    if rank == 0 and n_total == 1 and not args.no_cpu_baseline:
-        v, info = cpu_reference_builds_per_sec(w, args.cpu_seconds, 2, 1)
-        cpu = dict(info, value=v, unit=UNIT)
 
     if dist is not None:
         dist.barrier()
@@ -417,6 +503,7 @@ def run_b200(args):
         "data": data_label(w), "config": cfg, "e2e": e2e, "options": args.opt,
         "gpu_launches": int(li.kernel_launches_per_build) * args.steps * n_total,
         "gpu_launches_per_build_per_gpu": int(li.kernel_launches_per_build),
+        "graph_replays": graph_replays, "parity_check": parity,
         "clocks": clocks, "roofline": roofline, "cpu_baseline": cpu,
         "stage_ms": {k: round(v, 4) for k, v in stage_ms.items()},
     }

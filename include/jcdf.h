@@ -211,6 +211,7 @@ typedef struct jcdf_layout_info {
     int64_t bytes_B, bytes_W; /* device bytes, summed over this process's devices (bytes_B includes the
                                * partner-compacted second copy when the per-function family is active)   */
     int64_t kernel_launches_per_build; /* launches of this library's own kernels per build  */
+    int64_t graph_replays;    /* builds (summed over devices) whose kernel sequence ran as a CUDA-graph replay */
 } jcdf_layout_info;
 int32_t jcdf_get_layout(jcdf_handle* h, jcdf_layout_info* out);
 
@@ -236,8 +237,11 @@ double jcdf_synthetic_value(uint64_t seed, int64_t Q_total, int64_t q_aux, int64
  * "pp_max_bytes" (cap on the compact copy per shard; above it — or when cudaMalloc refuses — the automatic choice falls
  * back to the tile family, ht_mode = 2 reports JCDF_ERR_CUDA; 0 = no cap),
  * "coulomb_pp_fused" (0 = default: two streaming passes; 1 = one cooperative single-pass kernel, measured slower),
- * "exchange_balance" (1 = default: cost-balanced exchange work lists; 0 = round-robin).  "regroup", "ht_mode",
- * "exchange_slices" and "exchange_balance" must be set before jcdf_set_mask.  Unknown names -> JCDF_ERR_INVALID.   */
+ * "exchange_balance" (1 = default: cost-balanced exchange work lists; 0 = round-robin),
+ * "graph" (1 = default: the kernel sequence of a build, prep .. epilogue, is captured into a CUDA graph on the first build
+ * and replayed afterwards; 0 = every kernel launched eagerly).  "regroup", "ht_mode", "pp_layout", "pp_max_bytes",
+ * "exchange_slices" and "exchange_balance" must be set before jcdf_set_mask.  A refused call (unknown name, value out of
+ * range, too late) returns JCDF_ERR_INVALID and leaves the handle unchanged.                                          */
 int32_t jcdf_set_option(jcdf_handle* h, const char* name, int64_t value);
 
 /* Per-kernel device time of the last build of device `dev` in ms (CUDA events on the launching stream):

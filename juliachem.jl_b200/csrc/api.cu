@@ -20,6 +20,23 @@ namespace jcdf {
 static thread_local std::string g_err;
 void set_error(const std::string& msg) { g_err = msg; }
 
+struct EighCache {
+    int dev = 0;
+    cublasHandle_t blas = nullptr;
+    cusolverDnHandle_t sol = nullptr;
+    double *dF = nullptr, *dX = nullptr, *dT = nullptr, *dW = nullptr, *work = nullptr;
+    int lwork = 0;
+    int* dinfo = nullptr;
+    ~EighCache() {
+        cudaSetDevice(dev);
+        void* ptrs[] = {dF, dX, dT, dW, work, dinfo};
+        for (void* p : ptrs)
+            if (p) cudaFree(p);
+        if (blas) cublasDestroy(blas);
+        if (sol) cusolverDnDestroy(sol);
+    }
+};
+
 static inline int64_t round_up(int64_t x, int64_t m) { return (x + m - 1) / m * m; }
 
 template <typename T>
@@ -33,6 +50,9 @@ static int dev_alloc(T** p, size_t count) {
 // keep_metric: the two-centre metric / its inverse factor do not depend on the mask (jcdf_set_mask keeps them)
 static void free_shard_buffers(Shard& s, bool keep_metric = false) {
     cudaSetDevice(s.dev);
+    if (s.gexec) { cudaGraphExecDestroy(s.gexec); s.gexec = nullptr; }  // the graph holds the old buffer addresses
+    s.gkey = 0;
+    s.graph_broken = false;
     void* ptrs[] = {s.d_pp_trirow, s.ppj_flag, s.ppj_vp, s.d_ppitems, s.d_ppoff, s.d_xcycles, s.Ksum, s.d_xitems, s.d_xoff, s.Bc, s.Ci, s.d_pp_off, s.d_pp_q, s.d_pp_src, s.d_pp_p, s.d_pp_jdst, s.dvec, s.VpartP, s.Vitem, s.Jpart, s.Vpart, s.Vready, s.Bp, s.W, s.Cs, s.Craw, s.dt, s.Jt, s.V, s.Kpart, s.F, s.Hdev, s.Traw, s.d_tile_index, s.d_tile_a,
                     s.d_tile_b, s.d_dest_of_col, s.d_fn_mask, s.d_kb_list, s.d_kb_count, s.d_perm, s.d_inv, s.d_tile_strips};
     for (void* p : ptrs)
@@ -263,37 +283,39 @@ static int ensure_comm(jcdf_handle* h) {
 // potrf!('L') of s.Metric (Q x Q, lower triangle read) in place and s.Linv = L^-1 by a triangular solve against the
 // identity (same result as trtri!('L','N'), DensityFitting.jl:138-139) on the shard's device and stream.
 int factor_metric_on_device(Shard& s, int64_t Q) {
-    cusolverDnHandle_t sol = nullptr;
-    cublasHandle_t blas = nullptr;
-    JC_CUSOLVER(cusolverDnCreate(&sol));
-    JC_CUSOLVER(cusolverDnSetStream(sol, s.stream));
-    JC_CUBLAS(cublasCreate(&blas));
-    JC_CUBLAS(cublasSetStream(blas, s.stream));
+    struct Guard {  // released on every exit path
+        cusolverDnHandle_t sol = nullptr;
+        cublasHandle_t blas = nullptr;
+        double* work = nullptr;
+        int* dinfo = nullptr;
+        ~Guard() {
+            if (work) cudaFree(work);
+            if (dinfo) cudaFree(dinfo);
+            if (sol) cusolverDnDestroy(sol);
+            if (blas) cublasDestroy(blas);
+        }
+    } g;
+    JC_CUSOLVER(cusolverDnCreate(&g.sol));
+    JC_CUSOLVER(cusolverDnSetStream(g.sol, s.stream));
+    JC_CUBLAS(cublasCreate(&g.blas));
+    JC_CUBLAS(cublasSetStream(g.blas, s.stream));
     int lwork = 0, rc;
-    JC_CUSOLVER(cusolverDnDpotrf_bufferSize(sol, CUBLAS_FILL_MODE_LOWER, (int)Q, s.Metric, (int)Q, &lwork));
-    double* work = nullptr;
-    int* dinfo = nullptr;
-    if ((rc = dev_alloc(&work, (size_t)lwork))) return rc;
-    if ((rc = dev_alloc(&dinfo, 1))) return rc;
-    JC_CUSOLVER(cusolverDnDpotrf(sol, CUBLAS_FILL_MODE_LOWER, (int)Q, s.Metric, (int)Q, work, lwork, dinfo));
+    JC_CUSOLVER(cusolverDnDpotrf_bufferSize(g.sol, CUBLAS_FILL_MODE_LOWER, (int)Q, s.Metric, (int)Q, &lwork));
+    if ((rc = dev_alloc(&g.work, (size_t)lwork))) return rc;
+    if ((rc = dev_alloc(&g.dinfo, 1))) return rc;
+    JC_CUSOLVER(cusolverDnDpotrf(g.sol, CUBLAS_FILL_MODE_LOWER, (int)Q, s.Metric, (int)Q, g.work, lwork, g.dinfo));
     int info = 0;
-    JC_CUDA(cudaMemcpyAsync(&info, dinfo, sizeof(int), cudaMemcpyDeviceToHost, s.stream));
+    JC_CUDA(cudaMemcpyAsync(&info, g.dinfo, sizeof(int), cudaMemcpyDeviceToHost, s.stream));
     JC_CUDA(cudaStreamSynchronize(s.stream));
-    cudaFree(work);
-    cudaFree(dinfo);
     if (info != 0) {
-        cusolverDnDestroy(sol);
-        cublasDestroy(blas);
         set_error("two-centre metric is not positive definite (potrf info = " + std::to_string(info) + ")");
         return JCDF_ERR_NUMERIC;
     }
     launch_set_identity(s.Linv, Q, s.stream);
     const double one = 1.0;
-    JC_CUBLAS(cublasDtrsm(blas, CUBLAS_SIDE_LEFT, CUBLAS_FILL_MODE_LOWER, CUBLAS_OP_N, CUBLAS_DIAG_NON_UNIT, (int)Q, (int)Q,
+    JC_CUBLAS(cublasDtrsm(g.blas, CUBLAS_SIDE_LEFT, CUBLAS_FILL_MODE_LOWER, CUBLAS_OP_N, CUBLAS_DIAG_NON_UNIT, (int)Q, (int)Q,
                           &one, s.Metric, (int)Q, s.Linv, (int)Q));
     JC_CUDA(cudaStreamSynchronize(s.stream));
-    cusolverDnDestroy(sol);
-    cublasDestroy(blas);
     return JCDF_OK;
 }
 
@@ -514,6 +536,8 @@ int32_t jcdf_destroy(jcdf_handle* h) {
     if (!h) return JCDF_OK;
     scf_destroy(h);
     integrals_destroy(h);
+    delete h->eigh;
+    h->eigh = nullptr;
     for (Shard& s : h->shards) {
         cudaSetDevice(s.dev);
         if (s.stream) cudaStreamSynchronize(s.stream);
@@ -534,6 +558,11 @@ int32_t jcdf_set_shards(jcdf_handle* h, const int64_t* q_begin, const int64_t* q
     for (size_t d = 0; d < h->shards.size(); d++) {
         JC_REQUIRE(q_begin[d] >= 0 && q_len[d] >= 0 && q_begin[d] + q_len[d] <= h->lay.Q,
                    "jcdf_set_shards: shard outside [0, Q)");
+        for (size_t e = 0; e < d; e++)  // shards of one process must not overlap (each row would be contracted twice)
+            JC_REQUIRE(q_len[d] == 0 || q_len[e] == 0 || q_begin[d] >= q_begin[e] + q_len[e] || q_begin[e] >= q_begin[d] + q_len[d],
+                       "jcdf_set_shards: shards overlap");
+    }
+    for (size_t d = 0; d < h->shards.size(); d++) {
         h->shards[d].q_begin = q_begin[d];
         h->shards[d].q_len = q_len[d];
     }
@@ -916,6 +945,133 @@ int32_t jcdf_set_core_hamiltonian(jcdf_handle* h, const double* H) {
     return JCDF_OK;
 }
 
+// What the per-build launch sequence of one shard depends on (everything else is fixed once jcdf_set_mask has run).
+struct BuildSchedule {
+    bool use_pp, pp_j, v_in_ht, overlap, add_H;
+    uint64_t key(const jcdf_handle* h) const {
+        return 1ull | (uint64_t)use_pp << 1 | (uint64_t)pp_j << 2 | (uint64_t)v_in_ht << 3 | (uint64_t)overlap << 4 |
+               (uint64_t)add_H << 5 | (uint64_t)(h->opt_coulomb_fused & 3) << 6 | (uint64_t)(h->opt_coulomb_pp_fused & 1) << 8;
+    }
+};
+
+// Launches prep .. epilogue of one shard on its stream (between the H2D copies and the all-reduce).  Called eagerly, or
+// once under stream capture to build the graph the later builds replay.
+static int issue_build_kernels(jcdf_handle* h, Shard& s, const BuildSchedule& b) {
+    const Layout& L = h->lay;
+    if (!b.pp_j) launch_prep(L, s, L.N);
+    if (b.use_pp) launch_pp_prep(L, s, L.N);
+    // V = sum_p sum_i C[p,i] W[Q,i,p] comes out of the half-transform's accumulators: no density, no V sweep
+    if (b.pp_j && !b.v_in_ht) launch_pp_density(L, s);
+    JC_CUDA(record_event(s, s.ev[EV_PREP], s.stream));
+    if (b.use_pp) launch_pp_half_transform(L, s, h->sm_count, b.v_in_ht);
+    else launch_half_transform(L, s, h->sm_count);
+    JC_CUDA(cudaPeekAtLastError());  // a launch that did not fit fails the build here, not as a wrong Fock matrix
+    JC_CUDA(record_event(s, s.ev[EV_W], s.stream));
+    launch_exchange(L, s, h->sm_count);
+    JC_CUDA(cudaPeekAtLastError());
+    JC_CUDA(record_event(s, s.ev[EV_K], s.stream));
+    // Coulomb sweeps (HBM-bound, 32-40 registers, no dynamic smem).  With coulomb_overlap they go to a second,
+    // lower-priority stream: their CTAs co-reside with the persistent tensor-core CTAs (one per SM, compute-bound,
+    // issue slots ~16 % busy) and soak up the idle HBM bandwidth instead of queueing behind them.
+    cudaStream_t sj = b.overlap ? s.stream_j : s.stream;
+    if (b.overlap) JC_CUDA(cudaStreamWaitEvent(sj, s.ev[EV_PREP], 0));
+    JC_CUDA(record_event(s, s.ev[EV_JBEGIN], sj));
+    JC_CUDA(record_event(s, s.ev[EV_V], sj));  // two-pass: overwritten at the V | J boundary; fused: V time reads 0
+    if (b.pp_j) {
+        s.last_coulomb_fused = false;
+        s.last_ppj_fused = h->opt_coulomb_pp_fused && launch_pp_coulomb_fused(L, s, h->sm_count, sj);
+        if (!s.last_ppj_fused) {
+            if (b.v_in_ht && b.overlap) JC_CUDA(cudaStreamWaitEvent(sj, s.ev[EV_W], 0));  // the partials come from the half-transform
+            launch_pp_coulomb(L, s, sj, s.ev[EV_V], b.v_in_ht);
+        }
+    } else {
+        // fused single pass pays off on long column segments (w50 dense: 3.8 TB/s effective against <= 3.05 for two
+        // passes at the copy bandwidth); on short ones its per-chunk grid-wide flags dominate and two streaming
+        // passes are faster (measured: benzene dimer 1.01 -> 0.91 ms, C20H42 5.54 -> 5.26 ms)
+        const bool want_fused = h->opt_coulomb_fused == 1 ||
+                                (h->opt_coulomb_fused == 2 && L.row_len / std::max(1, h->sm_count) >= 4500);
+        s.last_coulomb_fused = want_fused && launch_coulomb_fused(L, s, h->sm_count, sj);
+        if (!s.last_coulomb_fused) launch_coulomb(L, s, h->sm_count, sj);
+    }
+    s.last_pp_j = b.pp_j;
+    s.last_v_in_ht = b.v_in_ht && !s.last_ppj_fused;
+    JC_CUDA(record_event(s, s.ev[EV_J], sj));
+    if (b.overlap) JC_CUDA(cudaStreamWaitEvent(s.stream, s.ev[EV_J], 0));
+    launch_epilogue(L, s, b.add_H);
+    JC_CUDA(record_event(s, s.ev[EV_EPI], s.stream));
+    JC_CUDA(cudaGetLastError());
+    return JCDF_OK;
+}
+
+// Replays the shard's graph of issue_build_kernels, capturing it first when there is none for this schedule.  Any failure
+// of capture / instantiation marks the shard and the build is launched eagerly instead (same kernels, same order).
+static int run_build_kernels(jcdf_handle* h, Shard& s, const BuildSchedule& b) {
+    // the second-stream variant forks and joins through the timing events themselves: launched eagerly
+    const bool want_graph = h->opt_graph && !s.graph_broken && !b.overlap;
+    if (!want_graph) return issue_build_kernels(h, s, b);
+    const uint64_t key = b.key(h);
+    if (s.gexec == nullptr || s.gkey != key) {
+        if (s.gexec) { cudaGraphExecDestroy(s.gexec); s.gexec = nullptr; }
+        cudaGraph_t g = nullptr;
+        int rc = JCDF_OK;
+        if (cudaStreamBeginCapture(s.stream, cudaStreamCaptureModeThreadLocal) != cudaSuccess) {
+            cudaGetLastError();
+            s.graph_broken = true;
+            return issue_build_kernels(h, s, b);
+        }
+        s.capturing = true;
+        rc = issue_build_kernels(h, s, b);
+        s.capturing = false;
+        const cudaError_t ec = cudaStreamEndCapture(s.stream, &g);
+        if (rc != JCDF_OK || ec != cudaSuccess || g == nullptr ||
+            cudaGraphInstantiate(&s.gexec, g, 0) != cudaSuccess) {
+            cudaGetLastError();
+            if (g) cudaGraphDestroy(g);
+            s.gexec = nullptr;
+            s.graph_broken = true;
+            return issue_build_kernels(h, s, b);
+        }
+        cudaGraphDestroy(g);
+        s.gkey = key;
+    }
+    JC_CUDA(cudaGraphLaunch(s.gexec, s.stream));
+    s.graph_replays++;
+    return JCDF_OK;
+}
+
+// Once per communicator: the q_len of all shards of all ranks must add up to Q (a rank left on the default shards, or
+// ranges that overlap across ranks, would otherwise return a wrong Fock matrix without any error).
+static int check_global_coverage(jcdf_handle* h) {
+    if (h->coverage_checked) return JCDF_OK;
+    const int nd = (int)h->shards.size();
+    const NcclApi& n = nccl();
+    std::vector<double> got((size_t)nd, 0.0);
+    JC_NCCL(n.GroupStart());
+    for (int d = 0; d < nd; d++) {
+        Shard& s = h->shards[d];
+        JC_CUDA(cudaSetDevice(s.dev));
+        const double mine = (double)s.q_len;
+        JC_CUDA(cudaMemcpyAsync(s.V, &mine, sizeof(double), cudaMemcpyHostToDevice, s.stream));  // V is rebuilt every build
+        JC_CUDA(cudaStreamSynchronize(s.stream));
+        JC_NCCL(n.AllReduce(s.V, s.V, 1, NCCL_DOUBLE, NCCL_SUM, s.nccl_comm, s.stream));
+    }
+    JC_NCCL(n.GroupEnd());
+    for (int d = 0; d < nd; d++) {
+        Shard& s = h->shards[d];
+        JC_CUDA(cudaSetDevice(s.dev));
+        JC_CUDA(cudaMemcpyAsync(&got[(size_t)d], s.V, sizeof(double), cudaMemcpyDeviceToHost, s.stream));
+        JC_CUDA(cudaStreamSynchronize(s.stream));
+    }
+    for (int d = 0; d < nd; d++)
+        if (got[(size_t)d] != (double)h->lay.Q) {
+            set_error("jcdf_fock_build: the shards of all ranks hold " + std::to_string((int64_t)got[(size_t)d]) +
+                      " auxiliary rows in total, expected Q = " + std::to_string(h->lay.Q) + " (jcdf_set_shards on every rank)");
+            return JCDF_ERR_INVALID;
+        }
+    h->coverage_checked = true;
+    return JCDF_OK;
+}
+
 int fock_build_impl(jcdf_handle* h, const double* C_occ, int64_t ldc, const double* H, double* F_out,
                            double* stage_seconds, bool device_ptrs) {
     JC_REQUIRE(h && C_occ && F_out, "jcdf_fock_build: NULL argument");
@@ -926,9 +1082,10 @@ int fock_build_impl(jcdf_handle* h, const double* C_occ, int64_t ldc, const doub
     for (int d = 0; d < nd; d++) JC_REQUIRE(h->shards[d].b_ready, "jcdf_fock_build: B has not been formed on every device");
     int rc = ensure_comm(h);
     if (rc) return rc;
-    auto t0 = std::chrono::steady_clock::now();
     const bool owns_rank0 = (h->rank == 0);
     const bool reduce = (h->n_ranks * nd > 1);
+    if (reduce && (rc = check_global_coverage(h))) return rc;
+    auto t0 = std::chrono::steady_clock::now();
     const size_t nn = (size_t)L.N * L.N;
 
     for (int d = 0; d < nd; d++) {
@@ -936,74 +1093,30 @@ int fock_build_impl(jcdf_handle* h, const double* C_occ, int64_t ldc, const doub
         JC_CUDA(cudaSetDevice(s.dev));
         JC_CUDA(cudaEventRecord(s.ev[EV_START], s.stream));
         // C_occ -> device, compacted to ld = N
-        if (device_ptrs) {
-            JC_CUDA(cudaMemcpy2DAsync(s.Craw, sizeof(double) * L.N, C_occ, sizeof(double) * ldc, sizeof(double) * L.N,
-                                      (size_t)L.occ, cudaMemcpyDefault, s.stream));
-        } else {
-            JC_CUDA(cudaMemcpy2DAsync(s.Craw, sizeof(double) * L.N, C_occ, sizeof(double) * ldc, sizeof(double) * L.N,
-                                      (size_t)L.occ, cudaMemcpyHostToDevice, s.stream));
-        }
-        bool add_H = false;
+        JC_CUDA(cudaMemcpy2DAsync(s.Craw, sizeof(double) * L.N, C_occ, sizeof(double) * ldc, sizeof(double) * L.N,
+                                  (size_t)L.occ, device_ptrs ? cudaMemcpyDefault : cudaMemcpyHostToDevice, s.stream));
+        BuildSchedule b;
+        b.add_H = false;
         if (d == 0 && owns_rank0) {
             if (H != nullptr) {
                 JC_CUDA(cudaMemcpyAsync(s.Hdev, H, sizeof(double) * nn, device_ptrs ? cudaMemcpyDefault : cudaMemcpyHostToDevice,
                                         s.stream));
                 s.has_H = true;
             }
-            add_H = s.has_H;
+            b.add_H = s.has_H;
         }
         JC_CUDA(cudaEventRecord(s.ev[EV_H2D], s.stream));
-        const bool use_pp = L.pp_enabled && s.Bc != nullptr;
-        if (use_pp && !s.bc_valid) {  // first build after B changed: refresh the partner-compacted copy
+        b.use_pp = L.pp_enabled && s.Bc != nullptr;
+        if (b.use_pp && !s.bc_valid) {  // first build after B changed: refresh the partner-compacted copy
             launch_pp_pack(L, s);
             s.bc_valid = true;
         }
-        const bool pp_j = use_pp && h->opt_coulomb_pp;  // Coulomb over the compact copy as well
-        if (!pp_j) launch_prep(L, s, L.N);
-        if (use_pp) launch_pp_prep(L, s, L.N);
-        // V = sum_p sum_i C[p,i] W[Q,i,p] comes out of the half-transform's accumulators: no density, no V sweep
-        const bool v_in_ht = pp_j && h->opt_coulomb_v_in_ht && !h->opt_coulomb_pp_fused && s.Vitem != nullptr;
-        if (pp_j && !v_in_ht) launch_pp_density(L, s);
-        JC_CUDA(cudaEventRecord(s.ev[EV_PREP], s.stream));
-        if (use_pp) launch_pp_half_transform(L, s, h->sm_count, v_in_ht);
-        else launch_half_transform(L, s, h->sm_count);
-        JC_CUDA(cudaPeekAtLastError());  // a launch that did not fit fails the build here, not as a wrong Fock matrix
-        JC_CUDA(cudaEventRecord(s.ev[EV_W], s.stream));
-        launch_exchange(L, s, h->sm_count);
-        JC_CUDA(cudaPeekAtLastError());
-        JC_CUDA(cudaEventRecord(s.ev[EV_K], s.stream));
-        // Coulomb sweeps (HBM-bound, 32-40 registers, no dynamic smem).  With coulomb_overlap they go to a second,
-        // lower-priority stream: their CTAs co-reside with the persistent tensor-core CTAs (one per SM, compute-bound,
-        // issue slots ~16 % busy) and soak up the idle HBM bandwidth instead of queueing behind them.
-        const bool overlap = h->opt_coulomb_overlap && (pp_j || !h->opt_coulomb_fused);
-        cudaStream_t sj = overlap ? s.stream_j : s.stream;
-        if (overlap) JC_CUDA(cudaStreamWaitEvent(sj, s.ev[EV_PREP], 0));
-        JC_CUDA(cudaEventRecord(s.ev[EV_JBEGIN], sj));
-        JC_CUDA(cudaEventRecord(s.ev[EV_V], sj));  // two-pass: overwritten at the V | J boundary; fused: V time reads 0
-        if (pp_j) {
-            s.last_coulomb_fused = false;
-            s.last_ppj_fused = h->opt_coulomb_pp_fused && launch_pp_coulomb_fused(L, s, h->sm_count, sj);
-            if (!s.last_ppj_fused) {
-                if (v_in_ht && overlap) JC_CUDA(cudaStreamWaitEvent(sj, s.ev[EV_W], 0));  // the partials come from the half-transform
-                launch_pp_coulomb(L, s, sj, s.ev[EV_V], v_in_ht);
-            }
-        } else {
-            // fused single pass pays off on long column segments (w50 dense: 3.8 TB/s effective against <= 3.05 for two
-            // passes at the copy bandwidth); on short ones its per-chunk grid-wide flags dominate and two streaming
-            // passes are faster (measured: benzene dimer 1.01 -> 0.91 ms, C20H42 5.54 -> 5.26 ms)
-            const bool want_fused = h->opt_coulomb_fused == 1 ||
-                                    (h->opt_coulomb_fused == 2 && L.row_len / std::max(1, h->sm_count) >= 4500);
-            s.last_coulomb_fused = want_fused && launch_coulomb_fused(L, s, h->sm_count, sj);
-            if (!s.last_coulomb_fused) launch_coulomb(L, s, h->sm_count, sj);
-        }
-        s.last_pp_j = pp_j;
-        s.last_v_in_ht = v_in_ht && !s.last_ppj_fused;
-        JC_CUDA(cudaEventRecord(s.ev[EV_J], sj));
-        if (overlap) JC_CUDA(cudaStreamWaitEvent(s.stream, s.ev[EV_J], 0));
-        launch_epilogue(L, s, add_H);
-        JC_CUDA(cudaEventRecord(s.ev[EV_EPI], s.stream));
-        JC_CUDA(cudaGetLastError());
+        b.pp_j = b.use_pp && h->opt_coulomb_pp;  // Coulomb over the compact copy as well
+        b.v_in_ht = b.pp_j && h->opt_coulomb_v_in_ht && !h->opt_coulomb_pp_fused && s.Vitem != nullptr;
+        b.overlap = h->opt_coulomb_overlap && (b.pp_j || !h->opt_coulomb_fused);
+        if ((rc = run_build_kernels(h, s, b))) return rc;
     }
+    auto t_launched = std::chrono::steady_clock::now();
     if (reduce) {
         const NcclApi& n = nccl();
         JC_NCCL(n.GroupStart());
@@ -1052,6 +1165,7 @@ int fock_build_impl(jcdf_handle* h, const double* C_occ, int64_t ldc, const doub
         s.last_ms[JCDF_T_TOTAL] = std::chrono::duration<double, std::milli>(t1 - t0).count();
         for (int i = 0; i < JCDF_N_STAGES; i++) mx[i] = std::max(mx[i], s.last_ms[i]);
     }
+    h->last_host_launch_ms = std::chrono::duration<double, std::milli>(t_launched - t0).count();
     if (stage_seconds)
         for (int i = 0; i < JCDF_N_STAGES; i++) stage_seconds[i] = mx[i] * 1e-3;
     return JCDF_OK;
@@ -1072,40 +1186,43 @@ int32_t jcdf_eigh(jcdf_handle* h, const double* F, const double* X, double* eval
     const int64_t N = h->lay.N;
     Shard& s = h->shards[0];
     JC_CUDA(cudaSetDevice(s.dev));
-    double *dF = nullptr, *dX = nullptr, *dT = nullptr, *dW = nullptr, *work = nullptr;
-    int* dinfo = nullptr;
+    // called once per SCF iteration from iteration(): handles and workspaces live in the handle
+    if (!h->eigh) h->eigh = new (std::nothrow) EighCache();
+    JC_REQUIRE(h->eigh != nullptr, "jcdf_eigh: out of host memory");
+    EighCache& e = *h->eigh;
+    e.dev = s.dev;
     int rc;
-    if ((rc = dev_alloc(&dF, (size_t)N * N))) return rc;
-    if ((rc = dev_alloc(&dX, (size_t)N * N))) return rc;
-    if ((rc = dev_alloc(&dT, (size_t)N * N))) return rc;
-    if ((rc = dev_alloc(&dW, (size_t)N))) return rc;
-    if ((rc = dev_alloc(&dinfo, 1))) return rc;
-    cublasHandle_t blas = nullptr;
-    cusolverDnHandle_t sol = nullptr;
-    JC_CUBLAS(cublasCreate(&blas));
-    JC_CUBLAS(cublasSetStream(blas, s.stream));
-    JC_CUSOLVER(cusolverDnCreate(&sol));
-    JC_CUSOLVER(cusolverDnSetStream(sol, s.stream));
-    JC_CUDA(cudaMemcpyAsync(dF, F, sizeof(double) * N * N, cudaMemcpyHostToDevice, s.stream));
-    JC_CUDA(cudaMemcpyAsync(dX, X, sizeof(double) * N * N, cudaMemcpyHostToDevice, s.stream));
+    if (!e.blas) {
+        JC_CUBLAS(cublasCreate(&e.blas));
+        JC_CUBLAS(cublasSetStream(e.blas, s.stream));
+    }
+    if (!e.sol) {
+        JC_CUSOLVER(cusolverDnCreate(&e.sol));
+        JC_CUSOLVER(cusolverDnSetStream(e.sol, s.stream));
+    }
+    if (!e.dF && (rc = dev_alloc(&e.dF, (size_t)N * N))) return rc;
+    if (!e.dX && (rc = dev_alloc(&e.dX, (size_t)N * N))) return rc;
+    if (!e.dT && (rc = dev_alloc(&e.dT, (size_t)N * N))) return rc;
+    if (!e.dW && (rc = dev_alloc(&e.dW, (size_t)N))) return rc;
+    if (!e.dinfo && (rc = dev_alloc(&e.dinfo, 1))) return rc;
+    if (!e.work) {
+        JC_CUSOLVER(cusolverDnDsyevd_bufferSize(e.sol, CUSOLVER_EIG_MODE_VECTOR, CUBLAS_FILL_MODE_UPPER, (int)N, e.dF, (int)N, e.dW, &e.lwork));
+        if ((rc = dev_alloc(&e.work, (size_t)e.lwork))) return rc;
+    }
+    JC_CUDA(cudaMemcpyAsync(e.dF, F, sizeof(double) * N * N, cudaMemcpyHostToDevice, s.stream));
+    JC_CUDA(cudaMemcpyAsync(e.dX, X, sizeof(double) * N * N, cudaMemcpyHostToDevice, s.stream));
     const double one = 1.0, zero = 0.0;
     // workspace_a = X^T F ; Fp = workspace_a X   (symm!/gemm!, SCF.jl:1083-1084)
-    JC_CUBLAS(cublasDgemm(blas, CUBLAS_OP_T, CUBLAS_OP_N, (int)N, (int)N, (int)N, &one, dX, (int)N, dF, (int)N, &zero, dT, (int)N));
-    JC_CUBLAS(cublasDgemm(blas, CUBLAS_OP_N, CUBLAS_OP_N, (int)N, (int)N, (int)N, &one, dT, (int)N, dX, (int)N, &zero, dF, (int)N));
-    int lwork = 0;
-    JC_CUSOLVER(cusolverDnDsyevd_bufferSize(sol, CUSOLVER_EIG_MODE_VECTOR, CUBLAS_FILL_MODE_UPPER, (int)N, dF, (int)N, dW, &lwork));
-    if ((rc = dev_alloc(&work, (size_t)lwork))) return rc;
-    JC_CUSOLVER(cusolverDnDsyevd(sol, CUSOLVER_EIG_MODE_VECTOR, CUBLAS_FILL_MODE_UPPER, (int)N, dF, (int)N, dW, work, lwork, dinfo));
+    JC_CUBLAS(cublasDgemm(e.blas, CUBLAS_OP_T, CUBLAS_OP_N, (int)N, (int)N, (int)N, &one, e.dX, (int)N, e.dF, (int)N, &zero, e.dT, (int)N));
+    JC_CUBLAS(cublasDgemm(e.blas, CUBLAS_OP_N, CUBLAS_OP_N, (int)N, (int)N, (int)N, &one, e.dT, (int)N, e.dX, (int)N, &zero, e.dF, (int)N));
+    JC_CUSOLVER(cusolverDnDsyevd(e.sol, CUSOLVER_EIG_MODE_VECTOR, CUBLAS_FILL_MODE_UPPER, (int)N, e.dF, (int)N, e.dW, e.work, e.lwork, e.dinfo));
     // C = X U  (symm!, SCF.jl:1095)
-    JC_CUBLAS(cublasDgemm(blas, CUBLAS_OP_N, CUBLAS_OP_N, (int)N, (int)N, (int)N, &one, dX, (int)N, dF, (int)N, &zero, dT, (int)N));
+    JC_CUBLAS(cublasDgemm(e.blas, CUBLAS_OP_N, CUBLAS_OP_N, (int)N, (int)N, (int)N, &one, e.dX, (int)N, e.dF, (int)N, &zero, e.dT, (int)N));
     int info = 0;
-    JC_CUDA(cudaMemcpyAsync(&info, dinfo, sizeof(int), cudaMemcpyDeviceToHost, s.stream));
-    JC_CUDA(cudaMemcpyAsync(evals, dW, sizeof(double) * N, cudaMemcpyDeviceToHost, s.stream));
-    JC_CUDA(cudaMemcpyAsync(C, dT, sizeof(double) * N * N, cudaMemcpyDeviceToHost, s.stream));
+    JC_CUDA(cudaMemcpyAsync(&info, e.dinfo, sizeof(int), cudaMemcpyDeviceToHost, s.stream));
+    JC_CUDA(cudaMemcpyAsync(evals, e.dW, sizeof(double) * N, cudaMemcpyDeviceToHost, s.stream));
+    JC_CUDA(cudaMemcpyAsync(C, e.dT, sizeof(double) * N * N, cudaMemcpyDeviceToHost, s.stream));
     JC_CUDA(cudaStreamSynchronize(s.stream));
-    cublasDestroy(blas);
-    cusolverDnDestroy(sol);
-    cudaFree(dF); cudaFree(dX); cudaFree(dT); cudaFree(dW); cudaFree(work); cudaFree(dinfo);
     if (info != 0) {
         set_error("syevd did not converge (info = " + std::to_string(info) + ")");
         return JCDF_ERR_NUMERIC;
@@ -1127,6 +1244,9 @@ int32_t jcdf_comm_init_rank(jcdf_handle* h, int32_t n_ranks, int32_t rank, const
     JC_REQUIRE(h && id_bytes, "jcdf_comm_init_rank: NULL argument");
     JC_REQUIRE(n_ranks >= 1 && rank >= 0 && rank < n_ranks, "jcdf_comm_init_rank: bad rank");
     JC_REQUIRE(!h->comm_ready, "jcdf_comm_init_rank: communicator already initialised");
+    // the default shards split ALL of Q over this process's devices: with several ranks every rank would contract every
+    // auxiliary row and the all-reduce would return H + n_ranks (2J - K)
+    JC_REQUIRE(n_ranks == 1 || h->shards_set, "jcdf_comm_init_rank: call jcdf_set_shards with this rank's auxiliary rows first");
     const NcclApi& n = nccl();
     if (!n.ok) { set_error(std::string("NCCL unavailable: ") + n.why); return JCDF_ERR_NCCL; }
     const int nd = (int)h->shards.size();
@@ -1158,6 +1278,7 @@ int32_t jcdf_get_layout(jcdf_handle* h, jcdf_layout_info* o) {
         o->bytes_B += s.q_len * L.row_len * 8;
         if (L.pp_enabled && s.Bc) o->bytes_B += (int64_t)s.pp_chunks * L.pp_rows * 128 * 8;
         o->bytes_W += (int64_t)s.xplan.chunks * L.npt64 * 2048 * 8;
+        o->graph_replays += s.graph_replays;
     }
     // prep_cs, density, half_transform, exchange, coulomb (fused: 1, two-pass: 2), epilogue
     // per-function path with its own Coulomb: prep, density, half_transform, exchange, V, V reduce, J, J reduce, epilogue
@@ -1186,35 +1307,41 @@ int32_t jcdf_fill_synthetic_B(jcdf_handle* h, uint64_t seed, double decay_length
 int32_t jcdf_set_option(jcdf_handle* h, const char* name, int64_t value) {
     JC_REQUIRE(h && name, "jcdf_set_option: NULL argument");
     const std::string n(name);
-    if (n == "coulomb_fused") h->opt_coulomb_fused = value;
-    else if (n == "coulomb_overlap") h->opt_coulomb_overlap = value;
-    else if (n == "pp_max_bytes") h->opt_pp_max_bytes = value;
-    else if (n == "pp_layout") {
-        h->opt_pp_layout = value;
-        for (Shard& s : h->shards) JC_REQUIRE(s.Bp == nullptr, "pp_layout must be set before jcdf_set_mask");
+    struct Opt { const char* name; int64_t* slot; bool before_mask; int64_t lo, hi; };
+    const int64_t big = (int64_t)1 << 62;
+    const Opt opts[] = {
+        {"coulomb_fused", &h->opt_coulomb_fused, false, 0, 2},
+        {"coulomb_overlap", &h->opt_coulomb_overlap, false, 0, 1},
+        {"pp_max_bytes", &h->opt_pp_max_bytes, true, 0, big},
+        {"pp_layout", &h->opt_pp_layout, true, -1, 1},
+        {"coulomb_pp", &h->opt_coulomb_pp, false, 0, 1},
+        {"coulomb_v_in_ht", &h->opt_coulomb_v_in_ht, false, 0, 1},
+        {"coulomb_pp_fused", &h->opt_coulomb_pp_fused, false, 0, 1},
+        {"exchange_balance", &h->opt_exchange_balance, true, 0, 1},
+        {"ht_mode", &h->opt_ht_mode, true, 0, 2},
+        {"regroup", &h->opt_regroup, true, 0, 1},
+        {"exchange_slices", &h->opt_exchange_slices, true, 0, 1 << 20},
+        {"graph", &h->opt_graph, false, 0, 1},
+    };
+    for (const Opt& o : opts) {
+        if (n != o.name) continue;
+        // validate BEFORE storing: a refused call leaves the handle as it was
+        if (value < o.lo || value > o.hi) {
+            set_error("jcdf_set_option: value " + std::to_string(value) + " out of range for '" + n + "'");
+            return JCDF_ERR_INVALID;
+        }
+        if (o.before_mask)
+            for (Shard& s : h->shards)
+                if (s.Bp != nullptr) {
+                    set_error("jcdf_set_option: '" + n + "' must be set before jcdf_set_mask");
+                    return JCDF_ERR_INVALID;
+                }
+        *o.slot = value;
+        if (!o.before_mask) h->graph_dirty = true;  // the captured launch sequence depends on the schedule options
+        return JCDF_OK;
     }
-    else if (n == "coulomb_pp") h->opt_coulomb_pp = value;
-    else if (n == "coulomb_v_in_ht") h->opt_coulomb_v_in_ht = value;
-    else if (n == "coulomb_pp_fused") h->opt_coulomb_pp_fused = value;
-    else if (n == "exchange_balance") {
-        h->opt_exchange_balance = value;
-        for (Shard& s : h->shards) JC_REQUIRE(s.Bp == nullptr, "exchange_balance must be set before jcdf_set_mask");
-    }
-    else if (n == "ht_mode") {
-        JC_REQUIRE(value >= 0 && value <= 2, "ht_mode must be 0 (automatic), 1 (tile kernel) or 2 (per-function kernel)");
-        h->opt_ht_mode = value;
-        for (Shard& s : h->shards) JC_REQUIRE(s.Bp == nullptr, "ht_mode must be set before jcdf_set_mask");
-    } else if (n == "regroup") {
-        h->opt_regroup = value;
-        for (Shard& s : h->shards) JC_REQUIRE(s.Bp == nullptr, "regroup must be set before jcdf_set_mask");
-    } else if (n == "exchange_slices") {
-        h->opt_exchange_slices = value;
-        for (Shard& s : h->shards) JC_REQUIRE(s.Bp == nullptr, "exchange_slices must be set before jcdf_set_mask");
-    } else {
-        set_error("jcdf_set_option: unknown option '" + n + "'");
-        return JCDF_ERR_INVALID;
-    }
-    return JCDF_OK;
+    set_error("jcdf_set_option: unknown option '" + n + "'");
+    return JCDF_ERR_INVALID;
 }
 
 int32_t jcdf_last_kernel_ms(jcdf_handle* h, int32_t dev, double* out) {

@@ -128,12 +128,19 @@ struct Shard {
     bool t_uploaded = false;
     ExchangePlan xplan;
     cudaEvent_t ev[EV_COUNT] = {};
+    // CUDA graph of the per-build kernel sequence (prep .. epilogue): captured on the first build, replayed afterwards
+    cudaGraphExec_t gexec = nullptr;
+    uint64_t gkey = 0;             // schedule the graph was captured for (family, Coulomb variant, H add)
+    bool capturing = false;        // the launchers record timing events as external event-record nodes while set
+    bool graph_broken = false;     // capture or instantiation failed once: this shard launches eagerly from then on
+    int64_t graph_replays = 0;
     double last_ms[JCDF_N_STAGES] = {};
     void* nccl_comm = nullptr;
 };
 
 struct ScfState;        // scf.cu
 struct IntegralsState;  // integrals.cu
+struct EighCache;       // api.cu: handles + workspaces of jcdf_eigh, created on first use, released by jcdf_destroy
 
 }  // namespace jcdf
 
@@ -158,8 +165,13 @@ struct jcdf_handle {
     int64_t opt_pp_max_bytes = 0;      // cap on the partner-compacted copy per shard (0 = whatever cudaMalloc grants)
     int64_t opt_coulomb_pp = 1;       // Coulomb over the partner-compacted copy whenever the per-function path is active
     int64_t opt_ht_mode = 0;          // half-transform: 0 = choose from the mask, 1 = tile kernel, 2 = per-function kernel
+    int64_t opt_graph = 1;            // replay the per-build launch sequence as a CUDA graph (device-pointer builds)
+    bool graph_dirty = true;          // options / operands changed since the capture
+    double last_host_launch_ms = 0.0;  // host time the last build spent issuing work before the collective
+    bool coverage_checked = false;    // the shards of all ranks were seen to cover Q exactly once
     jcdf::ScfState* scf = nullptr;    // on-device SCF driver state (jcdf_scf_*), owned
     jcdf::IntegralsState* ints = nullptr;  // basis sets + integral scratch (jcdf_set_basis / jcdf_compute_*), owned
+    jcdf::EighCache* eigh = nullptr;       // jcdf_eigh state, owned
     bool metric_on_device = false;    // shards[0].Metric holds (P|Q) (jcdf_compute_two_center) — consumed by the factorisation
     double max_PP = 0.0;              // max_P |(P|P)| of the last metric seen (get_max_P_P, SchwarzScreening.jl:86-95)
 };
@@ -193,6 +205,11 @@ int exchange_tile_cost(int tile, int N);  // kernels_k.cu: DMMA row units per k-
 int kernels_per_build();
 
 void set_error(const std::string& msg);
+// timing event on the shard's stream: a plain record when launching eagerly, an external event-record NODE while the
+// launch sequence is being captured into a graph (so every replay still timestamps the stage boundaries)
+inline cudaError_t record_event(const Shard& s, cudaEvent_t ev, cudaStream_t st) {
+    return s.capturing ? cudaEventRecordWithFlags(ev, st, cudaEventRecordExternal) : cudaEventRecord(ev, st);
+}
 void scf_destroy(jcdf_handle* h);        // scf.cu
 void integrals_destroy(jcdf_handle* h);  // integrals.cu
 void integrals_on_set_mask(jcdf_handle* h);

@@ -103,7 +103,7 @@ void launch_coulomb(const Layout& L, Shard& s, int sm_count, cudaStream_t st) {
     if (s.q_len <= 0) return;
     int grid_v = (int)std::min<int64_t>(s.q_len, (int64_t)sm_count * 8);
     k_coulomb_v<<<grid_v, 256, 0, st>>>(s.Bp, s.dt, s.V, L.row_len, (int)s.q_len);
-    cudaEventRecord(s.ev[EV_V], st);  // boundary V | J
+    record_event(s, s.ev[EV_V], st);  // boundary V | J
     const int64_t n2 = L.row_len / 2;
     int gx = (int)((n2 + 255) / 256);
     // enough CTAs to fill the machine twice; deterministic (no atomics) whenever one slab suffices

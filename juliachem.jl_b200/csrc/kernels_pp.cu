@@ -678,7 +678,7 @@ void launch_pp_coulomb(const Layout& L, Shard& s, cudaStream_t st, cudaEvent_t e
         k_pp_coulomb_v<<<grid, 256, 0, st>>>(s.Bc, s.dvec, s.VpartP, L.pp_rows, qpad);
         k_pp_vreduce<<<(qpad + 127) / 128, 128, 0, st>>>(s.VpartP, s.V, n_slab, qpad, (int)s.q_len);
     }
-    if (ev_v) cudaEventRecord(ev_v, st);
+    if (ev_v) record_event(s, ev_v, st);
     k_pp_coulomb_j<<<grid, 256, 0, st>>>(s.Bc, s.V, s.d_pp_jdst, s.Jpart, L.pp_rows, (int)s.q_len);
     k_pp_jreduce<<<(unsigned)((L.pp_rows + 255) / 256), 256, 0, st>>>(s.Jpart, s.d_pp_jdst, s.Jt, L.pp_rows, s.pp_chunks);
 }

@@ -59,7 +59,8 @@ class JCTiming:
 # libjcdf stage slot -> the reference's JCTiming constant (JCTiming.jl:58-65, 75-90)
 _STAGE_TO_JCTC = {
     "W": "W_time", "K": "K_time", "V": "V_time", "J": "J_time", "allreduce": "fock_MPI_time",
-    "density": "density_time", "h2d": "gpu_copy_coeff_time", "d2h": "fock_gpu_cpu_copy_reduce_time",
+    # h2d: what the fork books as JCTiming_GPUkey(JCTC.GPU_non_zero_coeff_time, 1) (GPUDF.jl:288, JCTiming.jl:88, 143-145)
+    "density": "density_time", "h2d": "GPU_1_non_zero_coeff_time", "d2h": "fock_gpu_cpu_copy_reduce_time",
     "total": "fock_time", "epilogue": "gpu_copy_J_time",
 }
 
@@ -401,6 +402,29 @@ class IntegralSource:
         """Optional shortcut: rows of B = L^-1 (P|mn) when the caller already holds them; None = not available."""
         return None
 
+    def device_basis(self):
+        """Optional: (primary, auxiliary) flat shell arrays, each the argument tuple of B200Data.set_basis — what
+        basis_sets.primary / basis_sets.auxillary hold (BasisStructs.jl:170-185).  When given, (P|Q), the Schwarz mask and
+        B are computed on the devices (julia/B200DF.jl: setup_device_integrals_B200!), for any number of ranks."""
+        return None
+
+
+def uses_dense_contraction(scf_options: SCFOptions, N: int, n_ranks: int) -> bool:
+    """run_gpu_fock_build!'s choice between the dense and the screened statement of the contraction
+    (DensityFitting.jl:79-90): df_force_dense, or df_use_adaptive on a small system (N < 800) with a single rank."""
+    return bool(scf_options.df_force_dense or (scf_options.df_use_adaptive and N < 800 and n_ranks == 1))
+
+
+def check_supported_options(scf_options: SCFOptions) -> None:
+    """Options of the reference the B200 path cannot honour are refused, not ignored (SCFOptions.jl:86-93).
+    df_exchange_n_blocks only names the reference's K block grid (ScreenedDF.jl:385-417): without df_exchange_screen it
+    changes no result, so any value is accepted."""
+    if scf_options.df_screen_exchange:
+        raise NotImplementedError("B200 path: df_exchange_screen is not implemented (the exchange computes every "
+                                  "lower-triangular tile)")
+    if scf_options.df_exchange_n_blocks < 0:
+        raise ValueError("df_exchange_n_blocks must be >= 0")
+
 
 def df_rhf_fock_build_B200(scf_data: SCFData, integrals: IntegralSource, occupied_orbital_coefficients: np.ndarray,
                            iteration: int, scf_options: SCFOptions, H: np.ndarray, jc_timing: JCTiming,
@@ -408,7 +432,10 @@ def df_rhf_fock_build_B200(scf_data: SCFData, integrals: IntegralSource, occupie
     """The branch `contraction_mode == "B200"` of df_rhf_fock_build! (DensityFitting.jl:51-60) — same stage order as
     df_rhf_fock_build_GPU! (GPUDF.jl:11-304) with every device-side step behind libjcdf:
 
-      iteration 1:  (P|Q)            -> jcdf_upload_metric            (GPUDF.jl:44, TwoCenterIntegrals.jl:7)
+      iteration 1, device integrals (IntegralSource.device_basis given; any number of ranks):
+                    basis sets -> jcdf_set_basis, jcdf_compute_two_center, jcdf_compute_schwarz_mask, jcdf_compute_B
+      iteration 1, host integrals (one rank):
+                    (P|Q)            -> jcdf_upload_metric            (GPUDF.jl:44, TwoCenterIntegrals.jl:7)
                     Schwarz mask     -> jcdf_set_mask                 (GPUDF.jl:45, ScreenedDF.jl:16)
                     shard ranges     -> jcdf_set_shards               (GPUDF.jl:50, :1026-1056)
                     (P|mn) per shard -> jcdf_upload_three_center      (GPUDF.jl:51-57)
@@ -418,6 +445,7 @@ def df_rhf_fock_build_B200(scf_data: SCFData, integrals: IntegralSource, occupie
     `occupied_orbital_coefficients` is C[:, 1:occ] (DensityFitting.jl:49).  Returns scf_data.two_electron_fock, which
     the caller may mutate afterwards (DIIS, SCF.jl:472-508)."""
     if iteration == 1:
+        check_supported_options(scf_options)
         N, Q = integrals.N, integrals.Q
         scf_data.mu, scf_data.A = N, Q
         scf_data.occ = integrals.n_electrons // 2  # DensityFitting.jl:37
@@ -425,6 +453,10 @@ def df_rhf_fock_build_B200(scf_data: SCFData, integrals: IntegralSource, occupie
         ndev = scf_options.num_devices
         if ndev > device_count():  # GPUDF.jl:39-41
             raise RuntimeError("Number of devices requested is greater than the number of devices available")
+        if n_ranks > 1 and comm_id is None:
+            raise ValueError("comm_id required when n_ranks > 1")
+        dense = uses_dense_contraction(scf_options, N, n_ranks)
+        sigma = 0.0 if dense else scf_options.df_screening_sigma
         gd = B200Data(N, Q, scf_data.occ, ndev)
         scf_data.gpu_data = gd
         # shard ranges: ranks x devices contiguous pieces (GPUDF.jl:1026-1056 splits a rank's range over its devices)
@@ -436,28 +468,39 @@ def df_rhf_fock_build_B200(scf_data: SCFData, integrals: IntegralSource, occupie
             allr = balanced_function_shards(Q, total)
             ranges = allr[rank * ndev:(rank + 1) * ndev]
         gd.set_shards(ranges)
-        mask = integrals.screening_matrix(scf_options.df_screening_sigma)
-        sd = ScreeningData(mask, N)
-        scf_data.screening_data = sd
-        gd.set_mask(sd)
-        if n_ranks > 1:
-            if comm_id is None:
-                raise ValueError("comm_id required when n_ranks > 1")
-            gd.comm_init_rank(n_ranks, rank, comm_id)
-        have_B = True
-        for d, r in enumerate(ranges):
-            Brows = integrals.B_rows(r, sd)
-            if Brows is None:
-                have_B = False
-                break
-            gd.set_B(d, Brows)
-        if not have_B:
+        basis = integrals.device_basis()
+        if basis is not None:
+            # integral front-end of the library: nothing but the basis sets crosses the boundary, any number of ranks
+            gd.set_basis(0, *basis[0])
+            gd.set_basis(1, *basis[1])
+            gd.compute_two_center(False)
+            mask, _ = gd.compute_schwarz_mask(sigma)  # ends with jcdf_set_mask
+            scf_data.screening_data = ScreeningData(None if sigma <= 0 else mask, N)
             if n_ranks > 1:
-                raise RuntimeError("multi-rank B formation requires B_rows from the caller (SURVEY §8f-3)")
-            gd.upload_metric(integrals.two_center_integrals())
+                gd.comm_init_rank(n_ranks, rank, comm_id)
+            gd.compute_B()
+        else:
+            mask = None if dense else integrals.screening_matrix(sigma)
+            sd = ScreeningData(mask, N)
+            scf_data.screening_data = sd
+            gd.set_mask(sd)
+            if n_ranks > 1:
+                gd.comm_init_rank(n_ranks, rank, comm_id)
+            have_B = True
             for d, r in enumerate(ranges):
-                gd.upload_three_center(d, integrals.three_center_integrals(r, sd))
-            gd.factor_and_form_B()
+                Brows = integrals.B_rows(r, sd)
+                if Brows is None:
+                    have_B = False
+                    break
+                gd.set_B(d, Brows)
+            if not have_B:
+                if n_ranks > 1:
+                    raise RuntimeError("host-integral route with several ranks needs B_rows from the caller; give "
+                                       "device_basis() to let every rank compute its own rows (jcdf_compute_B)")
+                gd.upload_metric(integrals.two_center_integrals())
+                for d, r in enumerate(ranges):
+                    gd.upload_three_center(d, integrals.three_center_integrals(r, sd))
+                gd.factor_and_form_B()
     gd = scf_data.gpu_data
     if gd is None:
         raise RuntimeError("df_rhf_fock_build_B200 called with iteration > 1 before iteration 1")

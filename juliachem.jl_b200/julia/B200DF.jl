@@ -1,22 +1,27 @@
 # B200DF.jl — the Julia side of the B200 drop-in for JuliaChem's density-fitted RHF Fock build.
 #
 # A maintainer adds this file next to GPUDF.jl (src/rhf/energy/DensityFitting/) and includes it from Energy.jl:20-29;
-# INTEGRATION.md lists the three other one-line edits (Constants.jl, GPUData.jl, DensityFitting.jl).  Everything
-# device-side lives in libjcdf.so (include/jcdf.h); this file only marshals pointers, in the style of the module's own
-# raw BLAS call `call_gemm!` (ScreenedDF.jl:645-673).  It mirrors df_rhf_fock_build_GPU! (GPUDF.jl:11-304) stage by
-# stage; juliachem.jl_b200/df.py is the same wrapper in Python (Julia is not present in the build image) and is what
+# INTEGRATION.md lists the other one-line edits (Constants.jl, SCF.jl, DensityFitting.jl).  Everything device-side lives
+# in libjcdf.so (include/jcdf.h); this file only marshals pointers, in the style of the module's own raw BLAS call
+# `call_gemm!` (ScreenedDF.jl:645-673).  It follows df_rhf_fock_build_GPU! (GPUDF.jl:11-304) stage by stage;
+# juliachem.jl_b200/df.py + rhf.py are the same wrapper in Python (Julia is not present in the build image) and are what
 # the test-suite drives.
 #
-# NOT EXECUTED in this repository's CI (no Julia toolchain in the image) — kept ccall-for-ccall in step with df.py.
+# NOT EXECUTED in this repository's CI (no Julia toolchain in the image).  tests/test_julia_binding.py parses every
+# `ccall` below and checks symbol, arity and C types against the table the Python wrapper binds (_lib.SIGNATURES), and
+# every JCTC.<name> against src/shared/JCTiming.jl:50-107 when the reference checkout is present.
 
 using Libdl
 
 const libjcdf = get(ENV, "JULIACHEM_LIBJCDF", "libjcdf")   # deps/build.jl puts libjcdf.so next to libjeri.so
 
 const JCDF_N_STAGES = 10
-# stage slot (0-based in jcdf.h) -> JCTiming constant (src/shared/JCTiming.jl:58-90)
+# stage slot (0-based in jcdf.h) -> JCTiming key prefix (src/shared/JCTiming.jl:58-107).  Slot 6 (C_occ upload) is what
+# the fork's GPU path books as GPU_non_zero_coeff_time of device 1 (GPUDF.jl:288); slot 9 (J scatter + H add + mirror)
+# as gpu_copy_J_time (GPUDF.jl:289).
 const JCDF_STAGE_KEYS = (JCTC.W_time, JCTC.K_time, JCTC.V_time, JCTC.J_time, JCTC.fock_MPI_time, JCTC.density_time,
-    JCTC.gpu_copy_coeff_time, JCTC.fock_gpu_cpu_copy_reduce_time, JCTC.fock_time, JCTC.gpu_copy_J_time)
+    JCTiming_GPUkey(JCTC.GPU_non_zero_coeff_time, 1), JCTC.fock_gpu_cpu_copy_reduce_time, JCTC.fock_time,
+    JCTC.gpu_copy_J_time)
 
 # what scf_data.gpu_data holds for contraction_mode == "B200" (cf. SCFGPUData_cuda, GPUData_cuda.jl:4-38)
 mutable struct SCFGPUDataB200 <: SCFGPUData
@@ -37,6 +42,98 @@ end
     error(unsafe_string(ccall((:jcdf_last_error, libjcdf), Cstring, ())))   # same convention as error(...) GPUDF.jl:40
 end
 
+# JCModules.Shell keeps the contraction coefficients AFTER calculate_coefficients(..., unnormalize = true) divided each of
+# them by sqrt((pi/2a)^1.5 * {p: 1/(2*2a), d: 3/(4*(2a)^2), f: 15/(8*(2a)^3)}) (BasisStructs.jl:62-80); libint — and
+# jcdf_set_basis — take the RAW basis-set-exchange values (JCBasis.jl:301-307, jeri-core.hpp:41-62).  Undo the division.
+function jcdf_raw_coefficients(shell)
+    raw = Vector{Float64}(undef, shell.nprim)
+    for iprim in 1:shell.nprim
+        two_exp = 2.0 * shell.exponents[iprim]
+        f = (pi / two_exp)^1.5
+        f *= shell.am == 2 ? 0.5 / two_exp : 1.0
+        f *= shell.am == 3 ? 0.75 / (two_exp^2) : 1.0
+        f *= shell.am == 4 ? 1.875 / (two_exp^3) : 1.0
+        raw[iprim] = shell.coefficients[iprim] * sqrt(f)
+    end
+    return raw
+end
+
+# flat shell arrays of one Basis (BasisStructs.jl:170-178) -> jcdf_set_basis; which = 0 primary, 1 auxiliary
+function jcdf_set_basis_from!(handle::Ptr{Cvoid}, which::Integer, basis)
+    nshell = length(basis.shells)
+    am = Vector{Cint}(undef, nshell)
+    nprim = Vector{Cint}(undef, nshell)
+    centers = Matrix{Float64}(undef, 3, nshell)
+    exponents = Float64[]
+    coefficients = Float64[]
+    for (i, sh) in enumerate(basis.shells)
+        am[i] = sh.am - 1                      # JuliaChem counts s = 1 (JCBasis.jl:301 passes am - 1 to libint as well)
+        nprim[i] = sh.nprim
+        centers[:, i] .= sh.atom_center        # bohr, after the centre-of-mass shift (JCBasis.jl:86-101)
+        append!(exponents, sh.exponents[1:sh.nprim])
+        append!(coefficients, jcdf_raw_coefficients(sh))
+    end
+    GC.@preserve am nprim centers exponents coefficients begin
+        jcdf_check(ccall((:jcdf_set_basis, libjcdf), Cint,
+            (Ptr{Cvoid}, Cint, Int64, Ptr{Cint}, Ptr{Cint}, Ptr{Float64}, Ptr{Float64}, Ptr{Float64}),
+            handle, Cint(which), Int64(nshell), am, nprim, centers, exponents, coefficients))
+    end
+end
+
+# Iteration-1 set-up with the reference's own host integral drivers (libint through JERI) and an H2D upload of their
+# results — the route of GPUDF.jl:44-57.  One MPI rank only: jcdf_factor_and_form_B cannot reach another rank's (P|mn).
+function setup_host_integrals_B200!(gd::SCFGPUDataB200, scf_data, jeri_engine_thread_df, jeri_engine_thread, basis_sets,
+    scf_options, jc_timing, num_devices::Int)
+    two_center_integrals = calculate_two_center_intgrals(jeri_engine_thread_df, basis_sets, scf_options)
+    get_screening_metadata!(scf_data, scf_options.df_screening_sigma, jeri_engine_thread, two_center_integrals,
+        basis_sets, jc_timing)
+    sd = scf_data.screening_data
+    # mask + pair compaction -> tile-compacted HBM layout (replaces setup_gpu_screening_data!, GPUDF.jl:347-420)
+    GC.@preserve sd begin
+        jcdf_check(ccall((:jcdf_set_mask, libjcdf), Cint, (Ptr{Cvoid}, Ptr{Bool}, Ptr{Int64}), gd.handle,
+            sd.basis_function_screen_matrix, sd.sparse_pq_index_map))
+    end
+    for device_id in 1:num_devices   # screened (P|mn) rows of each device's shard (GPUDF.jl:51-57)
+        T3 = calculate_three_center_integrals(jeri_engine_thread_df, basis_sets, scf_options, scf_data,
+            device_id - 1, num_devices, true)                                   # (Q_dev, P) column-major
+        GC.@preserve T3 jcdf_check(ccall((:jcdf_upload_three_center, libjcdf), Cint,
+            (Ptr{Cvoid}, Cint, Ptr{Float64}, Int64), gd.handle, Cint(device_id - 1), T3, Int64(size(T3, 1))))
+    end
+    # potrf + trtri + B = L^-1 T on the devices (replaces calculate_B_GPU!, GPUDF.jl:828-1008, incl. its CPU LAPACK step)
+    jcdf_check(ccall((:jcdf_upload_metric, libjcdf), Cint, (Ptr{Cvoid}, Ptr{Float64}), gd.handle, two_center_integrals))
+    jcdf_check(ccall((:jcdf_factor_and_form_B, libjcdf), Cint, (Ptr{Cvoid},), gd.handle))
+end
+
+# Iteration-1 set-up with the integral front-end of the library (default; any number of MPI ranks): (P|Q), the Schwarz
+# mask with the reference's rule (SchwarzScreening.jl:9-83) and B = L^-1 (P|mn) are computed on the devices; every device
+# recomputes the auxiliary rows it needs, so no rank ever waits for another rank's integrals (jcdf_compute_B).
+function setup_device_integrals_B200!(gd::SCFGPUDataB200, scf_data, basis_sets, scf_options, n_ranks::Int, rank::Int, comm)
+    jcdf_set_basis_from!(gd.handle, 0, basis_sets.primary)
+    jcdf_set_basis_from!(gd.handle, 1, basis_sets.auxillary)
+    jcdf_check(ccall((:jcdf_compute_two_center, libjcdf), Cint, (Ptr{Cvoid}, Ptr{Float64}), gd.handle, C_NULL))
+    N = scf_data.μ
+    # the reference's choice between its dense and its screened GPU algorithm (run_gpu_fock_build!, DensityFitting.jl:79-90):
+    # dense = no Schwarz mask at all, which jcdf_compute_schwarz_mask does for sigma <= 0 (SchwarzScreening.jl:97-111)
+    dense = scf_options.df_force_dense || (scf_options.df_use_adaptive && N < 800 && n_ranks == 1)
+    sigma = dense ? 0.0 : Float64(scf_options.df_screening_sigma)
+    fn_mask = Matrix{Bool}(undef, N, N)
+    pairs_kept = Ref{Int64}(0)
+    GC.@preserve fn_mask begin   # ends with jcdf_set_mask on the result
+        jcdf_check(ccall((:jcdf_compute_schwarz_mask, libjcdf), Cint, (Ptr{Cvoid}, Float64, Ptr{Bool}, Ref{Int64}),
+            gd.handle, sigma, fn_mask, pairs_kept))
+    end
+    scf_data.screening_data.basis_function_screen_matrix = fn_mask
+    scf_data.screening_data.screened_indices_count = pairs_kept[]
+    if n_ranks > 1   # NCCL communicator over all devices of all ranks; the 128-byte id travels by MPI
+        id = zeros(UInt8, 128)
+        rank == 0 && jcdf_check(ccall((:jcdf_comm_unique_id, libjcdf), Cint, (Ptr{UInt8},), id))
+        MPI.Bcast!(id, 0, comm)
+        jcdf_check(ccall((:jcdf_comm_init_rank, libjcdf), Cint, (Ptr{Cvoid}, Cint, Cint, Ptr{UInt8}), gd.handle,
+            Cint(n_ranks), Cint(rank), id))
+    end
+    jcdf_check(ccall((:jcdf_compute_B, libjcdf), Cint, (Ptr{Cvoid},), gd.handle))
+end
+
 function df_rhf_fock_build_B200!(scf_data, jeri_engine_thread_df::Vector{T}, jeri_engine_thread::Vector{T2},
     basis_sets::CalculationBasisSets, occupied_orbital_coefficients, iteration, scf_options::SCFOptions,
     H::Array{Float64}, jc_timing::JCTiming) where {T<:DFRHFTEIEngine,T2<:RHFTEIEngine}
@@ -49,22 +146,27 @@ function df_rhf_fock_build_B200!(scf_data, jeri_engine_thread_df::Vector{T}, jer
     gd = scf_data.gpu_data::SCFGPUDataB200
 
     if iteration == 1
+        host_integrals = get(ENV, "JULIACHEM_B200_HOST_INTEGRALS", "0") == "1"
+        # refuse BEFORE any collective or integral work (the reference's options the library does not take are refused
+        # the same way: SCFOptions.jl:86-93)
+        if host_integrals && n_ranks > 1
+            error("B200 path: JULIACHEM_B200_HOST_INTEGRALS=1 needs one MPI rank (B formation from uploaded integrals does not cross ranks); unset it to compute the integrals on the devices")
+        end
+        if scf_options.df_screen_exchange
+            error("B200 path: df_exchange_screen is not implemented (the exchange computes every lower-triangular tile; df_exchange_n_blocks only names the reference's block grid and changes no result without it)")
+        end
+        if host_integrals && scf_options.df_force_dense
+            error("B200 path: df_force_dense needs the device integral route (unset JULIACHEM_B200_HOST_INTEGRALS)")
+        end
         navail = ccall((:jcdf_device_count, libjcdf), Cint, ())
         if num_devices > navail                                                     # GPUDF.jl:39-41
             error("Number of devices requested is greater than the number of devices available")
         end
         h = Ref{Ptr{Cvoid}}(C_NULL)
         jcdf_check(ccall((:jcdf_create, libjcdf), Cint, (Int64, Int64, Int64, Cint, Ptr{Cint}, Ref{Ptr{Cvoid}}),
-            scf_data.μ, scf_data.A, scf_data.occ, num_devices, C_NULL, h))
+            Int64(scf_data.μ), Int64(scf_data.A), Int64(scf_data.occ), Cint(num_devices), C_NULL, h))
         gd.handle = h[]
         gd.number_of_devices_used = num_devices
-
-        # (P|Q) and the Schwarz mask stay in Julia / libint (GPUDF.jl:44-49)
-        two_center_integrals = calculate_two_center_intgrals(jeri_engine_thread_df, basis_sets, scf_options)
-        get_screening_metadata!(scf_data, scf_options.df_screening_sigma, jeri_engine_thread, two_center_integrals,
-            basis_sets, jc_timing)
-        sd = scf_data.screening_data
-
         # Q shards: the reference's contiguous-auxiliary-shell rule per global device (GPUDF.jl:50, DynamicLoad.jl:160-203)
         q_begin = Vector{Int64}(undef, num_devices)
         q_len = Vector{Int64}(undef, num_devices)
@@ -76,43 +178,25 @@ function df_rhf_fock_build_B200!(scf_data, jeri_engine_thread_df::Vector{T}, jer
         end
         jcdf_check(ccall((:jcdf_set_shards, libjcdf), Cint, (Ptr{Cvoid}, Ptr{Int64}, Ptr{Int64}), gd.handle, q_begin, q_len))
 
-        # mask + pair compaction -> tile-compacted HBM layout (replaces setup_gpu_screening_data!, GPUDF.jl:347-420)
-        GC.@preserve sd begin
-            jcdf_check(ccall((:jcdf_set_mask, libjcdf), Cint, (Ptr{Cvoid}, Ptr{Bool}, Ptr{Int64}), gd.handle,
-                sd.basis_function_screen_matrix, sd.sparse_pq_index_map))
+        if host_integrals
+            setup_host_integrals_B200!(gd, scf_data, jeri_engine_thread_df, jeri_engine_thread, basis_sets, scf_options,
+                jc_timing, num_devices)
+        else
+            setup_device_integrals_B200!(gd, scf_data, basis_sets, scf_options, n_ranks, rank, comm)
         end
-
-        if n_ranks > 1   # NCCL communicator over all devices of all ranks; the id travels by MPI
-            id = zeros(UInt8, 128)
-            rank == 0 && jcdf_check(ccall((:jcdf_comm_unique_id, libjcdf), Cint, (Ptr{UInt8},), id))
-            MPI.Bcast!(id, 0, comm)
-            jcdf_check(ccall((:jcdf_comm_init_rank, libjcdf), Cint, (Ptr{Cvoid}, Cint, Cint, Ptr{UInt8}), gd.handle,
-                n_ranks, rank, id))
-        end
-
-        # screened (P|mn) rows of each device's shard, computed on the host by libint exactly as today (GPUDF.jl:51-57)
-        for device_id in 1:num_devices
-            global_device_id = device_id + rank * num_devices
-            T3 = calculate_three_center_integrals(jeri_engine_thread_df, basis_sets, scf_options, scf_data,
-                global_device_id - 1, num_devices_global, true)                    # (Q_dev, P) column-major
-            GC.@preserve T3 jcdf_check(ccall((:jcdf_upload_three_center, libjcdf), Cint,
-                (Ptr{Cvoid}, Cint, Ptr{Float64}, Int64), gd.handle, device_id - 1, T3, size(T3, 1)))
-        end
-        # potrf + trtri + B = L^-1 T on the devices (replaces calculate_B_GPU!, GPUDF.jl:828-1008, incl. its CPU LAPACK step)
-        jcdf_check(ccall((:jcdf_upload_metric, libjcdf), Cint, (Ptr{Cvoid}, Ptr{Float64}), gd.handle, two_center_integrals))
-        n_ranks == 1 || error("B200 path: multi-rank B formation not available yet (SURVEY §8f-3); use one rank with num_devices GPUs")
-        jcdf_check(ccall((:jcdf_factor_and_form_B, libjcdf), Cint, (Ptr{Cvoid},), gd.handle))
         jcdf_check(ccall((:jcdf_set_core_hamiltonian, libjcdf), Cint, (Ptr{Cvoid}, Ptr{Float64}), gd.handle, H))
     end
 
-    # every iteration: one call.  F_out is scf_data.two_electron_fock (caller-owned; DIIS mutates it afterwards).
+    # every iteration: one call.  F_out is scf_data.two_electron_fock (caller-owned; DIIS mutates it afterwards).  The
+    # library adds H on global shard 0 and all-reduces over every device of every rank, so the caller skips both
+    # `F .+= H` (DensityFitting.jl:62-65) and MPI.Allreduce! (:68-71) for this mode.
     stage_seconds = zeros(Float64, JCDF_N_STAGES)
     C_occ = occupied_orbital_coefficients          # N x occ column-major, as sliced at DensityFitting.jl:49
     F = scf_data.two_electron_fock
     GC.@preserve C_occ F stage_seconds begin
         jcdf_check(ccall((:jcdf_fock_build, libjcdf), Cint,
             (Ptr{Cvoid}, Ptr{Float64}, Int64, Ptr{Float64}, Ptr{Float64}, Ptr{Float64}),
-            gd.handle, C_occ, stride(C_occ, 2), C_NULL, F, stage_seconds))
+            gd.handle, C_occ, Int64(stride(C_occ, 2)), C_NULL, F, stage_seconds))
     end
     for (slot, key) in enumerate(JCDF_STAGE_KEYS)
         jc_timing.timings[JCTiming_key(key, iteration)] = stage_seconds[slot]

@@ -381,7 +381,10 @@ def iteration(F: np.ndarray, H: np.ndarray, ortho: np.ndarray, nocc: int):
 # bench.py's cpu_baseline / --impl reference legs so the CPU number is the reference's own parallel decomposition.
 # --------------------------------------------------------------------------------------------------------------
 def fock_build_screened_rank_threaded(B: np.ndarray, C_occ: np.ndarray, sd: ScreeningData, n_threads: int,
-                                      df_exchange_n_blocks: int = 0, timings: dict | None = None) -> np.ndarray:
+                                      df_exchange_n_blocks: int = 0, timings: dict | None = None,
+                                      W_buffer: np.ndarray | None = None) -> np.ndarray:
+    """W_buffer: optional (Q, occ, N) column-major array reused between builds — the reference allocates scf_data.D_tilde
+    once at iteration 1 (ScreenedDF.jl:110) and overwrites it in every build (gemm with beta = 0)."""
     import time
     from concurrent.futures import ThreadPoolExecutor
 
@@ -393,7 +396,8 @@ def fock_build_screened_rank_threaded(B: np.ndarray, C_occ: np.ndarray, sd: Scre
     fock = np.zeros((N, N), dtype=np.float64, order="F")
     n_blocks, width, batch = exchange_block_layout(N, df_exchange_n_blocks, 10)
     mask = sd.basis_function_screen_matrix
-    W = np.zeros((Q, occ, N), dtype=np.float64, order="F")
+    W = W_buffer if W_buffer is not None else np.zeros((Q, occ, N), dtype=np.float64, order="F")
+    assert W.shape == (Q, occ, N) and W.flags.f_contiguous
     Wv = W.reshape((Q * occ, N), order="F")
     t0 = time.perf_counter()
     with ThreadPoolExecutor(max_workers=n_threads) as pool:

@@ -136,3 +136,42 @@ def test_water_scf_run_whole_loop(water):
     with pytest.raises(jc.JCDFError):
         gd.scf_get("nonsense")
     gd.close()
+
+
+class WaterBasisOnly(jc.IntegralSource):
+    """The device-integral route of the seam (julia/B200DF.jl: setup_device_integrals_B200!): only the basis sets cross
+    the boundary."""
+
+    def __init__(self, g, p):
+        from juliachem_jl_b200 import rhf
+        xyz = np.array([a["xyz_bohr"] for a in g["geometry"]]) / rhf.ANGSTROM_TO_BOHR
+        mol = rhf.run_basis({"geometry": xyz.ravel().tolist(), "symbols": [a["symbol"] for a in g["geometry"]],
+                             "molecular_charge": 0}, {"basis": "cc-pVDZ"})
+        self.mol, self.N, self.Q, self.n_electrons = mol, p["N"], p["Q"], mol["n_electrons"]
+
+    def aux_shell_nbas(self):
+        return self.mol["auxiliary"].nbas
+
+    def device_basis(self):
+        return self.mol["primary"].args(), self.mol["auxiliary"].args()
+
+
+@pytest.mark.parametrize("force_dense", [False, True])
+def test_seam_with_device_integrals_and_reference_options(water, force_dense):
+    g, p = water
+    H, nocc, B = p["H"], p["nocc"], p["B"]
+    src = WaterBasisOnly(g, p)
+    scf_data, timing = jc.SCFData(), jc.JCTiming()
+    opts = jc.SCFOptions(num_devices=1, df_force_dense=force_dense, df_use_adaptive=force_dense, df_exchange_n_blocks=3)
+    X = sr.orthogonalizer(p["S"])
+    _, _, C, _ = orc.iteration(np.array(H), H, X, nocc)
+    F = jc.df_rhf_fock_build_B200(scf_data, src, np.asfortranarray(C[:, :nocc]), 1, opts, H, timing)
+    F_ref = orc.df_rhf_fock_build([B], C, nocc, H, None, "dense")
+    assert np.abs(F - F_ref).max() < 1e-10
+    assert (scf_data.screening_data.basis_function_screen_matrix is None) == force_dense
+    # every stage slot lands on a key the reference's JCTiming knows (JCTiming.jl:50-107)
+    assert jc.JCTiming.key("GPU_1_non_zero_coeff_time", 1) in timing.timings
+    scf_data.gpu_data.close()
+    with pytest.raises(NotImplementedError):
+        jc.df_rhf_fock_build_B200(jc.SCFData(), src, np.asfortranarray(C[:, :nocc]), 1,
+                                  jc.SCFOptions(df_screen_exchange=True), H, jc.JCTiming())
