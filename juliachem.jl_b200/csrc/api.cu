@@ -239,8 +239,8 @@ static int alloc_shard_buffers(jcdf_handle* h, Shard& s) {
             if ((rc = dev_alloc(&s.ppj_vp, (size_t)s.pp_chunks * 4 * h->sm_count * 32))) return rc;
             if ((rc = dev_alloc(&s.VpartP, (size_t)pp_coulomb_slabs(L) * s.pp_chunks * 128))) return rc;
             if ((rc = dev_alloc(&s.Jpart, (size_t)s.pp_chunks * L.pp_rows))) return rc;
-            {   // partial V of every half-transform item; warps without valid rows or orbitals never write: cleared once
-                const size_t nv = (size_t)L.N * s.pp_chunks * pp_v_slots(L) * 128;
+            {   // partial V per (CTA, chunk, warp column); pairs a CTA's list never visits are never written: cleared once
+                const size_t nv = (size_t)std::max(1, s.pp_ctas) * s.pp_chunks * pp_v_slots(L) * 128;
                 if ((rc = dev_alloc(&s.Vitem, nv))) return rc;
                 JC_CUDA(cudaMemsetAsync(s.Vitem, 0, nv * sizeof(double), s.stream));
             }

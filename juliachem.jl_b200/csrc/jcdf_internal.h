@@ -50,7 +50,7 @@ struct Layout {
 };
 
 inline int pp_item_orbitals(const Layout& L) { return L.pp_layout ? 8 * L.pp_nt : 32 * L.pp_nt; }
-inline int pp_v_slots(const Layout& L) { return L.pp_n_nt * (L.pp_layout ? 1 : 4); }  // partial-V slots per (function, chunk)
+inline int pp_v_slots(const Layout& L) { return L.pp_layout ? 1 : 4; }  // partial-V slots (warp columns) per (CTA, chunk)
 
 // event points recorded on the shard's stream during one build, in launch order
 enum EvPoint { EV_START = 0, EV_H2D, EV_PREP, EV_W, EV_K, EV_JBEGIN, EV_V, EV_J, EV_EPI, EV_AR, EV_D2H, EV_COUNT };
@@ -88,7 +88,7 @@ struct Shard {
     int pp_ctas = 0;
     double* dvec = nullptr;    // [pp_rows] weighted density in partner-row space
     double* VpartP = nullptr;  // [slabs][pp_chunks * 128] partial V of the compact Coulomb pass
-    double* Vitem = nullptr;   // [N][pp_chunks][pp_v_slots][128] partial V left by the per-function half-transform
+    double* Vitem = nullptr;   // [pp_ctas][pp_chunks][pp_v_slots][128] partial V left by the per-function half-transform
     double* Jpart = nullptr;   // [pp_chunks][pp_rows] partial J per chunk
     int pp_chunks = 0;         // ceil(q_len / 128)
     bool bc_valid = false;     // Bc mirrors the current Bp

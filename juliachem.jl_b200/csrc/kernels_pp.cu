@@ -76,7 +76,7 @@ struct PPParams {
     int ldci, n_fn, n_nt, chunks, q_len, npt64, occ_w;
     const int32_t* item_list;  // items of CTA c: item_list[item_off[c] .. item_off[c + 1])  (cost-balanced on the host)
     const int32_t* item_off;
-    double* vitem;  // [function p][chunk][orbital tile][warp column][128] partial Coulomb V of the item (nullptr: not wanted)
+    double* vitem;  // [CTA][chunk][warp column][128] partial Coulomb V of the CTA's items of a chunk (nullptr: not wanted)
 };
 
 // One pipeline stage (nks k-steps of 4 partner rows) of a warp block of MTV x NTV DMMA tiles inside the warp's 8 x NT
@@ -269,16 +269,13 @@ __global__ void __launch_bounds__(PP_THREADS, 1) k_pp_half_transform(PPParams pr
         // Coulomb V from the accumulators: D[p,q] = sum_i C[p,i] C[q,i], so
         //     V[Q] = sum_pq B[Q,p,q] D[p,q] = sum_p sum_i C[p,i] W[Q,i,p]
         // and the item's share is a dot product of each accumulator row with row p of C: MTW * NT * 2 DFMA per thread
-        // and ITEM, no density pass and no first sweep over B.  Each warp leaves its rows in its own slot; skipped
-        // warps leave the zeros the buffer was cleared to.
+        // and ITEM, no density pass and no first sweep over B.
         if constexpr (WITH_V) {
             // opaque copies: nothing of this block may be hoisted above the k loop, where every register is taken
-            int pe = p, che = ch, nte = nt, lne = lane;
-            asm volatile("" : "+r"(pe), "+r"(che), "+r"(nte), "+r"(lne));
+            int pe = p, nte = nt, lne = lane;
+            asm volatile("" : "+r"(pe), "+r"(nte), "+r"(lne));
             const int te = lne & 3, ge = lne >> 2;
             const double* cp = prm.Ci + (int64_t)pe * prm.ldci + nte * NI + n0 + 2 * te;
-            constexpr int NW = LAYOUT ? 1 : 4;
-            double* vdst = prm.vitem + (((((int64_t)pe * chunks + che) * n_nt + nte) * NW + (LAYOUT ? 0 : (warp & 3))) * PP_QC) + m0 + ge;
             // after the W stores only the accumulators are live: row p of C is loaded whole (one latency), then MTW
             // independent dot-product chains
             double2 c[NT];
@@ -296,8 +293,16 @@ __global__ void __launch_bounds__(PP_THREADS, 1) k_pp_half_transform(PPParams pr
 #pragma unroll
             for (int jm = 0; jm < MTW; jm++) v[jm] += __shfl_xor_sync(0xffffffffu, v[jm], 2);
             if (te == 0) {
+                // The shares of all the CTA's items of one chunk add up in the warp's own slot [CTA][chunk][warp column][128]:
+                // one thread per address and program order, so the fire-and-forget reductions are bit-reproducible.  (Rows
+                // beyond q_len / orbitals beyond occ add exact zeros: zero rows of Bc, zero columns of C.  Summing in
+                // shared memory and flushing once per chunk made ptxas spill accumulators inside the k loop.)
+                int che = ch, we = warp;
+                asm volatile("" : "+r"(che), "+r"(we));
+                constexpr int NWC = LAYOUT ? 1 : 4;
+                double* vdst = prm.vitem + ((((int64_t)blockIdx.x * chunks + che) * NWC + (LAYOUT ? 0 : (we & 3))) * PP_QC) + m0 + ge;
 #pragma unroll
-                for (int jm = 0; jm < MTW; jm++) vdst[8 * jm] = v[jm];
+                for (int jm = 0; jm < MTW; jm++) asm volatile("red.global.add.f64 [%0], %1;" ::"l"(vdst + 8 * jm), "d"(v[jm]) : "memory");
             }
         }
     }
@@ -392,8 +397,8 @@ __global__ void k_pp_vreduce(const double* __restrict__ Vpart, double* __restric
     if (Q < q_len) V[Q] = v;
 }
 
-// V[Q] = sum of the per-item partials the half-transform left, in a fixed order.  One block per 32 auxiliary functions:
-// 32 groups of 32 threads take the functions p = k (mod 32), then one sum over the 32 groups.
+// V[Q] = sum of the per-(CTA, chunk) partials the half-transform left, in a fixed order.  One block per 32 auxiliary
+// functions: 32 groups of 32 threads take the CTAs k (mod 32) (n_fn = number of CTAs), then one sum over the 32 groups.
 __global__ void __launch_bounds__(1024) k_pp_vitem_reduce(const double* __restrict__ vitem, double* __restrict__ V,
                                                           int n_fn, int chunks, int slots, int q_len) {
     __shared__ double part[32][33];
@@ -673,7 +678,7 @@ void launch_pp_coulomb(const Layout& L, Shard& s, cudaStream_t st, cudaEvent_t e
     const int qpad = s.pp_chunks * PP_QC;
     dim3 grid((unsigned)n_slab, (unsigned)s.pp_chunks);
     if (v_in_ht) {
-        k_pp_vitem_reduce<<<s.pp_chunks * 4, 1024, 0, st>>>(s.Vitem, s.V, (int)L.N, s.pp_chunks, pp_v_slots(L), (int)s.q_len);
+        k_pp_vitem_reduce<<<s.pp_chunks * 4, 1024, 0, st>>>(s.Vitem, s.V, s.pp_ctas, s.pp_chunks, pp_v_slots(L), (int)s.q_len);
     } else {
         k_pp_coulomb_v<<<grid, 256, 0, st>>>(s.Bc, s.dvec, s.VpartP, L.pp_rows, qpad);
         k_pp_vreduce<<<(qpad + 127) / 128, 128, 0, st>>>(s.VpartP, s.V, n_slab, qpad, (int)s.q_len);
@@ -693,6 +698,7 @@ template <int NT, int LAYOUT>
 static void launch_pp_t(const PPParams& prm, int grid, cudaStream_t st) {
     const size_t smem = pp_smem_bytes(LAYOUT ? 8 * NT : 32 * NT);
     if (prm.vitem != nullptr) {
+        cudaMemsetAsync(prm.vitem, 0, sizeof(double) * (size_t)grid * prm.chunks * (LAYOUT ? 1 : 4) * PP_QC, st);  // the slots are summed into
         cudaFuncSetAttribute(k_pp_half_transform<NT, LAYOUT, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
         k_pp_half_transform<NT, LAYOUT, true><<<grid, PP_THREADS, smem, st>>>(prm);
     } else {
@@ -705,7 +711,7 @@ static void launch_pp_t(const PPParams& prm, int grid, cudaStream_t st) {
 // 128-row chunk, the ragged last orbital tile — and a static round-robin aliases with the chunk count (gly18 shard,
 // 10 chunks of which the last holds 15 rows: CTAs of one parity got all the cheap items and the others 11 % more than
 // the mean).  Items are dealt longest-first onto the least-loaded CTA from the DMMA count the busiest sub-partition
-// issues; each CTA then walks its list in ascending (p-major) order so co-running CTAs share C rows in L2.
+// issues; each CTA then walks its list chunk by chunk, p-major inside a chunk (C is 2.5 MB: its rows stay in L2 anyway).
 void plan_pp_items(const Layout& L, Shard& s, int sm_count, std::vector<int32_t>& list, std::vector<int32_t>& off) {
     const int chunks = s.pp_chunks, n_nt = L.pp_n_nt, NT = L.pp_nt;
     const int64_t n_items = (int64_t)L.N * n_nt * chunks;
@@ -763,7 +769,12 @@ void plan_pp_items(const Layout& L, Shard& s, int sm_count, std::vector<int32_t>
         std::push_heap(heap.begin(), heap.end(), cmp);
     }
     for (int c = 0; c < n_ctas; c++) {
-        std::sort(bins[(size_t)c].begin(), bins[(size_t)c].end());
+        // chunk-major, then p-major: the rows of Bc a CTA reads form ascending runs inside one chunk, and its share of the
+        // Coulomb vector of a chunk is finished (and leaves the SM) before the next chunk starts
+        std::sort(bins[(size_t)c].begin(), bins[(size_t)c].end(), [&](int32_t a, int32_t b) {
+            const int ca = a % chunks, cb = b % chunks;
+            return ca != cb ? ca < cb : a < b;
+        });
         off[(size_t)c] = (int32_t)list.size();
         list.insert(list.end(), bins[(size_t)c].begin(), bins[(size_t)c].end());
     }

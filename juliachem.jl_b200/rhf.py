@@ -154,7 +154,7 @@ def run_energy(mol: dict, scf_flags: dict | None = None, num_devices: int = 1, k
     out = {"Energy": iters[-1][1], "Converged?": converged, "Iterations": iters, "Timings": dict(t, jc=timing.timings),
            "Fock": gd.scf_get("F"), "Density": gd.scf_get("D"), "MO Coeff": gd.scf_get("C"), "Overlap": S,
            "Orbital Energies": gd.scf_get("evals"), "N": N, "Q": Q, "occ": occ, "pairs_kept": P, "E_nuc": E_nuc,
-           "layout": gd.layout()}
+           "Core Hamiltonian": H, "Screen Matrix": mask, "layout": gd.layout()}
     if keep_handle:
         out["handle"] = gd
     else:

@@ -135,3 +135,19 @@ def test_baseline_shapes_match_the_oracle_on_a_row_slab(name, q0, rows, ht_mode)
     print("%s rows [%d, %d) ht_mode %d: max|F_gpu - F_oracle| = %.3e on max|F| = %.3f" % (name, q0, q0 + rows, ht_mode, err, np.abs(F).max()))
     assert np.array_equal(F, F.T)
     assert err < TOL
+
+
+@pytest.mark.slow
+def test_w50_converged_energy_matches_the_oracle_scf():
+    """North star: converged total energy within 1e-8 Eh.  The whole real-w50 SCF on the device with the benched (default)
+    kernels against the oracle's replay of the reference's loop on the host cores, same S, H, E_nuc, mask and B
+    (tools/w50_scf_parity.py; about three minutes of CPU time).  JCDF_SCF_PARITY_MOLECULES shrinks the cluster."""
+    import sys
+    sys.path.insert(0, os.path.join(ROOT, "tools"))
+    import w50_scf_parity
+    n = int(os.environ.get("JCDF_SCF_PARITY_MOLECULES", "50"))
+    out = w50_scf_parity.run(n, 50)
+    print({k: v for k, v in out.items() if k != "per_iteration"})
+    assert out["converged_gpu"] and out["converged_oracle"]
+    assert out["iterations_gpu"] == out["iterations_oracle"]
+    assert out["abs_diff"] <= 1e-8
