@@ -420,8 +420,10 @@ def check_supported_options(scf_options: SCFOptions) -> None:
     df_exchange_n_blocks only names the reference's K block grid (ScreenedDF.jl:385-417): without df_exchange_screen it
     changes no result, so any value is accepted."""
     if scf_options.df_screen_exchange:
-        raise NotImplementedError("B200 path: df_exchange_screen is not implemented (the exchange computes every "
-                                  "lower-triangular tile)")
+        # ScreenedDF.jl:459-545 writes only the computed blocks of scf_data.two_electron_fock: a dropped block keeps the
+        # previous iteration's Fock values and receives the new J on top, so the result depends on the iteration history
+        raise NotImplementedError("B200 path: df_exchange_screen is refused: the reference's block-screened exchange leaves "
+                                  "dropped blocks holding the previous iteration's values (history-dependent result)")
     if scf_options.df_exchange_n_blocks < 0:
         raise ValueError("df_exchange_n_blocks must be >= 0")
 

@@ -153,7 +153,10 @@ function df_rhf_fock_build_B200!(scf_data, jeri_engine_thread_df::Vector{T}, jer
             error("B200 path: JULIACHEM_B200_HOST_INTEGRALS=1 needs one MPI rank (B formation from uploaded integrals does not cross ranks); unset it to compute the integrals on the devices")
         end
         if scf_options.df_screen_exchange
-            error("B200 path: df_exchange_screen is not implemented (the exchange computes every lower-triangular tile; df_exchange_n_blocks only names the reference's block grid and changes no result without it)")
+            # ScreenedDF.jl:459-545 writes only the computed blocks of scf_data.two_electron_fock: a dropped block keeps the
+            # previous iteration's values and receives the new J on top (history-dependent); df_exchange_n_blocks alone
+            # only names the reference's block grid and changes no result
+            error("B200 path: df_exchange_screen is refused: the reference's block-screened exchange leaves dropped blocks holding the previous iteration's values")
         end
         if host_integrals && scf_options.df_force_dense
             error("B200 path: df_force_dense needs the device integral route (unset JULIACHEM_B200_HOST_INTEGRALS)")
