@@ -155,6 +155,25 @@ def run_energy(mol: dict, scf_flags: dict | None = None, num_devices: int = 1, k
            "Fock": gd.scf_get("F"), "Density": gd.scf_get("D"), "MO Coeff": gd.scf_get("C"), "Overlap": S,
            "Orbital Energies": gd.scf_get("evals"), "N": N, "Q": Q, "occ": occ, "pairs_kept": P, "E_nuc": E_nuc,
            "Core Hamiltonian": H, "Screen Matrix": mask, "layout": gd.layout()}
+    if f.get("timings_file"):
+        # the HDF5 file example_scripts/jc_timings_write.jl writes after a run, for the reference's plotting scripts
+        from .timing_io import save_jc_timings_to_hdf5
+        timing.non_timing_data.update({"n_basis_functions": str(N), "n_auxiliary_basis_functions": str(Q),
+                                       "n_electrons": str(mol["n_electrons"]), "n_oo": str(occ),
+                                       "n_atoms": str(len(mol["symbols"])), "n_ranks": "1", "n_iterations": str(len(iters)),
+                                       "contraction_algorithm": "B200", "screened_indices_count": str(P),
+                                       "GPU_num_devices": str(num_devices)})
+        for name, sec in t.items():
+            timing.timings[{"two_center": "two_eri_time", "three_center": "three_eri_time", "form_B": "B_time",
+                            "schwarz": "screening_time", "one_electron": "H_time"}.get(name, name + "_time")] = sec
+        opts = {"density_fitting": "true", "contraction_mode": "B200", "load": "static", "guess": "hcore",
+                "df_energy_convergence": f["dele"], "df_density_convergence": f["rmsd"], "energy_convergence": f["dele"],
+                "density_convergence": f["rmsd"], "max_iterations": f["niter"], "df_max_iterations": f["niter"],
+                "df_exchange_n_blocks": 0, "df_screening_sigma": f["df_sigma"], "df_screen_exchange": "false",
+                "df_force_dense": "false", "df_use_adaptive": "false", "num_devices": num_devices,
+                "df_use_K_sym": "false", "df_K_sym_type": ""}
+        save_jc_timings_to_hdf5(timing, f["timings_file"], run_time=sum(t.values()), run_name=str(f.get("run_name", "")),
+                                converged=converged, scf_energy=iters[-1][1], options=opts, user_options=opts)
     if keep_handle:
         out["handle"] = gd
     else:

@@ -44,7 +44,7 @@ def water_oracle():
 
 
 @pytest.mark.parametrize("ndev", [1, 2, 3])
-def test_s10_water_scf_matches_oracle_and_log(water_oracle, ndev):
+def test_s10_water_scf_matches_oracle_and_log(water_oracle, ndev, tmp_path):
     _ndev_or_skip(ndev)
     from juliachem_jl_b200 import rhf
     p, ref = water_oracle
@@ -52,7 +52,14 @@ def test_s10_water_scf_matches_oracle_and_log(water_oracle, ndev):
     mol = rhf.run_basis(_molecule(g), {"basis": GOLDEN["basis_name"]})
     assert np.abs(mol["centers"] - np.array([a["xyz_bohr"] for a in g["geometry"]])).max() < 1e-12
     assert (mol["primary"].n_functions, mol["auxiliary"].n_functions, mol["n_electrons"]) == (47, 166, 10)
-    res = rhf.run_energy(mol, {"niter": 20, "df_sigma": GOLDEN["settings"]["df_sigma"]}, num_devices=ndev)
+    h5 = str(tmp_path / "timings.h5")
+    res = rhf.run_energy(mol, {"niter": 20, "df_sigma": GOLDEN["settings"]["df_sigma"], "timings_file": h5,
+                               "run_name": "s10-water"}, num_devices=ndev)
+    # the timing file the reference's plotting scripts read (example_scripts/jc_timings_write.jl), SURVEY §8f-4
+    from juliachem_jl_b200 import timing_io
+    tabs = timing_io.read_string_tables(h5)
+    assert dict(tabs["run_level_data"])["n_iterations"] == "13" and dict(tabs["run_level_data"])["converged"] == "true"
+    assert "fock_time-13" in dict(tabs["timings"]) and "B_time" in dict(tabs["timings"])
     assert res["Converged?"] and len(res["Iterations"]) == len(ref["iterations"]) == 13
     for (it, E, dE, drms), (_, Eo, _, drmso), gl in zip(res["Iterations"], ref["iterations"], g["iterations"]):
         assert abs(E - Eo) <= (1e-7 if it <= 3 else 1e-8), (it, E, Eo)
