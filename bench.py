@@ -254,6 +254,34 @@ def workload_config(w, n_gpus):
             "l2": "inputs larger than L2 (packed B shard streamed from HBM every build)"}
 
 
+def parse_cpu_affinity(topo_text: str, gpu_index: int):
+    """Core set of the "CPU Affinity" column of `nvidia-smi topo -m` for GPU<gpu_index> (tab-separated table)."""
+    lines = [ln for ln in topo_text.splitlines() if ln.strip()]
+    head = [c.strip() for c in next(ln for ln in lines if "CPU Affinity" in ln).split("\t")]
+    col = head.index("CPU Affinity")
+    row = [c.strip() for c in next(ln for ln in lines if ln.split("\t")[0].strip() == "GPU%d" % gpu_index).split("\t")]
+    cores = set()
+    for part in row[col].split(","):
+        a, _, b = part.partition("-")
+        cores.update(range(int(a), int(b or a) + 1))
+    return cores
+
+
+def bind_to_gpu_numa_node(gpu_index: int):
+    """One process per GPU: run this rank (and first-touch its pinned buffers) on the host cores next to its GPU, as
+    `nvidia-smi topo -m` reports them ("CPU Affinity"), so the per-build H2D / D2H copies of eight ranks do not all cross
+    one socket's memory controller.  Returns the number of cores bound to, or None when it cannot be determined."""
+    try:
+        txt = subprocess.run(["nvidia-smi", "topo", "-m"], capture_output=True, text=True, timeout=20).stdout
+        allowed = parse_cpu_affinity(txt, gpu_index) & set(os.sched_getaffinity(0))
+        if not allowed:
+            return None
+        os.sched_setaffinity(0, allowed)
+        return len(allowed)
+    except Exception:
+        return None
+
+
 # ----------------------------------------------------------------------------------------------------------------------
 # B200 arm
 # ----------------------------------------------------------------------------------------------------------------------
@@ -270,9 +298,11 @@ def run_b200(args):
     if not torch.cuda.is_available():
         raise SystemExit("bench.py: no CUDA device — the B200 arm has no CPU fallback")
     dist = None
+    affinity = None
     if world > 1:
         import torch.distributed as dist
         torch.cuda.set_device(local_rank)
+        affinity = bind_to_gpu_numa_node(local_rank)
         dist.init_process_group("nccl", device_id=torch.device("cuda", local_rank))
         ndev_local, dev_ids, n_total = 1, [local_rank], world
     else:
@@ -503,7 +533,7 @@ def run_b200(args):
         "data": data_label(w), "config": cfg, "e2e": e2e, "options": args.opt,
         "gpu_launches": int(li.kernel_launches_per_build) * args.steps * n_total,
         "gpu_launches_per_build_per_gpu": int(li.kernel_launches_per_build),
-        "graph_replays": graph_replays, "parity_check": parity,
+        "graph_replays": graph_replays, "parity_check": parity, "rank0_cpu_affinity": affinity,
         "clocks": clocks, "roofline": roofline, "cpu_baseline": cpu,
         "stage_ms": {k: round(v, 4) for k, v in stage_ms.items()},
     }

@@ -52,3 +52,18 @@ def test_two_rank_gloo(tmp_path):
     for r, (p, o) in enumerate(zip(procs, outs)):
         assert p.returncode == 0, o
         assert "rank %d ok" % r in o
+
+
+def test_bench_parses_the_gpu_cpu_affinity_table():
+    """bench.py binds every rank to the host cores next to its GPU (nvidia-smi topo -m, tab-separated)."""
+    import importlib.util
+    import os
+    spec = importlib.util.spec_from_file_location("bench", os.path.join(os.path.dirname(os.path.dirname(os.path.abspath(__file__))), "bench.py"))
+    bench = importlib.util.module_from_spec(spec)
+    spec.loader.exec_module(bench)
+    topo = ("\tGPU0\tGPU1\tNIC0\tCPU Affinity\tNUMA Affinity\tGPU NUMA ID\n"
+            "GPU0\t X \tNV18\tPIX\t0-3,8-9\t0\t\tN/A\n"
+            "GPU1\tNV18\t X \tSYS\t56-57\t1\t\tN/A\n"
+            "NIC0\tPIX\tSYS\t X \t\t\t\t\n\nLegend:\n  X    = Self\n")
+    assert bench.parse_cpu_affinity(topo, 0) == {0, 1, 2, 3, 8, 9}
+    assert bench.parse_cpu_affinity(topo, 1) == {56, 57}
