@@ -238,9 +238,10 @@ double jcdf_synthetic_value(uint64_t seed, int64_t Q_total, int64_t q_aux, int64
  * back to the tile family, ht_mode = 2 reports JCDF_ERR_CUDA; 0 = no cap),
  * "coulomb_pp_fused" (0 = default: two streaming passes; 1 = one cooperative single-pass kernel, measured slower),
  * "exchange_balance" (1 = default: cost-balanced exchange work lists; 0 = round-robin),
+ * "pp_order" (work lists of the per-function kernel: 0 = default, a CTA walks its items chunk by chunk; 1 = p-major),
  * "graph" (1 = default: the kernel sequence of a build, prep .. epilogue, is captured into a CUDA graph on the first build
- * and replayed afterwards; 0 = every kernel launched eagerly).  "regroup", "ht_mode", "pp_layout", "pp_max_bytes",
- * "exchange_slices" and "exchange_balance" must be set before jcdf_set_mask.  A refused call (unknown name, value out of
+ * and replayed afterwards; 0 = every kernel launched eagerly).  "regroup", "ht_mode", "pp_layout", "pp_order",
+ * "pp_max_bytes", "exchange_slices" and "exchange_balance" must be set before jcdf_set_mask.  A refused call (unknown name, value out of
  * range, too late) returns JCDF_ERR_INVALID and leaves the handle unchanged.                                          */
 int32_t jcdf_set_option(jcdf_handle* h, const char* name, int64_t value);
 

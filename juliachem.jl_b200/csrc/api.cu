@@ -86,7 +86,7 @@ static void free_shard_buffers(Shard& s, bool keep_metric = false) {
 }
 
 // Split of the exchange contraction index: items = tiles x slices dealt round-robin to one CTA per SM.
-static void plan_exchange(const Layout& L, Shard& s, int sm_count, bool balance) {
+static void plan_exchange(const Layout& L, Shard& s, int sm_count, bool balance, int64_t forced_slices) {
     ExchangePlan& x = s.xplan;
     x.chunks = (int)((s.q_len * L.occ_w + 31) / 32);
     x.n_tiles = L.n128 * (L.n128 + 1) / 2;
@@ -101,6 +101,7 @@ static void plan_exchange(const Layout& L, Shard& s, int sm_count, bool balance)
         double eff = (double)items / (double)(waves * sm_count);
         if (eff > best_eff + 1e-9) { best_eff = eff; best = c; }
     }
+    if (forced_slices > 0) best = (int)std::min<int64_t>(forced_slices, std::max(1, x.chunks));  // option "exchange_slices"
     x.chunks_per_slice = (x.chunks + best - 1) / best;
     if (x.chunks_per_slice < 1) x.chunks_per_slice = 1;
     x.n_slices = std::max(1, (x.chunks + x.chunks_per_slice - 1) / x.chunks_per_slice);
@@ -146,7 +147,7 @@ static void plan_exchange(const Layout& L, Shard& s, int sm_count, bool balance)
 static int alloc_shard_buffers(jcdf_handle* h, Shard& s) {
     Layout& L = h->lay;
     JC_CUDA(cudaSetDevice(s.dev));
-    plan_exchange(L, s, h->sm_count, h->opt_exchange_balance != 0);
+    plan_exchange(L, s, h->sm_count, h->opt_exchange_balance != 0, h->opt_exchange_slices);
     int rc;
     const size_t nB = (size_t)s.q_len * (size_t)L.row_len;
     if ((rc = dev_alloc(&s.Bp, nB))) return rc;
@@ -226,7 +227,7 @@ static int alloc_shard_buffers(jcdf_handle* h, Shard& s) {
             JC_CUDA(cudaMemcpyAsync(s.d_pp_jdst, L.pp_jdst.data(), sizeof(int32_t) * L.pp_jdst.size(), cudaMemcpyHostToDevice, s.stream));
             {
                 std::vector<int32_t> list, off;
-                plan_pp_items(L, s, h->sm_count, list, off);
+                plan_pp_items(L, s, h->sm_count, h->opt_pp_order == 1, list, off);
                 if ((rc = dev_alloc(&s.d_ppitems, list.size()))) return rc;
                 if ((rc = dev_alloc(&s.d_ppoff, off.size()))) return rc;
                 JC_CUDA(cudaMemcpy(s.d_ppitems, list.data(), sizeof(int32_t) * list.size(), cudaMemcpyHostToDevice));
@@ -1321,6 +1322,7 @@ int32_t jcdf_set_option(jcdf_handle* h, const char* name, int64_t value) {
         {"ht_mode", &h->opt_ht_mode, true, 0, 2},
         {"regroup", &h->opt_regroup, true, 0, 1},
         {"exchange_slices", &h->opt_exchange_slices, true, 0, 1 << 20},
+        {"pp_order", &h->opt_pp_order, true, 0, 1},
         {"graph", &h->opt_graph, false, 0, 1},
     };
     for (const Opt& o : opts) {

@@ -155,7 +155,8 @@ struct jcdf_handle {
     int64_t opt_coulomb_fused = 2;    // tile-family Coulomb: 2 = single-pass cooperative kernel on long column segments,
                                       // two streaming passes on short ones; 1 = single pass whenever it fits; 0 = two passes
     int64_t opt_coulomb_overlap = 0;  // two-pass sweeps on a second stream, concurrent with the tensor-core kernels
-    int64_t opt_exchange_slices = 0;
+    int64_t opt_exchange_slices = 0;   // > 0: that many slices of the exchange contraction index per tile (0 = chosen from the sizes)
+    int64_t opt_pp_order = 0;          // per-function work lists: 0 = chunk-major inside a CTA, 1 = p-major (round-1 order)
     int64_t opt_exchange_balance = 1;  // cost-balanced exchange item lists (0: round-robin in item order)
     int64_t opt_regroup = 1;          // mask-driven regrouping of the basis functions into 32-wide blocks
     int64_t opt_coulomb_v_in_ht = 1;   // compact Coulomb: V from the per-function half-transform's accumulators (no density, no V sweep)
@@ -185,7 +186,7 @@ void launch_pp_pack(const Layout& L, Shard& s);                        // kernel
 void launch_pp_prep(const Layout& L, Shard& s, int64_t ldc);           // C_occ -> Ci
 void launch_pp_half_transform(const Layout& L, Shard& s, int sm_count, bool v_in_ht);
 void launch_pp_density(const Layout& L, Shard& s);
-void plan_pp_items(const Layout& L, Shard& s, int sm_count, std::vector<int32_t>& list, std::vector<int32_t>& off);
+void plan_pp_items(const Layout& L, Shard& s, int sm_count, bool p_major, std::vector<int32_t>& list, std::vector<int32_t>& off);
 void launch_pp_coulomb(const Layout& L, Shard& s, cudaStream_t st, cudaEvent_t ev_v, bool v_in_ht);
 int64_t pp_coulomb_slabs(const Layout& L);
 bool launch_pp_coulomb_fused(const Layout& L, Shard& s, int sm_count, cudaStream_t st);

@@ -712,7 +712,7 @@ static void launch_pp_t(const PPParams& prm, int grid, cudaStream_t st) {
 // 10 chunks of which the last holds 15 rows: CTAs of one parity got all the cheap items and the others 11 % more than
 // the mean).  Items are dealt longest-first onto the least-loaded CTA from the DMMA count the busiest sub-partition
 // issues; each CTA then walks its list chunk by chunk, p-major inside a chunk (C is 2.5 MB: its rows stay in L2 anyway).
-void plan_pp_items(const Layout& L, Shard& s, int sm_count, std::vector<int32_t>& list, std::vector<int32_t>& off) {
+void plan_pp_items(const Layout& L, Shard& s, int sm_count, bool p_major, std::vector<int32_t>& list, std::vector<int32_t>& off) {
     const int chunks = s.pp_chunks, n_nt = L.pp_n_nt, NT = L.pp_nt;
     const int64_t n_items = (int64_t)L.N * n_nt * chunks;
     const int n_ctas = (int)std::max<int64_t>(1, std::min<int64_t>(n_items, sm_count));
@@ -773,7 +773,7 @@ void plan_pp_items(const Layout& L, Shard& s, int sm_count, std::vector<int32_t>
         // Coulomb vector of a chunk is finished (and leaves the SM) before the next chunk starts
         std::sort(bins[(size_t)c].begin(), bins[(size_t)c].end(), [&](int32_t a, int32_t b) {
             const int ca = a % chunks, cb = b % chunks;
-            return ca != cb ? ca < cb : a < b;
+            return (!p_major && ca != cb) ? ca < cb : a < b;
         });
         off[(size_t)c] = (int32_t)list.size();
         list.insert(list.end(), bins[(size_t)c].begin(), bins[(size_t)c].end());
