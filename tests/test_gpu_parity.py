@@ -477,3 +477,57 @@ def test_regrouped_synthetic_fill_matches_host_twin():
     ref = reference_layout_rows(wl.synthetic_B_rows(w, range(0, w.Q), mask), range(0, w.Q), mask)
     assert np.array_equal(got, ref)
     gd.close()
+
+
+@pytest.mark.parametrize("ht_mode", [1, 2])
+def test_graph_replay_is_bit_identical_to_eager_launches(ht_mode):
+    """The per-build kernel sequence captured into a CUDA graph (default) against eager launches: same kernels, same order,
+    bit-identical Fock matrices; the replay counter shows the graph really ran; stage times stay available (the timing
+    events are external event-record nodes of the graph)."""
+    N, Q, occ = 203, 131, 27
+    mask = _scattered_mask(N, 19, 1, seed=77)
+    B, C_occ, H = random_inputs(N, Q, occ, seed=78, mask=mask)
+    F_ref = oracle_fock(B, C_occ, H, mask)
+    res = {}
+    for graph in (1, 0):
+        gd = jc.B200Data(N, Q, occ, 1)
+        gd.set_option("ht_mode", ht_mode)
+        gd.set_option("graph", graph)
+        gd.set_mask(jc.ScreeningData(mask, N))
+        gd.set_B(0, reference_layout_rows(B, range(0, Q), mask))
+        Fs = [gd.fock_build(C_occ, H)[0].copy() for _ in range(3)]
+        C2 = np.asfortranarray(C_occ[:, ::-1])  # another density through the same graph
+        F2, st = gd.fock_build(C2, None)
+        assert np.array_equal(Fs[0], Fs[1]) and np.array_equal(Fs[1], Fs[2])
+        assert np.abs(Fs[0] - F_ref).max() < TOL
+        assert gd.layout().graph_replays == (4 if graph else 0)
+        assert st["W"] > 0 and st["K"] > 0 and st["total"] > 0
+        res[graph] = (Fs[0], F2.copy())
+        gd.close()
+    assert np.array_equal(res[1][0], res[0][0]) and np.array_equal(res[1][1], res[0][1])
+
+
+def test_refused_options_leave_the_handle_unchanged():
+    N, Q, occ = 70, 40, 9
+    gd = jc.B200Data(N, Q, occ, 1)
+    for name, value in (("ht_mode", 3), ("coulomb_fused", -1), ("pp_layout", 2), ("nonsense", 1), ("graph", 2)):
+        with pytest.raises(jc.JCDFError):
+            gd.set_option(name, value)
+    mask = banded_mask(N, 20, seed=N)
+    B, C_occ, H = random_inputs(N, Q, occ, seed=N + 1, mask=mask)
+    gd.set_mask(jc.ScreeningData(mask, N))
+    for name in ("ht_mode", "regroup", "exchange_slices", "exchange_balance", "pp_layout", "pp_order", "pp_max_bytes"):
+        with pytest.raises(jc.JCDFError):
+            gd.set_option(name, 1)  # too late: the layout exists
+    gd.set_B(0, reference_layout_rows(B, range(0, Q), mask))
+    assert np.abs(gd.fock_build(C_occ, H)[0] - oracle_fock(B, C_occ, H, mask)).max() < TOL
+    with pytest.raises(jc.JCDFError):
+        gd.set_shards([range(0, 10)])  # after jcdf_set_mask
+    gd.close()
+    gd = jc.B200Data(N, Q, occ, 1)
+    gd.set_option("exchange_slices", 3)  # a forced split of the exchange contraction index
+    gd.set_option("pp_order", 1)
+    gd.set_mask(jc.ScreeningData(mask, N))
+    gd.set_B(0, reference_layout_rows(B, range(0, Q), mask))
+    assert np.abs(gd.fock_build(C_occ, H)[0] - oracle_fock(B, C_occ, H, mask)).max() < TOL
+    gd.close()

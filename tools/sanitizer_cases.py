@@ -1,0 +1,58 @@
+#!/usr/bin/env python
+"""The smallest parity case of every kernel family, for compute-sanitizer (one --tool per gpurun call):
+    compute-sanitizer --tool memcheck|racecheck|synccheck python tools/sanitizer_cases.py
+Each case builds one Fock matrix through the C-ABI and checks it against the oracle (1e-10), so a sanitizer report can be
+read next to a known-correct result.  Families: tile half-transform (MT 2 and 6) with the fused cooperative / the
+two-pass Coulomb; per-function half-transform 2 x 4 and 8 x 1 with V from the accumulators, with the density + V pass, and
+with the cooperative compact Coulomb; sliced exchange with reduce; graph replay and eager launch."""
+import os
+import sys
+
+import numpy as np
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+sys.path.insert(0, ROOT)
+sys.path.insert(0, os.path.join(ROOT, "tests"))
+
+from helpers import banded_mask, jc, oracle_fock, random_inputs, reference_layout_rows  # noqa: E402
+
+CASES = [
+    # name, N, Q, occ, options
+    ("tiles_fused_coulomb", 70, 40, 9, {"ht_mode": 1, "coulomb_fused": 1}),
+    ("tiles_two_pass_coulomb", 70, 40, 41, {"ht_mode": 1, "coulomb_fused": 0}),
+    ("pp_2x4_v_in_ht", 96, 140, 40, {"ht_mode": 2, "coulomb_pp_fused": 0, "coulomb_v_in_ht": 1}),
+    ("pp_2x4_density_v_pass", 96, 140, 40, {"ht_mode": 2, "coulomb_pp_fused": 0, "coulomb_v_in_ht": 0}),
+    ("pp_8x1_v_in_ht", 96, 129, 81, {"ht_mode": 2, "coulomb_pp_fused": 0, "pp_layout": 1}),
+    ("pp_coulomb_cooperative", 96, 140, 24, {"ht_mode": 2, "coulomb_pp_fused": 1}),
+    ("sliced_exchange_eager", 140, 64, 33, {"ht_mode": 2, "exchange_slices": 4, "graph": 0}),
+    ("dense_no_mask", 64, 32, 8, {}),
+]
+
+
+def main():
+    only = sys.argv[1:]
+    worst = 0.0
+    for name, N, Q, occ, opts in CASES:
+        if only and name not in only:
+            continue
+        mask = None if name == "dense_no_mask" else banded_mask(N, max(8, N // 3), seed=N)
+        B, C_occ, H = random_inputs(N, Q, occ, seed=N + occ, mask=mask)
+        gd = jc.B200Data(N, Q, occ, 1)
+        for k, v in opts.items():
+            gd.set_option(k, v)
+        gd.set_mask(jc.ScreeningData(mask, N))
+        gd.set_B(0, reference_layout_rows(B, range(0, Q), mask))
+        F = gd.fock_build(C_occ, H)[0].copy()
+        F2 = gd.fock_build(C_occ, None)[0]
+        err = float(np.abs(F - oracle_fock(B, C_occ, H, mask)).max())
+        li = gd.layout()
+        gd.close()
+        worst = max(worst, err)
+        print("%-26s N=%d Q=%d occ=%d launches/build=%d graph_replays=%d  max|F-F_oracle|=%.2e  repeat identical=%s" % (
+            name, N, Q, occ, li.kernel_launches_per_build, li.graph_replays, err, bool(np.array_equal(F, F2))), flush=True)
+    if not worst < 1e-10:
+        raise SystemExit("parity failed: %.3e" % worst)
+
+
+if __name__ == "__main__":
+    main()
