@@ -951,7 +951,8 @@ struct BuildSchedule {
     bool use_pp, pp_j, v_in_ht, overlap, add_H;
     uint64_t key(const jcdf_handle* h) const {
         return 1ull | (uint64_t)use_pp << 1 | (uint64_t)pp_j << 2 | (uint64_t)v_in_ht << 3 | (uint64_t)overlap << 4 |
-               (uint64_t)add_H << 5 | (uint64_t)(h->opt_coulomb_fused & 3) << 6 | (uint64_t)(h->opt_coulomb_pp_fused & 1) << 8;
+               (uint64_t)add_H << 5 | (uint64_t)(h->opt_coulomb_fused & 3) << 6 | (uint64_t)(h->opt_coulomb_pp_fused & 1) << 8 |
+               (uint64_t)(h->opt_pp_bigreg & 1) << 9;
     }
 };
 
@@ -964,7 +965,7 @@ static int issue_build_kernels(jcdf_handle* h, Shard& s, const BuildSchedule& b)
     // V = sum_p sum_i C[p,i] W[Q,i,p] comes out of the half-transform's accumulators: no density, no V sweep
     if (b.pp_j && !b.v_in_ht) launch_pp_density(L, s);
     JC_CUDA(record_event(s, s.ev[EV_PREP], s.stream));
-    if (b.use_pp) launch_pp_half_transform(L, s, h->sm_count, b.v_in_ht);
+    if (b.use_pp) launch_pp_half_transform(L, s, h->sm_count, b.v_in_ht, h->opt_pp_bigreg != 0);
     else launch_half_transform(L, s, h->sm_count);
     JC_CUDA(cudaPeekAtLastError());  // a launch that did not fit fails the build here, not as a wrong Fock matrix
     JC_CUDA(record_event(s, s.ev[EV_W], s.stream));
@@ -1323,6 +1324,7 @@ int32_t jcdf_set_option(jcdf_handle* h, const char* name, int64_t value) {
         {"regroup", &h->opt_regroup, true, 0, 1},
         {"exchange_slices", &h->opt_exchange_slices, true, 0, 1 << 20},
         {"pp_order", &h->opt_pp_order, true, 0, 1},
+        {"pp_bigreg", &h->opt_pp_bigreg, false, 0, 1},
         {"graph", &h->opt_graph, false, 0, 1},
     };
     for (const Opt& o : opts) {

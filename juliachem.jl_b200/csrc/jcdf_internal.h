@@ -156,6 +156,7 @@ struct jcdf_handle {
                                       // two streaming passes on short ones; 1 = single pass whenever it fits; 0 = two passes
     int64_t opt_coulomb_overlap = 0;  // two-pass sweeps on a second stream, concurrent with the tensor-core kernels
     int64_t opt_exchange_slices = 0;   // > 0: that many slices of the exchange contraction index per tile (0 = chosen from the sizes)
+    int64_t opt_pp_bigreg = 1;         // per-function kernel: setmaxnreg register split between producer and consumer warpgroups
     int64_t opt_pp_order = 0;          // per-function work lists: 0 = chunk-major inside a CTA, 1 = p-major (round-1 order)
     int64_t opt_exchange_balance = 1;  // cost-balanced exchange item lists (0: round-robin in item order)
     int64_t opt_regroup = 1;          // mask-driven regrouping of the basis functions into 32-wide blocks
@@ -184,7 +185,7 @@ void launch_prep(const Layout& L, Shard& s, int64_t ldc);
 void launch_half_transform(const Layout& L, Shard& s, int sm_count);
 void launch_pp_pack(const Layout& L, Shard& s);                        // kernels_pp.cu: Bp -> Bc
 void launch_pp_prep(const Layout& L, Shard& s, int64_t ldc);           // C_occ -> Ci
-void launch_pp_half_transform(const Layout& L, Shard& s, int sm_count, bool v_in_ht);
+void launch_pp_half_transform(const Layout& L, Shard& s, int sm_count, bool v_in_ht, bool bigreg);
 void launch_pp_density(const Layout& L, Shard& s);
 void plan_pp_items(const Layout& L, Shard& s, int sm_count, bool p_major, std::vector<int32_t>& list, std::vector<int32_t>& off);
 void launch_pp_coulomb(const Layout& L, Shard& s, cudaStream_t st, cudaEvent_t ev_v, bool v_in_ht);

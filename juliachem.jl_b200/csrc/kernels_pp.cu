@@ -29,6 +29,11 @@ constexpr int PP_KS = 32;        // partner rows per pipeline stage
 constexpr int PP_NSTAGE = 3;
 constexpr int PP_CONSUMERS = 8;  // 2 (M halves of 64 rows) x 4 (N quarters of 8 * NT orbitals)
 constexpr int PP_THREADS = (PP_CONSUMERS + 1) * 32;
+// Warp-specialised register split (setmaxnreg): the CTA is launched with 12 warps = 3 warpgroups at 168 registers per thread;
+// the producer's warpgroup (warp 8 + three warps that exit at once) gives registers back (-> 40) and the two consumer
+// warpgroups take them (-> 232), so ptxas can keep a whole k-step of fragments in flight (it uses 186) instead of loading
+// every a fragment right before its first DMMA.  128 x 40 + 256 x 232 = 64512 <= 65536.
+constexpr int PP_THREADS_BIG = (PP_CONSUMERS + 4) * 32;
 
 // ---------------------------------------------------------------------------------------------------------------------
 // Bp (tile-packed, one auxiliary row contiguous) -> Bc (partner-compacted, 128 auxiliary rows contiguous).  One-off per
@@ -139,9 +144,9 @@ __device__ __forceinline__ void pp_slab_mn(double (&acc)[MTW][NT][2], const doub
 //           11 tiles instead of 12 on the busiest sub-partition).
 // WITH_V: the epilogue also leaves the item's share of the Coulomb vector V (a separate instantiation: the block costs
 //         registers the NT = 4 kernel does not have to spare).
-template <int NT, int LAYOUT, bool WITH_V>
-// 9 warps are allocated like 12 (register file granularity of 4 warps): 168 registers per thread is the cap
-__global__ void __launch_bounds__(PP_THREADS, 1) k_pp_half_transform(PPParams prm) {
+template <int NT, int LAYOUT, bool WITH_V, bool BIGREG>
+// 9 warps are allocated like 12 (register file granularity of 4 warps): 168 registers per thread is the cap at launch
+__global__ void __launch_bounds__(BIGREG ? PP_THREADS_BIG : PP_THREADS, 1) k_pp_half_transform(PPParams prm) {
     constexpr int MTW = LAYOUT ? 2 : 8;             // 8-row DMMA tiles per warp
     constexpr int NI = LAYOUT ? 8 * NT : 32 * NT;   // orbitals per item
     constexpr int LDC = NI + 4;  // = 4 (or 12) mod 16 doubles: the b fragment rows t = 0..3 fall on distinct bank quads
@@ -164,7 +169,11 @@ __global__ void __launch_bounds__(PP_THREADS, 1) k_pp_half_transform(PPParams pr
 
     const int chunks = prm.chunks, n_nt = prm.n_nt;
 
-    if (warp == PP_CONSUMERS) {
+    if (warp >= PP_CONSUMERS) {
+        if constexpr (BIGREG) {
+            asm volatile("setmaxnreg.dec.sync.aligned.u32 40;");  // all four warps of the producer's warpgroup
+            if (warp > PP_CONSUMERS) return;
+        }
         // ------------------------------------------------ producer warp ------------------------------------------------
         PipeState pp;
         for (int j = prm.item_off[blockIdx.x]; j < prm.item_off[blockIdx.x + 1]; j++) {
@@ -196,6 +205,7 @@ __global__ void __launch_bounds__(PP_THREADS, 1) k_pp_half_transform(PPParams pr
     }
 
     // --------------------------------------------------- consumers ---------------------------------------------------
+    if constexpr (BIGREG) asm volatile("setmaxnreg.inc.sync.aligned.u32 232;");
     PipeState ps;
     const int g = lane >> 2, t = lane & 3;
     const int m0 = LAYOUT ? warp * 16 : (warp >> 2) * 64;
@@ -694,16 +704,22 @@ static size_t pp_smem_bytes(int ni) {
     return (size_t)PP_NSTAGE * (PP_KS * PP_QC + PP_KS * (ni + 4)) * 8 + 2 * PP_NSTAGE * 8 + 16;
 }
 
+template <int NT, int LAYOUT, bool WITH_V, bool BIGREG>
+static void launch_pp_k(const PPParams& prm, int grid, size_t smem, cudaStream_t st) {
+    cudaFuncSetAttribute(k_pp_half_transform<NT, LAYOUT, WITH_V, BIGREG>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+    k_pp_half_transform<NT, LAYOUT, WITH_V, BIGREG><<<grid, BIGREG ? PP_THREADS_BIG : PP_THREADS, smem, st>>>(prm);
+}
+
 template <int NT, int LAYOUT>
-static void launch_pp_t(const PPParams& prm, int grid, cudaStream_t st) {
+static void launch_pp_t(const PPParams& prm, int grid, bool bigreg, cudaStream_t st) {
     const size_t smem = pp_smem_bytes(LAYOUT ? 8 * NT : 32 * NT);
     if (prm.vitem != nullptr) {
         cudaMemsetAsync(prm.vitem, 0, sizeof(double) * (size_t)grid * prm.chunks * (LAYOUT ? 1 : 4) * PP_QC, st);  // the slots are summed into
-        cudaFuncSetAttribute(k_pp_half_transform<NT, LAYOUT, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
-        k_pp_half_transform<NT, LAYOUT, true><<<grid, PP_THREADS, smem, st>>>(prm);
+        if (bigreg) launch_pp_k<NT, LAYOUT, true, true>(prm, grid, smem, st);
+        else launch_pp_k<NT, LAYOUT, true, false>(prm, grid, smem, st);
     } else {
-        cudaFuncSetAttribute(k_pp_half_transform<NT, LAYOUT, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
-        k_pp_half_transform<NT, LAYOUT, false><<<grid, PP_THREADS, smem, st>>>(prm);
+        if (bigreg) launch_pp_k<NT, LAYOUT, false, true>(prm, grid, smem, st);
+        else launch_pp_k<NT, LAYOUT, false, false>(prm, grid, smem, st);
     }
 }
 
@@ -794,7 +810,7 @@ void launch_pp_prep(const Layout& L, Shard& s, int64_t ldc) {
     k_pp_prep<<<blocks, 256, 0, s.stream>>>(s.Craw, ldc, s.Ci, (int)L.N, (int)L.occ, L.n_pad + 1, ldci, s.d_inv);
 }
 
-void launch_pp_half_transform(const Layout& L, Shard& s, int sm_count, bool v_in_ht) {
+void launch_pp_half_transform(const Layout& L, Shard& s, int sm_count, bool v_in_ht, bool bigreg) {
     PPParams prm;
     prm.Bc = s.Bc;
     prm.Ci = s.Ci;
@@ -817,26 +833,26 @@ void launch_pp_half_transform(const Layout& L, Shard& s, int sm_count, bool v_in
     if (grid <= 0) return;
     if (L.pp_layout == 0) {
         switch (L.pp_nt) {
-            case 1: launch_pp_t<1, 0>(prm, grid, s.stream); break;
-            case 2: launch_pp_t<2, 0>(prm, grid, s.stream); break;
-            case 3: launch_pp_t<3, 0>(prm, grid, s.stream); break;
-            case 4: launch_pp_t<4, 0>(prm, grid, s.stream); break;
+            case 1: launch_pp_t<1, 0>(prm, grid, bigreg, s.stream); break;
+            case 2: launch_pp_t<2, 0>(prm, grid, bigreg, s.stream); break;
+            case 3: launch_pp_t<3, 0>(prm, grid, bigreg, s.stream); break;
+            case 4: launch_pp_t<4, 0>(prm, grid, bigreg, s.stream); break;
             default: break;
         }
     } else {
         switch (L.pp_nt) {
-            case 1: launch_pp_t<1, 1>(prm, grid, s.stream); break;
-            case 2: launch_pp_t<2, 1>(prm, grid, s.stream); break;
-            case 3: launch_pp_t<3, 1>(prm, grid, s.stream); break;
-            case 4: launch_pp_t<4, 1>(prm, grid, s.stream); break;
-            case 5: launch_pp_t<5, 1>(prm, grid, s.stream); break;
-            case 6: launch_pp_t<6, 1>(prm, grid, s.stream); break;
-            case 7: launch_pp_t<7, 1>(prm, grid, s.stream); break;
-            case 8: launch_pp_t<8, 1>(prm, grid, s.stream); break;
-            case 9: launch_pp_t<9, 1>(prm, grid, s.stream); break;
-            case 10: launch_pp_t<10, 1>(prm, grid, s.stream); break;
-            case 11: launch_pp_t<11, 1>(prm, grid, s.stream); break;
-            case 12: launch_pp_t<12, 1>(prm, grid, s.stream); break;
+            case 1: launch_pp_t<1, 1>(prm, grid, bigreg, s.stream); break;
+            case 2: launch_pp_t<2, 1>(prm, grid, bigreg, s.stream); break;
+            case 3: launch_pp_t<3, 1>(prm, grid, bigreg, s.stream); break;
+            case 4: launch_pp_t<4, 1>(prm, grid, bigreg, s.stream); break;
+            case 5: launch_pp_t<5, 1>(prm, grid, bigreg, s.stream); break;
+            case 6: launch_pp_t<6, 1>(prm, grid, bigreg, s.stream); break;
+            case 7: launch_pp_t<7, 1>(prm, grid, bigreg, s.stream); break;
+            case 8: launch_pp_t<8, 1>(prm, grid, bigreg, s.stream); break;
+            case 9: launch_pp_t<9, 1>(prm, grid, bigreg, s.stream); break;
+            case 10: launch_pp_t<10, 1>(prm, grid, bigreg, s.stream); break;
+            case 11: launch_pp_t<11, 1>(prm, grid, bigreg, s.stream); break;
+            case 12: launch_pp_t<12, 1>(prm, grid, bigreg, s.stream); break;
             default: break;
         }
     }

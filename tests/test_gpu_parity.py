@@ -531,3 +531,26 @@ def test_refused_options_leave_the_handle_unchanged():
     gd.set_B(0, reference_layout_rows(B, range(0, Q), mask))
     assert np.abs(gd.fock_build(C_occ, H)[0] - oracle_fock(B, C_occ, H, mask)).max() < TOL
     gd.close()
+
+
+@pytest.mark.parametrize("N,Q,occ,pp_layout", [(180, 300, 130, 0), (96, 129, 81, 1), (333, 257, 40, 0)])
+def test_register_split_variant_is_bit_identical(N, Q, occ, pp_layout):
+    """Per-function half-transform with the setmaxnreg register split (12 warps, default) against the 9-warp kernel at the
+    launch cap: same arithmetic in the same order, so W, V and F agree bit for bit; both match the oracle."""
+    mask = _scattered_mask(N, 19, 1, seed=N + 4)
+    B, C_occ, H = random_inputs(N, Q, occ, seed=N + 9, mask=mask)
+    F_ref = oracle_fock(B, C_occ, H, mask)
+    out = []
+    for bigreg in (1, 0):
+        gd = jc.B200Data(N, Q, occ, 1)
+        gd.set_option("ht_mode", 2)
+        gd.set_option("pp_layout", pp_layout)
+        gd.set_option("pp_bigreg", bigreg)
+        gd.set_mask(jc.ScreeningData(mask, N))
+        gd.set_B(0, reference_layout_rows(B, range(0, Q), mask))
+        F = gd.fock_build(C_occ, H)[0].copy()
+        assert np.abs(F - F_ref).max() < TOL
+        assert np.array_equal(gd.fock_build(C_occ, H)[0], F)
+        out.append(F)
+        gd.close()
+    assert np.array_equal(out[0], out[1])
