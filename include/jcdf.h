@@ -239,7 +239,7 @@ double jcdf_synthetic_value(uint64_t seed, int64_t Q_total, int64_t q_aux, int64
  * "coulomb_pp_fused" (0 = default: two streaming passes; 1 = one cooperative single-pass kernel, measured slower),
  * "exchange_balance" (1 = default: cost-balanced exchange work lists; 0 = round-robin),
  * "pp_order" (work lists of the per-function kernel: 0 = default, a CTA walks its items chunk by chunk; 1 = p-major),
- * "pp_bigreg" (1 = default: the per-function kernel runs 12 warps and moves registers from the producer's warpgroup to the
+ * "pp_bigreg" (1 = default: both half-transform kernels run 12 warps and moves registers from the producer's warpgroup to the
  * consumers with setmaxnreg, 40 / 232 per thread; 0 = 9 warps at the 168-register launch cap),
  * "graph" (1 = default: the kernel sequence of a build, prep .. epilogue, is captured into a CUDA graph on the first build
  * and replayed afterwards; 0 = every kernel launched eagerly).  "regroup", "ht_mode", "pp_layout", "pp_order",

@@ -966,7 +966,7 @@ static int issue_build_kernels(jcdf_handle* h, Shard& s, const BuildSchedule& b)
     if (b.pp_j && !b.v_in_ht) launch_pp_density(L, s);
     JC_CUDA(record_event(s, s.ev[EV_PREP], s.stream));
     if (b.use_pp) launch_pp_half_transform(L, s, h->sm_count, b.v_in_ht, h->opt_pp_bigreg != 0);
-    else launch_half_transform(L, s, h->sm_count);
+    else launch_half_transform(L, s, h->sm_count, h->opt_pp_bigreg != 0);
     JC_CUDA(cudaPeekAtLastError());  // a launch that did not fit fails the build here, not as a wrong Fock matrix
     JC_CUDA(record_event(s, s.ev[EV_W], s.stream));
     launch_exchange(L, s, h->sm_count);

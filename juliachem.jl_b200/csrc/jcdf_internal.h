@@ -182,7 +182,7 @@ namespace jcdf {
 
 // ---- kernel launchers (kernels_k.cu / kernels_j.cu / kernels_misc.cu) ----------------------------------------------
 void launch_prep(const Layout& L, Shard& s, int64_t ldc);
-void launch_half_transform(const Layout& L, Shard& s, int sm_count);
+void launch_half_transform(const Layout& L, Shard& s, int sm_count, bool bigreg);
 void launch_pp_pack(const Layout& L, Shard& s);                        // kernels_pp.cu: Bp -> Bc
 void launch_pp_prep(const Layout& L, Shard& s, int64_t ldc);           // C_occ -> Ci
 void launch_pp_half_transform(const Layout& L, Shard& s, int sm_count, bool v_in_ht, bool bigreg);

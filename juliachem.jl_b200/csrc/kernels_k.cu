@@ -26,6 +26,9 @@ constexpr int CONSUMER_WARPS = 8;
 // fills that sub-partition's register file, so no Coulomb CTA could co-reside.)
 constexpr int CTA_THREADS = CONSUMER_WARPS * 32;
 constexpr int HT_THREADS = CTA_THREADS + 32;  // half-transform: plus one dedicated producer warp (168 registers/thread)
+// register split with setmaxnreg (see kernels_pp.cu): 12 warps, the producer's warpgroup drops to 40 registers per thread and
+// the two consumer warpgroups rise to 232
+constexpr int HT_THREADS_BIG = CTA_THREADS + 128;
 constexpr int MAX_REGS = 208;
 
 // =====================================================================================================================
@@ -153,8 +156,8 @@ __device__ __forceinline__ void ht_slab(double (&acc)[MT / 2][4][2], const doubl
 
 // Launched with HT_THREADS = 288: warp 8 is a dedicated copy producer (its lane 0 runs the whole produce() sequence, as
 // far ahead as the ring allows) and warps 0-7 only compute.
-template <int MT>
-__global__ void __launch_bounds__(HT_THREADS, 1) k_half_transform(HTParams prm) {
+template <int MT, bool BIGREG>
+__global__ void __launch_bounds__(BIGREG ? HT_THREADS_BIG : HT_THREADS, 1) k_half_transform(HTParams prm) {
     constexpr int BM = 8 * MT;
     constexpr int MH = MT / 2;
     constexpr int STAGE_DOUBLES = 32 * BM + 4 * TILE_ELEMS;
@@ -178,8 +181,9 @@ __global__ void __launch_bounds__(HT_THREADS, 1) k_half_transform(HTParams prm) 
     const int nb = prm.nb, n_mt = prm.n_mt;
 
     // ---- producer warp: walks the same (item, stored tile) sequence ahead of the consumers ----
-    if (warp == CONSUMER_WARPS) {
-        if (lane != 0) return;
+    if (warp >= CONSUMER_WARPS) {
+        if constexpr (BIGREG) asm volatile("setmaxnreg.dec.sync.aligned.u32 40;");  // all four warps of this warpgroup
+        if (warp > CONSUMER_WARPS || lane != 0) return;
         PipeState pp;
         for (int64_t item = blockIdx.x; item < prm.n_items; item += gridDim.x) {
             const int mt = (int)(item % n_mt);
@@ -210,6 +214,7 @@ __global__ void __launch_bounds__(HT_THREADS, 1) k_half_transform(HTParams prm) 
     }
 
     // ---------------------------------------------------- consumers ----------------------------------------------------
+    if constexpr (BIGREG) asm volatile("setmaxnreg.inc.sync.aligned.u32 232;");
     PipeState ps;
     const int g = lane >> 2, t = lane & 3;
     const int j = warp & 3;                 // auxiliary row inside the quad
@@ -270,13 +275,18 @@ size_t half_transform_smem_bytes(int bm) {
 }
 
 template <int MT>
-static void launch_ht_t(const HTParams& prm, int grid, cudaStream_t st) {
+static void launch_ht_t(const HTParams& prm, int grid, bool bigreg, cudaStream_t st) {
     size_t smem = half_transform_smem_bytes(8 * MT);
-    cudaFuncSetAttribute(k_half_transform<MT>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
-    k_half_transform<MT><<<grid, HT_THREADS, smem, st>>>(prm);
+    if (bigreg) {
+        cudaFuncSetAttribute(k_half_transform<MT, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+        k_half_transform<MT, true><<<grid, HT_THREADS_BIG, smem, st>>>(prm);
+    } else {
+        cudaFuncSetAttribute(k_half_transform<MT, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+        k_half_transform<MT, false><<<grid, HT_THREADS, smem, st>>>(prm);
+    }
 }
 
-void launch_half_transform(const Layout& L, Shard& s, int sm_count) {
+void launch_half_transform(const Layout& L, Shard& s, int sm_count, bool bigreg) {
     HTParams prm;
     prm.Bp = s.Bp;
     prm.row_len = L.row_len;
@@ -296,14 +306,14 @@ void launch_half_transform(const Layout& L, Shard& s, int sm_count) {
     int grid = (int)std::min<int64_t>(prm.n_items, sm_count);
     if (grid <= 0) return;
     switch (L.bm / 8) {
-        case 2: launch_ht_t<2>(prm, grid, s.stream); break;
-        case 4: launch_ht_t<4>(prm, grid, s.stream); break;
-        case 6: launch_ht_t<6>(prm, grid, s.stream); break;
-        case 8: launch_ht_t<8>(prm, grid, s.stream); break;
-        case 10: launch_ht_t<10>(prm, grid, s.stream); break;
-        case 12: launch_ht_t<12>(prm, grid, s.stream); break;
-        case 14: launch_ht_t<14>(prm, grid, s.stream); break;
-        case 16: launch_ht_t<16>(prm, grid, s.stream); break;
+        case 2: launch_ht_t<2>(prm, grid, bigreg, s.stream); break;
+        case 4: launch_ht_t<4>(prm, grid, bigreg, s.stream); break;
+        case 6: launch_ht_t<6>(prm, grid, bigreg, s.stream); break;
+        case 8: launch_ht_t<8>(prm, grid, bigreg, s.stream); break;
+        case 10: launch_ht_t<10>(prm, grid, bigreg, s.stream); break;
+        case 12: launch_ht_t<12>(prm, grid, bigreg, s.stream); break;
+        case 14: launch_ht_t<14>(prm, grid, bigreg, s.stream); break;
+        case 16: launch_ht_t<16>(prm, grid, bigreg, s.stream); break;
         default: break;
     }
 }

@@ -533,9 +533,10 @@ def test_refused_options_leave_the_handle_unchanged():
     gd.close()
 
 
+@pytest.mark.parametrize("ht_mode", [2, 1])
 @pytest.mark.parametrize("N,Q,occ,pp_layout", [(180, 300, 130, 0), (96, 129, 81, 1), (333, 257, 40, 0)])
-def test_register_split_variant_is_bit_identical(N, Q, occ, pp_layout):
-    """Per-function half-transform with the setmaxnreg register split (12 warps, default) against the 9-warp kernel at the
+def test_register_split_variant_is_bit_identical(N, Q, occ, pp_layout, ht_mode):
+    """Both half-transform kernels with the setmaxnreg register split (12 warps, default) against the 9-warp kernels at the
     launch cap: same arithmetic in the same order, so W, V and F agree bit for bit; both match the oracle."""
     mask = _scattered_mask(N, 19, 1, seed=N + 4)
     B, C_occ, H = random_inputs(N, Q, occ, seed=N + 9, mask=mask)
@@ -543,7 +544,7 @@ def test_register_split_variant_is_bit_identical(N, Q, occ, pp_layout):
     out = []
     for bigreg in (1, 0):
         gd = jc.B200Data(N, Q, occ, 1)
-        gd.set_option("ht_mode", 2)
+        gd.set_option("ht_mode", ht_mode)
         gd.set_option("pp_layout", pp_layout)
         gd.set_option("pp_bigreg", bigreg)
         gd.set_mask(jc.ScreeningData(mask, N))

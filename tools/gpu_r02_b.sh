@@ -19,6 +19,7 @@ b q600_auto --workload w50_q600 --no-e2e
 b benzene --workload benzene_dimer
 b benzene_overlap --workload benzene_dimer --opt coulomb_overlap=1
 b benzene_nograph --workload benzene_dimer --opt graph=0
+b benzene_9warps --workload benzene_dimer --opt pp_bigreg=0
 b c20h42 --workload c20h42
 b c20h42_overlap --workload c20h42 --opt coulomb_overlap=1
 b water --workload water
