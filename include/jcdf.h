@@ -241,6 +241,8 @@ double jcdf_synthetic_value(uint64_t seed, int64_t Q_total, int64_t q_aux, int64
  * "pp_order" (work lists of the per-function kernel: 0 = default, a CTA walks its items chunk by chunk; 1 = p-major),
  * "pp_bigreg" (1 = default: both half-transform kernels run 12 warps and moves registers from the producer's warpgroup to the
  * consumers with setmaxnreg, 40 / 232 per thread; 0 = 9 warps at the 168-register launch cap),
+ * "exchange_producer" (1 = default: the exchange kernel runs 12 warps with a dedicated copy-producer warp and the same register
+ * split; 0 = 8 warps, thread 0 of a DMMA warp also issues the copies),
  * "graph" (1 = default: the kernel sequence of a build, prep .. epilogue, is captured into a CUDA graph on the first build
  * and replayed afterwards; 0 = every kernel launched eagerly).  "regroup", "ht_mode", "pp_layout", "pp_order",
  * "pp_max_bytes", "exchange_slices" and "exchange_balance" must be set before jcdf_set_mask.  A refused call (unknown name, value out of

@@ -952,7 +952,7 @@ struct BuildSchedule {
     uint64_t key(const jcdf_handle* h) const {
         return 1ull | (uint64_t)use_pp << 1 | (uint64_t)pp_j << 2 | (uint64_t)v_in_ht << 3 | (uint64_t)overlap << 4 |
                (uint64_t)add_H << 5 | (uint64_t)(h->opt_coulomb_fused & 3) << 6 | (uint64_t)(h->opt_coulomb_pp_fused & 1) << 8 |
-               (uint64_t)(h->opt_pp_bigreg & 1) << 9;
+               (uint64_t)(h->opt_pp_bigreg & 1) << 9 | (uint64_t)(h->opt_exchange_producer & 1) << 10;
     }
 };
 
@@ -969,7 +969,7 @@ static int issue_build_kernels(jcdf_handle* h, Shard& s, const BuildSchedule& b)
     else launch_half_transform(L, s, h->sm_count, h->opt_pp_bigreg != 0);
     JC_CUDA(cudaPeekAtLastError());  // a launch that did not fit fails the build here, not as a wrong Fock matrix
     JC_CUDA(record_event(s, s.ev[EV_W], s.stream));
-    launch_exchange(L, s, h->sm_count);
+    launch_exchange(L, s, h->sm_count, h->opt_exchange_producer != 0);
     JC_CUDA(cudaPeekAtLastError());
     JC_CUDA(record_event(s, s.ev[EV_K], s.stream));
     // Coulomb sweeps (HBM-bound, 32-40 registers, no dynamic smem).  With coulomb_overlap they go to a second,
@@ -1325,6 +1325,7 @@ int32_t jcdf_set_option(jcdf_handle* h, const char* name, int64_t value) {
         {"exchange_slices", &h->opt_exchange_slices, true, 0, 1 << 20},
         {"pp_order", &h->opt_pp_order, true, 0, 1},
         {"pp_bigreg", &h->opt_pp_bigreg, false, 0, 1},
+        {"exchange_producer", &h->opt_exchange_producer, false, 0, 1},
         {"graph", &h->opt_graph, false, 0, 1},
     };
     for (const Opt& o : opts) {

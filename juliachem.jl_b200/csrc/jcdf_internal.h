@@ -157,6 +157,7 @@ struct jcdf_handle {
     int64_t opt_coulomb_overlap = 0;  // two-pass sweeps on a second stream, concurrent with the tensor-core kernels
     int64_t opt_exchange_slices = 0;   // > 0: that many slices of the exchange contraction index per tile (0 = chosen from the sizes)
     int64_t opt_pp_bigreg = 1;         // per-function kernel: setmaxnreg register split between producer and consumer warpgroups
+    int64_t opt_exchange_producer = 1;  // exchange kernel: dedicated producer warp + setmaxnreg split (0: thread 0 of a DMMA warp produces)
     int64_t opt_pp_order = 0;          // per-function work lists: 0 = chunk-major inside a CTA, 1 = p-major (round-1 order)
     int64_t opt_exchange_balance = 1;  // cost-balanced exchange item lists (0: round-robin in item order)
     int64_t opt_regroup = 1;          // mask-driven regrouping of the basis functions into 32-wide blocks
@@ -191,7 +192,7 @@ void plan_pp_items(const Layout& L, Shard& s, int sm_count, bool p_major, std::v
 void launch_pp_coulomb(const Layout& L, Shard& s, cudaStream_t st, cudaEvent_t ev_v, bool v_in_ht);
 int64_t pp_coulomb_slabs(const Layout& L);
 bool launch_pp_coulomb_fused(const Layout& L, Shard& s, int sm_count, cudaStream_t st);
-void launch_exchange(const Layout& L, Shard& s, int sm_count);
+void launch_exchange(const Layout& L, Shard& s, int sm_count, bool dedicated_producer);
 void launch_coulomb(const Layout& L, Shard& s, int sm_count, cudaStream_t st);
 bool launch_coulomb_fused(const Layout& L, Shard& s, int sm_count, cudaStream_t st);
 void launch_epilogue(const Layout& L, Shard& s, bool add_H);

@@ -474,7 +474,11 @@ __device__ __forceinline__ void x_slab_mt(double (&acc)[8][4][2], const double* 
     }
 }
 
-__global__ void __maxnreg__(MAX_REGS) k_exchange(XParams prm) {
+// DEDICATED = false: 8 warps, thread 0 doubles as the copy producer (it refills a slot only after ALL warps released it, so
+//   warp 0 meets the slowest warp at every stage).  DEDICATED = true: 12 warps with the setmaxnreg register split of the
+//   half-transform kernels — warp 8 only produces, the eight DMMA warps never look at the empty barriers.
+template <bool DEDICATED>
+__device__ __forceinline__ void exchange_body(const XParams& prm) {
     extern __shared__ __align__(128) unsigned char smem_raw[];
     double* stages = reinterpret_cast<double*>(smem_raw);
     uint64_t* full = reinterpret_cast<uint64_t*>(stages + (size_t)NSTAGE * X_STAGE_DOUBLES);
@@ -493,7 +497,7 @@ __global__ void __maxnreg__(MAX_REGS) k_exchange(XParams prm) {
 
     const long long t_begin = clock64();
     const int npt64 = prm.npt64;
-    const bool is_producer = (threadIdx.x == 0);
+    const bool is_producer = DEDICATED ? (threadIdx.x == CTA_THREADS) : (threadIdx.x == 0);
     const int j_begin = prm.item_off[blockIdx.x], j_end = prm.item_off[blockIdx.x + 1];
 
     auto decode = [&](int item, int& ta, int& tb, int& kc0, int& kc1) {
@@ -531,8 +535,18 @@ __global__ void __maxnreg__(MAX_REGS) k_exchange(XParams prm) {
         pp.advance<NSTAGE>();
         p_kc++;
     };
-    if (is_producer)
-        for (int s = 0; s < NSTAGE - 1; s++) produce();
+    if constexpr (DEDICATED) {
+        if (warp >= CONSUMER_WARPS) {
+            asm volatile("setmaxnreg.dec.sync.aligned.u32 40;");  // all four warps of the producer's warpgroup
+            if (is_producer)
+                while (p_j < j_end) produce();
+            return;
+        }
+        asm volatile("setmaxnreg.inc.sync.aligned.u32 232;");
+    } else {
+        if (is_producer)
+            for (int s = 0; s < NSTAGE - 1; s++) produce();
+    }
 
     PipeState ps;
     const int g = lane >> 2, t = lane & 3;
@@ -560,8 +574,10 @@ __global__ void __maxnreg__(MAX_REGS) k_exchange(XParams prm) {
             // stage times to land.  (Also tried: register double-buffering of the fragments across k-steps and stage
             // boundaries — 244 registers, 3 % slower; the two warps per sub-partition already cover each other's bubbles.)
             // Also tried: cp.async.bulk.prefetch.L2 of the chunk four stages beyond the ring — 6 % slower.
-            if (is_producer) produce();
-            __syncwarp();
+            if constexpr (!DEDICATED) {
+                if (is_producer) produce();
+                __syncwarp();
+            }
             const double* sA = stages + (size_t)ps.stage * X_STAGE_DOUBLES + a_off;
             const double* sB = stages + (size_t)ps.stage * X_STAGE_DOUBLES + b_off;
             if (whole) x_slab<8, 4>(acc, sA, sB, g, t);
@@ -591,9 +607,12 @@ __global__ void __maxnreg__(MAX_REGS) k_exchange(XParams prm) {
     if (threadIdx.x == 0) prm.cta_cycles[blockIdx.x] = clock64() - t_begin;
 }
 
+__global__ void __maxnreg__(MAX_REGS) k_exchange(XParams prm) { exchange_body<false>(prm); }
+__global__ void __launch_bounds__(HT_THREADS_BIG, 1) k_exchange_ws(XParams prm) { exchange_body<true>(prm); }
+
 size_t exchange_smem_bytes() { return (size_t)NSTAGE * X_STAGE_DOUBLES * 8 + 2 * NSTAGE * 8 + 16; }
 
-void launch_exchange(const Layout& L, Shard& s, int sm_count) {
+void launch_exchange(const Layout& L, Shard& s, int sm_count, bool dedicated_producer) {
     XParams prm;
     prm.W = s.W;
     prm.Kpart = s.Kpart;
@@ -609,8 +628,13 @@ void launch_exchange(const Layout& L, Shard& s, int sm_count) {
     const int grid = s.xplan.n_ctas;
     if (grid <= 0) return;
     size_t smem = exchange_smem_bytes();
-    cudaFuncSetAttribute(k_exchange, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
-    k_exchange<<<grid, CTA_THREADS, smem, s.stream>>>(prm);
+    if (dedicated_producer) {
+        cudaFuncSetAttribute(k_exchange_ws, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+        k_exchange_ws<<<grid, HT_THREADS_BIG, smem, s.stream>>>(prm);
+    } else {
+        cudaFuncSetAttribute(k_exchange, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+        k_exchange<<<grid, CTA_THREADS, smem, s.stream>>>(prm);
+    }
 }
 
 // =====================================================================================================================

@@ -547,6 +547,7 @@ def test_register_split_variant_is_bit_identical(N, Q, occ, pp_layout, ht_mode):
         gd.set_option("ht_mode", ht_mode)
         gd.set_option("pp_layout", pp_layout)
         gd.set_option("pp_bigreg", bigreg)
+        gd.set_option("exchange_producer", bigreg)  # the exchange kernel's dedicated-producer variant likewise
         gd.set_mask(jc.ScreeningData(mask, N))
         gd.set_B(0, reference_layout_rows(B, range(0, Q), mask))
         F = gd.fock_build(C_occ, H)[0].copy()

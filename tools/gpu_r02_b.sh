@@ -13,6 +13,7 @@ b w50_default
 b w50_pmajor --opt pp_order=1
 b w50_nograph --opt graph=0
 b w50_9warps --opt pp_bigreg=0
+b w50_xinwarp --opt exchange_producer=0
 b c20h42_9warps --workload c20h42 --opt pp_bigreg=0
 for s in 24 33 48 64; do b q600_s$s --workload w50_q600 --no-e2e --opt exchange_slices=$s; done
 b q600_auto --workload w50_q600 --no-e2e

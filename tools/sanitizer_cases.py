@@ -21,7 +21,7 @@ CASES = [
     ("tiles_fused_coulomb", 70, 40, 9, {"ht_mode": 1, "coulomb_fused": 1}),
     ("tiles_two_pass_coulomb", 70, 40, 41, {"ht_mode": 1, "coulomb_fused": 0}),
     ("pp_2x4_v_in_ht", 96, 140, 40, {"ht_mode": 2, "coulomb_pp_fused": 0, "coulomb_v_in_ht": 1}),
-    ("pp_2x4_v_in_ht_9_warps", 96, 140, 40, {"ht_mode": 2, "coulomb_pp_fused": 0, "coulomb_v_in_ht": 1, "pp_bigreg": 0}),
+    ("pp_2x4_v_in_ht_9_warps", 96, 140, 40, {"ht_mode": 2, "coulomb_pp_fused": 0, "coulomb_v_in_ht": 1, "pp_bigreg": 0, "exchange_producer": 0}),
     ("pp_2x4_density_v_pass", 96, 140, 40, {"ht_mode": 2, "coulomb_pp_fused": 0, "coulomb_v_in_ht": 0}),
     ("pp_8x1_v_in_ht", 96, 129, 81, {"ht_mode": 2, "coulomb_pp_fused": 0, "pp_layout": 1}),
     ("pp_coulomb_cooperative", 96, 140, 24, {"ht_mode": 2, "coulomb_pp_fused": 1}),
