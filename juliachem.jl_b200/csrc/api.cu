@@ -513,6 +513,7 @@ int32_t jcdf_create(int64_t N, int64_t Q, int64_t occ, int32_t ndev, const int32
         if (e == cudaSuccess) e = cudaStreamCreateWithPriority(&s.stream, cudaStreamNonBlocking, prio_hi);
         if (e == cudaSuccess) e = cudaStreamCreateWithPriority(&s.stream_j, cudaStreamNonBlocking, prio_lo);
         for (int i = 0; i < EV_COUNT && e == cudaSuccess; i++) e = cudaEventCreate(&s.ev[i]);
+        for (int i = 0; i < 3 && e == cudaSuccess; i++) e = cudaEventCreateWithFlags(&s.ev_dep[i], cudaEventDisableTiming);
         if (e != cudaSuccess) {
             set_error(std::string("jcdf_create: ") + cudaGetErrorString(e));
             delete h;
@@ -546,6 +547,8 @@ int32_t jcdf_destroy(jcdf_handle* h) {
         free_shard_buffers(s);
         for (int i = 0; i < EV_COUNT; i++)
             if (s.ev[i]) cudaEventDestroy(s.ev[i]);
+        for (int i = 0; i < 3; i++)
+            if (s.ev_dep[i]) cudaEventDestroy(s.ev_dep[i]);
         if (s.stream_j) cudaStreamDestroy(s.stream_j);
         if (s.stream) cudaStreamDestroy(s.stream);
     }
@@ -965,25 +968,32 @@ static int issue_build_kernels(jcdf_handle* h, Shard& s, const BuildSchedule& b)
     // V = sum_p sum_i C[p,i] W[Q,i,p] comes out of the half-transform's accumulators: no density, no V sweep
     if (b.pp_j && !b.v_in_ht) launch_pp_density(L, s);
     JC_CUDA(record_event(s, s.ev[EV_PREP], s.stream));
+    if (b.overlap) JC_CUDA(cudaEventRecord(s.ev_dep[0], s.stream));
     if (b.use_pp) launch_pp_half_transform(L, s, h->sm_count, b.v_in_ht, h->opt_pp_bigreg != 0);
     else launch_half_transform(L, s, h->sm_count, h->opt_pp_bigreg != 0);
     JC_CUDA(cudaPeekAtLastError());  // a launch that did not fit fails the build here, not as a wrong Fock matrix
     JC_CUDA(record_event(s, s.ev[EV_W], s.stream));
+    if (b.overlap) JC_CUDA(cudaEventRecord(s.ev_dep[1], s.stream));
     launch_exchange(L, s, h->sm_count, h->opt_exchange_producer != 0);
     JC_CUDA(cudaPeekAtLastError());
     JC_CUDA(record_event(s, s.ev[EV_K], s.stream));
     // Coulomb sweeps (HBM-bound, 32-40 registers, no dynamic smem).  With coulomb_overlap they go to a second,
     // lower-priority stream: their CTAs co-reside with the persistent tensor-core CTAs (one per SM, compute-bound,
     // issue slots ~16 % busy) and soak up the idle HBM bandwidth instead of queueing behind them.
+    // (fork / join through dedicated dependency events: plain records, which a capture turns into graph edges)
     cudaStream_t sj = b.overlap ? s.stream_j : s.stream;
-    if (b.overlap) JC_CUDA(cudaStreamWaitEvent(sj, s.ev[EV_PREP], 0));
+    if (b.overlap) {
+        // the fork point is after the half-transform when it leaves the Coulomb partials, after the prep kernels otherwise:
+        // recorded here, i.e. after the exchange launch, it would serialise the two streams, so the events are recorded
+        // at their places above (dep[0] after prep, dep[1] after the half-transform)
+        JC_CUDA(cudaStreamWaitEvent(sj, s.ev_dep[b.pp_j && b.v_in_ht ? 1 : 0], 0));
+    }
     JC_CUDA(record_event(s, s.ev[EV_JBEGIN], sj));
     JC_CUDA(record_event(s, s.ev[EV_V], sj));  // two-pass: overwritten at the V | J boundary; fused: V time reads 0
     if (b.pp_j) {
         s.last_coulomb_fused = false;
         s.last_ppj_fused = h->opt_coulomb_pp_fused && launch_pp_coulomb_fused(L, s, h->sm_count, sj);
         if (!s.last_ppj_fused) {
-            if (b.v_in_ht && b.overlap) JC_CUDA(cudaStreamWaitEvent(sj, s.ev[EV_W], 0));  // the partials come from the half-transform
             launch_pp_coulomb(L, s, sj, s.ev[EV_V], b.v_in_ht);
         }
     } else {
@@ -998,7 +1008,10 @@ static int issue_build_kernels(jcdf_handle* h, Shard& s, const BuildSchedule& b)
     s.last_pp_j = b.pp_j;
     s.last_v_in_ht = b.v_in_ht && !s.last_ppj_fused;
     JC_CUDA(record_event(s, s.ev[EV_J], sj));
-    if (b.overlap) JC_CUDA(cudaStreamWaitEvent(s.stream, s.ev[EV_J], 0));
+    if (b.overlap) {
+        JC_CUDA(cudaEventRecord(s.ev_dep[2], sj));
+        JC_CUDA(cudaStreamWaitEvent(s.stream, s.ev_dep[2], 0));
+    }
     launch_epilogue(L, s, b.add_H);
     JC_CUDA(record_event(s, s.ev[EV_EPI], s.stream));
     JC_CUDA(cudaGetLastError());
@@ -1008,8 +1021,7 @@ static int issue_build_kernels(jcdf_handle* h, Shard& s, const BuildSchedule& b)
 // Replays the shard's graph of issue_build_kernels, capturing it first when there is none for this schedule.  Any failure
 // of capture / instantiation marks the shard and the build is launched eagerly instead (same kernels, same order).
 static int run_build_kernels(jcdf_handle* h, Shard& s, const BuildSchedule& b) {
-    // the second-stream variant forks and joins through the timing events themselves: launched eagerly
-    const bool want_graph = h->opt_graph && !s.graph_broken && !b.overlap;
+    const bool want_graph = h->opt_graph && !s.graph_broken;
     if (!want_graph) return issue_build_kernels(h, s, b);
     const uint64_t key = b.key(h);
     if (s.gexec == nullptr || s.gkey != key) {

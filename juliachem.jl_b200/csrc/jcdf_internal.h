@@ -128,6 +128,7 @@ struct Shard {
     bool t_uploaded = false;
     ExchangePlan xplan;
     cudaEvent_t ev[EV_COUNT] = {};
+    cudaEvent_t ev_dep[3] = {};    // fork (after prep / after the half-transform) and join of the Coulomb stream (coulomb_overlap)
     // CUDA graph of the per-build kernel sequence (prep .. epilogue): captured on the first build, replayed afterwards
     cudaGraphExec_t gexec = nullptr;
     uint64_t gkey = 0;             // schedule the graph was captured for (family, Coulomb variant, H add)
