@@ -689,6 +689,7 @@ int32_t jcdf_set_mask(jcdf_handle* h, const uint8_t* fn_mask, const int64_t* map
             L.src_of_col[(size_t)col] = L.dest_of_col[(size_t)col];
         }
     build_partner_lists(h, [&](int64_t ri, int64_t ci) { return kept(ri, ci); });
+    const bool pp_wanted = L.pp_enabled;
     L.mask_set = true;
     integrals_on_set_mask(h);
     for (Shard& s : h->shards) {
@@ -698,6 +699,18 @@ int32_t jcdf_set_mask(jcdf_handle* h, const uint8_t* fn_mask, const int64_t* map
             JC_CUDA(cudaSetDevice(s.dev));
             if ((rc = dev_alloc(&s.d_fn_mask, (size_t)N * N))) return rc;
             JC_CUDA(cudaMemcpy(s.d_fn_mask, fn_mask, (size_t)N * N, cudaMemcpyHostToDevice));
+        }
+    }
+    if (pp_wanted && !L.pp_enabled) {
+        // the compact copy did not fit on some shard and every shard falls back to the tile family: give back what the
+        // shards allocated before that one (up to 7.9 GB each at w50)
+        for (Shard& s : h->shards) {
+            cudaSetDevice(s.dev);
+            void** ptrs[] = {(void**)&s.Bc, (void**)&s.Ci, (void**)&s.Vitem, (void**)&s.Jpart, (void**)&s.VpartP, (void**)&s.dvec,
+                             (void**)&s.ppj_vp, (void**)&s.d_ppitems, (void**)&s.d_ppoff};
+            for (void** q : ptrs)
+                if (*q) { cudaFree(*q); *q = nullptr; }
+            s.pp_ctas = 0;
         }
     }
     return JCDF_OK;

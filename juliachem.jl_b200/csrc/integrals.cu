@@ -806,10 +806,15 @@ int32_t jcdf_compute_B(jcdf_handle* h) {
         // ---- B_g += Linv[Q_g, chunk] T_chunk over the rows h < q_begin + q_len ----
         const int64_t q_end = s.q_begin + s.q_len;
         int64_t R = std::max<int64_t>(32, std::min<int64_t>(q_end, ((int64_t)3 << 27) / std::max<int64_t>(L.row_len, 1)));  // <= 3 GiB
-        double* T = nullptr;
-        JC_CUDA(cudaMalloc(reinterpret_cast<void**>(&T), sizeof(double) * (size_t)R * (size_t)L.row_len));
-        cublasHandle_t blas = nullptr;
-        JC_CUBLAS(cublasCreate(&blas));
+        struct Scratch {  // released on every exit path
+            double* T = nullptr;
+            cublasHandle_t blas = nullptr;
+            ~Scratch() { if (blas) cublasDestroy(blas); if (T) cudaFree(T); }
+        } sc;
+        JC_CUDA(cudaMalloc(reinterpret_cast<void**>(&sc.T), sizeof(double) * (size_t)R * (size_t)L.row_len));
+        double* const T = sc.T;
+        JC_CUBLAS(cublasCreate(&sc.blas));
+        cublasHandle_t blas = sc.blas;
         JC_CUBLAS(cublasSetStream(blas, s.stream));
         bool first = true;
         for (int64_t h0 = 0; h0 < q_end; h0 += R) {
@@ -829,8 +834,6 @@ int32_t jcdf_compute_B(jcdf_handle* h) {
             first = false;
         }
         JC_CUDA(cudaStreamSynchronize(s.stream));
-        cublasDestroy(blas);
-        cudaFree(T);
         s.t_uploaded = false;
         s.b_ready = true;
         s.bc_valid = false;
