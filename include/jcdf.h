@@ -243,6 +243,10 @@ double jcdf_synthetic_value(uint64_t seed, int64_t Q_total, int64_t q_aux, int64
  * consumers with setmaxnreg, 40 / 232 per thread; 0 = 9 warps at the 168-register launch cap),
  * "exchange_producer" (1 = default: the exchange kernel runs 12 warps with a dedicated copy-producer warp and the same register
  * split; 0 = 8 warps, thread 0 of a DMMA warp also issues the copies),
+ * "register_output" (0 = default; 1 = a host F_out that arrives twice in a row is page-locked in place with
+ * cudaHostRegister until it changes or the handle is destroyed — scf_data.two_electron_fock is a pageable Julia Array, and
+ * a copy into pageable memory runs at a fraction of the PCIe rate.  Opt-in: the caller must keep that buffer alive until
+ * jcdf_destroy; julia/B200DF.jl holds a reference to it inside SCFGPUDataB200 for exactly that reason),
  * "graph" (1 = default: the kernel sequence of a build, prep .. epilogue, is captured into a CUDA graph on the first build
  * and replayed afterwards; 0 = every kernel launched eagerly).  "regroup", "ht_mode", "pp_layout", "pp_order",
  * "pp_max_bytes", "exchange_slices" and "exchange_balance" must be set before jcdf_set_mask.  A refused call (unknown name, value out of

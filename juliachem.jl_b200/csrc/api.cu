@@ -540,6 +540,11 @@ int32_t jcdf_destroy(jcdf_handle* h) {
     integrals_destroy(h);
     delete h->eigh;
     h->eigh = nullptr;
+    if (h->fout_registered) {
+        cudaHostUnregister(h->fout_registered);
+        cudaGetLastError();
+        h->fout_registered = nullptr;
+    }
     for (Shard& s : h->shards) {
         cudaSetDevice(s.dev);
         if (s.stream) cudaStreamSynchronize(s.stream);
@@ -1112,8 +1117,28 @@ int fock_build_impl(jcdf_handle* h, const double* C_occ, int64_t ldc, const doub
     const bool owns_rank0 = (h->rank == 0);
     const bool reduce = (h->n_ranks * nd > 1);
     if (reduce && (rc = check_global_coverage(h))) return rc;
-    auto t0 = std::chrono::steady_clock::now();
     const size_t nn = (size_t)L.N * L.N;
+    if (!device_ptrs && h->opt_register_output) {
+        // The reference hands over scf_data.two_electron_fock, a pageable Julia Array that lives as long as the SCF
+        // (DensityFitting.jl:45): a device-to-host copy into pageable memory is staged by the driver at a fraction of the
+        // PCIe rate.  Once the same pointer arrives a second time it is page-locked in place (cudaHostRegister) and stays so
+        // until another buffer shows up or the handle is destroyed.  Already pinned or managed memory is left alone;
+        // a refusal is not an error.  (C_occ is a fresh slice every iteration, DensityFitting.jl:49 — not worth registering.)
+        if (h->fout_registered && h->fout_registered != (void*)F_out) {
+            cudaHostUnregister(h->fout_registered);
+            cudaGetLastError();
+            h->fout_registered = nullptr;
+        }
+        if (!h->fout_registered && h->fout_seen == (const void*)F_out) {
+            cudaPointerAttributes at;
+            if (cudaPointerGetAttributes(&at, F_out) == cudaSuccess && at.type == cudaMemoryTypeUnregistered &&
+                cudaHostRegister(F_out, sizeof(double) * nn, cudaHostRegisterPortable) == cudaSuccess)
+                h->fout_registered = F_out;
+            cudaGetLastError();
+        }
+        h->fout_seen = F_out;
+    }
+    auto t0 = std::chrono::steady_clock::now();
 
     for (int d = 0; d < nd; d++) {
         Shard& s = h->shards[d];
@@ -1352,6 +1377,7 @@ int32_t jcdf_set_option(jcdf_handle* h, const char* name, int64_t value) {
         {"pp_bigreg", &h->opt_pp_bigreg, false, 0, 1},
         {"exchange_producer", &h->opt_exchange_producer, false, 0, 1},
         {"graph", &h->opt_graph, false, 0, 1},
+        {"register_output", &h->opt_register_output, false, 0, 1},
     };
     for (const Opt& o : opts) {
         if (n != o.name) continue;

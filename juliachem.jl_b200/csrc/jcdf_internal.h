@@ -171,6 +171,10 @@ struct jcdf_handle {
     int64_t opt_ht_mode = 0;          // half-transform: 0 = choose from the mask, 1 = tile kernel, 2 = per-function kernel
     int64_t opt_graph = 1;            // replay the per-build launch sequence as a CUDA graph (device-pointer builds)
     bool graph_dirty = true;          // options / operands changed since the capture
+    int64_t opt_register_output = 0;  // 1: page-lock the caller's F_out once it has been seen twice (a Julia Array is pageable);
+                                      // opt-in, because the caller must keep that buffer alive until jcdf_destroy
+    const void* fout_seen = nullptr;  // F_out of the previous host-pointer build
+    void* fout_registered = nullptr;  // range this handle registered with cudaHostRegister (released by jcdf_destroy)
     double last_host_launch_ms = 0.0;  // host time the last build spent issuing work before the collective
     bool coverage_checked = false;    // the shards of all ranks were seen to cover Q exactly once
     jcdf::ScfState* scf = nullptr;    // on-device SCF driver state (jcdf_scf_*), owned

@@ -27,8 +27,9 @@ const JCDF_STAGE_KEYS = (JCTC.W_time, JCTC.K_time, JCTC.V_time, JCTC.J_time, JCT
 mutable struct SCFGPUDataB200 <: SCFGPUData
     handle::Ptr{Cvoid}
     number_of_devices_used::Int
+    pinned_fock::Any   # scf_data.two_electron_fock, page-locked by the library ("register_output"): kept alive until the finalizer
     function SCFGPUDataB200()
-        d = new(C_NULL, 0)
+        d = new(C_NULL, 0, nothing)
         finalizer(d) do x   # device memory lives exactly as long as scf_data
             x.handle == C_NULL || ccall((:jcdf_destroy, libjcdf), Cint, (Ptr{Cvoid},), x.handle)
             x.handle = C_NULL
@@ -188,6 +189,10 @@ function df_rhf_fock_build_B200!(scf_data, jeri_engine_thread_df::Vector{T}, jer
             setup_device_integrals_B200!(gd, scf_data, basis_sets, scf_options, n_ranks, rank, comm)
         end
         jcdf_check(ccall((:jcdf_set_core_hamiltonian, libjcdf), Cint, (Ptr{Cvoid}, Ptr{Float64}), gd.handle, H))
+        # two_electron_fock is allocated once per SCF (DensityFitting.jl:45) and is pageable: let the library page-lock it in
+        # place after its second use; the reference held here keeps it alive until the handle is destroyed
+        gd.pinned_fock = scf_data.two_electron_fock
+        jcdf_check(ccall((:jcdf_set_option, libjcdf), Cint, (Ptr{Cvoid}, Cstring, Int64), gd.handle, "register_output", Int64(1)))
     end
 
     # every iteration: one call.  F_out is scf_data.two_electron_fock (caller-owned; DIIS mutates it afterwards).  The

@@ -556,3 +556,28 @@ def test_register_split_variant_is_bit_identical(N, Q, occ, pp_layout, ht_mode):
         out.append(F)
         gd.close()
     assert np.array_equal(out[0], out[1])
+
+
+def test_registered_output_buffer():
+    """register_output = 1 (what julia/B200DF.jl sets): a pageable F_out that arrives twice is page-locked in place; results
+    are unchanged, a different buffer afterwards works, and destroy releases the registration while the array is alive."""
+    N, Q, occ = 160, 64, 16
+    mask = banded_mask(N, 33, seed=N)
+    B, C_occ, H = random_inputs(N, Q, occ, seed=N + 1, mask=mask)
+    F_ref = oracle_fock(B, C_occ, H, mask)
+    gd = jc.B200Data(N, Q, occ, 1)
+    gd.set_option("register_output", 1)
+    gd.set_mask(jc.ScreeningData(mask, N))
+    gd.set_B(0, reference_layout_rows(B, range(0, Q), mask))
+    F = np.empty((N, N), order="F")
+    for _ in range(4):  # the second call registers the buffer
+        F[:] = 0.0
+        gd.fock_build(C_occ, H, F)
+        assert np.abs(F - F_ref).max() < TOL
+    G = np.empty((N, N), order="F")
+    gd.fock_build(C_occ, H, G)
+    gd.fock_build(C_occ, H, G)
+    assert np.array_equal(F, G)
+    gd.close()
+    F[:] = 1.0  # still ordinary memory
+    assert F.sum() == N * N
