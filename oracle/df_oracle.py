@@ -156,6 +156,45 @@ def exchange_block_layout(N: int, df_exchange_n_blocks: int = 0, default_n_block
     return n_blocks, width, batch
 
 
+def exchange_block_screen_matrix(fn_mask: np.ndarray, n_blocks: int, width: int, batch, df_screen_exchange: bool):
+    """Second half of a7 (ScreenedDF.jl:425-456): blocks_to_calculate (0-based positions in `batch`) and the Bool
+    block_screen_matrix.  With df_exchange_screen a lower-triangular block (pp, qq) is kept iff its width x width
+    sub-block of basis_function_screen_matrix holds any kept pair (:433-441); without it every block is kept (:443-446)."""
+    block_screen = np.zeros((n_blocks, n_blocks), dtype=bool)
+    todo = []
+    for idx, (pp, qq) in enumerate(batch):
+        keep = True
+        if df_screen_exchange:
+            keep = bool(fn_mask[(pp - 1) * width:pp * width, (qq - 1) * width:qq * width].sum() != 0)
+        if keep:
+            todo.append(idx)
+            block_screen[pp - 1, qq - 1] = True
+    return todo, block_screen
+
+
+def calculate_K_lower_diagonal_block(W: np.ndarray, fock: np.ndarray, n_blocks: int, width: int, batch, blocks_to_calculate):
+    """ScreenedDF.jl:459-545 (df_exchange_screen = true): like the no-screen variant, but ONLY the blocks in
+    blocks_to_calculate are computed and written (:494-510).  The GEMM's beta = 0 write is the only thing that ever
+    overwrites scf_data.two_electron_fock, so a dropped block keeps whatever the matrix held — after the first iteration
+    that is the previous iteration's F (H, J, K and all), onto which calculate_coulomb_screened then adds the new J.
+    libjcdf refuses the option for that reason; this restatement exists to show the behaviour in a test."""
+    Q, occ, N = W.shape
+    Wv = W.reshape((Q * occ, N), order="F")
+    for idx in blocks_to_calculate:
+        bp, bq = batch[idx]
+        ps, qs = (bp - 1) * width, (bq - 1) * width
+        blk = sblas.dgemm(-1.0, Wv[:, ps:ps + width], Wv[:, qs:qs + width], trans_a=1)
+        fock[ps:ps + width, qs:qs + width] = blk
+        if bp != bq:
+            fock[qs:qs + width, ps:ps + width] = blk.T
+    if N % n_blocks == 0:
+        return
+    q0 = N - (N % n_blocks)
+    strip = sblas.dgemm(-1.0, Wv, Wv[:, q0:], trans_a=1)  # the remainder strip is never screened (:519-544)
+    fock[:, q0:] = strip
+    fock[q0:, :] = strip.T
+
+
 # --------------------------------------------------------------------------------------------------------------
 # a4  B formation (DensityFitting.jl:137-152 / ScreenedDF.jl:92-103)
 # --------------------------------------------------------------------------------------------------------------

@@ -103,3 +103,39 @@ def test_slab_sum_of_the_threaded_build_is_the_whole_build():
     assert np.abs(F - _einsum_fock(B, C_occ, H)).max() < 1e-11
     assert np.abs(F - (orc.fock_build_screened_rank_threaded(Bs, C_occ, sd, 3) + H)).max() < 1e-11
     assert set(tm) == {"W", "K", "J"}
+
+
+def test_block_screened_exchange_of_the_reference_depends_on_the_iteration_history():
+    """Row a7 with df_exchange_screen = true (ScreenedDF.jl:433-449, 459-545), restated: the blocks whose mask sub-block is
+    empty are neither computed NOR written, so two_electron_fock keeps its previous content there and the new J is added on
+    top.  The same (B, C) therefore gives different Fock matrices depending on what the buffer held — which is why libjcdf
+    refuses the option instead of reproducing it."""
+    N, Q, occ = 120, 16, 7
+    mask = banded_mask(N, 18, seed=3, speckle=False)
+    B, C_occ, H = random_inputs(N, Q, occ, seed=4, mask=mask)
+    sd = orc.ScreeningData(mask)
+    Bs = orc.dense_to_screened(B, sd)
+    n_blocks, width, batch = orc.exchange_block_layout(N, 10, 10)
+    todo, block_screen = orc.exchange_block_screen_matrix(mask, n_blocks, width, batch, True)
+    assert 0 < len(todo) < len(batch) and not block_screen[n_blocks - 1, 0]
+    todo_all, _ = orc.exchange_block_screen_matrix(mask, n_blocks, width, batch, False)
+    assert todo_all == list(range(len(batch)))
+    C_T = np.asfortranarray(C_occ.T)
+    W = orc.calculate_W_screened(Bs, C_T, sd)
+
+    def build(fock):
+        orc.calculate_K_lower_diagonal_block(W, fock, n_blocks, width, batch, todo)
+        orc.calculate_coulomb_screened(Bs, C_T, sd, fock)
+        return fock
+
+    first = build(np.zeros((N, N), order="F"))           # iteration 1: the buffer starts as zeros (DensityFitting.jl:45)
+    stale = np.asfortranarray(first + H)                  # what the buffer holds when iteration 2 starts (F .+= H, :62-65)
+    second = build(stale.copy())                          # same B, same C
+    dropped = ~np.kron(block_screen | block_screen.T, np.ones((width, width), dtype=bool))
+    assert np.abs(second - first)[~dropped].max() < 1e-12          # computed blocks: overwritten, identical
+    assert np.abs(second - first)[dropped].max() > 1e-3            # dropped blocks: previous values leak through
+    # with every block computed the build is a function of (B, C) again and equals the default algorithm
+    full = np.zeros((N, N), order="F")
+    orc.calculate_K_lower_diagonal_block(W, full, n_blocks, width, batch, todo_all)
+    orc.calculate_coulomb_screened(Bs, C_T, sd, full)
+    assert np.abs(full - orc.fock_build_screened_rank(Bs, C_occ, sd, 10)).max() < 1e-12
