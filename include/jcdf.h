@@ -238,7 +238,8 @@ double jcdf_synthetic_value(uint64_t seed, int64_t Q_total, int64_t q_aux, int64
  * back to the tile family, ht_mode = 2 reports JCDF_ERR_CUDA; 0 = no cap),
  * "coulomb_pp_fused" (0 = default: two streaming passes; 1 = one cooperative single-pass kernel, measured slower),
  * "exchange_balance" (1 = default: cost-balanced exchange work lists; 0 = round-robin),
- * "pp_order" (work lists of the per-function kernel: 0 = default, a CTA walks its items chunk by chunk; 1 = p-major),
+ * "pp_order" (work lists of the per-function kernel: 1 = default, a CTA walks its items function by function, so CTAs that
+ * run side by side gather the same rows of C; 0 = chunk by chunk — measured 3 % slower at w50),
  * "pp_bigreg" (1 = default: both half-transform kernels run 12 warps and moves registers from the producer's warpgroup to the
  * consumers with setmaxnreg, 40 / 232 per thread; 0 = 9 warps at the 168-register launch cap),
  * "exchange_producer" (1 = default: the exchange kernel runs 12 warps with a dedicated copy-producer warp and the same register

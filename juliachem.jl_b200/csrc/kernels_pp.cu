@@ -79,7 +79,10 @@ struct PPParams {
     const int32_t* q;
     int64_t rows;
     int ldci, n_fn, n_nt, chunks, q_len, npt64, occ_w;
-    const int32_t* item_list;  // items of CTA c: item_list[item_off[c] .. item_off[c + 1])  (cost-balanced on the host)
+    // items of CTA c: item_rec[item_off[c] .. item_off[c + 1])  (cost-balanced on the host).  One 16-byte record per item,
+    // { p, chunk | orbital tile << 24, first partner row of p, padded partner count of p }: no divisions and no dependent
+    // loads at an item start
+    const int4* item_rec;
     const int32_t* item_off;
     double* vitem;  // [CTA][chunk][warp column][128] partial Coulomb V of the CTA's items of a chunk (nullptr: not wanted)
 };
@@ -177,13 +180,10 @@ __global__ void __launch_bounds__(BIGREG ? PP_THREADS_BIG : PP_THREADS, 1) k_pp_
         // ------------------------------------------------ producer warp ------------------------------------------------
         PipeState pp;
         for (int j = prm.item_off[blockIdx.x]; j < prm.item_off[blockIdx.x + 1]; j++) {
-            const int item = prm.item_list[j];
-            const int ch = (int)(item % chunks);
-            const int64_t r1 = item / chunks;
-            const int nt = (int)(r1 % n_nt);
-            const int p = (int)(r1 / n_nt);
-            const int r_begin = prm.off[p];
-            const int k4 = prm.off[p + 1] - r_begin;
+            const int4 rec = prm.item_rec[j];
+            const int ch = rec.y & 0xFFFFFF, nt = rec.y >> 24;
+            const int r_begin = rec.z;
+            const int k4 = rec.w;
             const double* Abase = prm.Bc + ((int64_t)ch * prm.rows + r_begin) * PP_QC;
             const double* Cbase = prm.Ci + (int64_t)nt * NI;
             for (int k0 = 0; k0 < k4; k0 += PP_KS) {
@@ -210,23 +210,23 @@ __global__ void __launch_bounds__(BIGREG ? PP_THREADS_BIG : PP_THREADS, 1) k_pp_
     const int g = lane >> 2, t = lane & 3;
     const int m0 = LAYOUT ? warp * 16 : (warp >> 2) * 64;
     const int n0 = LAYOUT ? 0 : (warp & 3) * 8 * NT;
-    // the partner count of the NEXT item is fetched while the current one computes (the k loop bound would otherwise
-    // wait on two dependent global loads at every item start)
+    // with the register split the record of the NEXT item is fetched while the current one computes (four registers the
+    // 168-register variant does not have: it reads its record at the item start)
     const int j_end = prm.item_off[blockIdx.x + 1];
-    auto count_of = [&](int jj) -> int {
-        if (jj >= j_end) return 0;
-        const int pf = prm.item_list[jj] / chunks / n_nt;
-        return prm.off[pf + 1] - prm.off[pf];
-    };
-    int k4_next = count_of(prm.item_off[blockIdx.x]);
+    int4 rec_next = make_int4(0, 0, 0, 0);
+    if constexpr (BIGREG) {
+        if (prm.item_off[blockIdx.x] < j_end) rec_next = prm.item_rec[prm.item_off[blockIdx.x]];
+    }
     for (int j = prm.item_off[blockIdx.x]; j < j_end; j++) {
-        const int item = prm.item_list[j];
-        const int ch = (int)(item % chunks);
-        const int64_t r1 = item / chunks;
-        const int nt = (int)(r1 % n_nt);
-        const int p = (int)(r1 / n_nt);
-        const int k4 = k4_next;
-        k4_next = count_of(j + 1);
+        int4 rec;
+        if constexpr (BIGREG) {
+            rec = rec_next;
+            if (j + 1 < j_end) rec_next = prm.item_rec[j + 1];
+        } else {
+            rec = prm.item_rec[j];
+        }
+        const int p = rec.x, ch = rec.y & 0xFFFFFF, nt = rec.y >> 24;
+        const int k4 = rec.w;
         const int rows_valid = min(PP_QC, prm.q_len - ch * PP_QC);
         const int mt_valid = max(0, min(MTW, (rows_valid - m0 + 7) >> 3));
         const int nt_valid = max(0, min(NT, (prm.occ_w - nt * NI - n0 + 7) >> 3));
@@ -263,17 +263,30 @@ __global__ void __launch_bounds__(BIGREG ? PP_THREADS_BIG : PP_THREADS, 1) k_pp_
         const int q0 = ch * PP_QC + m0 + g;
         // every row and orbital of the warp's block exists (a last 8-row tile may be partly beyond q_len: guarded stores)
         const bool all_in = (rows_valid - m0 >= 8 * MTW) && (nt * NI + n0 + 8 * NT <= prm.occ_w);
+        if (BIGREG && all_in) {  // the common case: no bounds to check (a second copy of the store loop: only where registers allow)
 #pragma unroll
-        for (int jm = 0; jm < MTW; jm++) {
-            const int Qrow = q0 + 8 * jm;
-            if (!all_in && Qrow >= prm.q_len) continue;
-            const int krow0 = Qrow * prm.occ_w + i0;
+            for (int jm = 0; jm < MTW; jm++) {
+                const int krow0 = (q0 + 8 * jm) * prm.occ_w + i0;
 #pragma unroll
-            for (int jn = 0; jn < NT; jn++) {
-                if (!all_in && i0 + 8 * jn >= prm.occ_w) continue;  // i and occ_w are even: the pair is in or out together
-                const int krow = krow0 + 8 * jn;
-                double* dst = wbase + (int64_t)((krow >> 5) * tile_stride) * 2048 + ((krow & 31) ^ sw);
-                *reinterpret_cast<double2*>(dst) = make_double2(acc[jm][jn][0], acc[jm][jn][1]);
+                for (int jn = 0; jn < NT; jn++) {
+                    const int krow = krow0 + 8 * jn;
+                    double* dst = wbase + (int64_t)((krow >> 5) * tile_stride) * 2048 + ((krow & 31) ^ sw);
+                    *reinterpret_cast<double2*>(dst) = make_double2(acc[jm][jn][0], acc[jm][jn][1]);
+                }
+            }
+        } else {
+#pragma unroll
+            for (int jm = 0; jm < MTW; jm++) {
+                const int Qrow = q0 + 8 * jm;
+                if (!all_in && Qrow >= prm.q_len) continue;
+                const int krow0 = Qrow * prm.occ_w + i0;
+#pragma unroll
+                for (int jn = 0; jn < NT; jn++) {
+                    if (!all_in && i0 + 8 * jn >= prm.occ_w) continue;  // i and occ_w are even: the pair is in or out together
+                    const int krow = krow0 + 8 * jn;
+                    double* dst = wbase + (int64_t)((krow >> 5) * tile_stride) * 2048 + ((krow & 31) ^ sw);
+                    *reinterpret_cast<double2*>(dst) = make_double2(acc[jm][jn][0], acc[jm][jn][1]);
+                }
             }
         }
         // Coulomb V from the accumulators: D[p,q] = sum_i C[p,i] C[q,i], so
@@ -727,8 +740,9 @@ static void launch_pp_t(const PPParams& prm, int grid, bool bigreg, cudaStream_t
 // 128-row chunk, the ragged last orbital tile — and a static round-robin aliases with the chunk count (gly18 shard,
 // 10 chunks of which the last holds 15 rows: CTAs of one parity got all the cheap items and the others 11 % more than
 // the mean).  Items are dealt longest-first onto the least-loaded CTA from the DMMA count the busiest sub-partition
-// issues; each CTA then walks its list chunk by chunk, p-major inside a chunk (C is 2.5 MB: its rows stay in L2 anyway).
+// issues; each CTA then walks its list in ascending (p-major) order so co-running CTAs share C rows in L2.
 void plan_pp_items(const Layout& L, Shard& s, int sm_count, bool p_major, std::vector<int32_t>& list, std::vector<int32_t>& off) {
+    // list: four int32 per item (the int4 records the kernel reads)
     const int chunks = s.pp_chunks, n_nt = L.pp_n_nt, NT = L.pp_nt;
     const int64_t n_items = (int64_t)L.N * n_nt * chunks;
     const int n_ctas = (int)std::max<int64_t>(1, std::min<int64_t>(n_items, sm_count));
@@ -785,16 +799,22 @@ void plan_pp_items(const Layout& L, Shard& s, int sm_count, bool p_major, std::v
         std::push_heap(heap.begin(), heap.end(), cmp);
     }
     for (int c = 0; c < n_ctas; c++) {
-        // chunk-major, then p-major: the rows of Bc a CTA reads form ascending runs inside one chunk, and its share of the
-        // Coulomb vector of a chunk is finished (and leaves the SM) before the next chunk starts
+        // p-major (default: co-running CTAs work on the same functions and share their gathered rows of C in L2; w50 14.9 ms)
+        // or chunk-major (the rows of Bc a CTA reads form ascending runs inside one chunk; 15.4 ms)
         std::sort(bins[(size_t)c].begin(), bins[(size_t)c].end(), [&](int32_t a, int32_t b) {
             const int ca = a % chunks, cb = b % chunks;
             return (!p_major && ca != cb) ? ca < cb : a < b;
         });
-        off[(size_t)c] = (int32_t)list.size();
-        list.insert(list.end(), bins[(size_t)c].begin(), bins[(size_t)c].end());
+        off[(size_t)c] = (int32_t)(list.size() / 4);
+        for (int32_t it : bins[(size_t)c]) {
+            const int ch = it % chunks, nt = (it / chunks) % n_nt, p = it / chunks / n_nt;
+            list.push_back(p);
+            list.push_back(ch | (nt << 24));
+            list.push_back(L.pp_off[(size_t)p]);
+            list.push_back(L.pp_off[(size_t)p + 1] - L.pp_off[(size_t)p]);
+        }
     }
-    off[(size_t)n_ctas] = (int32_t)list.size();
+    off[(size_t)n_ctas] = (int32_t)(list.size() / 4);
 }
 
 void launch_pp_pack(const Layout& L, Shard& s) {
@@ -825,7 +845,7 @@ void launch_pp_half_transform(const Layout& L, Shard& s, int sm_count, bool v_in
     prm.q_len = (int)s.q_len;
     prm.npt64 = L.npt64;
     prm.occ_w = L.occ_w;
-    prm.item_list = s.d_ppitems;
+    prm.item_rec = reinterpret_cast<const int4*>(s.d_ppitems);
     prm.item_off = s.d_ppoff;
     prm.vitem = v_in_ht ? s.Vitem : nullptr;
     const int grid = s.pp_ctas;
