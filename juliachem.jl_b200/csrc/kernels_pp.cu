@@ -111,43 +111,6 @@ __device__ __forceinline__ void pp_slab(double (&acc)[MTW][NT][2], const double*
     }
 }
 
-// D(8x8) = A(8x4) * B(4x8): the first k-step of an item starts from zero without a pass that clears the accumulators
-__device__ __forceinline__ void dmma_zero(double& c0, double& c1, double a, double b) {
-    asm volatile("mma.sync.aligned.m8n8k4.row.col.f64.f64.f64.f64 {%0,%1}, {%2}, {%3}, {%4,%5};"
-                 : "=d"(c0), "=d"(c1)
-                 : "d"(a), "d"(b), "d"(0.0), "d"(0.0));
-}
-
-// First stage of an item whose warp block is whole (register-split variant).  Its first k-step overwrites the accumulators
-// (C = 0), and when the PREVIOUS item left its W block in them (`pend`), every accumulator pair is stored to that item's
-// place in W immediately before the DMMA that overwrites it: the 32 stores of the old item ride in the shadow of the 32
-// DMMAs of the new one instead of idling the tensor pipe between two items.
-template <int MTW, int NT, int LDC>
-__device__ __forceinline__ void pp_slab_first(double (&acc)[MTW][NT][2], const double* __restrict__ sA,
-                                              const double* __restrict__ sC, int m0, int n0, int g, int t, int nks, bool pend,
-                                              double* wbase, int krow00, int sw, int occ_w, int tile_stride) {
-    const double* pa0 = sA + t * PP_QC + ((m0 + g) ^ (t << 2));
-    const double* pa1 = sA + t * PP_QC + ((m0 + 8 + g) ^ (t << 2)) - 8;
-    const double* pc = sC + t * LDC + n0 + g;
-    double a[MTW], b[NT];
-#pragma unroll
-    for (int jm = 0; jm < MTW; jm++) a[jm] = ((jm & 1) ? pa1 : pa0)[8 * jm];
-#pragma unroll
-    for (int jn = 0; jn < NT; jn++) b[jn] = pc[8 * jn];
-#pragma unroll
-    for (int jm = 0; jm < MTW; jm++) {
-        const int krow0 = krow00 + 8 * jm * occ_w;
-#pragma unroll
-        for (int jn = 0; jn < NT; jn++) {
-            const int krow = krow0 + 8 * jn;
-            double* dst = wbase + (int64_t)((krow >> 5) * tile_stride) * 2048 + ((krow & 31) ^ sw);
-            if (pend) *reinterpret_cast<double2*>(dst) = make_double2(acc[jm][jn][0], acc[jm][jn][1]);  // predicated store
-            dmma_zero(acc[jm][jn][0], acc[jm][jn][1], a[jm], b[jn]);
-        }
-    }
-    if (nks > 1) pp_slab<MTW, NT, LDC, MTW, NT>(acc, sA + 4 * PP_QC, sC + 4 * LDC, m0, n0, g, t, nks - 1);
-}
-
 template <int MTW, int NT, int LDC, int NTV>
 __device__ __forceinline__ void pp_slab_m(double (&acc)[MTW][NT][2], const double* sA, const double* sC, int m0, int n0,
                                           int g, int t, int nks, int mtv) {
@@ -250,34 +213,15 @@ __global__ void __launch_bounds__(BIGREG ? PP_THREADS_BIG : PP_THREADS, 1) k_pp_
     // with the register split the record of the NEXT item is fetched while the current one computes (four registers the
     // 168-register variant does not have: it reads its record at the item start)
     const int j_end = prm.item_off[blockIdx.x + 1];
-    int4 rec_next = make_int4(0, 0x7FFFFF, 0, 0);  // the empty record: a chunk beyond q_len, no partner rows
+    int4 rec_next = make_int4(0, 0, 0, 0);
     if constexpr (BIGREG) {
         if (prm.item_off[blockIdx.x] < j_end) rec_next = prm.item_rec[prm.item_off[blockIdx.x]];
     }
-    double acc[MTW][NT][2];
-    // register-split variant: the W block of a finished whole item stays in the accumulators and is stored during the first
-    // k-step of the next item (pp_slab_first)
-    bool pend = false;
-    double* pend_wbase = nullptr;
-    int pend_krow00 = 0, pend_sw = 0;
-    auto store_pending = [&]() {
-#pragma unroll
-        for (int jm = 0; jm < MTW; jm++) {
-            const int krow0 = pend_krow00 + 8 * jm * prm.occ_w;
-#pragma unroll
-            for (int jn = 0; jn < NT; jn++) {
-                const int krow = krow0 + 8 * jn;
-                double* dst = pend_wbase + (int64_t)((krow >> 5) * prm.npt64) * 2048 + ((krow & 31) ^ pend_sw);
-                *reinterpret_cast<double2*>(dst) = make_double2(acc[jm][jn][0], acc[jm][jn][1]);
-            }
-        }
-        pend = false;
-    };
-    for (int j = prm.item_off[blockIdx.x]; j < j_end + (BIGREG ? 1 : 0); j++) {
+    for (int j = prm.item_off[blockIdx.x]; j < j_end; j++) {
         int4 rec;
         if constexpr (BIGREG) {
-            rec = rec_next;  // at j == j_end (one extra pass that only stores the last item's block): an empty record
-            rec_next = (j + 1 < j_end) ? prm.item_rec[j + 1] : make_int4(0, 0x7FFFFF, 0, 0);
+            rec = rec_next;
+            if (j + 1 < j_end) rec_next = prm.item_rec[j + 1];
         } else {
             rec = prm.item_rec[j];
         }
@@ -288,16 +232,11 @@ __global__ void __launch_bounds__(BIGREG ? PP_THREADS_BIG : PP_THREADS, 1) k_pp_
         const int nt_valid = max(0, min(NT, (prm.occ_w - nt * NI - n0 + 7) >> 3));
         const bool any = mt_valid > 0 && nt_valid > 0;
         const bool whole = mt_valid == MTW && nt_valid == NT;
-        if (!(BIGREG && whole)) {  // a whole block of the register-split variant starts from C = 0 in its first k-step instead
-            if constexpr (BIGREG) {
-                if (pend) store_pending();
-                if (j == j_end) break;
-            }
+        double acc[MTW][NT][2];
 #pragma unroll
-            for (int jm = 0; jm < MTW; jm++)
+        for (int jm = 0; jm < MTW; jm++)
 #pragma unroll
-                for (int jn = 0; jn < NT; jn++) acc[jm][jn][0] = acc[jm][jn][1] = 0.0;
-        }
+            for (int jn = 0; jn < NT; jn++) acc[jm][jn][0] = acc[jm][jn][1] = 0.0;
         if constexpr (WITH_V) {  // the epilogue reads the warp's 8 NT orbitals of row p of C: have them in L1 by then
             if (lane < NT) asm volatile("prefetch.global.L1 [%0];" ::"l"(prm.Ci + (int64_t)p * prm.ldci + nt * NI + n0 + 8 * lane));
         }
@@ -307,17 +246,8 @@ __global__ void __launch_bounds__(BIGREG ? PP_THREADS_BIG : PP_THREADS, 1) k_pp_
             mbar_wait(&full[ps.stage], ps.phase);
             const double* sA = stages + (size_t)ps.stage * STAGE_DOUBLES;
             const double* sC = sA + PP_KS * PP_QC;
-            if (whole) {
-                if (BIGREG && k0 == 0) {
-                    pp_slab_first<MTW, NT, LDC>(acc, sA, sC, m0, n0, g, t, nks, pend, pend_wbase, pend_krow00, pend_sw, prm.occ_w,
-                                                prm.npt64);
-                    pend = false;
-                } else {
-                    pp_slab<MTW, NT, LDC, MTW, NT>(acc, sA, sC, m0, n0, g, t, nks);
-                }
-            } else if (any) {
-                pp_slab_mn<MTW, NT, LDC>(acc, sA, sC, m0, n0, g, t, nks, mt_valid, nt_valid);
-            }
+            if (whole) pp_slab<MTW, NT, LDC, MTW, NT>(acc, sA, sC, m0, n0, g, t, nks);
+            else if (any) pp_slab_mn<MTW, NT, LDC>(acc, sA, sC, m0, n0, g, t, nks, mt_valid, nt_valid);
             __syncwarp();
             if (lane == 0) mbar_arrive(&empty[ps.stage]);
             ps.advance<PP_NSTAGE>();
@@ -333,13 +263,20 @@ __global__ void __launch_bounds__(BIGREG ? PP_THREADS_BIG : PP_THREADS, 1) k_pp_
         const int q0 = ch * PP_QC + m0 + g;
         // every row and orbital of the warp's block exists (a last 8-row tile may be partly beyond q_len: guarded stores)
         const bool all_in = (rows_valid - m0 >= 8 * MTW) && (nt * NI + n0 + 8 * NT <= prm.occ_w);
-        if (BIGREG && all_in) {
-            // the common case: every row and orbital exists.  The block stays in the accumulators; its 32 stores are issued
-            // between the DMMAs of the next item's first k-step (pp_slab_first) or, failing that, by store_pending()
-            pend = true;
-            pend_wbase = wbase;
-            pend_krow00 = q0 * prm.occ_w + i0;
-            pend_sw = sw;
+        // (Tried: leave the block in the accumulators and issue its 32 stores between the DMMAs of the next item's first k-step,
+        // which then starts from C = 0 without a clearing pass — parity green, but 15.02 ms against 14.73 at w50: the stores
+        // and their address arithmetic inside the DMMA stream cost more than the idle gap they remove.)
+        if (BIGREG && all_in) {  // the common case: no bounds to check (a second copy of the store loop: only where registers allow)
+#pragma unroll
+            for (int jm = 0; jm < MTW; jm++) {
+                const int krow0 = (q0 + 8 * jm) * prm.occ_w + i0;
+#pragma unroll
+                for (int jn = 0; jn < NT; jn++) {
+                    const int krow = krow0 + 8 * jn;
+                    double* dst = wbase + (int64_t)((krow >> 5) * tile_stride) * 2048 + ((krow & 31) ^ sw);
+                    *reinterpret_cast<double2*>(dst) = make_double2(acc[jm][jn][0], acc[jm][jn][1]);
+                }
+            }
         } else {
 #pragma unroll
             for (int jm = 0; jm < MTW; jm++) {
