@@ -18,8 +18,13 @@ def main():
     raw = subprocess.run(["ncu", "-i", rep, "--page", "source", "--csv", "--kernel-name", "regex:" + kregex],
                          capture_output=True, text=True).stdout
     rows = list(csv.reader(io.StringIO(raw)))
-    hdr, data = rows[1], rows[2:]
+    hdr = rows[1]
     ix = {h: i for i, h in enumerate(hdr)}
+    data = []
+    for r in rows[2:]:  # one section per captured launch: the first one
+        if len(r) < len(hdr):
+            break
+        data.append(r)
     with tempfile.TemporaryDirectory() as td:
         subprocess.run(["cuobjdump", "-xelf", "all", os.path.abspath(obj)], cwd=td, capture_output=True)
         cubin = [f for f in os.listdir(td) if f.endswith(".cubin")][0]
