@@ -7,7 +7,8 @@ import ctypes as C
 import os
 
 _HERE = os.path.dirname(os.path.abspath(__file__))
-LIB_PATH = os.path.join(_HERE, "libjcdf.so")
+# JCDF_LIBRARY selects another build of the same ABI (the bounds-checked libjcdf_checked.so, `make CHECKED=1`)
+LIB_PATH = os.environ.get("JCDF_LIBRARY") or os.path.join(_HERE, "libjcdf.so")
 
 N_STAGES = 10
 STAGE_NAMES = ("W", "K", "V", "J", "allreduce", "density", "h2d", "d2h", "total", "epilogue")

@@ -4,6 +4,24 @@
 #include <cstdint>
 #include <cuda_runtime.h>
 
+#include <cstdio>
+
+// Bounds-checked build (make CHECKED=1 -> libjcdf_checked.so): every global store / bulk-copy source of the pipelined kernels
+// is compared with the extent of its buffer; a violation prints the place and traps.  compute-sanitizer is closed on this
+// pool, so this build over the smallest case of every kernel family (tools/sanitizer_cases.py) stands in for memcheck.
+#ifdef JCDF_CHECKED
+#define JC_CHECK(cond, what)                                                                                             \
+    do {                                                                                                                 \
+        if (!(cond)) {                                                                                                   \
+            printf("JCDF_CHECKED violation: %s at %s:%d (block %d, thread %d)\n", what, __FILE__, __LINE__, (int)blockIdx.x, \
+                   (int)threadIdx.x);                                                                                    \
+            __trap();                                                                                                    \
+        }                                                                                                                \
+    } while (0)
+#else
+#define JC_CHECK(cond, what) ((void)0)
+#endif
+
 namespace jcdf {
 
 constexpr int TILE = 32;                  // edge of a packed B tile (doubles)

@@ -111,6 +111,7 @@ struct HTParams {
     double* W;
     int q_len, nb, n_mt, npt64, occ_w, n_valid_last;
     int64_t n_items;
+    int64_t w_elems, bp_elems, cs_elems;  // buffer extents in doubles (read by the bounds-checked build only)
 };
 
 // One work item = (quad of auxiliary rows Q0..Q0+3, 32-wide p block pb, M tile of BM = 8*MT occupied orbitals):
@@ -202,6 +203,9 @@ __global__ void __launch_bounds__(BIGREG ? HT_THREADS_BIG : HT_THREADS, 1) k_hal
                 const uint32_t sm = (uint32_t)prm.tile_strips[tix];
                 stage_kb[pp.stage] = kb | (int)(((kb >= pb) ? (sm & 0xFFu) : ((sm >> 8) & 0xFFu)) << 16);
                 double* st = stages + (size_t)pp.stage * STAGE_DOUBLES;
+                JC_CHECK(tix >= 0 && ((int64_t)kb * n_mt + mt + 1) * (32 * BM) <= prm.cs_elems &&
+                             (q0 + nq - 1) * prm.row_len + ((int64_t)tix + 1) * TILE_ELEMS <= prm.bp_elems,
+                         "tile half-transform: copy outside Cs / Bp");
                 mbar_arrive_expect_tx(&full[pp.stage], 32u * BM * 8u + (uint32_t)nq * (TILE_ELEMS * 8u));
                 bulk_g2s(st, prm.Cs + ((int64_t)kb * n_mt + mt) * (32 * BM), 32u * BM * 8u, &full[pp.stage]);
                 for (int j = 0; j < nq; j++)
@@ -261,6 +265,7 @@ __global__ void __launch_bounds__(BIGREG ? HT_THREADS_BIG : HT_THREADS, 1) k_hal
                         const int p = 32 * pb + 8 * jn + 2 * t;  // even: p and p + 1 share the 64-wide tile
                         const int p64 = p >> 6, pr = p & 63;
                         double* w = prm.W + ((kc * prm.npt64 + p64) * 64 + pr) * 32;
+                        JC_CHECK(w >= prm.W && w + 64 <= prm.W + prm.w_elems, "tile half-transform: W store outside W");
                         w[swz(pr, kr)] = acc[jm][jn][0];
                         w[32 + swz(pr + 1, kr)] = acc[jm][jn][1];
                     }
@@ -303,6 +308,9 @@ void launch_half_transform(const Layout& L, Shard& s, int sm_count, bool bigreg)
     prm.occ_w = L.occ_w;
     prm.n_valid_last = (int)(L.N - 32 * (L.nb - 1));
     prm.n_items = ((int64_t)s.q_len + 3) / 4 * L.nb * L.n_mt;
+    prm.w_elems = (int64_t)s.xplan.chunks * L.npt64 * 2048;
+    prm.bp_elems = (int64_t)s.q_len * L.row_len;
+    prm.cs_elems = (int64_t)L.nb * L.n_mt * 32 * L.bm;
     int grid = (int)std::min<int64_t>(prm.n_items, sm_count);
     if (grid <= 0) return;
     switch (L.bm / 8) {
@@ -328,6 +336,7 @@ struct XParams {
     const int32_t* item_off;
     long long* cta_cycles;     // [gridDim.x] busy cycles of this launch (profiling aid)
     int npt64, n_tiles, n_slices, chunks, chunks_per_slice, N;
+    int64_t w_elems, kpart_elems;  // buffer extents in doubles (read by the bounds-checked build only)
 };
 
 constexpr int X_STAGE_DOUBLES = 4 * 32 * 64;  // A0 A1 B0 B1, each a [64 p][32 k] W tile
@@ -530,6 +539,9 @@ __device__ __forceinline__ void exchange_body(const XParams& prm) {
         mbar_arrive_expect_tx(&full[pp.stage], (uint32_t)p_nvalid * 32u * 64u * 8u);
 #pragma unroll
         for (int x = 0; x < 4; x++)
+            JC_CHECK(p_col[x] >= npt64 || ((int64_t)p_kc * npt64 + p_col[x] + 1) * 2048 <= prm.w_elems, "exchange: copy outside W");
+#pragma unroll
+        for (int x = 0; x < 4; x++)
             if (p_col[x] < npt64)
                 bulk_g2s(st + x * 2048, prm.W + ((int64_t)p_kc * npt64 + p_col[x]) * 2048, 2048u * 8u, &full[pp.stage]);
         pp.advance<NSTAGE>();
@@ -600,6 +612,7 @@ __device__ __forceinline__ void exchange_body(const XParams& prm) {
             for (int jn = 0; jn < 4; jn++) {
                 if (jn >= nt) continue;
                 const int n = 8 * (c0 + jn) + 2 * t;
+                JC_CHECK(m < 128 && n + 1 < 128 && (int64_t)(item + 1) * (128 * 128) <= prm.kpart_elems, "exchange: store outside Kpart");
                 *reinterpret_cast<double2*>(out + m * 128 + n) = make_double2(acc[jm][jn][0], acc[jm][jn][1]);
             }
         }
@@ -625,6 +638,8 @@ void launch_exchange(const Layout& L, Shard& s, int sm_count, bool dedicated_pro
     prm.chunks = s.xplan.chunks;
     prm.chunks_per_slice = s.xplan.chunks_per_slice;
     prm.N = (int)L.N;
+    prm.w_elems = (int64_t)s.xplan.chunks * L.npt64 * 2048;
+    prm.kpart_elems = (int64_t)s.xplan.n_tiles * s.xplan.n_slices * 128 * 128;
     const int grid = s.xplan.n_ctas;
     if (grid <= 0) return;
     size_t smem = exchange_smem_bytes();

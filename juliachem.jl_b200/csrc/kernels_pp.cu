@@ -54,6 +54,8 @@ __global__ void __launch_bounds__(256) k_pp_pack(const double* __restrict__ Bp, 
     __syncthreads();
     for (int idx = threadIdx.x; idx < 32 * PP_QC; idx += 256) {
         const int r = idx >> 7, m = idx & (PP_QC - 1);
+        JC_CHECK(r0 + r >= rows || ((int64_t)ch * rows + r0 + r) * PP_QC + (m ^ ((r & 3) << 2)) < (int64_t)gridDim.y * rows * PP_QC,
+                 "pack: write outside Bc");
         if (r0 + r < rows) Bc[((int64_t)ch * rows + r0 + r) * PP_QC + (m ^ ((r & 3) << 2))] = tile[r][m];
     }
 }
@@ -85,6 +87,7 @@ struct PPParams {
     const int4* item_rec;
     const int32_t* item_off;
     double* vitem;  // [CTA][chunk][warp column][128] partial Coulomb V of the CTA's items of a chunk (nullptr: not wanted)
+    int64_t w_elems, bc_elems, ci_elems, vitem_elems;  // buffer extents in doubles (read by the bounds-checked build only)
 };
 
 // One pipeline stage (nks k-steps of 4 partner rows) of a warp block of MTV x NTV DMMA tiles inside the warp's 8 x NT
@@ -192,10 +195,14 @@ __global__ void __launch_bounds__(BIGREG ? PP_THREADS_BIG : PP_THREADS, 1) k_pp_
                 mbar_wait(&empty[pp.stage], pp.phase ^ 1u);
                 double* st = stages + (size_t)pp.stage * STAGE_DOUBLES;
                 if (lane == 0) {
+                    JC_CHECK(Abase + (int64_t)k0 * PP_QC >= prm.Bc && Abase + (int64_t)(k0 + nr) * PP_QC <= prm.Bc + prm.bc_elems,
+                             "half-transform: A copy outside Bc");
                     mbar_arrive_expect_tx(&full[pp.stage], (uint32_t)nr * (uint32_t)((PP_QC + NI) * 8));
                     bulk_g2s(st, Abase + (int64_t)k0 * PP_QC, (uint32_t)nr * PP_QC * 8u, &full[pp.stage]);
                 }
                 __syncwarp();
+                if (lane < nr)
+                    JC_CHECK(qrow >= 0 && Cbase + (int64_t)qrow * prm.ldci + NI <= prm.Ci + prm.ci_elems, "half-transform: C row outside Ci");
                 if (lane < nr)
                     bulk_g2s(st + PP_KS * PP_QC + lane * LDC, Cbase + (int64_t)qrow * prm.ldci, NI * 8u, &full[pp.stage]);
                 pp.advance<PP_NSTAGE>();
@@ -274,6 +281,7 @@ __global__ void __launch_bounds__(BIGREG ? PP_THREADS_BIG : PP_THREADS, 1) k_pp_
                 for (int jn = 0; jn < NT; jn++) {
                     const int krow = krow0 + 8 * jn;
                     double* dst = wbase + (int64_t)((krow >> 5) * tile_stride) * 2048 + ((krow & 31) ^ sw);
+                    JC_CHECK(dst >= prm.W && dst + 2 <= prm.W + prm.w_elems, "half-transform: W store outside W");
                     *reinterpret_cast<double2*>(dst) = make_double2(acc[jm][jn][0], acc[jm][jn][1]);
                 }
             }
@@ -288,6 +296,7 @@ __global__ void __launch_bounds__(BIGREG ? PP_THREADS_BIG : PP_THREADS, 1) k_pp_
                     if (!all_in && i0 + 8 * jn >= prm.occ_w) continue;  // i and occ_w are even: the pair is in or out together
                     const int krow = krow0 + 8 * jn;
                     double* dst = wbase + (int64_t)((krow >> 5) * tile_stride) * 2048 + ((krow & 31) ^ sw);
+                    JC_CHECK(dst >= prm.W && dst + 2 <= prm.W + prm.w_elems, "half-transform: W store outside W");
                     *reinterpret_cast<double2*>(dst) = make_double2(acc[jm][jn][0], acc[jm][jn][1]);
                 }
             }
@@ -327,6 +336,7 @@ __global__ void __launch_bounds__(BIGREG ? PP_THREADS_BIG : PP_THREADS, 1) k_pp_
                 asm volatile("" : "+r"(che), "+r"(we));
                 constexpr int NWC = LAYOUT ? 1 : 4;
                 double* vdst = prm.vitem + ((((int64_t)blockIdx.x * chunks + che) * NWC + (LAYOUT ? 0 : (we & 3))) * PP_QC) + m0 + ge;
+                JC_CHECK(vdst >= prm.vitem && vdst + 8 * (MTW - 1) < prm.vitem + prm.vitem_elems, "half-transform: V slot outside Vitem");
 #pragma unroll
                 for (int jm = 0; jm < MTW; jm++) asm volatile("red.global.add.f64 [%0], %1;" ::"l"(vdst + 8 * jm), "d"(v[jm]) : "memory");
             }
@@ -851,6 +861,10 @@ void launch_pp_half_transform(const Layout& L, Shard& s, int sm_count, bool v_in
     prm.item_rec = reinterpret_cast<const int4*>(s.d_ppitems);
     prm.item_off = s.d_ppoff;
     prm.vitem = v_in_ht ? s.Vitem : nullptr;
+    prm.w_elems = (int64_t)s.xplan.chunks * L.npt64 * 2048;
+    prm.bc_elems = (int64_t)s.pp_chunks * L.pp_rows * PP_QC;
+    prm.ci_elems = (int64_t)(L.n_pad + 1) * prm.ldci;
+    prm.vitem_elems = (int64_t)std::max(1, s.pp_ctas) * s.pp_chunks * pp_v_slots(L) * PP_QC;
     const int grid = s.pp_ctas;
     (void)sm_count;
     if (grid <= 0) return;
