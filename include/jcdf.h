@@ -271,6 +271,13 @@ int32_t jcdf_exchange_cta_cycles(jcdf_handle* h, int32_t dev, int64_t* out, int3
  * The same function drives the kernel and the cost model of the work lists.                                        */
 int32_t jcdf_debug_exchange_block(int32_t ta, int32_t tb, int32_t warp, int64_t N, int32_t* out5);
 
+/* 1 when the library is the bounds-checked build (make CHECKED=1: every global store and bulk-copy source of the pipelined
+ * kernels is compared with its buffer's extent, a violation prints its place and traps), else 0.  fire != 0 on a checked build
+ * launches a kernel whose check must fail and returns the resulting CUDA error code (> 0): the proof that the checks are live;
+ * the CUDA context is unusable afterwards.  compute-sanitizer is closed on the development pool; this build stands in for
+ * its memcheck tool.                                                                                                   */
+int32_t jcdf_checked_selftest(int32_t fire);
+
 /* The CUDA stream (cudaStream_t, returned as void*) every kernel, copy and all-reduce of device `dev` is issued on —
  * so a caller can bracket builds with its own CUDA events or order its own work against them (the fork's CUDA.jl
  * path uses the task-local default stream and CUDA.synchronize() instead, GPUDF.jl:206-263).                     */

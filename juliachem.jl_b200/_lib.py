@@ -61,6 +61,7 @@ SIGNATURES = {
     "jcdf_debug_exchange_block": (_i32, [_i32, _i32, _i32, _i64, _p]),
     "jcdf_set_option": (_i32, [_p, C.c_char_p, _i64]),
     "jcdf_get_stream": (_i32, [_p, _i32, C.POINTER(_p)]),
+    "jcdf_checked_selftest": (_i32, [_i32]),
     "jcdf_set_basis": (_i32, [_p, _i32, _i64, _p, _p, _p, _p, _p]),
     "jcdf_compute_two_center": (_i32, [_p, _p]),
     "jcdf_compute_schwarz_mask": (_i32, [_p, _f64, _p, C.POINTER(_i64)]),

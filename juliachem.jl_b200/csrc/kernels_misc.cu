@@ -123,6 +123,30 @@ void launch_fill_synthetic(const Layout& L, Shard& s, uint64_t seed, double deca
 
 }  // namespace jcdf
 
+namespace jcdf {
+__global__ void k_checked_selftest(const double* base, int64_t elems, int64_t index) {
+    JC_CHECK(index >= 0 && index < elems, "self-test: index outside its buffer (expected)");
+    if (index >= 0 && index < elems && base[index] == 12345.0) printf("\n");
+}
+}  // namespace jcdf
+
+// 1 when this library was built with JCDF_CHECKED (make CHECKED=1), else 0.  With fire != 0 a one-thread kernel is launched whose
+// JC_CHECK must fail: the call then returns the CUDA error code the trap produces (non-zero; the context is dead afterwards —
+// call it last, in a process of its own).  Proves that the bounds checks of the checked build are live.
+extern "C" int32_t jcdf_checked_selftest(int32_t fire) {
+#ifdef JCDF_CHECKED
+    if (!fire) return 1;
+    double* d = nullptr;
+    if (cudaMalloc(&d, 64) != cudaSuccess) return -2;
+    jcdf::k_checked_selftest<<<1, 1>>>(d, 8, 8);
+    const cudaError_t e = cudaDeviceSynchronize();
+    return e == cudaSuccess ? -3 : (int32_t)e;
+#else
+    (void)fire;
+    return 0;
+#endif
+}
+
 extern "C" double jcdf_synthetic_value(uint64_t seed, int64_t Q_total, int64_t q_aux, int64_t p, int64_t q,
                                        double decay_length) {
     const int64_t lo = p < q ? p : q, hi = p < q ? q : p;

@@ -31,7 +31,9 @@ CASES = [
 
 
 def main():
-    only = sys.argv[1:]
+    only = [a for a in sys.argv[1:] if a != "--fire"]
+    lib = jc.load_library()
+    print("library: %s  (bounds-checked build: %s)" % (jc.LIB_PATH, bool(lib.jcdf_checked_selftest(0))), flush=True)
     worst = 0.0
     for name, N, Q, occ, opts in CASES:
         if only and name not in only:
@@ -53,6 +55,11 @@ def main():
             name, N, Q, occ, li.kernel_launches_per_build, li.graph_replays, err, bool(np.array_equal(F, F2))), flush=True)
     if not worst < 1e-10:
         raise SystemExit("parity failed: %.3e" % worst)
+    if "--fire" in sys.argv:  # last: a check that MUST fail (kills the context)
+        rc = lib.jcdf_checked_selftest(1)
+        print("self-test of the checks: CUDA error %d after a deliberate violation (0 = not a checked build, < 0 = no trap)" % rc, flush=True)
+        if rc <= 0:
+            raise SystemExit("the bounds checks did not fire")
 
 
 if __name__ == "__main__":
