@@ -53,7 +53,7 @@ static void free_shard_buffers(Shard& s, bool keep_metric = false) {
     if (s.gexec) { cudaGraphExecDestroy(s.gexec); s.gexec = nullptr; }  // the graph holds the old buffer addresses
     s.gkey = 0;
     s.graph_broken = false;
-    void* ptrs[] = {s.d_pp_trirow, s.ppj_flag, s.ppj_vp, s.d_ppitems, s.d_ppoff, s.d_xcycles, s.Ksum, s.d_xitems, s.d_xoff, s.Bc, s.Ci, s.d_pp_off, s.d_pp_q, s.d_pp_src, s.d_pp_p, s.d_pp_jdst, s.dvec, s.VpartP, s.Vitem, s.Jpart, s.Vpart, s.Vready, s.Bp, s.W, s.Cs, s.Craw, s.dt, s.Jt, s.V, s.Kpart, s.F, s.Hdev, s.Traw, s.d_tile_index, s.d_tile_a,
+    void* ptrs[] = {s.d_pp_trirow, s.ppj_flag, s.ppj_vp, s.d_ppitems, s.d_ppoff, s.d_xcycles, s.Ksum, s.d_xitems, s.d_xoff, s.Bc, s.Ci, s.d_pp_off, s.d_pp_q, s.d_pp_src, s.d_pp_p, s.d_pp_jdst, s.dvec, s.VpartP, s.Vitem, s.Vt, s.Jpart, s.Vpart, s.Vready, s.Bp, s.W, s.Cs, s.Craw, s.dt, s.Jt, s.V, s.Kpart, s.F, s.Hdev, s.Traw, s.d_tile_index, s.d_tile_a,
                     s.d_tile_b, s.d_dest_of_col, s.d_fn_mask, s.d_kb_list, s.d_kb_count, s.d_perm, s.d_inv, s.d_tile_strips};
     for (void* p : ptrs)
         if (p) cudaFree(p);
@@ -68,7 +68,7 @@ static void free_shard_buffers(Shard& s, bool keep_metric = false) {
     s.Vready = nullptr;
     s.Bc = s.Ci = nullptr;
     s.d_pp_off = s.d_pp_q = s.d_pp_src = s.d_pp_p = s.d_pp_jdst = nullptr;
-    s.dvec = s.VpartP = s.Vitem = s.Jpart = nullptr;
+    s.dvec = s.VpartP = s.Vitem = s.Vt = s.Jpart = nullptr;
     s.d_xitems = s.d_xoff = nullptr;
     s.d_xcycles = nullptr;
     s.d_ppitems = s.d_ppoff = nullptr;
@@ -163,6 +163,7 @@ static int alloc_shard_buffers(jcdf_handle* h, Shard& s) {
     if ((rc = dev_alloc(&s.V, (size_t)std::max<int64_t>(s.q_len, 1)))) return rc;
     if ((rc = dev_alloc(&s.Vpart, (size_t)std::max<int64_t>(s.q_len, 1) * h->sm_count))) return rc;
     if ((rc = dev_alloc(&s.Vready, (size_t)std::max<int64_t>(s.q_len, 1)))) return rc;
+    if ((rc = dev_alloc(&s.Vt, (size_t)std::max<int64_t>(s.q_len, 1) * h->sm_count * 2))) return rc;
     if ((rc = dev_alloc(&s.Kpart, (size_t)s.xplan.n_tiles * s.xplan.n_slices * 128 * 128))) return rc;
     // Kpart is zeroed once: blocks no warp owns (above the diagonal, beyond N) are never written but are summed by
     // k_exchange_reduce, and uninitialised memory could hold NaN patterns
@@ -970,10 +971,11 @@ int32_t jcdf_set_core_hamiltonian(jcdf_handle* h, const double* H) {
 // What the per-build launch sequence of one shard depends on (everything else is fixed once jcdf_set_mask has run).
 struct BuildSchedule {
     bool use_pp, pp_j, v_in_ht, overlap, add_H;
+    bool tile_v;  // tile family: V from the half-transform's accumulators, then the J sweep alone
     uint64_t key(const jcdf_handle* h) const {
         return 1ull | (uint64_t)use_pp << 1 | (uint64_t)pp_j << 2 | (uint64_t)v_in_ht << 3 | (uint64_t)overlap << 4 |
                (uint64_t)add_H << 5 | (uint64_t)(h->opt_coulomb_fused & 3) << 6 | (uint64_t)(h->opt_coulomb_pp_fused & 1) << 8 |
-               (uint64_t)(h->opt_pp_bigreg & 1) << 9 | (uint64_t)(h->opt_exchange_producer & 1) << 10;
+               (uint64_t)(h->opt_pp_bigreg & 1) << 9 | (uint64_t)(h->opt_exchange_producer & 1) << 10 | (uint64_t)tile_v << 11;
     }
 };
 
@@ -981,14 +983,14 @@ struct BuildSchedule {
 // once under stream capture to build the graph the later builds replay.
 static int issue_build_kernels(jcdf_handle* h, Shard& s, const BuildSchedule& b) {
     const Layout& L = h->lay;
-    if (!b.pp_j) launch_prep(L, s, L.N);
+    if (!b.pp_j) launch_prep(L, s, L.N, !b.tile_v);
     if (b.use_pp) launch_pp_prep(L, s, L.N);
     // V = sum_p sum_i C[p,i] W[Q,i,p] comes out of the half-transform's accumulators: no density, no V sweep
     if (b.pp_j && !b.v_in_ht) launch_pp_density(L, s);
     JC_CUDA(record_event(s, s.ev[EV_PREP], s.stream));
     if (b.overlap) JC_CUDA(cudaEventRecord(s.ev_dep[0], s.stream));
     if (b.use_pp) launch_pp_half_transform(L, s, h->sm_count, b.v_in_ht, h->opt_pp_bigreg != 0);
-    else launch_half_transform(L, s, h->sm_count, h->opt_pp_bigreg != 0);
+    else launch_half_transform(L, s, h->sm_count, h->opt_pp_bigreg != 0, b.tile_v);
     JC_CUDA(cudaPeekAtLastError());  // a launch that did not fit fails the build here, not as a wrong Fock matrix
     JC_CUDA(record_event(s, s.ev[EV_W], s.stream));
     if (b.overlap) JC_CUDA(cudaEventRecord(s.ev_dep[1], s.stream));
@@ -1004,7 +1006,7 @@ static int issue_build_kernels(jcdf_handle* h, Shard& s, const BuildSchedule& b)
         // the fork point is after the half-transform when it leaves the Coulomb partials, after the prep kernels otherwise:
         // recorded here, i.e. after the exchange launch, it would serialise the two streams, so the events are recorded
         // at their places above (dep[0] after prep, dep[1] after the half-transform)
-        JC_CUDA(cudaStreamWaitEvent(sj, s.ev_dep[b.pp_j && b.v_in_ht ? 1 : 0], 0));
+        JC_CUDA(cudaStreamWaitEvent(sj, s.ev_dep[((b.pp_j && b.v_in_ht) || b.tile_v) ? 1 : 0], 0));
     }
     JC_CUDA(record_event(s, s.ev[EV_JBEGIN], sj));
     JC_CUDA(record_event(s, s.ev[EV_V], sj));  // two-pass: overwritten at the V | J boundary; fused: V time reads 0
@@ -1018,12 +1020,13 @@ static int issue_build_kernels(jcdf_handle* h, Shard& s, const BuildSchedule& b)
         // fused single pass pays off on long column segments (w50 dense: 3.8 TB/s effective against <= 3.05 for two
         // passes at the copy bandwidth); on short ones its per-chunk grid-wide flags dominate and two streaming
         // passes are faster (measured: benzene dimer 1.01 -> 0.91 ms, C20H42 5.54 -> 5.26 ms)
-        const bool want_fused = h->opt_coulomb_fused == 1 ||
-                                (h->opt_coulomb_fused == 2 && L.row_len / std::max(1, h->sm_count) >= 4500);
+        const bool want_fused = !b.tile_v && (h->opt_coulomb_fused == 1 ||
+                                              (h->opt_coulomb_fused == 2 && L.row_len / std::max(1, h->sm_count) >= 4500));
         s.last_coulomb_fused = want_fused && launch_coulomb_fused(L, s, h->sm_count, sj);
-        if (!s.last_coulomb_fused) launch_coulomb(L, s, h->sm_count, sj);
+        if (!s.last_coulomb_fused) launch_coulomb(L, s, h->sm_count, sj, b.tile_v);  // tile_v: V is there already, J sweep only
     }
     s.last_pp_j = b.pp_j;
+    s.last_tile_v = b.tile_v;
     s.last_v_in_ht = b.v_in_ht && !s.last_ppj_fused;
     JC_CUDA(record_event(s, s.ev[EV_J], sj));
     if (b.overlap) {
@@ -1165,7 +1168,10 @@ int fock_build_impl(jcdf_handle* h, const double* C_occ, int64_t ldc, const doub
         }
         b.pp_j = b.use_pp && h->opt_coulomb_pp;  // Coulomb over the compact copy as well
         b.v_in_ht = b.pp_j && h->opt_coulomb_v_in_ht && !h->opt_coulomb_pp_fused && s.Vitem != nullptr;
-        b.overlap = h->opt_coulomb_overlap && (b.pp_j || !h->opt_coulomb_fused);
+        // tile family with the automatic Coulomb choice: V from the accumulators of the tile half-transform, then one J sweep
+        // (an explicit coulomb_fused = 0 / 1 keeps the two-pass / single-pass kernels selectable)
+        b.tile_v = !b.use_pp && h->opt_coulomb_v_in_ht && h->opt_coulomb_fused == 2 && s.Vt != nullptr;
+        b.overlap = h->opt_coulomb_overlap && (b.pp_j || !h->opt_coulomb_fused || b.tile_v);
         if ((rc = run_build_kernels(h, s, b))) return rc;
     }
     auto t_launched = std::chrono::steady_clock::now();
@@ -1211,7 +1217,7 @@ int fock_build_impl(jcdf_handle* h, const double* C_occ, int64_t ldc, const doub
         s.last_ms[JCDF_T_K] = el(EV_W, EV_K);
         s.last_ms[JCDF_T_V] = el(EV_JBEGIN, EV_V);
         s.last_ms[JCDF_T_J] = el(EV_V, EV_J);
-        s.last_ms[JCDF_T_EPILOGUE] = (h->opt_coulomb_overlap && (s.last_pp_j || !h->opt_coulomb_fused)) ? el(EV_K, EV_EPI) : el(EV_J, EV_EPI);
+        s.last_ms[JCDF_T_EPILOGUE] = (h->opt_coulomb_overlap && (s.last_pp_j || !h->opt_coulomb_fused || s.last_tile_v)) ? el(EV_K, EV_EPI) : el(EV_J, EV_EPI);
         s.last_ms[JCDF_T_ALLREDUCE] = el(EV_EPI, EV_AR);
         s.last_ms[JCDF_T_D2H] = d == 0 ? el(EV_AR, EV_D2H) : 0.0;
         s.last_ms[JCDF_T_TOTAL] = std::chrono::duration<double, std::milli>(t1 - t0).count();
@@ -1338,7 +1344,9 @@ int32_t jcdf_get_layout(jcdf_handle* h, jcdf_layout_info* o) {
     const int kred = (!h->shards.empty() && h->shards[0].xplan.n_slices > 1) ? 1 : 0;  // k_exchange_reduce
     const bool ppjf = ppj && h->shards[0].last_ppj_fused;  // one cooperative Coulomb kernel instead of V, V reduce, J, J reduce
     const bool vht = ppj && !ppjf && h->opt_coulomb_v_in_ht && !h->opt_coulomb_pp_fused;  // density, V pass, V reduce -> one reduce
-    o->kernel_launches_per_build = kred + (ppjf ? 6 : ppj ? (vht ? 7 : 9) : ((!h->shards.empty() && h->shards[0].last_coulomb_fused) ? 6 : 7)) +
+    // tile family with V from the half-transform: prep, half_transform, V reduce, exchange, J sweep, epilogue
+    const bool tile_v = !ppj && !h->shards.empty() && h->shards[0].last_tile_v;
+    o->kernel_launches_per_build = kred + (ppjf ? 6 : ppj ? (vht ? 7 : 9) : (tile_v || (!h->shards.empty() && h->shards[0].last_coulomb_fused) ? 6 : 7)) +
                                    ((h->n_ranks * (int)h->shards.size() > 1) ? 1 : 0);  // + mirror after the all-reduce
     return JCDF_OK;
 }

@@ -83,11 +83,13 @@ struct Shard {
     double* ppj_vp = nullptr;          // [pp_chunks * 4][sm_count][32] per-CTA partial V
     bool last_ppj_fused = false;
     bool last_v_in_ht = false;
+    bool last_tile_v = false;  // the last build took V from the TILE half-transform's accumulators
     int32_t* d_ppitems = nullptr;  // cost-balanced work lists of the per-function half-transform
     int32_t* d_ppoff = nullptr;
     int pp_ctas = 0;
     double* dvec = nullptr;    // [pp_rows] weighted density in partner-row space
     double* VpartP = nullptr;  // [slabs][pp_chunks * 128] partial V of the compact Coulomb pass
+    double* Vt = nullptr;      // [sm_count][2][q_len] partial V left by the tile half-transform (coulomb_v_in_ht)
     double* Vitem = nullptr;   // [pp_ctas][pp_chunks][pp_v_slots][128] partial V left by the per-function half-transform
     double* Jpart = nullptr;   // [pp_chunks][pp_rows] partial J per chunk
     int pp_chunks = 0;         // ceil(q_len / 128)
@@ -187,8 +189,8 @@ struct jcdf_handle {
 namespace jcdf {
 
 // ---- kernel launchers (kernels_k.cu / kernels_j.cu / kernels_misc.cu) ----------------------------------------------
-void launch_prep(const Layout& L, Shard& s, int64_t ldc);
-void launch_half_transform(const Layout& L, Shard& s, int sm_count, bool bigreg);
+void launch_prep(const Layout& L, Shard& s, int64_t ldc, bool with_density);
+void launch_half_transform(const Layout& L, Shard& s, int sm_count, bool bigreg, bool v_in_ht);
 void launch_pp_pack(const Layout& L, Shard& s);                        // kernels_pp.cu: Bp -> Bc
 void launch_pp_prep(const Layout& L, Shard& s, int64_t ldc);           // C_occ -> Ci
 void launch_pp_half_transform(const Layout& L, Shard& s, int sm_count, bool v_in_ht, bool bigreg);
@@ -198,7 +200,7 @@ void launch_pp_coulomb(const Layout& L, Shard& s, cudaStream_t st, cudaEvent_t e
 int64_t pp_coulomb_slabs(const Layout& L);
 bool launch_pp_coulomb_fused(const Layout& L, Shard& s, int sm_count, cudaStream_t st);
 void launch_exchange(const Layout& L, Shard& s, int sm_count, bool dedicated_producer);
-void launch_coulomb(const Layout& L, Shard& s, int sm_count, cudaStream_t st);
+void launch_coulomb(const Layout& L, Shard& s, int sm_count, cudaStream_t st, bool have_v);
 bool launch_coulomb_fused(const Layout& L, Shard& s, int sm_count, cudaStream_t st);
 void launch_epilogue(const Layout& L, Shard& s, bool add_H);
 void launch_mirror_lower(const Layout& L, Shard& s);

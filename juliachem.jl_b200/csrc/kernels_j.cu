@@ -99,10 +99,11 @@ __global__ void __launch_bounds__(256) k_coulomb_j(const double* __restrict__ Bp
     }
 }
 
-void launch_coulomb(const Layout& L, Shard& s, int sm_count, cudaStream_t st) {
+void launch_coulomb(const Layout& L, Shard& s, int sm_count, cudaStream_t st, bool have_v) {
     if (s.q_len <= 0) return;
     int grid_v = (int)std::min<int64_t>(s.q_len, (int64_t)sm_count * 8);
-    k_coulomb_v<<<grid_v, 256, 0, st>>>(s.Bp, s.dt, s.V, L.row_len, (int)s.q_len);
+    // have_v: V already came out of the half-transform's accumulators (no density, no first sweep over B)
+    if (!have_v) k_coulomb_v<<<grid_v, 256, 0, st>>>(s.Bp, s.dt, s.V, L.row_len, (int)s.q_len);
     record_event(s, s.ev[EV_V], st);  // boundary V | J
     const int64_t n2 = L.row_len / 2;
     int gx = (int)((n2 + 255) / 256);

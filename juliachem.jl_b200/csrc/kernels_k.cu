@@ -88,12 +88,13 @@ __global__ void __launch_bounds__(256) k_density_packed(const double* __restrict
     }
 }
 
-void launch_prep(const Layout& L, Shard& s, int64_t ldc) {
+void launch_prep(const Layout& L, Shard& s, int64_t ldc, bool with_density) {
     int64_t total = (int64_t)L.nb * L.n_mt * 32 * L.bm;
     int blocks = (int)std::min<int64_t>((total + 255) / 256, 148 * 16);
     if (!(L.pp_enabled && s.Bc != nullptr))  // the per-function half-transform reads Ci (launch_pp_prep) instead
         k_prep_cs<<<blocks, 256, 0, s.stream>>>(s.Craw, ldc, s.Cs, (int)L.N, (int)L.occ, L.nb, L.n_mt, L.bm, s.d_inv);
-    k_density_packed<<<(int)L.tiles_kept, 256, 0, s.stream>>>(s.Craw, ldc, s.dt, s.d_tile_a, s.d_tile_b, (int)L.N,
+    if (with_density)
+        k_density_packed<<<(int)L.tiles_kept, 256, 0, s.stream>>>(s.Craw, ldc, s.dt, s.d_tile_a, s.d_tile_b, (int)L.N,
                                                                (int)L.occ, s.d_inv);
 }
 
@@ -112,6 +113,7 @@ struct HTParams {
     int q_len, nb, n_mt, npt64, occ_w, n_valid_last;
     int64_t n_items;
     int64_t w_elems, bp_elems, cs_elems;  // buffer extents in doubles (read by the bounds-checked build only)
+    double* vt;   // [CTA][M half][q_len] partial Coulomb vector from the accumulators (WITH_V; nullptr otherwise)
 };
 
 // One work item = (quad of auxiliary rows Q0..Q0+3, 32-wide p block pb, M tile of BM = 8*MT occupied orbitals):
@@ -157,7 +159,9 @@ __device__ __forceinline__ void ht_slab(double (&acc)[MT / 2][4][2], const doubl
 
 // Launched with HT_THREADS = 288: warp 8 is a dedicated copy producer (its lane 0 runs the whole produce() sequence, as
 // far ahead as the ring allows) and warps 0-7 only compute.
-template <int MT, bool BIGREG>
+// WITH_V: the epilogue also adds the item's share of the Coulomb vector, V[Q] = sum_p sum_i C[p,i] W[Q,i,p], to
+// the slot of (CTA, M half, Q) — one warp, hence one thread, per address: the reductions are bit-reproducible.
+template <int MT, bool BIGREG, bool WITH_V>
 __global__ void __launch_bounds__(BIGREG ? HT_THREADS_BIG : HT_THREADS, 1) k_half_transform(HTParams prm) {
     constexpr int BM = 8 * MT;
     constexpr int MH = MT / 2;
@@ -271,27 +275,61 @@ __global__ void __launch_bounds__(BIGREG ? HT_THREADS_BIG : HT_THREADS, 1) k_hal
                     }
                 }
             }
+            if constexpr (WITH_V) {
+                // C[p, i] of the warp's block comes from the same Cs slab the k loop used for q block pb (zero beyond N / occ)
+                const double* cs = prm.Cs + ((int64_t)pb * n_mt + mt) * (32 * BM);
+                double v = 0.0;
+#pragma unroll
+                for (int jm = 0; jm < MH; jm++) {
+                    const int m = m0 + 8 * jm + g;
+#pragma unroll
+                    for (int jn = 0; jn < 4; jn++) {
+                        const int kr0 = 8 * jn + 2 * t;
+                        v = fma(acc[jm][jn][0], cs[kr0 * BM + swz(kr0, m)], v);
+                        v = fma(acc[jm][jn][1], cs[(kr0 + 1) * BM + swz(kr0 + 1, m)], v);
+                    }
+                }
+                v = warp_sum(v);
+                if (lane == 0)
+                    asm volatile("red.global.add.f64 [%0], %1;" ::"l"(prm.vt + ((int64_t)blockIdx.x * 2 + (warp >> 2)) * prm.q_len + qrow), "d"(v)
+                                 : "memory");
+            }
         }
     }
+}
+
+// V[Q] = sum over (CTA, M half) of the partial Coulomb vectors the tile half-transform left, in a fixed order
+__global__ void k_vt_reduce(const double* __restrict__ vt, double* __restrict__ V, int n_parts, int q_len) {
+    const int q = blockIdx.x * blockDim.x + threadIdx.x;
+    if (q >= q_len) return;
+    double v = 0.0;
+    for (int c = 0; c < n_parts; c++) v += vt[(int64_t)c * q_len + q];
+    V[q] = v;
 }
 
 size_t half_transform_smem_bytes(int bm) {
     return (size_t)NSTAGE * (32 * bm + 4 * TILE_ELEMS) * 8 + 2 * NSTAGE * 8 + NSTAGE * 4 + 16;
 }
 
+template <int MT, bool BIGREG, bool WITH_V>
+static void launch_ht_k(const HTParams& prm, int grid, size_t smem, cudaStream_t st) {
+    cudaFuncSetAttribute(k_half_transform<MT, BIGREG, WITH_V>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+    k_half_transform<MT, BIGREG, WITH_V><<<grid, BIGREG ? HT_THREADS_BIG : HT_THREADS, smem, st>>>(prm);
+}
+
 template <int MT>
 static void launch_ht_t(const HTParams& prm, int grid, bool bigreg, cudaStream_t st) {
     size_t smem = half_transform_smem_bytes(8 * MT);
-    if (bigreg) {
-        cudaFuncSetAttribute(k_half_transform<MT, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
-        k_half_transform<MT, true><<<grid, HT_THREADS_BIG, smem, st>>>(prm);
+    if (prm.vt != nullptr) {
+        if (bigreg) launch_ht_k<MT, true, true>(prm, grid, smem, st);
+        else launch_ht_k<MT, false, true>(prm, grid, smem, st);
     } else {
-        cudaFuncSetAttribute(k_half_transform<MT, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
-        k_half_transform<MT, false><<<grid, HT_THREADS, smem, st>>>(prm);
+        if (bigreg) launch_ht_k<MT, true, false>(prm, grid, smem, st);
+        else launch_ht_k<MT, false, false>(prm, grid, smem, st);
     }
 }
 
-void launch_half_transform(const Layout& L, Shard& s, int sm_count, bool bigreg) {
+void launch_half_transform(const Layout& L, Shard& s, int sm_count, bool bigreg, bool v_in_ht) {
     HTParams prm;
     prm.Bp = s.Bp;
     prm.row_len = L.row_len;
@@ -313,6 +351,8 @@ void launch_half_transform(const Layout& L, Shard& s, int sm_count, bool bigreg)
     prm.cs_elems = (int64_t)L.nb * L.n_mt * 32 * L.bm;
     int grid = (int)std::min<int64_t>(prm.n_items, sm_count);
     if (grid <= 0) return;
+    prm.vt = (v_in_ht && s.Vt != nullptr) ? s.Vt : nullptr;
+    if (prm.vt) cudaMemsetAsync(s.Vt, 0, sizeof(double) * (size_t)grid * 2 * (size_t)s.q_len, s.stream);  // the slots are summed into
     switch (L.bm / 8) {
         case 2: launch_ht_t<2>(prm, grid, bigreg, s.stream); break;
         case 4: launch_ht_t<4>(prm, grid, bigreg, s.stream); break;
@@ -324,6 +364,7 @@ void launch_half_transform(const Layout& L, Shard& s, int sm_count, bool bigreg)
         case 16: launch_ht_t<16>(prm, grid, bigreg, s.stream); break;
         default: break;
     }
+    if (prm.vt) k_vt_reduce<<<(unsigned)((s.q_len + 127) / 128), 128, 0, s.stream>>>(s.Vt, s.V, grid * 2, (int)s.q_len);
 }
 
 // =====================================================================================================================

@@ -29,8 +29,9 @@ def _build(N, Q, occ, B, C_occ, H, mask, ndev=1, shards=None, fused=1, overlap=0
 
 
 @pytest.mark.parametrize("N,Q,occ", [(25, 96, 5), (64, 32, 8), (70, 40, 9), (33, 7, 1), (129, 50, 17), (203, 131, 27)])
-@pytest.mark.parametrize("fused,ht_mode", [(1, 1), (0, 1), (1, 2)])
+@pytest.mark.parametrize("fused,ht_mode", [(1, 1), (0, 1), (2, 1), (1, 2)])
 def test_dense_parity(N, Q, occ, fused, ht_mode):
+    # fused = 2 is the default: with the tile family, V from the half-transform's accumulators + one J sweep
     B, C_occ, H = random_inputs(N, Q, occ, seed=N * 1000 + Q)
     F_ref = oracle_fock(B, C_occ, H, None)
     gd, F, st = _build(N, Q, occ, B, C_occ, H, None, fused=fused, ht_mode=ht_mode)
@@ -40,7 +41,8 @@ def test_dense_parity(N, Q, occ, fused, ht_mode):
 
 
 @pytest.mark.parametrize("fused,overlap,ht_mode,coulomb_pp",
-                         [(1, 0, 1, 1), (0, 0, 1, 1), (0, 1, 1, 1), (1, 0, 2, 1), (1, 0, 2, 2), (1, 0, 2, 0), (0, 0, 2, 0)])
+                         [(1, 0, 1, 1), (0, 0, 1, 1), (0, 1, 1, 1), (2, 0, 1, 1), (2, 1, 1, 1), (1, 0, 2, 1), (1, 0, 2, 2), (1, 0, 2, 0),
+                          (0, 0, 2, 0)])
 @pytest.mark.parametrize("N,Q,occ,hw", [(70, 40, 9, 20), (203, 131, 27, 60), (160, 64, 16, 33), (300, 90, 40, 70)])
 def test_screened_parity(N, Q, occ, hw, fused, overlap, ht_mode, coulomb_pp):
     """All three Coulomb schedules (single-pass cooperative kernel, two-pass sweeps, two-pass on the second stream) and
@@ -51,7 +53,7 @@ def test_screened_parity(N, Q, occ, hw, fused, overlap, ht_mode, coulomb_pp):
     # coulomb_pp: 1 = compact Coulomb as one cooperative single-pass kernel, 2 = as two streaming passes, 0 = tile space
     gd, F, st = _build(N, Q, occ, B, C_occ, H, mask, fused=fused, overlap=overlap, ht_mode=ht_mode,
                        coulomb_pp=min(coulomb_pp, 1), pp_fused=int(coulomb_pp == 1))
-    base = (6 if coulomb_pp == 1 else 7) if (ht_mode == 2 and coulomb_pp) else 6 if fused else 7
+    base = (6 if coulomb_pp == 1 else 7) if (ht_mode == 2 and coulomb_pp) else 6 if (fused and ht_mode == 1) or fused == 1 else 7
     assert gd.layout().kernel_launches_per_build in (base, base + 1)  # + k_exchange_reduce when the contraction is sliced
     li = gd.layout()
     assert li.pairs_kept == int(mask.sum())
