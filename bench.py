@@ -230,7 +230,7 @@ def run_reference(args):
         "steps": info["steps_timed"], "warmup": info["warmup"], "steps_requested": args.steps, "warmup_requested": args.warmup,
         "ms_per_step": 1e3 / value, "higher_is_better": True, "scaling": "strong",
         "vs_baseline": None, "dtype": "f64", "extrapolated": info["extrapolated"],
-        "data": "synthetic: random B of the w50 shape and its real Schwarz mask (this arm never touches the GPU library); "
+        "data": "synthetic: random B of the workload's shape and its real Schwarz mask (this arm never touches the GPU library); "
                 "synthetic orthonormal C_occ" if w.real_molecules else "synthetic",
         "config": workload_config(w, args.gpus),
         "cpu_baseline": dict(info, value=value, unit=UNIT),
@@ -242,6 +242,9 @@ def run_reference(args):
 
 
 def data_label(w):
+    if w.real_s22:
+        return ("real: B = L^-1 (P|mn) from 6-31G(2df,p) / cc-pVTZ-JKFIT integrals of S22 complex %d computed on the device, real "
+                "Schwarz mask (df_sigma 1e-5); synthetic orthonormal C_occ and symmetric H (timing is value-independent)" % w.real_s22)
     if w.real_molecules:
         return ("real: B = L^-1 (P|mn) from cc-pVDZ / cc-pVDZ-RIFIT integrals of the w50 geometry computed on the device, "
                 "real Schwarz mask (df_sigma 1e-5); synthetic orthonormal C_occ and symmetric H (timing is value-independent)")
@@ -325,7 +328,7 @@ def run_b200(args):
         # real integrals: basis -> (P|Q) -> Schwarz mask (reference rule, df_sigma 1e-5) -> B = L^-1 (P|mn), all on the
         # device; every rank recomputes what it needs (jcdf_compute_B), so there is no setup exchange between ranks
         from juliachem_jl_b200 import rhf
-        mol = rhf.run_basis(wl.real_molecule(w), {"basis": "cc-pVDZ"})
+        mol = rhf.run_basis(wl.real_molecule(w), {"basis": w.basis})
         assert (mol["primary"].n_functions, mol["auxiliary"].n_functions, mol["n_electrons"] // 2) == (N, Q, occ)
         gd.set_basis(0, *mol["primary"].args())
         gd.set_basis(1, *mol["auxiliary"].args())

@@ -27,6 +27,9 @@ class Workload:
     seed: int
     real_molecules: int = 0  # > 0: the first n molecules of tests/golden/w50_geometry.json with REAL cc-pVDZ/cc-pVDZ-RIFIT
                              # integrals computed on the device (mask from the reference's Schwarz rule, df_sigma = 1e-5)
+    real_s22: int = 0        # > 0: that S22 complex (tests/golden/s22_hco.json, the reference's example_inputs/S22) with REAL
+                             # 6-31G(2df,p) / cc-pVTZ-JKFIT integrals computed on the device
+    basis: str = "cc-pVDZ"   # basis-set name of a real workload (rhf.load_basis_library)
 
 
 WORKLOADS = {
@@ -44,6 +47,10 @@ WORKLOADS = {
     # one rank's share of w50 when Q is sharded over 8 GPUs (profiling stand-in for the 8-GPU per-device work)
     "w50_q600": Workload("w50_q600", "w50 water cluster DF-RHF cc-pVDZ, the 600 auxiliary rows one of 8 GPUs owns", 1250, 600,
                          250, "none", 50, 0.0, 400.0, 1003),
+    # the S22 benzene dimer (parallel displaced) itself with real integrals and its real Schwarz mask (67 % of the pairs
+    # survive) — in the basis the reference's own S22 inputs use, because cc-pVTZ data are not in the snapshot
+    "benzene_dimer_real": Workload("benzene_dimer_real", "S22 benzene dimer DF-RHF, real 6-31G(2df,p) / cc-pVTZ-JKFIT integrals on 1 B200",
+                                   468, 1572, 42, "real", 24, 0.0, 0.0, 1012, real_molecules=1, real_s22=11, basis="6-31G(2df,p)"),
     "c20h42": Workload("c20h42", "C20H42 alkane DF-RHF cc-pVTZ with shell-pair screening mask", 1330, 3490, 81,
                        "chain", 20, 6.5, 300.0, 1004),
     "gly18": Workload("gly18", "glycine oligomer DF-RHF cc-pVTZ, largest B tensor, 8 B200", 3395, 9333, 275, "chain",
@@ -101,6 +108,9 @@ def real_molecule(w: Workload) -> dict:
     import json
     import os
     root = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+    if w.real_s22:
+        m = json.load(open(os.path.join(root, "tests", "golden", "s22_hco.json")))["molecules"][str(w.real_s22)]
+        return {"geometry": m["geometry"], "symbols": m["symbols"], "molecular_charge": m["molecular_charge"]}
     geo = json.load(open(os.path.join(root, "tests", "golden", "w50_geometry.json")))
     n = w.real_molecules
     return {"geometry": geo["geometry"][:9 * n], "symbols": geo["symbols"][:3 * n], "molecular_charge": 0}
@@ -111,9 +121,12 @@ def real_mask(w: Workload):
     bench.py can run without a GPU (tests/golden/w50_mask_sigma1e-5.npy, made by tools/dump_w50_mask.py)."""
     import os
     root = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
-    if w.real_molecules != 50:
+    if w.real_s22:
+        bits = np.load(os.path.join(root, "tests", "golden", "s22_%d_mask_sigma1e-5.npy" % w.real_s22))
+    elif w.real_molecules != 50:
         raise ValueError("only the 50-molecule mask is committed")
-    bits = np.load(os.path.join(root, "tests", "golden", "w50_mask_sigma1e-5.npy"))
+    else:
+        bits = np.load(os.path.join(root, "tests", "golden", "w50_mask_sigma1e-5.npy"))
     m = np.unpackbits(bits)[:w.N * w.N].reshape(w.N, w.N).astype(bool)
     return np.asfortranarray(m)
 
