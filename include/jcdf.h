@@ -277,6 +277,10 @@ int32_t jcdf_debug_exchange_block(int32_t ta, int32_t tb, int32_t warp, int64_t 
  * the CUDA context is unusable afterwards.  compute-sanitizer is closed on the development pool; this build stands in for
  * its memcheck tool.                                                                                                   */
 int32_t jcdf_checked_selftest(int32_t fire);
+/* Checked build only (a no-op otherwise): schedule fuzzing.  With seed != 0 every mbarrier wait / arrive, bulk-copy issue and
+ * grid-wide flag operation of the pipelined kernels is preceded, one time in four, by a pseudo-random sleep of up to 4 us;
+ * results must not depend on the seed.  The stand-in for compute-sanitizer's racecheck, which is closed on the pool.        */
+int32_t jcdf_checked_set_fuzz(jcdf_handle* h, uint32_t seed);
 
 /* The CUDA stream (cudaStream_t, returned as void*) every kernel, copy and all-reduce of device `dev` is issued on —
  * so a caller can bracket builds with its own CUDA events or order its own work against them (the fork's CUDA.jl

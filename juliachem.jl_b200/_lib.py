@@ -62,6 +62,7 @@ SIGNATURES = {
     "jcdf_set_option": (_i32, [_p, C.c_char_p, _i64]),
     "jcdf_get_stream": (_i32, [_p, _i32, C.POINTER(_p)]),
     "jcdf_checked_selftest": (_i32, [_i32]),
+    "jcdf_checked_set_fuzz": (_i32, [_p, C.c_uint32]),
     "jcdf_set_basis": (_i32, [_p, _i32, _i64, _p, _p, _p, _p, _p]),
     "jcdf_compute_two_center": (_i32, [_p, _p]),
     "jcdf_compute_schwarz_mask": (_i32, [_p, _f64, _p, C.POINTER(_i64)]),

@@ -1428,6 +1428,19 @@ int32_t jcdf_exchange_cta_cycles(jcdf_handle* h, int32_t dev, int64_t* out, int3
     return s.xplan.n_ctas;
 }
 
+int32_t jcdf_checked_set_fuzz(jcdf_handle* h, uint32_t seed) {
+    JC_REQUIRE(h != nullptr, "jcdf_checked_set_fuzz: NULL handle");
+    for (Shard& s : h->shards) {
+        JC_CUDA(cudaSetDevice(s.dev));
+        JC_CUDA(cudaStreamSynchronize(s.stream));
+        set_fuzz_seed_k(seed);
+        set_fuzz_seed_pp(seed);
+        set_fuzz_seed_j(seed);
+        JC_CUDA(cudaGetLastError());
+    }
+    return JCDF_OK;
+}
+
 int32_t jcdf_get_stream(jcdf_handle* h, int32_t dev, void** stream_out) {
     JC_REQUIRE(h && stream_out, "jcdf_get_stream: NULL argument");
     JC_REQUIRE(dev >= 0 && dev < (int)h->shards.size(), "jcdf_get_stream: device index out of range");

@@ -18,8 +18,29 @@
             __trap();                                                                                                    \
         }                                                                                                                \
     } while (0)
+// Schedule fuzzing of the checked build (no racecheck on this pool): with a non-zero seed every mbarrier wait / arrive, every
+// bulk-copy issue and every grid-wide flag operation is preceded, one time in four, by a pseudo-random sleep of up to 4 us that
+// depends on the seed, the CTA, the warp and the clock.  The pipelines must then give bit-identical results for every seed;
+// a missing ordering shows up as a changed result (tools/sanitizer_cases.py --fuzz N).  One copy of the seed per translation
+// unit; JC_DEFINE_FUZZ_SETTER(name) generates the host function that sets it.
+static __device__ unsigned int jc_fuzz_seed = 0;
+__device__ __forceinline__ void jc_fuzz(unsigned int salt) {
+    const unsigned int s = jc_fuzz_seed;
+    if (s == 0) return;
+    unsigned int h = s ^ (salt * 0x9E3779B1u) ^ (blockIdx.x * 2654435761u) ^ ((threadIdx.x >> 5) * 40503u) ^ (unsigned int)clock();
+    h ^= h >> 13;
+    h *= 0x5bd1e995u;
+    h ^= h >> 15;
+    if ((h & 3u) == 0u) __nanosleep((h >> 20) & 0xFFFu);
+}
+#define JC_FUZZ(salt) jc_fuzz(salt)
+#define JC_DEFINE_FUZZ_SETTER(name) \
+    void name(unsigned int seed) { cudaMemcpyToSymbol(jc_fuzz_seed, &seed, sizeof(seed)); }
 #else
 #define JC_CHECK(cond, what) ((void)0)
+#define JC_FUZZ(salt) ((void)0)
+#define JC_DEFINE_FUZZ_SETTER(name) \
+    void name(unsigned int) {}
 #endif
 
 namespace jcdf {
@@ -45,12 +66,15 @@ __device__ __forceinline__ void fence_barrier_init() {
 }
 __device__ __forceinline__ void fence_proxy_async() { asm volatile("fence.proxy.async.shared::cta;" ::: "memory"); }
 __device__ __forceinline__ void mbar_arrive_expect_tx(uint64_t* bar, uint32_t bytes) {
+    JC_FUZZ(1);
     asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(smem_u32(bar)), "r"(bytes) : "memory");
 }
 __device__ __forceinline__ void mbar_arrive(uint64_t* bar) {
+    JC_FUZZ(2);
     asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0];" ::"r"(smem_u32(bar)) : "memory");
 }
 __device__ __forceinline__ void mbar_wait(uint64_t* bar, uint32_t parity) {
+    JC_FUZZ(3);
     asm volatile(
         "{\n"
         ".reg .pred P1;\n"
@@ -65,6 +89,7 @@ __device__ __forceinline__ void mbar_wait(uint64_t* bar, uint32_t parity) {
 }
 // 1-D bulk async copy global -> shared, completion counted in bytes on an mbarrier (TMA unit; SASS UBLKCP).
 __device__ __forceinline__ void bulk_g2s(void* dst_smem, const void* src_gmem, uint32_t bytes, uint64_t* bar) {
+    JC_FUZZ(4);
     asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];" ::"r"(
                      smem_u32(dst_smem)),
                  "l"(src_gmem), "r"(bytes), "r"(smem_u32(bar))

@@ -214,6 +214,9 @@ size_t exchange_smem_bytes();
 int exchange_tile_cost(int tile, int N);  // kernels_k.cu: DMMA row units per k-step on the busiest sub-partition
 int kernels_per_build();
 
+void set_fuzz_seed_k(unsigned int seed);   // checked build: schedule-fuzzing seed of each kernel translation unit
+void set_fuzz_seed_pp(unsigned int seed);
+void set_fuzz_seed_j(unsigned int seed);
 void set_error(const std::string& msg);
 // timing event on the shard's stream: a plain record when launching eagerly, an external event-record NODE while the
 // launch sequence is being captured into a graph (so every replay still timestamps the stage boundaries)

@@ -153,11 +153,13 @@ struct FJParams {
 };
 
 __device__ __forceinline__ unsigned int ld_acquire_u32(const unsigned int* p) {
+    JC_FUZZ(5);
     unsigned int v;
     asm volatile("ld.acquire.gpu.global.u32 %0, [%1];" : "=r"(v) : "l"(p) : "memory");
     return v;
 }
 __device__ __forceinline__ void red_release_add_u32(unsigned int* p, unsigned int v) {
+    JC_FUZZ(6);
     asm volatile("red.release.gpu.global.add.u32 [%0], %1;" ::"l"(p), "r"(v) : "memory");
 }
 
@@ -372,5 +374,7 @@ bool launch_coulomb_fused(const Layout& L, Shard& s, int sm_count, cudaStream_t 
     }
     return true;
 }
+
+JC_DEFINE_FUZZ_SETTER(set_fuzz_seed_j)
 
 }  // namespace jcdf

@@ -768,6 +768,8 @@ void launch_epilogue(const Layout& L, Shard& s, bool add_H) {
                                                   (int)L.N, L.nb, s.xplan.n_tiles, n_slices);
 }
 
+JC_DEFINE_FUZZ_SETTER(set_fuzz_seed_k)
+
 }  // namespace jcdf
 
 extern "C" int32_t jcdf_debug_exchange_block(int32_t ta, int32_t tb, int32_t warp, int64_t N, int32_t* out4 /* 5 values */) {

@@ -540,11 +540,13 @@ struct PJFParams {
 };
 
 __device__ __forceinline__ unsigned int pjf_ld_acquire(const unsigned int* p) {
+    JC_FUZZ(7);
     unsigned int v;
     asm volatile("ld.acquire.gpu.global.u32 %0, [%1];" : "=r"(v) : "l"(p) : "memory");
     return v;
 }
 __device__ __forceinline__ void pjf_red_release(unsigned int* p) {
+    JC_FUZZ(8);
     asm volatile("red.release.gpu.global.add.u32 [%0], 1;" ::"l"(p) : "memory");
 }
 __device__ __forceinline__ double2 pjf_ld2(const double* p) {  // plain (L2-allocating) 16-byte load
@@ -894,5 +896,7 @@ void launch_pp_half_transform(const Layout& L, Shard& s, int sm_count, bool v_in
         }
     }
 }
+
+JC_DEFINE_FUZZ_SETTER(set_fuzz_seed_pp)
 
 }  // namespace jcdf

@@ -332,6 +332,10 @@ class B200Data:
             check(n)
         return out[:n]
 
+    def checked_set_fuzz(self, seed: int) -> None:
+        """Checked build only: seed of the schedule fuzzing (0 = off); results must not depend on it."""
+        check(self._lib.jcdf_checked_set_fuzz(self._h, int(seed)))
+
     def stream(self, dev: int = 0) -> int:
         """cudaStream_t (as an integer) the builds of device `dev` run on — wrap with torch.cuda.ExternalStream."""
         out = C.c_void_p()

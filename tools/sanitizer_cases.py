@@ -31,7 +31,9 @@ CASES = [
 
 
 def main():
-    only = [a for a in sys.argv[1:] if a != "--fire"]
+    args = sys.argv[1:]
+    n_fuzz = int(args[args.index("--fuzz") + 1]) if "--fuzz" in args else 0
+    only = [a for i, a in enumerate(args) if a not in ("--fire", "--fuzz") and not (i > 0 and args[i - 1] == "--fuzz")]
     lib = jc.load_library()
     print("library: %s  (bounds-checked build: %s)" % (jc.LIB_PATH, bool(lib.jcdf_checked_selftest(0))), flush=True)
     worst = 0.0
@@ -49,10 +51,24 @@ def main():
         F2 = gd.fock_build(C_occ, None)[0]
         err = float(np.abs(F - oracle_fock(B, C_occ, H, mask)).max())
         li = gd.layout()
+        fuzz_note = ""
+        if n_fuzz:  # schedule fuzzing (checked build): random sleeps at every barrier / copy / flag; results must not move
+            worst_f, changed = 0.0, 0
+            for seed in range(1, n_fuzz + 1):
+                gd.checked_set_fuzz(seed)
+                Ff = gd.fock_build(C_occ, None)[0]
+                d = float(np.abs(Ff - F).max())
+                worst_f = max(worst_f, d)
+                changed += int(not np.array_equal(Ff, F))
+            gd.checked_set_fuzz(0)
+            fuzz_note = "  fuzz seeds=%d changed=%d max|dF|=%.1e" % (n_fuzz, changed, worst_f)
+            # (the tile family's two-pass J sweep adds row slabs with atomics when rows are short: equal to rounding only)
+            if worst_f > (1e-12 if name == "tiles_two_pass_coulomb" else 0.0):
+                raise SystemExit("%s: the result depends on the schedule (max|dF| = %.3e)%s" % (name, worst_f, fuzz_note))
         gd.close()
         worst = max(worst, err)
         print("%-26s N=%d Q=%d occ=%d launches/build=%d graph_replays=%d  max|F-F_oracle|=%.2e  repeat identical=%s" % (
-            name, N, Q, occ, li.kernel_launches_per_build, li.graph_replays, err, bool(np.array_equal(F, F2))), flush=True)
+            name, N, Q, occ, li.kernel_launches_per_build, li.graph_replays, err, bool(np.array_equal(F, F2))) + fuzz_note, flush=True)
     if not worst < 1e-10:
         raise SystemExit("parity failed: %.3e" % worst)
     if "--fire" in sys.argv:  # last: a check that MUST fail (kills the context)
