@@ -229,9 +229,9 @@ double jcdf_synthetic_value(uint64_t seed, int64_t Q_total, int64_t q_aux, int64
  * 0 = default, chosen from the mask by executed DMMA count; 1 = 32 x 32 tiles with strip skipping; 2 = per-function
  * partner lists over a partner-compacted copy of B = calculate_W_screened's own blocking, ScreenedDF.jl:242-289),
  * "coulomb_pp" (1 = default: with the per-function kernel the Coulomb passes stream the compact copy too),
- * "coulomb_v_in_ht" (1 = default: with the per-function kernel and the compact Coulomb, V[Q] = sum_p sum_i C[p,i] W[Q,i,p]
- * is taken from the half-transform's accumulators, so the Coulomb build needs no density pass and streams B once
- * instead of twice; 0 = density + separate V pass),
+ * "coulomb_v_in_ht" (1 = default: V[Q] = sum_p sum_i C[p,i] W[Q,i,p] is taken from the half-transform's accumulators — by the
+ * per-function kernel whenever the compact Coulomb is active, by the tile kernel when "coulomb_fused" is left at 2 — so the
+ * Coulomb build needs no density pass and streams B once instead of twice; 0 = density + separate V pass),
  * "pp_layout" (consumer warp arrangement of the per-function kernel: -1 = default, chosen from occ; 0 = 2 x 4 warps,
  * orbitals padded to 32 per item; 1 = 8 x 1 warps, no padding beyond the 8-wide DMMA tile),
  * "pp_max_bytes" (cap on the compact copy per shard; above it — or when cudaMalloc refuses — the automatic choice falls
