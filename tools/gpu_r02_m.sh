@@ -27,3 +27,7 @@ try:
 except Exception as e:
     print("gly18 failed", e)
 PY
+# which NCCL algorithm serves the 12.5 MB all-reduce at 8 ranks (NVLS = in-switch reduction)
+NCCL_DEBUG=INFO NCCL_DEBUG_SUBSYS=INIT,COLL,TUNING timeout 600 python -m torch.distributed.run --nnodes=1 --nproc-per-node 8 --master-addr 127.0.0.1 --master-port 29531 \
+    bench.py --gpus 8 --steps 3 --warmup 3 --no-e2e > gpurun_out/m_nccl_debug.json 2> gpurun_out/m_nccl_debug.err
+grep -E "NVLS|Using network|Channel|algorithm|Algo|nvls" gpurun_out/m_nccl_debug.err | sort | uniq -c | sort -rn | head -12 > gpurun_out/m_nccl_summary.txt; cat gpurun_out/m_nccl_summary.txt | cut -c1-200
