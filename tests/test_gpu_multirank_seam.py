@@ -2,7 +2,8 @@
 its rank, the rank count and the NCCL id (julia/B200DF.jl does the same with MPI.Comm_rank / MPI.Bcast!), shards by the
 reference's auxiliary-shell rule, computes its own rows of B on its device (jcdf_compute_B) and receives the full Fock matrix
 from the NCCL all-reduce inside the library.  Checked on every rank against the oracle's screened build over the same number
-of emulated ranks (1e-10) and for bit-identity across ranks.  Needs as many GPUs as ranks."""
+of emulated ranks — on the B rows read back from the devices (1e-10) and on the oracle's own integrals (5e-9: the metric's
+conditioning) — and for bit-identity across ranks.  Needs as many GPUs as ranks."""
 import json
 import os
 import subprocess
@@ -27,4 +28,5 @@ def test_seam_on_several_ranks_matches_the_oracle(world):
     assert sorted(l["rank"] for l in lines) == list(range(world))
     assert sum(l["q_local"] for l in lines) == 332          # the shards of all ranks cover the auxiliary basis exactly once
     for l in lines:
-        assert l["max_abs_err"] < 1e-10 and l["identical_to_rank0"] and l["allreduce_key"]
+        assert l["max_abs_err"] < 1e-10 and l["max_abs_err_independent_integrals"] < 5e-9
+        assert l["identical_to_rank0"] and l["allreduce_key"]
