@@ -287,6 +287,28 @@ int32_t jcdf_checked_set_fuzz(jcdf_handle* h, uint32_t seed);
  * path uses the task-local default stream and CUDA.synchronize() instead, GPUDF.jl:206-263).                     */
 int32_t jcdf_get_stream(jcdf_handle* h, int32_t dev, void** stream_out);
 
+/* No counterpart in the reference: added for callers that may not allocate (code
+ * under CUDA graph capture, tight serving loops, harnesses that forbid cudaMalloc).  One dense Fock build
+ *     F = H + 2 J[D] - K[D],  D = C_occ C_occ^T,  over B = L^-1 (P|mn)
+ * — the contraction of jcdf_fock_build on a single unscreened shard — that calls no cudaMalloc / cudaFree and no allocating
+ * library routine: its scratch (the half-transformed W, the Coulomb vector, per-chunk partial Fock matrices) is a fixed
+ * file-scope __device__ array of 1 722 368 bytes (csrc/no_alloc.cu) that every GPU loading the library holds until exit.
+ * Sizes beyond JCDF_NO_ALLOC_MAX_* are refused with JCDF_ERR_INVALID (use jcdf_create + jcdf_fock_build there).
+ *   B_dev      Q x N^2 column-major, leading dimension ldb >= Q: B[Q, p + N q], symmetric in (p, q) — the layout
+ *              jcdf_set_B takes when no mask is set
+ *   C_occ_dev  N x occ column-major, leading dimension ldc >= N;  H_dev  N x N column-major or NULL
+ *   F_out_dev  N x N column-major, fully overwritten, exactly symmetric
+ *   stream     cudaStream_t (NULL = the default stream) of the CURRENT device, to which all four pointers must belong; the
+ *              four kernels are enqueued there and the call returns without synchronising.
+ * All calls on one GPU share the array and it keeps the last call's contents (every word read is rewritten first, nothing
+ * needs clearing): calls ordered on one stream are safe, calls that overlap on the GPU race.  The first call on each device
+ * looks up the array's device address (cudaGetSymbolAddress); make that call outside a stream capture.                  */
+#define JCDF_NO_ALLOC_MAX_N 48
+#define JCDF_NO_ALLOC_MAX_Q 256
+#define JCDF_NO_ALLOC_MAX_OCC 16
+int32_t jcdf_fock_build_no_alloc(int64_t N, int64_t Q, int64_t occ, const double* B_dev, int64_t ldb,
+                                 const double* C_occ_dev, int64_t ldc, const double* H_dev, double* F_out_dev, void* stream);
+
 #ifdef __cplusplus
 }
 #endif

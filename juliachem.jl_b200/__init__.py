@@ -7,6 +7,6 @@ shim `juliachem_jl_b200` (or importlib)."""
 from ._lib import JCDFError, LayoutInfo, STAGE_NAMES, load_library, LIB_PATH  # noqa: F401
 from .df import (  # noqa: F401
     B200Data, CONTRACTION_MODE_B200, IntegralSource, JCTiming, SCFData, SCFOptions, ScreeningData,
-    balanced_function_shards, device_count, df_rhf_fock_build_B200, get_df_static_shell_indices,
+    balanced_function_shards, device_count, df_rhf_fock_build_B200, fock_build_no_alloc, get_df_static_shell_indices,
     sparse_pq_index_map, static_load_rank_indicies, unique_id,
 )

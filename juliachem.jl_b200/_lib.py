@@ -63,6 +63,7 @@ SIGNATURES = {
     "jcdf_get_stream": (_i32, [_p, _i32, C.POINTER(_p)]),
     "jcdf_checked_selftest": (_i32, [_i32]),
     "jcdf_checked_set_fuzz": (_i32, [_p, C.c_uint32]),
+    "jcdf_fock_build_no_alloc": (_i32, [_i64, _i64, _i64, _p, _i64, _p, _i64, _p, _p, _p]),
     "jcdf_set_basis": (_i32, [_p, _i32, _i64, _p, _p, _p, _p, _p]),
     "jcdf_compute_two_center": (_i32, [_p, _p]),
     "jcdf_compute_schwarz_mask": (_i32, [_p, _f64, _p, C.POINTER(_i64)]),

@@ -360,6 +360,16 @@ def unique_id() -> bytes:
     return bytes(buf)
 
 
+def fock_build_no_alloc(N: int, Q: int, occ: int, B_ptr: int, ldb: int, C_occ_ptr: int, ldc: int, H_ptr: int | None,
+                        F_ptr: int, stream: int = 0) -> None:
+    """jcdf_fock_build_no_alloc (no counterpart in the reference; include/jcdf.h): dense F = H + 2J - K on raw device
+    addresses of the current device with the scratch in the library's fixed __device__ array — N <= 48, Q <= 256,
+    occ <= 16; enqueued on `stream`, not synchronised; no allocation on the call path."""
+    check(load_library().jcdf_fock_build_no_alloc(N, Q, occ, C.c_void_p(B_ptr), ldb, C.c_void_p(C_occ_ptr), ldc,
+                                                   C.c_void_p(H_ptr) if H_ptr else None, C.c_void_p(F_ptr),
+                                                   C.c_void_p(stream) if stream else None))
+
+
 def device_count() -> int:
     n = load_library().jcdf_device_count()
     if n < 0:
