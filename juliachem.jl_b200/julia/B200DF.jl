@@ -249,3 +249,15 @@ function scf_get_B200(scf_data, name::String)
     jcdf_check(ccall((:jcdf_scf_get, libjcdf), Cint, (Ptr{Cvoid}, Cstring, Ptr{Float64}), gd.handle, name, out))
     return out
 end
+
+# ---- allocation-free dense build (no counterpart in the reference) -------
+# For callers that may not allocate (CUDA graph capture, serving loops): B (Q x N^2), C_occ (N x occ), H and F are device
+# arrays of the CURRENT device — e.g. CUDA.jl CuArray{Float64}, passed as reinterpret(Ptr{Cvoid}, pointer(x)) — and
+# `stream` a cudaStream_t (C_NULL = default stream).  Scratch is a fixed __device__ array inside libjcdf: N <= 48, Q <= 256,
+# occ <= 16, refused beyond; calls that overlap on one GPU race on it.  The call enqueues and returns.
+function fock_build_no_alloc_B200!(F_dev::Ptr{Cvoid}, B_dev::Ptr{Cvoid}, C_occ_dev::Ptr{Cvoid}, H_dev::Ptr{Cvoid},
+    N::Int, Q::Int, occ::Int; ldb::Int = Q, ldc::Int = N, stream::Ptr{Cvoid} = C_NULL)
+    jcdf_check(ccall((:jcdf_fock_build_no_alloc, libjcdf), Cint,
+        (Int64, Int64, Int64, Ptr{Cvoid}, Int64, Ptr{Cvoid}, Int64, Ptr{Cvoid}, Ptr{Cvoid}, Ptr{Cvoid}),
+        Int64(N), Int64(Q), Int64(occ), B_dev, Int64(ldb), C_occ_dev, Int64(ldc), H_dev, F_dev, stream))
+end
