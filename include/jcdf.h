@@ -118,7 +118,9 @@ int32_t jcdf_set_core_hamiltonian(jcdf_handle* h, const double* H);
  * NCCL all-reduce on the devices.
  *   C_occ  N x occ column-major, leading dimension ldc (host)
  *   H      N x N column-major or NULL (host); only added when this process owns global shard 0
- *   F_out  N x N column-major (host), fully overwritten, exactly symmetric; not retained
+ *   F_out  N x N column-major (host), fully overwritten, exactly symmetric; not retained.  With the option
+ *          "exchange_block_screen" and a mask that drops K blocks it is IN/OUT like scf_data.two_electron_fock in the
+ *          reference: the elements of dropped blocks come back as F_out_in + H (rank 0), summed over ranks — see the option
  *   stage_seconds  NULL or double[JCDF_N_STAGES]                                                                 */
 int32_t jcdf_fock_build(jcdf_handle* h, const double* C_occ, int64_t ldc, const double* H, double* F_out,
                         double* stage_seconds);
@@ -212,6 +214,12 @@ typedef struct jcdf_layout_info {
                                * partner-compacted second copy when the per-function family is active)   */
     int64_t kernel_launches_per_build; /* launches of this library's own kernels per build  */
     int64_t graph_replays;    /* builds (summed over devices) whose kernel sequence ran as a CUDA-graph replay */
+    /* block-screened exchange (option "exchange_block_screen"; all 0 when it is off or the mask is NULL): */
+    int64_t exchange_blocks_total;   /* JCTC.total_exchange_blocks: lower-triangular K blocks of the reference's grid      */
+    int64_t exchange_blocks_kept;    /* JCTC.unscreened_exchange_blocks: length(blocks_to_calculate), ScreenedDF.jl:454      */
+    int64_t exchange_block_width;    /* K_block_width (:392-397)                                                            */
+    int64_t exchange_tiles_total;    /* this library's own 128 x 128 lower-triangular exchange tiles (always filled)       */
+    int64_t exchange_tiles_skipped;  /* ... of which left out of the work lists: every element lies in a dropped block     */
 } jcdf_layout_info;
 int32_t jcdf_get_layout(jcdf_handle* h, jcdf_layout_info* out);
 
@@ -249,8 +257,19 @@ double jcdf_synthetic_value(uint64_t seed, int64_t Q_total, int64_t q_aux, int64
  * a copy into pageable memory runs at a fraction of the PCIe rate.  Opt-in: the caller must keep that buffer alive until
  * jcdf_destroy; julia/B200DF.jl holds a reference to it inside SCFGPUDataB200 for exactly that reason),
  * "graph" (1 = default: the kernel sequence of a build, prep .. epilogue, is captured into a CUDA graph on the first build
- * and replayed afterwards; 0 = every kernel launched eagerly).  "regroup", "ht_mode", "pp_layout", "pp_order",
- * "pp_max_bytes", "exchange_slices" and "exchange_balance" must be set before jcdf_set_mask.  A refused call (unknown name, value out of
+ * and replayed afterwards; 0 = every kernel launched eagerly),
+ * "exchange_block_screen" (0 = default, off; n > 0 = the reference's keyword df_exchange_screen = true with
+ * df_exchange_n_blocks = n, the caller having replaced 0 by the reference's default of 10: jcdf_set_mask builds
+ * calculate_exchange_block_screen_matrix's K block grid — below 100 functions one block, else width N div n, the remainder
+ * strip never screened — and its block_screen_matrix from the mask, ScreenedDF.jl:385-457, reported by jcdf_get_layout; the
+ * exchange is then calculate_K_lower_diagonal_block, :459-545: K is computed for the kept blocks only.  The reference neither
+ * computes NOR WRITES a dropped block, and its Coulomb copy skips it too because all its pairs are screened (:367-378), so
+ * there scf_data.two_electron_fock keeps what it held — the previous iteration's matrix after the caller's DIIS and damping,
+ * SCF.jl:471-508 — plus H on rank 0, and with n ranks the all-reduce sums n such copies (DensityFitting.jl:62-71).  libjcdf
+ * reproduces exactly that: F_out is read before the build and each shard acts as one rank.  A NULL mask (dense statement)
+ * has no K blocks and ignores the option),
+ * "regroup", "ht_mode", "pp_layout", "pp_order", "pp_max_bytes", "exchange_slices", "exchange_balance" and
+ * "exchange_block_screen" must be set before jcdf_set_mask.  A refused call (unknown name, value out of
  * range, too late) returns JCDF_ERR_INVALID and leaves the handle unchanged.                                          */
 int32_t jcdf_set_option(jcdf_handle* h, const char* name, int64_t value);
 

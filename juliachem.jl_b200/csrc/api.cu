@@ -54,7 +54,7 @@ static void free_shard_buffers(Shard& s, bool keep_metric = false) {
     s.gkey = 0;
     s.graph_broken = false;
     void* ptrs[] = {s.d_pp_trirow, s.ppj_flag, s.ppj_vp, s.d_ppitems, s.d_ppoff, s.d_xcycles, s.Ksum, s.d_xitems, s.d_xoff, s.Bc, s.Ci, s.d_pp_off, s.d_pp_q, s.d_pp_src, s.d_pp_p, s.d_pp_jdst, s.dvec, s.VpartP, s.Vitem, s.Vt, s.Jpart, s.Vpart, s.Vready, s.Bp, s.W, s.Cs, s.Craw, s.dt, s.Jt, s.V, s.Kpart, s.F, s.Hdev, s.Traw, s.d_tile_index, s.d_tile_a,
-                    s.d_tile_b, s.d_dest_of_col, s.d_fn_mask, s.d_kb_list, s.d_kb_count, s.d_perm, s.d_inv, s.d_tile_strips};
+                    s.d_tile_b, s.d_dest_of_col, s.d_fn_mask, s.d_kb_list, s.d_kb_count, s.d_perm, s.d_inv, s.d_tile_strips, s.Fprev, s.d_xs_blk_of, s.d_xs_keep};
     for (void* p : ptrs)
         if (p) cudaFree(p);
     if (!keep_metric) {
@@ -66,6 +66,9 @@ static void free_shard_buffers(Shard& s, bool keep_metric = false) {
     s.d_tile_index = s.d_tile_a = s.d_tile_b = s.d_kb_list = s.d_kb_count = s.d_perm = s.d_inv = s.d_tile_strips = nullptr;
     s.Vpart = nullptr;
     s.Vready = nullptr;
+    s.Fprev = nullptr;
+    s.d_xs_blk_of = nullptr;
+    s.d_xs_keep = nullptr;
     s.Bc = s.Ci = nullptr;
     s.d_pp_off = s.d_pp_q = s.d_pp_src = s.d_pp_p = s.d_pp_jdst = nullptr;
     s.dvec = s.VpartP = s.Vitem = s.Vt = s.Jpart = nullptr;
@@ -85,18 +88,82 @@ static void free_shard_buffers(Shard& s, bool keep_metric = false) {
     s.b_ready = s.t_uploaded = s.has_H = false;
 }
 
+// df_exchange_screen = true (option "exchange_block_screen" = the requested df_exchange_n_blocks, already defaulted by the
+// caller): the reference's K block grid and block_screen_matrix, calculate_exchange_block_screen_matrix
+// (ScreenedDF.jl:385-457) — below 100 functions one block of width N (:392-394), else width = N div n_blocks (:396); a
+// lower-triangular block is kept iff its sub-block of basis_function_screen_matrix holds any pair (:433-441); the strip
+// beyond width * n_blocks is never screened (:519-544).  The exchange tiles of this library live in the INTERNAL function
+// order, so a 128 x 128 tile is left out of the work lists only when every element of it maps into dropped blocks; the
+// epilogue decides element by element in the caller's order, which is what makes the result the reference's.
+static void plan_exchange_block_screen(jcdf_handle* h, const uint8_t* fn_mask) {
+    Layout& L = h->lay;
+    const int64_t N = L.N;
+    L.xs_nblk = L.xs_width = 0;
+    L.xs_blocks_total = L.xs_blocks_kept = L.xs_tiles_skipped = 0;
+    L.xs_any_dropped = false;
+    L.xs_blk_of.clear();
+    L.xs_keep.clear();
+    L.xs_tile_skip.clear();
+    // the dense statement of the contraction (NULL mask) has no K blocks: DensityFitting.jl:185-224
+    if (h->opt_exchange_block_screen <= 0 || fn_mask == nullptr) return;
+    int nblk = (int)std::min<int64_t>(h->opt_exchange_block_screen, N);
+    int width;
+    if (N < 100) { width = (int)N; nblk = 1; }
+    else width = (int)(N / nblk);
+    L.xs_nblk = nblk;
+    L.xs_width = width;
+    L.xs_blocks_total = (int64_t)nblk * (nblk + 1) / 2;
+    L.xs_blk_of.assign((size_t)N, -1);
+    for (int64_t p = 0; p < (int64_t)width * nblk; p++) L.xs_blk_of[(size_t)p] = (int32_t)(p / width);
+    L.xs_keep.assign((size_t)nblk * nblk, 0);
+    for (int bp = 0; bp < nblk; bp++)
+        for (int bq = 0; bq <= bp; bq++) {
+            bool any = false;
+            for (int64_t c = (int64_t)bq * width; c < (int64_t)(bq + 1) * width && !any; c++)
+                for (int64_t r = (int64_t)bp * width; r < (int64_t)(bp + 1) * width; r++)
+                    if (fn_mask[r + N * c]) { any = true; break; }
+            L.xs_keep[(size_t)bp * nblk + bq] = L.xs_keep[(size_t)bq * nblk + bp] = any ? 1 : 0;
+            L.xs_blocks_kept += any;
+        }
+    L.xs_any_dropped = L.xs_blocks_kept < L.xs_blocks_total;
+    // exchange tiles (internal order) whose every in-range element lies in a dropped block
+    const int n128 = L.n128;
+    L.xs_tile_skip.assign((size_t)n128 * (n128 + 1) / 2, 0);
+    if (!L.xs_any_dropped) return;
+    std::vector<std::vector<int32_t>> blocks_of_tile((size_t)n128);
+    std::vector<uint8_t> has_strip((size_t)n128, 0);
+    for (int t = 0; t < n128; t++) {
+        std::vector<uint8_t> seen((size_t)nblk, 0);
+        for (int64_t i = 128 * (int64_t)t; i < std::min<int64_t>(N, 128 * (int64_t)(t + 1)); i++) {
+            const int32_t b = L.xs_blk_of[(size_t)L.inv[(size_t)i]];
+            if (b < 0) has_strip[(size_t)t] = 1;
+            else if (!seen[(size_t)b]) { seen[(size_t)b] = 1; blocks_of_tile[(size_t)t].push_back(b); }
+        }
+    }
+    for (int ta = 0; ta < n128; ta++)
+        for (int tb = 0; tb <= ta; tb++) {
+            bool skip = !has_strip[(size_t)ta] && !has_strip[(size_t)tb];
+            for (size_t i = 0; skip && i < blocks_of_tile[(size_t)ta].size(); i++)
+                for (int32_t bq : blocks_of_tile[(size_t)tb])
+                    if (L.xs_keep[(size_t)blocks_of_tile[(size_t)ta][i] * nblk + bq]) { skip = false; break; }
+            L.xs_tile_skip[(size_t)ta * (ta + 1) / 2 + tb] = skip ? 1 : 0;
+            L.xs_tiles_skipped += skip;
+        }
+}
+
 // Split of the exchange contraction index: items = tiles x slices dealt round-robin to one CTA per SM.
 static void plan_exchange(const Layout& L, Shard& s, int sm_count, bool balance, int64_t forced_slices) {
     ExchangePlan& x = s.xplan;
     x.chunks = (int)((s.q_len * L.occ_w + 31) / 32);
     x.n_tiles = L.n128 * (L.n128 + 1) / 2;
     int max_slices = std::max(1, x.chunks / 8);
-    int want = std::max(1, (12 * sm_count + x.n_tiles - 1) / x.n_tiles);
+    const int live_tiles = std::max(1, x.n_tiles - (int)L.xs_tiles_skipped);  // block-screened exchange: tiles with work
+    int want = std::max(1, (12 * sm_count + live_tiles - 1) / live_tiles);
     int s0 = std::min(want, max_slices);
     int best = s0;
     double best_eff = -1;
     for (int c = s0; c <= std::min(max_slices, s0 + 48); c++) {
-        int64_t items = (int64_t)x.n_tiles * c;
+        int64_t items = (int64_t)live_tiles * c;
         int64_t waves = (items + sm_count - 1) / sm_count;
         double eff = (double)items / (double)(waves * sm_count);
         if (eff > best_eff + 1e-9) { best_eff = eff; best = c; }
@@ -108,7 +175,8 @@ static void plan_exchange(const Layout& L, Shard& s, int sm_count, bool balance,
     // Items cost differently (diagonal tiles issue 10/16 of a full tile's DMMAs, the last tile row is clipped to N, the
     // last slice may be short): deal them to the persistent CTAs longest-first onto the least-loaded CTA.
     const int n_items = x.n_tiles * x.n_slices;
-    x.n_ctas = std::max(1, std::min(n_items, sm_count));
+    auto skipped = [&](int it) { return !L.xs_tile_skip.empty() && L.xs_tile_skip[(size_t)(it % x.n_tiles)] != 0; };
+    x.n_ctas = std::max(1, std::min(live_tiles * x.n_slices, sm_count));
     std::vector<int64_t> cost((size_t)n_items);
     std::vector<int> tile_cost((size_t)x.n_tiles);
     for (int t = 0; t < x.n_tiles; t++) tile_cost[(size_t)t] = exchange_tile_cost(t, (int)L.N);
@@ -117,15 +185,17 @@ static void plan_exchange(const Layout& L, Shard& s, int sm_count, bool balance,
         const int kc0 = slice * x.chunks_per_slice, kc1 = std::min(x.chunks, kc0 + x.chunks_per_slice);
         cost[(size_t)it] = (int64_t)tile_cost[(size_t)(it % x.n_tiles)] * std::max(0, kc1 - kc0) + 6 * 32;  // + epilogue
     }
-    std::vector<int32_t> order((size_t)n_items);
-    for (int it = 0; it < n_items; it++) order[(size_t)it] = it;
-    std::stable_sort(order.begin(), order.end(), [&](int32_t a, int32_t b) { return cost[(size_t)a] > cost[(size_t)b]; });
+    std::vector<int32_t> order;
+    order.reserve((size_t)n_items);
+    for (int it = 0; it < n_items; it++)
+        if (!skipped(it)) order.push_back(it);  // a skipped tile's Kpart stays at its initial zeros and is never read
     std::vector<int64_t> load((size_t)x.n_ctas, 0);
     std::vector<std::vector<int32_t>> bins((size_t)x.n_ctas);
     if (!balance) {  // plain round-robin in item order
-        for (int it = 0; it < n_items; it++) bins[(size_t)(it % x.n_ctas)].push_back(it);
+        for (size_t k = 0; k < order.size(); k++) bins[k % (size_t)x.n_ctas].push_back(order[k]);
         order.clear();
     }
+    std::stable_sort(order.begin(), order.end(), [&](int32_t a, int32_t b) { return cost[(size_t)a] > cost[(size_t)b]; });
     for (int32_t it : order) {
         int best_c = 0;
         for (int c = 1; c < x.n_ctas; c++)
@@ -176,6 +246,14 @@ static int alloc_shard_buffers(jcdf_handle* h, Shard& s) {
     JC_CUDA(cudaMemcpyAsync(s.d_xoff, s.xplan.item_off.data(), sizeof(int32_t) * s.xplan.item_off.size(), cudaMemcpyHostToDevice, s.stream));
     if ((rc = dev_alloc(&s.F, (size_t)L.N * L.N))) return rc;
     if ((rc = dev_alloc(&s.Hdev, (size_t)L.N * L.N))) return rc;
+    if (L.xs_any_dropped) {  // block-screened exchange: the caller's F_out as it arrived + the block tables of the epilogue
+        if ((rc = dev_alloc(&s.Fprev, (size_t)L.N * L.N))) return rc;
+        if ((rc = dev_alloc(&s.d_xs_blk_of, L.xs_blk_of.size()))) return rc;
+        if ((rc = dev_alloc(&s.d_xs_keep, L.xs_keep.size()))) return rc;
+        JC_CUDA(cudaMemsetAsync(s.Fprev, 0, sizeof(double) * L.N * L.N, s.stream));
+        JC_CUDA(cudaMemcpyAsync(s.d_xs_blk_of, L.xs_blk_of.data(), sizeof(int32_t) * L.xs_blk_of.size(), cudaMemcpyHostToDevice, s.stream));
+        JC_CUDA(cudaMemcpyAsync(s.d_xs_keep, L.xs_keep.data(), L.xs_keep.size(), cudaMemcpyHostToDevice, s.stream));
+    }
     if ((rc = dev_alloc(&s.d_tile_index, (size_t)L.nb * L.nb))) return rc;
     if ((rc = dev_alloc(&s.d_tile_a, (size_t)L.tiles_kept))) return rc;
     if ((rc = dev_alloc(&s.d_tile_b, (size_t)L.tiles_kept))) return rc;
@@ -695,6 +773,7 @@ int32_t jcdf_set_mask(jcdf_handle* h, const uint8_t* fn_mask, const int64_t* map
             L.src_of_col[(size_t)col] = L.dest_of_col[(size_t)col];
         }
     build_partner_lists(h, [&](int64_t ri, int64_t ci) { return kept(ri, ci); });
+    plan_exchange_block_screen(h, fn_mask);
     const bool pp_wanted = L.pp_enabled;
     L.mask_set = true;
     integrals_on_set_mask(h);
@@ -1160,6 +1239,12 @@ int fock_build_impl(jcdf_handle* h, const double* C_occ, int64_t ldc, const doub
             }
             b.add_H = s.has_H;
         }
+        if (L.xs_any_dropped)
+            // block-screened exchange: F_out is IN/OUT.  The reference's dropped K blocks are neither computed nor written
+            // (ScreenedDF.jl:494-510), the Coulomb copy skips them too (all their pairs are screened, :367-378), so they keep
+            // what scf_data.two_electron_fock held — the caller's buffer — and receive H on rank 0 (DensityFitting.jl:62-65).
+            JC_CUDA(cudaMemcpyAsync(s.Fprev, F_out, sizeof(double) * nn, device_ptrs ? cudaMemcpyDefault : cudaMemcpyHostToDevice,
+                                    s.stream));
         JC_CUDA(cudaEventRecord(s.ev[EV_H2D], s.stream));
         b.use_pp = L.pp_enabled && s.Bc != nullptr;
         if (b.use_pp && !s.bc_valid) {  // first build after B changed: refresh the partner-compacted copy
@@ -1331,6 +1416,11 @@ int32_t jcdf_get_layout(jcdf_handle* h, jcdf_layout_info* o) {
     o->tiles_total = L.tiles_total; o->tiles_kept = L.tiles_kept;
     o->pairs_kept = L.pairs_kept; o->pairs_tri = L.pairs_tri;
     o->packed_row_len = L.row_len;
+    o->exchange_blocks_total = L.xs_blocks_total;
+    o->exchange_blocks_kept = L.xs_blocks_kept;
+    o->exchange_block_width = L.xs_width;
+    o->exchange_tiles_total = (int64_t)L.n128 * (L.n128 + 1) / 2;
+    o->exchange_tiles_skipped = L.xs_tiles_skipped;
     for (const Shard& s : h->shards) {
         o->q_local += s.q_len;
         o->bytes_B += s.q_len * L.row_len * 8;
@@ -1381,6 +1471,7 @@ int32_t jcdf_set_option(jcdf_handle* h, const char* name, int64_t value) {
         {"ht_mode", &h->opt_ht_mode, true, 0, 2},
         {"regroup", &h->opt_regroup, true, 0, 1},
         {"exchange_slices", &h->opt_exchange_slices, true, 0, 1 << 20},
+        {"exchange_block_screen", &h->opt_exchange_block_screen, true, 0, 1 << 20},
         {"pp_order", &h->opt_pp_order, true, 0, 1},
         {"pp_bigreg", &h->opt_pp_bigreg, false, 0, 1},
         {"exchange_producer", &h->opt_exchange_producer, false, 0, 1},

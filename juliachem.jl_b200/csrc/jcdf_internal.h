@@ -47,6 +47,15 @@ struct Layout {
     std::vector<int32_t> pp_trirow;    // indices of the q >= p rows (pp_jdst >= 0), ascending
     int64_t pp_n_tri = 0;
     std::vector<int32_t> pp_jdst;      // [pp_rows] q >= p rows (the Coulomb half): offset of (q, p) inside Jt; -1 elsewhere
+    // ---- block-screened exchange (option "exchange_block_screen" = df_exchange_screen, ScreenedDF.jl:385-457) ----
+    int xs_nblk = 0;                   // the reference's df_exchange_n_blocks after its own adjustments (0 = option off)
+    int xs_width = 0;                  // K_block_width
+    int64_t xs_blocks_total = 0, xs_blocks_kept = 0;  // lower-triangular blocks / blocks_to_calculate
+    bool xs_any_dropped = false;
+    std::vector<int32_t> xs_blk_of;    // [N] block of a function in the CALLER's order, -1 in the never-screened remainder strip
+    std::vector<uint8_t> xs_keep;      // [xs_nblk * xs_nblk] symmetric block_screen_matrix
+    std::vector<uint8_t> xs_tile_skip;  // [n128 (n128 + 1) / 2] 128 x 128 exchange tiles lying wholly inside dropped blocks
+    int64_t xs_tiles_skipped = 0;
 };
 
 inline int pp_item_orbitals(const Layout& L) { return L.pp_layout ? 8 * L.pp_nt : 32 * L.pp_nt; }
@@ -108,6 +117,9 @@ struct Shard {
     int32_t* d_xoff = nullptr;
     long long* d_xcycles = nullptr;  // [n_ctas] busy cycles of the last exchange launch
     double* F = nullptr;       // N x N column-major partial / reduced Fock
+    double* Fprev = nullptr;   // N x N: the caller's F_out as it arrived (block-screened exchange: dropped blocks keep it)
+    int32_t* d_xs_blk_of = nullptr;  // [N]
+    uint8_t* d_xs_keep = nullptr;    // [xs_nblk * xs_nblk]
     double* Hdev = nullptr;    // N x N (only where H is added)
     double* Traw = nullptr;    // staging window for uploads
     int64_t traw_capacity = 0;
@@ -171,6 +183,7 @@ struct jcdf_handle {
     int64_t opt_pp_max_bytes = 0;      // cap on the partner-compacted copy per shard (0 = whatever cudaMalloc grants)
     int64_t opt_coulomb_pp = 1;       // Coulomb over the partner-compacted copy whenever the per-function path is active
     int64_t opt_ht_mode = 0;          // half-transform: 0 = choose from the mask, 1 = tile kernel, 2 = per-function kernel
+    int64_t opt_exchange_block_screen = 0;  // > 0: df_exchange_screen = true with that many K blocks (ScreenedDF.jl:433-449, 459-545)
     int64_t opt_graph = 1;            // replay the per-build launch sequence as a CUDA graph (device-pointer builds)
     bool graph_dirty = true;          // options / operands changed since the capture
     int64_t opt_register_output = 0;  // 1: page-lock the caller's F_out once it has been seen twice (a Julia Array is pageable);

@@ -699,10 +699,28 @@ void launch_exchange(const Layout& L, Shard& s, int sm_count, bool dedicated_pro
 // =====================================================================================================================
 __global__ void k_fock_epilogue(double* __restrict__ F, const double* __restrict__ H, const double* __restrict__ Jt,
                                 const double* __restrict__ Kpart, const int32_t* __restrict__ tile_index,
-                                const int32_t* __restrict__ perm, int N, int nb, int n_tiles, int n_slices) {
+                                const int32_t* __restrict__ perm, int N, int nb, int n_tiles, int n_slices,
+                                const double* __restrict__ Fprev, const int32_t* __restrict__ xs_blk_of,
+                                const uint8_t* __restrict__ xs_keep, int xs_nblk) {
     const int q = blockIdx.x * blockDim.x + threadIdx.x;
     const int p = blockIdx.y;
     if (q > p || p >= N) return;
+    if (Fprev != nullptr) {
+        // block-screened exchange (calculate_K_lower_diagonal_block, ScreenedDF.jl:494-512): a dropped block is not
+        // written by the K GEMM and not touched by the Coulomb copy (:367-378: all its pairs are screened), so it keeps
+        // the content of two_electron_fock — the caller's buffer as it arrived — plus H on rank 0
+        const int bp = xs_blk_of[p], bq = xs_blk_of[q];
+        if (bp >= 0 && bq >= 0 && !xs_keep[bp * xs_nblk + bq]) {
+            double vpq = Fprev[p + (int64_t)N * q], vqp = Fprev[q + (int64_t)N * p];
+            if (H != nullptr) {
+                vpq += H[p + (int64_t)N * q];
+                vqp += H[q + (int64_t)N * p];
+            }
+            F[p + (int64_t)N * q] = vpq;
+            F[q + (int64_t)N * p] = vqp;
+            return;
+        }
+    }
     // (p, q) in the caller's order -> internal order; K and J are symmetric, so read the (hi, lo) element
     const int pi = perm[p], qi = perm[q];
     const int hi = max(pi, qi), lo = min(pi, qi);
@@ -765,7 +783,8 @@ void launch_epilogue(const Layout& L, Shard& s, bool add_H) {
     dim3 block(128);
     dim3 grid((unsigned)((L.N + 127) / 128), (unsigned)L.N);
     k_fock_epilogue<<<grid, block, 0, s.stream>>>(s.F, add_H ? s.Hdev : nullptr, s.Jt, K, s.d_tile_index, s.d_perm,
-                                                  (int)L.N, L.nb, s.xplan.n_tiles, n_slices);
+                                                  (int)L.N, L.nb, s.xplan.n_tiles, n_slices,
+                                                  L.xs_any_dropped ? s.Fprev : nullptr, s.d_xs_blk_of, s.d_xs_keep, L.xs_nblk);
 }
 
 JC_DEFINE_FUZZ_SETTER(set_fuzz_seed_k)

@@ -239,6 +239,9 @@ int32_t jcdf_scf_init(jcdf_handle* h, const double* S, const double* H, double E
     JC_CUDA(cudaMemcpyAsync(st->F, s0.Hdev, sizeof(double) * nn, cudaMemcpyDeviceToDevice, st->stream));
     if ((rc = scf_iteration(h, st))) return rc;
     JC_CUDA(cudaMemcpyAsync(st->Fold, st->F, sizeof(double) * nn, cudaMemcpyDeviceToDevice, st->stream));
+    // block-screened exchange: F is in/out for jcdf_fock_build, and iteration 1 of the reference starts from
+    // scf_data.two_electron_fock = zeros (DensityFitting.jl:45), not from the guess matrix
+    if (h->lay.xs_any_dropped) JC_CUDA(cudaMemsetAsync(st->F, 0, sizeof(double) * nn, st->stream));
     st->order.clear();
     st->B_dim = 1;
     st->iter = 0;

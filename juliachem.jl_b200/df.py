@@ -429,17 +429,24 @@ def uses_dense_contraction(scf_options: SCFOptions, N: int, n_ranks: int) -> boo
     return bool(scf_options.df_force_dense or (scf_options.df_use_adaptive and N < 800 and n_ranks == 1))
 
 
+DF_EXCHANGE_N_BLOCKS_CPU_DEFAULT = 10  # Constants.jl:13
+
+
 def check_supported_options(scf_options: SCFOptions) -> None:
     """Options of the reference the B200 path cannot honour are refused, not ignored (SCFOptions.jl:86-93).
-    df_exchange_n_blocks only names the reference's K block grid (ScreenedDF.jl:385-417): without df_exchange_screen it
-    changes no result, so any value is accepted."""
-    if scf_options.df_screen_exchange:
-        # ScreenedDF.jl:459-545 writes only the computed blocks of scf_data.two_electron_fock: a dropped block keeps the
-        # previous iteration's Fock values and receives the new J on top, so the result depends on the iteration history
-        raise NotImplementedError("B200 path: df_exchange_screen is refused: the reference's block-screened exchange leaves "
-                                  "dropped blocks holding the previous iteration's values (history-dependent result)")
+    df_exchange_n_blocks names the reference's K block grid (ScreenedDF.jl:385-417): without df_exchange_screen it
+    changes no result, so any value is accepted; with it the grid decides which K blocks exist (exchange_block_screen)."""
     if scf_options.df_exchange_n_blocks < 0:
         raise ValueError("df_exchange_n_blocks must be >= 0")
+
+
+def exchange_block_screen_blocks(scf_options: SCFOptions) -> int:
+    """Value of libjcdf's option "exchange_block_screen" for these options: 0 unless df_exchange_screen is set, else the
+    block count calculate_exchange_block_screen_matrix starts from (ScreenedDF.jl:388-390: 0 -> the CPU default of 10).
+    The N < 100 -> one block rule (:392-394) is applied by the library, which knows N."""
+    if not scf_options.df_screen_exchange:
+        return 0
+    return scf_options.df_exchange_n_blocks or DF_EXCHANGE_N_BLOCKS_CPU_DEFAULT
 
 
 def df_rhf_fock_build_B200(scf_data: SCFData, integrals: IntegralSource, occupied_orbital_coefficients: np.ndarray,
@@ -484,6 +491,10 @@ def df_rhf_fock_build_B200(scf_data: SCFData, integrals: IntegralSource, occupie
             allr = balanced_function_shards(Q, total)
             ranges = allr[rank * ndev:(rank + 1) * ndev]
         gd.set_shards(ranges)
+        # df_exchange_screen = true: K only for the blocks whose mask sub-block holds a pair; dropped blocks keep what
+        # scf_data.two_electron_fock held (ScreenedDF.jl:459-545) — F_out is read before every build.  Before the mask;
+        # the dense statement has no K blocks (DensityFitting.jl:185-224) and the library ignores the option there.
+        gd.set_option("exchange_block_screen", exchange_block_screen_blocks(scf_options))
         basis = integrals.device_basis()
         if basis is not None:
             # integral front-end of the library: nothing but the basis sets crosses the boundary, any number of ranks
@@ -517,6 +528,14 @@ def df_rhf_fock_build_B200(scf_data: SCFData, integrals: IntegralSource, occupie
                 for d, r in enumerate(ranges):
                     gd.upload_three_center(d, integrals.three_center_integrals(r, sd))
                 gd.factor_and_form_B()
+        if scf_options.df_screen_exchange:
+            # what calculate_exchange_block_screen_matrix books (ScreenedDF.jl:409-410, 454)
+            li = gd.layout()
+            if li.exchange_blocks_total:  # 0: dense statement of the contraction, which has no K blocks
+                n_blocks = 1 if N < 100 else exchange_block_screen_blocks(scf_options)
+                jc_timing.non_timing_data["total_exchange_blocks"] = str(li.exchange_blocks_total)
+                jc_timing.non_timing_data["unscreened_exchange_blocks"] = str(li.exchange_blocks_kept)
+                jc_timing.non_timing_data["df_exchange_n_blocks"] = str(n_blocks)
     gd = scf_data.gpu_data
     if gd is None:
         raise RuntimeError("df_rhf_fock_build_B200 called with iteration > 1 before iteration 1")

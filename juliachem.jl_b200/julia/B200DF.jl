@@ -16,6 +16,7 @@ using Libdl
 const libjcdf = get(ENV, "JULIACHEM_LIBJCDF", "libjcdf")   # deps/build.jl puts libjcdf.so next to libjeri.so
 
 const JCDF_N_STAGES = 10
+const JCDF_LAYOUT_INFO_FIELDS = 20   # jcdf_layout_info: 20 x int64_t (include/jcdf.h); 16-17 = exchange_blocks_total / _kept
 # stage slot (0-based in jcdf.h) -> JCTiming key prefix (src/shared/JCTiming.jl:58-107).  Slot 6 (C_occ upload) is what
 # the fork's GPU path books as GPU_non_zero_coeff_time of device 1 (GPUDF.jl:288); slot 9 (J scatter + H add + mirror)
 # as gpu_copy_J_time (GPUDF.jl:289).
@@ -153,12 +154,6 @@ function df_rhf_fock_build_B200!(scf_data, jeri_engine_thread_df::Vector{T}, jer
         if host_integrals && n_ranks > 1
             error("B200 path: JULIACHEM_B200_HOST_INTEGRALS=1 needs one MPI rank (B formation from uploaded integrals does not cross ranks); unset it to compute the integrals on the devices")
         end
-        if scf_options.df_screen_exchange
-            # ScreenedDF.jl:459-545 writes only the computed blocks of scf_data.two_electron_fock: a dropped block keeps the
-            # previous iteration's values and receives the new J on top (history-dependent); df_exchange_n_blocks alone
-            # only names the reference's block grid and changes no result
-            error("B200 path: df_exchange_screen is refused: the reference's block-screened exchange leaves dropped blocks holding the previous iteration's values")
-        end
         if host_integrals && scf_options.df_force_dense
             error("B200 path: df_force_dense needs the device integral route (unset JULIACHEM_B200_HOST_INTEGRALS)")
         end
@@ -181,6 +176,17 @@ function df_rhf_fock_build_B200!(scf_data, jeri_engine_thread_df::Vector{T}, jer
             q_len[device_id] = length(aux_indicies)
         end
         jcdf_check(ccall((:jcdf_set_shards, libjcdf), Cint, (Ptr{Cvoid}, Ptr{Int64}, Ptr{Int64}), gd.handle, q_begin, q_len))
+        if scf_options.df_screen_exchange
+            # df_exchange_screen = true (calculate_exchange_block_screen_matrix + calculate_K_lower_diagonal_block,
+            # ScreenedDF.jl:385-545): K only for the blocks of the df_exchange_n_blocks grid whose mask sub-block holds a pair.
+            # The reference never writes a dropped block, so it keeps what scf_data.two_electron_fock held (the last F after
+            # DIIS and damping) plus H; the library reproduces that by reading F_out before every build.  Set before the
+            # mask; the dense statement of the contraction (df_force_dense / adaptive) has no K blocks and ignores it.
+            n_blocks = scf_options.df_exchange_n_blocks == 0 ? SCF_Keywords.Screening.df_exchange_n_blocks_cpu_default :
+                       scf_options.df_exchange_n_blocks
+            jcdf_check(ccall((:jcdf_set_option, libjcdf), Cint, (Ptr{Cvoid}, Cstring, Int64), gd.handle,
+                "exchange_block_screen", Int64(n_blocks)))
+        end
 
         if host_integrals
             setup_host_integrals_B200!(gd, scf_data, jeri_engine_thread_df, jeri_engine_thread, basis_sets, scf_options,
@@ -189,6 +195,20 @@ function df_rhf_fock_build_B200!(scf_data, jeri_engine_thread_df::Vector{T}, jer
             setup_device_integrals_B200!(gd, scf_data, basis_sets, scf_options, n_ranks, rank, comm)
         end
         jcdf_check(ccall((:jcdf_set_core_hamiltonian, libjcdf), Cint, (Ptr{Cvoid}, Ptr{Float64}), gd.handle, H))
+        if scf_options.df_screen_exchange
+            # what calculate_exchange_block_screen_matrix books (ScreenedDF.jl:409-410, 454), from the library's own block grid
+            li = zeros(Int64, JCDF_LAYOUT_INFO_FIELDS)
+            jcdf_check(ccall((:jcdf_get_layout, libjcdf), Cint, (Ptr{Cvoid}, Ptr{Int64}), gd.handle, li))
+            jc_timing.non_timing_data[JCTC.total_exchange_blocks] = string(li[16])
+            jc_timing.non_timing_data[JCTC.unscreened_exchange_blocks] = string(li[17])
+            if scf_options.df_exchange_n_blocks == 0                                 # the reference updates the option in place
+                scf_options.df_exchange_n_blocks = SCF_Keywords.Screening.df_exchange_n_blocks_cpu_default   # :388-390
+            end
+            if scf_data.μ < 100
+                scf_options.df_exchange_n_blocks = 1                                  # :392-394
+            end
+            jc_timing.non_timing_data[JCTC.df_exchange_n_blocks] = string(scf_options.df_exchange_n_blocks)
+        end
         # two_electron_fock is allocated once per SCF (DensityFitting.jl:45) and is pageable: let the library page-lock it in
         # place after its second use; the reference held here keeps it alive until the handle is destroyed
         gd.pinned_fock = scf_data.two_electron_fock

@@ -96,9 +96,11 @@ def run_basis(molecule: dict, model: dict, library: dict | None = None) -> dict:
 
 
 def run_energy(mol: dict, scf_flags: dict | None = None, num_devices: int = 1, keep_handle: bool = False) -> dict:
-    """JCRHF.Energy.run for scf_type = "df", contraction_mode = "B200".  scf_flags: niter, ndiis, dele, rmsd, df_sigma
-    (Constants.jl defaults).  Returns the reference's result Dict (SCF.jl:251-259) plus "Timings" and "Iterations"."""
-    f = {"niter": 50, "ndiis": 10, "dele": 1e-6, "rmsd": 1e-6, "df_sigma": 1e-5}
+    """JCRHF.Energy.run for scf_type = "df", contraction_mode = "B200".  scf_flags: niter, ndiis, dele, rmsd, df_sigma,
+    df_exchange_screen, df_exchange_n_blocks (Constants.jl names and defaults).  Returns the reference's result Dict
+    (SCF.jl:251-259) plus "Timings" and "Iterations"."""
+    f = {"niter": 50, "ndiis": 10, "dele": 1e-6, "rmsd": 1e-6, "df_sigma": 1e-5, "df_exchange_screen": False,
+         "df_exchange_n_blocks": 0}
     f.update(scf_flags or {})
     prim, aux = mol["primary"], mol["auxiliary"]
     N, Q, occ = prim.n_functions, aux.n_functions, mol["n_electrons"] // 2
@@ -115,6 +117,8 @@ def run_energy(mol: dict, scf_flags: dict | None = None, num_devices: int = 1, k
         gd.set_shards([static_load_rank_indicies(d, num_devices, aux.nbas)[1] for d in range(num_devices)])
     gd.set_basis(0, *prim.args())
     gd.set_basis(1, *aux.args())
+    if f["df_exchange_screen"]:  # block-screened exchange, ScreenedDF.jl:385-545 (df.exchange_block_screen_blocks)
+        gd.set_option("exchange_block_screen", int(f["df_exchange_n_blocks"]) or 10)
     clock("setup", t0)
     t0 = time.perf_counter()
     S, T, V, E_nuc = gd.compute_one_electron(mol["charges"], mol["centers"])
@@ -169,7 +173,8 @@ def run_energy(mol: dict, scf_flags: dict | None = None, num_devices: int = 1, k
         opts = {"density_fitting": "true", "contraction_mode": "B200", "load": "static", "guess": "hcore",
                 "df_energy_convergence": f["dele"], "df_density_convergence": f["rmsd"], "energy_convergence": f["dele"],
                 "density_convergence": f["rmsd"], "max_iterations": f["niter"], "df_max_iterations": f["niter"],
-                "df_exchange_n_blocks": 0, "df_screening_sigma": f["df_sigma"], "df_screen_exchange": "false",
+                "df_exchange_n_blocks": f["df_exchange_n_blocks"], "df_screening_sigma": f["df_sigma"],
+                "df_screen_exchange": "true" if f["df_exchange_screen"] else "false",
                 "df_force_dense": "false", "df_use_adaptive": "false", "num_devices": num_devices,
                 "df_use_K_sym": "false", "df_K_sym_type": ""}
         save_jc_timings_to_hdf5(timing, f["timings_file"], run_time=sum(t.values()), run_name=str(f.get("run_name", "")),

@@ -176,8 +176,9 @@ def calculate_K_lower_diagonal_block(W: np.ndarray, fock: np.ndarray, n_blocks: 
     """ScreenedDF.jl:459-545 (df_exchange_screen = true): like the no-screen variant, but ONLY the blocks in
     blocks_to_calculate are computed and written (:494-510).  The GEMM's beta = 0 write is the only thing that ever
     overwrites scf_data.two_electron_fock, so a dropped block keeps whatever the matrix held — after the first iteration
-    that is the previous iteration's F (H, J, K and all), onto which calculate_coulomb_screened then adds the new J.
-    libjcdf refuses the option for that reason; this restatement exists to show the behaviour in a test."""
+    that is the previous iteration's F (H, J, K and all, after the caller's DIIS and damping: SCF.jl:471-508 mutate the very
+    array df_rhf_fock_build! returned).  calculate_coulomb_screened adds nothing there either: every pair of a dropped block
+    is screened (:367-378).  libjcdf's option "exchange_block_screen" reproduces this with F_out as an in/out argument."""
     Q, occ, N = W.shape
     Wv = W.reshape((Q * occ, N), order="F")
     for idx in blocks_to_calculate:
@@ -344,33 +345,54 @@ def fock_build_dense_rank(B_dense: np.ndarray, C_occ: np.ndarray) -> np.ndarray:
 
 
 def fock_build_screened_rank(B: np.ndarray, C_occ: np.ndarray, sd: ScreeningData,
-                             df_exchange_n_blocks: int = 0) -> np.ndarray:
+                             df_exchange_n_blocks: int = 0, df_screen_exchange: bool = False,
+                             two_electron_fock: np.ndarray | None = None) -> np.ndarray:
     """df_rhf_fock_build_screened! per-iteration part (ScreenedDF.jl:84, 130-131) for one rank's Q rows:
-    exchange first (overwrites fock), then Coulomb (+=)."""
+    exchange first (overwrites fock), then Coulomb (+=).  `two_electron_fock` is the rank's scf_data.two_electron_fock as
+    the iteration finds it (zeros at iteration 1, DensityFitting.jl:45); it only matters with df_screen_exchange, whose
+    dropped blocks are never written (calculate_exchange_screened!, :231-235)."""
     C_occ_T = np.asfortranarray(np.asarray(C_occ).T)
     N = C_occ_T.shape[1]
-    fock = np.zeros((N, N), dtype=np.float64, order="F")
+    fock = np.zeros((N, N), dtype=np.float64, order="F") if two_electron_fock is None else \
+        np.array(two_electron_fock, dtype=np.float64, order="F", copy=True)
     n_blocks, width, batch = exchange_block_layout(N, df_exchange_n_blocks, 10)
     W = calculate_W_screened(B, C_occ_T, sd)
-    calculate_K_lower_diagonal_block_no_screen(W, fock, n_blocks, width, batch)
+    if df_screen_exchange:
+        todo, _ = exchange_block_screen_matrix(sd.basis_function_screen_matrix, n_blocks, width, batch, True)
+        calculate_K_lower_diagonal_block(W, fock, n_blocks, width, batch, todo)
+    else:
+        calculate_K_lower_diagonal_block_no_screen(W, fock, n_blocks, width, batch)
     calculate_coulomb_screened(B, C_occ_T, sd, fock)
     return fock
 
 
 def df_rhf_fock_build(B_shards, C: np.ndarray, occ: int, H: np.ndarray, sd: ScreeningData | None = None,
-                      contraction_mode: str = "screened", df_exchange_n_blocks: int = 0) -> np.ndarray:
+                      contraction_mode: str = "screened", df_exchange_n_blocks: int = 0,
+                      df_screen_exchange: bool = False, two_electron_fock: np.ndarray | None = None) -> np.ndarray:
     """df_rhf_fock_build! (DensityFitting.jl:23-76) with the MPI ranks emulated as a list of shards:
     C_occ = C[:, 1:occ] (:49); every rank builds its partial two-electron Fock from its Q rows; rank 0 adds H (:62-65);
-    Allreduce SUM (:68-71).  B_shards[r] is (Q_r, N, N) for "dense" or (Q_r, P) for "screened"."""
+    Allreduce SUM (:68-71).  B_shards[r] is (Q_r, N, N) for "dense" or (Q_r, P) for "screened".
+    `two_electron_fock`: what scf_data.two_electron_fock holds on EVERY rank when the call starts — the matrix the previous
+    call returned, as mutated by the (replicated) SCF loop; None = zeros (iteration 1).  Read only by df_screen_exchange."""
     C_occ = np.asfortranarray(C[:, :occ])
     total = None
     for rank, Bs in enumerate(B_shards):
-        if Bs.shape[0] == 0:  # a rank that owns no auxiliary shell contributes a zero matrix (BLAS calls with M = 0)
+        if Bs.shape[0] == 0:
+            # a rank that owns no auxiliary shell contributes a zero matrix (BLAS calls with M = 0) — except in the blocks
+            # df_screen_exchange never writes, which keep the rank's old content
             f = np.zeros_like(H)
+            if df_screen_exchange and contraction_mode != "dense" and two_electron_fock is not None:
+                n_blocks, width, batch = exchange_block_layout(H.shape[0], df_exchange_n_blocks, 10)
+                _, bsm = exchange_block_screen_matrix(sd.basis_function_screen_matrix, n_blocks, width, batch, True)
+                for bp in range(n_blocks):
+                    for bq in range(n_blocks):
+                        if not (bsm[bp, bq] or bsm[bq, bp]):
+                            f[bp * width:(bp + 1) * width, bq * width:(bq + 1) * width] = \
+                                two_electron_fock[bp * width:(bp + 1) * width, bq * width:(bq + 1) * width]
         elif contraction_mode == "dense":
             f = fock_build_dense_rank(Bs, C_occ)
         else:
-            f = fock_build_screened_rank(Bs, C_occ, sd, df_exchange_n_blocks)
+            f = fock_build_screened_rank(Bs, C_occ, sd, df_exchange_n_blocks, df_screen_exchange, two_electron_fock)
         if rank == 0:
             f = f + H
         total = f if total is None else total + f

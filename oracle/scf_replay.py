@@ -48,9 +48,13 @@ def diis_extrapolate(e_array, F_array, B_dim: int) -> np.ndarray:
 
 
 def run_scf(S, Hcore, E_nuc: float, nocc: int, fock_build, ndiis: int = 10, dele: float = 1e-6, rmsd: float = 1e-6,
-            max_iterations: int = 50, record=None, iteration_fn=None):
+            max_iterations: int = 50, record=None, iteration_fn=None, pass_previous_fock: bool = False):
     """Returns dict(E, converged, iterations=[(iter, E, dE, D_rms)], C, D, F).  iteration_fn(F, H, X, nocc) ->
-    (E_elec, evals, C, D) replaces the oracle's iteration() (e.g. with libjcdf's on-device jcdf_eigh in GPU tests)."""
+    (E_elec, evals, C, D) replaces the oracle's iteration() (e.g. with libjcdf's on-device jcdf_eigh in GPU tests).
+    pass_previous_fock: call fock_build(C, iteration, two_electron_fock) where the third argument is what
+    scf_data.two_electron_fock holds at that moment — None at iteration 1 (zeros, DensityFitting.jl:45), afterwards the
+    matrix the previous call returned AFTER this loop's DIIS and damping, which act on that very array in place
+    (SCF.jl:463, 491, 505: `F` is scf_data.two_electron_fock).  Only df_exchange_screen reads it."""
     N = S.shape[0]
     ortho = orthogonalizer(S)
     iteration = iteration_fn or orc.iteration
@@ -65,7 +69,10 @@ def run_scf(S, Hcore, E_nuc: float, nocc: int, fock_build, ndiis: int = 10, dele
     converged = False
     F = np.array(Hcore)
     while True:
-        F = np.array(fock_build(C, it), dtype=np.float64, order="F")
+        if pass_previous_fock:
+            F = np.array(fock_build(C, it, None if it == 1 else F), dtype=np.float64, order="F")
+        else:
+            F = np.array(fock_build(C, it), dtype=np.float64, order="F")
         if record is not None:
             record(it, "F", F.copy())
         if ndiis > 0:

@@ -172,6 +172,11 @@ def test_seam_with_device_integrals_and_reference_options(water, force_dense):
     # every stage slot lands on a key the reference's JCTiming knows (JCTiming.jl:50-107)
     assert jc.JCTiming.key("GPU_1_non_zero_coeff_time", 1) in timing.timings
     scf_data.gpu_data.close()
-    with pytest.raises(NotImplementedError):
-        jc.df_rhf_fock_build_B200(jc.SCFData(), src, np.asfortranarray(C[:, :nocc]), 1,
-                                  jc.SCFOptions(df_screen_exchange=True), H, jc.JCTiming())
+    # df_exchange_screen on a molecule below 100 functions: one K block (ScreenedDF.jl:392-394), nothing dropped, same matrix
+    sd2, t2 = jc.SCFData(), jc.JCTiming()
+    F2 = jc.df_rhf_fock_build_B200(sd2, src, np.asfortranarray(C[:, :nocc]), 1,
+                                   jc.SCFOptions(df_screen_exchange=True, df_use_adaptive=False), H, t2)
+    assert np.abs(F2 - F_ref).max() < 1e-10
+    assert t2.non_timing_data["total_exchange_blocks"] == "1" and t2.non_timing_data["unscreened_exchange_blocks"] == "1"
+    assert t2.non_timing_data["df_exchange_n_blocks"] == "1"
+    sd2.gpu_data.close()

@@ -23,6 +23,9 @@ JCTC_KNOWN = {
     "density_time": "density_time-", "GPU_non_zero_coeff_time": "GPU_-N-_non_zero_coeff_time-",
     "fock_gpu_cpu_copy_reduce_time": "fock_gpu_cpu_copy_reduce_time-", "fock_time": "fock_time-",
     "gpu_copy_J_time": "gpu_copy_J_time-", "iteration_time": "iteration_time-",
+    # non_timing_data keys of calculate_exchange_block_screen_matrix (ScreenedDF.jl:409-410, 454; JCTiming.jl:42, 78-79)
+    "total_exchange_blocks": "total_exchange_blocks", "unscreened_exchange_blocks": "unscreened_exchange_blocks",
+    "df_exchange_n_blocks": "df_exchange_n_blocks",
 }
 
 JULIA_TO_C = {"Cint": C.c_int32, "Int64": C.c_int64, "Float64": C.c_double, "Cdouble": C.c_double, "UInt64": C.c_uint64,

@@ -108,8 +108,8 @@ def test_slab_sum_of_the_threaded_build_is_the_whole_build():
 def test_block_screened_exchange_of_the_reference_depends_on_the_iteration_history():
     """Row a7 with df_exchange_screen = true (ScreenedDF.jl:433-449, 459-545), restated: the blocks whose mask sub-block is
     empty are neither computed NOR written, so two_electron_fock keeps its previous content there and the new J is added on
-    top.  The same (B, C) therefore gives different Fock matrices depending on what the buffer held — which is why libjcdf
-    refuses the option instead of reproducing it."""
+    top.  The same (B, C) therefore gives different Fock matrices depending on what the buffer held — libjcdf reproduces it
+    with F_out as an in/out argument (option "exchange_block_screen", tests/test_gpu_block_screened_exchange.py)."""
     N, Q, occ = 120, 16, 7
     mask = banded_mask(N, 18, seed=3, speckle=False)
     B, C_occ, H = random_inputs(N, Q, occ, seed=4, mask=mask)
@@ -139,3 +139,31 @@ def test_block_screened_exchange_of_the_reference_depends_on_the_iteration_histo
     orc.calculate_K_lower_diagonal_block(W, full, n_blocks, width, batch, todo_all)
     orc.calculate_coulomb_screened(Bs, C_T, sd, full)
     assert np.abs(full - orc.fock_build_screened_rank(Bs, C_occ, sd, 10)).max() < 1e-12
+
+
+def test_block_screened_build_over_ranks_keeps_rank_count_copies_of_the_old_matrix():
+    """df_rhf_fock_build! with df_exchange_screen over n emulated ranks (DensityFitting.jl:62-71 around ScreenedDF.jl:459-545):
+    in the computed blocks the result is the default algorithm's; a dropped block comes back as n * old + H, because every
+    rank keeps its own copy of the old matrix there, rank 0 adds H and the all-reduce sums the ranks."""
+    N, Q, occ = 130, 18, 6
+    mask = banded_mask(N, 20, seed=5)
+    B, C_occ, H = random_inputs(N, Q, occ, seed=6, mask=mask)
+    sd = orc.ScreeningData(mask)
+    Cfull = np.zeros((N, N), order="F")
+    Cfull[:, :occ] = C_occ
+    n_blocks, width, batch = orc.exchange_block_layout(N, 0, 10)
+    assert (n_blocks, width) == (10, 13)
+    _, block_screen = orc.exchange_block_screen_matrix(mask, n_blocks, width, batch, True)
+    dropped = np.zeros((N, N), dtype=bool)
+    dropped[:n_blocks * width, :n_blocks * width] = ~np.kron(block_screen | block_screen.T, np.ones((width, width), dtype=bool))
+    assert dropped.any() and not dropped[:, n_blocks * width:].any()
+    old = np.asfortranarray(np.random.default_rng(9).standard_normal((N, N)))
+    old = np.asfortranarray(old + old.T)
+    for shards in ([range(0, Q)], [range(0, 7), range(7, 7), range(7, Q)]):
+        Bs = [orc.dense_to_screened(np.asfortranarray(B[r.start:r.stop]), sd) for r in shards]
+        F_default = orc.df_rhf_fock_build(Bs, Cfull, occ, H, sd, "screened")
+        F = orc.df_rhf_fock_build(Bs, Cfull, occ, H, sd, "screened", df_screen_exchange=True, two_electron_fock=old)
+        assert np.abs(F - F_default)[~dropped].max() < 1e-12
+        assert np.abs(F - (len(shards) * old + H))[dropped].max() < 1e-12
+        F1 = orc.df_rhf_fock_build(Bs, Cfull, occ, H, sd, "screened", df_screen_exchange=True)  # iteration 1: zeros
+        assert np.abs(F1 - H)[dropped].max() == 0.0

@@ -1,0 +1,78 @@
+#!/usr/bin/env python
+"""Block-screened exchange (option "exchange_block_screen" = the reference's df_exchange_screen, ScreenedDF.jl:385-545) on
+the REAL w50 tensor: for several df_exchange_n_blocks the K blocks the reference would compute, the 128 x 128 exchange tiles
+libjcdf leaves out of its work lists, the stage times of a build, and two checks of the result —
+  * elements of computed blocks: the committed ORACLE fixture of the default build (tests/golden/w50_fock_fixture.json), 1e-10;
+  * elements of dropped blocks: exactly F_in + H (what the reference leaves in scf_data.two_electron_fock), bit for bit.
+One JSON line per block count.   python tools/block_screen_w50.py [n_blocks ...]   (default: 0 10 25 50)"""
+import json
+import os
+import sys
+
+import numpy as np
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+sys.path.insert(0, ROOT)
+
+import juliachem_jl_b200 as jc  # noqa: E402
+from juliachem_jl_b200 import rhf, workloads as wl  # noqa: E402
+
+
+def dropped_elements(mask, n_blocks):
+    """calculate_exchange_block_screen_matrix (ScreenedDF.jl:385-457) as a per-element Bool matrix in the caller's order."""
+    N = mask.shape[0]
+    if n_blocks <= 0:
+        return np.zeros((N, N), dtype=bool), 0, 0
+    width = N if N < 100 else N // n_blocks
+    nb = 1 if N < 100 else n_blocks
+    sub = mask[:nb * width, :nb * width].reshape(nb, width, nb, width).any(axis=(1, 3))
+    out = np.zeros((N, N), dtype=bool)
+    out[:nb * width, :nb * width] = ~np.kron(sub, np.ones((width, width), dtype=bool))
+    return out, nb * (nb + 1) // 2, int(np.tril(sub).sum())
+
+
+def main():
+    blocks = [int(a) for a in sys.argv[1:]] or [0, 10, 25, 50]
+    w = wl.WORKLOADS["w50"]
+    N, Q, occ = w.N, w.Q, w.occ
+    mol = rhf.run_basis(wl.real_molecule(w), {"basis": w.basis})
+    C_occ, H = wl.occupied_coefficients(w), wl.core_hamiltonian(w)
+    fx = json.load(open(os.path.join(ROOT, "tests", "golden", "w50_fock_fixture.json")))
+    idx, val = np.array(fx["index"]), np.array(fx["value"])
+    rng = np.random.default_rng(5)
+    F_in = rng.standard_normal((N, N))
+    F_in = np.asfortranarray(F_in + F_in.T)
+    for nb in blocks:
+        gd = jc.B200Data(N, Q, occ, 1)
+        gd.set_basis(0, *mol["primary"].args())
+        gd.set_basis(1, *mol["auxiliary"].args())
+        gd.set_option("exchange_block_screen", nb)
+        gd.compute_two_center(False)
+        mask, _ = gd.compute_schwarz_mask(1e-5)
+        gd.compute_B()
+        li = gd.layout()
+        dropped, total, kept = dropped_elements(mask, nb)
+        assert (li.exchange_blocks_total, li.exchange_blocks_kept) == (total, kept), (li.exchange_blocks_total, li.exchange_blocks_kept, total, kept)
+        ms = []
+        F = None
+        for _ in range(6):
+            F = F_in.copy(order="F")
+            gd.fock_build(C_occ, H, F)
+            ms.append(gd.last_kernel_ms(0))
+        med = {k: float(np.median([m[k] for m in ms[1:]])) for k in ms[0]}
+        live = ~dropped[idx[:, 0], idx[:, 1]]
+        err_kept = float(np.abs(F[idx[live, 0], idx[live, 1]] - val[live]).max())
+        exact_dropped = bool(np.array_equal(F[dropped], (F_in + H)[dropped])) if dropped.any() else True
+        assert err_kept < 1e-10 and exact_dropped and np.array_equal(F, F.T)
+        print(json.dumps({"workload": "w50 real cc-pVDZ / cc-pVDZ-RIFIT", "df_exchange_n_blocks": nb,
+                          "K_block_width": int(li.exchange_block_width), "blocks_total": total, "blocks_kept": kept,
+                          "elements_dropped_fraction": round(float(dropped.mean()), 4),
+                          "exchange_tiles_total": int(li.exchange_tiles_total), "exchange_tiles_skipped": int(li.exchange_tiles_skipped),
+                          "stage_ms_median_of_5": {k: round(v, 4) for k, v in med.items()},
+                          "fixture_samples_in_kept_blocks": int(live.sum()), "max_abs_err_kept_vs_oracle_fixture": err_kept,
+                          "dropped_elements_equal_F_in_plus_H_bitwise": exact_dropped}), flush=True)
+        gd.close()
+
+
+if __name__ == "__main__":
+    main()
