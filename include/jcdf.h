@@ -241,7 +241,8 @@ double jcdf_synthetic_value(uint64_t seed, int64_t Q_total, int64_t q_aux, int64
  * per-function kernel whenever the compact Coulomb is active, by the tile kernel when "coulomb_fused" is left at 2 — so the
  * Coulomb build needs no density pass and streams B once instead of twice; 0 = density + separate V pass),
  * "pp_layout" (consumer warp arrangement of the per-function kernel: -1 = default, chosen from occ; 0 = 2 x 4 warps,
- * orbitals padded to 32 per item; 1 = 8 x 1 warps, no padding beyond the 8-wide DMMA tile),
+ * orbitals padded to 32 per item; 1 = 8 x 1 warps, no padding beyond the 8-wide DMMA tile; 2 = two CTAs per SM of 2 x 2 warps
+ * each, orbitals padded to 16 per item — measured slower than 0 / 1 on every benchmark shape, never chosen automatically),
  * "pp_max_bytes" (cap on the compact copy per shard; above it — or when cudaMalloc refuses — the automatic choice falls
  * back to the tile family, ht_mode = 2 reports JCDF_ERR_CUDA; 0 = no cap),
  * "coulomb_pp_fused" (0 = default: two streaming passes; 1 = one cooperative single-pass kernel, measured slower),

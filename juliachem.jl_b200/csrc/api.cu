@@ -470,6 +470,14 @@ static void build_partner_lists(jcdf_handle* h, Kept kept) {
     L.pp_layout = layout1 ? 1 : 0;
     L.pp_n_nt = layout1 ? n_nt1 : n_nt0;
     L.pp_nt = layout1 ? nt1 : nt0;
+    if (h->opt_pp_layout == 2) {
+        // Layout 2: two CTAs per SM, each 2 (M halves) x 2 (N halves of 8 nt orbitals, nt <= 4) consumer warps: items of
+        // 16 nt orbitals; the two CTAs of an SM run out of phase, so one's item epilogue / pipeline fill sits under the other's DMMAs
+        const int n_nt2 = (n8 + 7) / 8;
+        L.pp_layout = 2;
+        L.pp_n_nt = n_nt2;
+        L.pp_nt = ((n8 + n_nt2 - 1) / n_nt2 + 1) / 2;
+    }
     if (h->opt_ht_mode == 1 || L.row_len >= ((int64_t)1 << 31)) return;
     // executed multiply-adds per auxiliary row of either kernel
     double cost_tiles = 0.0;
@@ -488,7 +496,7 @@ static void build_partner_lists(jcdf_handle* h, Kept kept) {
         cnt[(size_t)p] = c;
         rows += (c + 3) / 4 * 4;
     }
-    const double cost_pp = (double)rows * L.pp_n_nt * (L.pp_layout ? 8.0 : 32.0) * L.pp_nt;
+    const double cost_pp = (double)rows * L.pp_n_nt * (double)pp_item_orbitals(L);
     if (rows >= ((int64_t)1 << 31)) return;
     // measured on the C20H42 shape (52.8 % of the pairs kept, cost ratio 0.93): per-function 18.2 ms + compact Coulomb
     // 4.4 ms against tiles 19.3 ms + 5.3 ms — the compact family wins as soon as it executes fewer DMMAs at all
@@ -1463,7 +1471,7 @@ int32_t jcdf_set_option(jcdf_handle* h, const char* name, int64_t value) {
         {"coulomb_fused", &h->opt_coulomb_fused, false, 0, 2},
         {"coulomb_overlap", &h->opt_coulomb_overlap, false, 0, 1},
         {"pp_max_bytes", &h->opt_pp_max_bytes, true, 0, big},
-        {"pp_layout", &h->opt_pp_layout, true, -1, 1},
+        {"pp_layout", &h->opt_pp_layout, true, -1, 2},
         {"coulomb_pp", &h->opt_coulomb_pp, false, 0, 1},
         {"coulomb_v_in_ht", &h->opt_coulomb_v_in_ht, false, 0, 1},
         {"coulomb_pp_fused", &h->opt_coulomb_pp_fused, false, 0, 1},

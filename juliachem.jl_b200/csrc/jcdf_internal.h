@@ -36,7 +36,8 @@ struct Layout {
     // ---- partner-compacted layout of the per-function half-transform (kernels_pp.cu) ----
     // For every function p (internal order) the kept partners q, ascending, padded to a multiple of 4 rows.
     bool pp_enabled = false;           // the per-function path is selected for this mask
-    int pp_layout = 0;                 // consumer warp arrangement: 0 = 2 x 4 (NI = 32 pp_nt orbitals per item), 1 = 8 x 1 (NI = 8 pp_nt)
+    int pp_layout = 0;                 // consumer warp arrangement: 0 = 2 x 4 (NI = 32 pp_nt orbitals per item), 1 = 8 x 1 (NI = 8 pp_nt),
+                                       // 2 = TWO CTAs per SM of 2 x 2 consumer warps each (NI = 16 pp_nt)
     int pp_nt = 0;                     // 8-wide occupied-orbital tiles per consumer warp
     int pp_n_nt = 0;                   // items along the occupied orbitals: pp_n_nt * NI >= occ_w
     int64_t pp_rows = 0;               // sum over p of the padded partner counts
@@ -58,8 +59,9 @@ struct Layout {
     int64_t xs_tiles_skipped = 0;
 };
 
-inline int pp_item_orbitals(const Layout& L) { return L.pp_layout ? 8 * L.pp_nt : 32 * L.pp_nt; }
-inline int pp_v_slots(const Layout& L) { return L.pp_layout ? 1 : 4; }  // partial-V slots (warp columns) per (CTA, chunk)
+inline int pp_item_orbitals(const Layout& L) { return (L.pp_layout == 1 ? 8 : L.pp_layout == 2 ? 16 : 32) * L.pp_nt; }
+inline int pp_v_slots(const Layout& L) { return L.pp_layout == 1 ? 1 : L.pp_layout == 2 ? 2 : 4; }  // partial-V slots (warp columns) per (CTA, chunk)
+inline int pp_ctas_per_sm(const Layout& L) { return L.pp_layout == 2 ? 2 : 1; }
 
 // event points recorded on the shard's stream during one build, in launch order
 enum EvPoint { EV_START = 0, EV_H2D, EV_PREP, EV_W, EV_K, EV_JBEGIN, EV_V, EV_J, EV_EPI, EV_AR, EV_D2H, EV_COUNT };
@@ -179,7 +181,8 @@ struct jcdf_handle {
     int64_t opt_coulomb_v_in_ht = 1;   // compact Coulomb: V from the per-function half-transform's accumulators (no density, no V sweep)
     int64_t opt_coulomb_pp_fused = 0;  // compact Coulomb as ONE HBM pass (cooperative kernel): measured slower than the two
                                        // streaming passes (2.1 vs 1.3 ms at w50: 150 grid-wide flag rounds), so off by default
-    int64_t opt_pp_layout = -1;        // per-function half-transform warp arrangement: -1 = chosen from occ, 0 = 2 x 4, 1 = 8 x 1
+    int64_t opt_pp_layout = -1;        // per-function half-transform warp arrangement: -1 = chosen from occ, 0 = 2 x 4, 1 = 8 x 1,
+                                       // 2 = two CTAs per SM of 2 x 2 consumer warps (one CTA's item epilogue under the other's DMMAs)
     int64_t opt_pp_max_bytes = 0;      // cap on the partner-compacted copy per shard (0 = whatever cudaMalloc grants)
     int64_t opt_coulomb_pp = 1;       // Coulomb over the partner-compacted copy whenever the per-function path is active
     int64_t opt_ht_mode = 0;          // half-transform: 0 = choose from the mask, 1 = tile kernel, 2 = per-function kernel

@@ -34,6 +34,14 @@ constexpr int PP_THREADS = (PP_CONSUMERS + 1) * 32;
 // warpgroups take them (-> 232), so ptxas can keep a whole k-step of fragments in flight (it uses 186) instead of loading
 // every a fragment right before its first DMMA.  128 x 40 + 256 x 232 = 64512 <= 65536.
 constexpr int PP_THREADS_BIG = (PP_CONSUMERS + 4) * 32;
+// Layout 2 (two CTAs per SM): one consumer warpgroup (2 x 2 warps) + the producer's warpgroup = 256 threads, launched at the
+// 128-register cap of two resident CTAs; the producer's warpgroup drops to 40, the consumers rise to 216
+// (2 x (128 x 40 + 128 x 216) = 65536); two stages of 49 KiB per CTA (4 in flight per SM).
+constexpr int PP2_CONSUMERS = 4;
+constexpr int PP2_THREADS = (PP2_CONSUMERS + 4) * 32;
+constexpr int PP2_NSTAGE = 2;
+__host__ __device__ constexpr int pp_layout_orbitals(int layout, int nt) { return (layout == 1 ? 8 : layout == 2 ? 16 : 32) * nt; }
+__host__ __device__ constexpr int pp_layout_slots(int layout) { return layout == 1 ? 1 : layout == 2 ? 2 : 4; }
 
 // ---------------------------------------------------------------------------------------------------------------------
 // Bp (tile-packed, one auxiliary row contiguous) -> Bc (partner-compacted, 128 auxiliary rows contiguous).  One-off per
@@ -150,23 +158,30 @@ __device__ __forceinline__ void pp_slab_mn(double (&acc)[MTW][NT][2], const doub
 //           11 tiles instead of 12 on the busiest sub-partition).
 // WITH_V: the epilogue also leaves the item's share of the Coulomb vector V (a separate instantiation: the block costs
 //         registers the NT = 4 kernel does not have to spare).
+// LAYOUT 2: TWO CTAs per SM, each 2 x 2 consumer warps of 64 x (8 NT) blocks, NI = 16 NT, two stages per CTA: the CTAs of
+//           an SM run out of phase, so the item epilogue (W stores, V dot products) and the pipeline refill of one sit under
+//           the DMMAs of the other; costs twice the passes over Bc of layout 0 (L2 hits: the items of a (p, chunk) are adjacent).
 template <int NT, int LAYOUT, bool WITH_V, bool BIGREG>
 // 9 warps are allocated like 12 (register file granularity of 4 warps): 168 registers per thread is the cap at launch
-__global__ void __launch_bounds__(BIGREG ? PP_THREADS_BIG : PP_THREADS, 1) k_pp_half_transform(PPParams prm) {
-    constexpr int MTW = LAYOUT ? 2 : 8;             // 8-row DMMA tiles per warp
-    constexpr int NI = LAYOUT ? 8 * NT : 32 * NT;   // orbitals per item
+__global__ void __launch_bounds__(LAYOUT == 2 ? PP2_THREADS : BIGREG ? PP_THREADS_BIG : PP_THREADS, LAYOUT == 2 ? 2 : 1)
+k_pp_half_transform(PPParams prm) {
+    static_assert(LAYOUT != 2 || BIGREG, "layout 2 exists with the register split only");
+    constexpr int MTW = LAYOUT == 1 ? 2 : 8;        // 8-row DMMA tiles per warp
+    constexpr int NI = pp_layout_orbitals(LAYOUT, NT);   // orbitals per item
     constexpr int LDC = NI + 4;  // = 4 (or 12) mod 16 doubles: the b fragment rows t = 0..3 fall on distinct bank quads
     constexpr int STAGE_DOUBLES = PP_KS * PP_QC + PP_KS * LDC;
+    constexpr int NSTG = LAYOUT == 2 ? PP2_NSTAGE : PP_NSTAGE;
+    constexpr int NCONS = LAYOUT == 2 ? PP2_CONSUMERS : PP_CONSUMERS;
     extern __shared__ __align__(128) unsigned char smem_raw[];
     double* stages = reinterpret_cast<double*>(smem_raw);
-    uint64_t* full = reinterpret_cast<uint64_t*>(stages + (size_t)PP_NSTAGE * STAGE_DOUBLES);
-    uint64_t* empty = full + PP_NSTAGE;
+    uint64_t* full = reinterpret_cast<uint64_t*>(stages + (size_t)NSTG * STAGE_DOUBLES);
+    uint64_t* empty = full + NSTG;
 
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
     if (threadIdx.x == 0) {
-        for (int s = 0; s < PP_NSTAGE; s++) {
+        for (int s = 0; s < NSTG; s++) {
             mbar_init(&full[s], 1);
-            mbar_init(&empty[s], PP_CONSUMERS);
+            mbar_init(&empty[s], NCONS);
         }
         fence_barrier_init();
         fence_proxy_async();
@@ -175,10 +190,10 @@ __global__ void __launch_bounds__(BIGREG ? PP_THREADS_BIG : PP_THREADS, 1) k_pp_
 
     const int chunks = prm.chunks, n_nt = prm.n_nt;
 
-    if (warp >= PP_CONSUMERS) {
+    if (warp >= NCONS) {
         if constexpr (BIGREG) {
             asm volatile("setmaxnreg.dec.sync.aligned.u32 40;");  // all four warps of the producer's warpgroup
-            if (warp > PP_CONSUMERS) return;
+            if (warp > NCONS) return;
         }
         // ------------------------------------------------ producer warp ------------------------------------------------
         PipeState pp;
@@ -205,18 +220,19 @@ __global__ void __launch_bounds__(BIGREG ? PP_THREADS_BIG : PP_THREADS, 1) k_pp_
                     JC_CHECK(qrow >= 0 && Cbase + (int64_t)qrow * prm.ldci + NI <= prm.Ci + prm.ci_elems, "half-transform: C row outside Ci");
                 if (lane < nr)
                     bulk_g2s(st + PP_KS * PP_QC + lane * LDC, Cbase + (int64_t)qrow * prm.ldci, NI * 8u, &full[pp.stage]);
-                pp.advance<PP_NSTAGE>();
+                pp.advance<NSTG>();
             }
         }
         return;
     }
 
     // --------------------------------------------------- consumers ---------------------------------------------------
-    if constexpr (BIGREG) asm volatile("setmaxnreg.inc.sync.aligned.u32 232;");
+    if constexpr (LAYOUT == 2) asm volatile("setmaxnreg.inc.sync.aligned.u32 216;");
+    else if constexpr (BIGREG) asm volatile("setmaxnreg.inc.sync.aligned.u32 232;");
     PipeState ps;
     const int g = lane >> 2, t = lane & 3;
-    const int m0 = LAYOUT ? warp * 16 : (warp >> 2) * 64;
-    const int n0 = LAYOUT ? 0 : (warp & 3) * 8 * NT;
+    const int m0 = LAYOUT == 1 ? warp * 16 : LAYOUT == 2 ? (warp >> 1) * 64 : (warp >> 2) * 64;
+    const int n0 = LAYOUT == 1 ? 0 : LAYOUT == 2 ? (warp & 1) * 8 * NT : (warp & 3) * 8 * NT;
     // with the register split the record of the NEXT item is fetched while the current one computes (four registers the
     // 168-register variant does not have: it reads its record at the item start)
     const int j_end = prm.item_off[blockIdx.x + 1];
@@ -257,7 +273,7 @@ __global__ void __launch_bounds__(BIGREG ? PP_THREADS_BIG : PP_THREADS, 1) k_pp_
             else if (any) pp_slab_mn<MTW, NT, LDC>(acc, sA, sC, m0, n0, g, t, nks, mt_valid, nt_valid);
             __syncwarp();
             if (lane == 0) mbar_arrive(&empty[ps.stage]);
-            ps.advance<PP_NSTAGE>();
+            ps.advance<NSTG>();
         }
         if (!any) continue;
         // epilogue: the thread's (i, i + 1) pair is adjacent in the k-fastest W tile -> 16-byte stores, 4 lanes = 64 bytes.
@@ -334,8 +350,8 @@ __global__ void __launch_bounds__(BIGREG ? PP_THREADS_BIG : PP_THREADS, 1) k_pp_
                 // shared memory and flushing once per chunk made ptxas spill accumulators inside the k loop.)
                 int che = ch, we = warp;
                 asm volatile("" : "+r"(che), "+r"(we));
-                constexpr int NWC = LAYOUT ? 1 : 4;
-                double* vdst = prm.vitem + ((((int64_t)blockIdx.x * chunks + che) * NWC + (LAYOUT ? 0 : (we & 3))) * PP_QC) + m0 + ge;
+                constexpr int NWC = pp_layout_slots(LAYOUT);
+                double* vdst = prm.vitem + ((((int64_t)blockIdx.x * chunks + che) * NWC + (we & (NWC - 1))) * PP_QC) + m0 + ge;
                 JC_CHECK(vdst >= prm.vitem && vdst + 8 * (MTW - 1) < prm.vitem + prm.vitem_elems, "half-transform: V slot outside Vitem");
 #pragma unroll
                 for (int jm = 0; jm < MTW; jm++) asm volatile("red.global.add.f64 [%0], %1;" ::"l"(vdst + 8 * jm), "d"(v[jm]) : "memory");
@@ -728,26 +744,26 @@ void launch_pp_coulomb(const Layout& L, Shard& s, cudaStream_t st, cudaEvent_t e
 
 int64_t pp_coulomb_slabs(const Layout& L) { return (L.pp_rows + PPJ_SLAB - 1) / PPJ_SLAB; }
 
-static size_t pp_smem_bytes(int ni) {
-    return (size_t)PP_NSTAGE * (PP_KS * PP_QC + PP_KS * (ni + 4)) * 8 + 2 * PP_NSTAGE * 8 + 16;
+static size_t pp_smem_bytes(int ni, int nstage) {
+    return (size_t)nstage * (PP_KS * PP_QC + PP_KS * (ni + 4)) * 8 + 2 * nstage * 8 + 16;
 }
 
 template <int NT, int LAYOUT, bool WITH_V, bool BIGREG>
 static void launch_pp_k(const PPParams& prm, int grid, size_t smem, cudaStream_t st) {
     cudaFuncSetAttribute(k_pp_half_transform<NT, LAYOUT, WITH_V, BIGREG>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
-    k_pp_half_transform<NT, LAYOUT, WITH_V, BIGREG><<<grid, BIGREG ? PP_THREADS_BIG : PP_THREADS, smem, st>>>(prm);
+    k_pp_half_transform<NT, LAYOUT, WITH_V, BIGREG><<<grid, LAYOUT == 2 ? PP2_THREADS : BIGREG ? PP_THREADS_BIG : PP_THREADS, smem, st>>>(prm);
 }
 
 template <int NT, int LAYOUT>
 static void launch_pp_t(const PPParams& prm, int grid, bool bigreg, cudaStream_t st) {
-    const size_t smem = pp_smem_bytes(LAYOUT ? 8 * NT : 32 * NT);
+    const size_t smem = pp_smem_bytes(pp_layout_orbitals(LAYOUT, NT), LAYOUT == 2 ? PP2_NSTAGE : PP_NSTAGE);
     if (prm.vitem != nullptr) {
-        cudaMemsetAsync(prm.vitem, 0, sizeof(double) * (size_t)grid * prm.chunks * (LAYOUT ? 1 : 4) * PP_QC, st);  // the slots are summed into
-        if (bigreg) launch_pp_k<NT, LAYOUT, true, true>(prm, grid, smem, st);
-        else launch_pp_k<NT, LAYOUT, true, false>(prm, grid, smem, st);
+        cudaMemsetAsync(prm.vitem, 0, sizeof(double) * (size_t)grid * prm.chunks * pp_layout_slots(LAYOUT) * PP_QC, st);  // the slots are summed into
+        if (bigreg || LAYOUT == 2) launch_pp_k<NT, LAYOUT, true, true>(prm, grid, smem, st);
+        else launch_pp_k<NT, LAYOUT, true, LAYOUT == 2>(prm, grid, smem, st);
     } else {
-        if (bigreg) launch_pp_k<NT, LAYOUT, false, true>(prm, grid, smem, st);
-        else launch_pp_k<NT, LAYOUT, false, false>(prm, grid, smem, st);
+        if (bigreg || LAYOUT == 2) launch_pp_k<NT, LAYOUT, false, true>(prm, grid, smem, st);
+        else launch_pp_k<NT, LAYOUT, false, LAYOUT == 2>(prm, grid, smem, st);
     }
 }
 
@@ -760,7 +776,7 @@ void plan_pp_items(const Layout& L, Shard& s, int sm_count, bool p_major, std::v
     // list: four int32 per item (the int4 records the kernel reads)
     const int chunks = s.pp_chunks, n_nt = L.pp_n_nt, NT = L.pp_nt;
     const int64_t n_items = (int64_t)L.N * n_nt * chunks;
-    const int n_ctas = (int)std::max<int64_t>(1, std::min<int64_t>(n_items, sm_count));
+    const int n_ctas = (int)std::max<int64_t>(1, std::min<int64_t>(n_items, (int64_t)sm_count * pp_ctas_per_sm(L)));
     s.pp_ctas = n_items > 0 ? n_ctas : 0;
     list.clear();
     off.assign((size_t)n_ctas + 1, 0);
@@ -770,7 +786,7 @@ void plan_pp_items(const Layout& L, Shard& s, int sm_count, bool p_major, std::v
     const int NI = pp_item_orbitals(L);
     for (int ch = 0; ch < chunks; ch++) {
         const int rows = (int)std::min<int64_t>(PP_QC, s.q_len - (int64_t)ch * PP_QC);
-        if (L.pp_layout == 0) {
+        if (L.pp_layout != 1) {
             const int m0 = std::max(0, std::min(8, (rows + 7) >> 3)), m1 = std::max(0, std::min(8, (rows - 64 + 7) >> 3));
             m_units[(size_t)ch] = m0 + m1;
         } else {  // warps w and w + 4 share a sub-partition, 16 rows each
@@ -870,7 +886,15 @@ void launch_pp_half_transform(const Layout& L, Shard& s, int sm_count, bool v_in
     const int grid = s.pp_ctas;
     (void)sm_count;
     if (grid <= 0) return;
-    if (L.pp_layout == 0) {
+    if (L.pp_layout == 2) {
+        switch (L.pp_nt) {
+            case 1: launch_pp_t<1, 2>(prm, grid, bigreg, s.stream); break;
+            case 2: launch_pp_t<2, 2>(prm, grid, bigreg, s.stream); break;
+            case 3: launch_pp_t<3, 2>(prm, grid, bigreg, s.stream); break;
+            case 4: launch_pp_t<4, 2>(prm, grid, bigreg, s.stream); break;
+            default: break;
+        }
+    } else if (L.pp_layout == 0) {
         switch (L.pp_nt) {
             case 1: launch_pp_t<1, 0>(prm, grid, bigreg, s.stream); break;
             case 2: launch_pp_t<2, 0>(prm, grid, bigreg, s.stream); break;

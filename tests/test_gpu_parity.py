@@ -331,10 +331,10 @@ def test_coulomb_v_folded_into_half_transform(N, Q, occ, overlap):
 
 
 @pytest.mark.parametrize("occ", [1, 7, 8, 9, 24, 25, 41, 81, 96, 97, 103, 104, 130, 193])
-@pytest.mark.parametrize("pp_layout", [0, 1])
+@pytest.mark.parametrize("pp_layout", [0, 1, 2])
 def test_per_function_warp_layouts(occ, pp_layout):
-    """Both consumer-warp arrangements of the per-function kernel (2 x 4 warps with the orbitals of an item padded to 32,
-    8 x 1 warps with 8-wide tiles only) over occupied counts that hit every ragged case: fewer than one tile, exact
+    """All consumer-warp arrangements of the per-function kernel (2 x 4 warps with the orbitals of an item padded to 32,
+    8 x 1 warps with 8-wide tiles only, two CTAs per SM of 2 x 2 warps with items padded to 16) over occupied counts that hit every ragged case: fewer than one tile, exact
     multiples of 8 / 32 / 96, one orbital over (97 = 13 tiles -> two items of 7 with 6 valid in the second), several
     items (193), and a Q range with a ragged last chunk of 9 rows (one warp busy in the 8 x 1 arrangement)."""
     N, Q = max(100, occ + 10), 137
@@ -512,7 +512,7 @@ def test_graph_replay_is_bit_identical_to_eager_launches(ht_mode):
 def test_refused_options_leave_the_handle_unchanged():
     N, Q, occ = 70, 40, 9
     gd = jc.B200Data(N, Q, occ, 1)
-    for name, value in (("ht_mode", 3), ("coulomb_fused", -1), ("pp_layout", 2), ("nonsense", 1), ("graph", 2)):
+    for name, value in (("ht_mode", 3), ("coulomb_fused", -1), ("pp_layout", 3), ("nonsense", 1), ("graph", 2)):
         with pytest.raises(jc.JCDFError):
             gd.set_option(name, value)
     mask = banded_mask(N, 20, seed=N)
