@@ -25,6 +25,10 @@ CASES = [
     ("pp_2x4_density_v_pass", 96, 140, 40, {"ht_mode": 2, "coulomb_pp_fused": 0, "coulomb_v_in_ht": 0}),
     ("pp_8x1_v_in_ht", 96, 129, 81, {"ht_mode": 2, "coulomb_pp_fused": 0, "pp_layout": 1}),
     ("pp_coulomb_cooperative", 96, 140, 24, {"ht_mode": 2, "coulomb_pp_fused": 1}),
+    ("pp_two_ctas_per_sm_v_in_ht", 96, 140, 40, {"ht_mode": 2, "coulomb_pp_fused": 0, "pp_layout": 2}),
+    ("pp_two_ctas_per_sm_v_pass", 96, 129, 81, {"ht_mode": 2, "coulomb_pp_fused": 0, "coulomb_v_in_ht": 0, "pp_layout": 2}),
+    # df_exchange_screen: width-14 K blocks, the far corner blocks dropped; F_out is in/out and starts as zeros (iteration 1)
+    ("block_screened_exchange", 140, 64, 33, {"ht_mode": 2, "exchange_block_screen": 10}),
     ("sliced_exchange_eager", 140, 64, 33, {"ht_mode": 2, "exchange_slices": 4, "graph": 0}),
     ("dense_no_mask", 64, 32, 8, {}),
 ]
@@ -47,16 +51,28 @@ def main():
             gd.set_option(k, v)
         gd.set_mask(jc.ScreeningData(mask, N))
         gd.set_B(0, reference_layout_rows(B, range(0, Q), mask))
-        F = gd.fock_build(C_occ, H)[0].copy()
-        F2 = gd.fock_build(C_occ, None)[0]
-        err = float(np.abs(F - oracle_fock(B, C_occ, H, mask)).max())
+        blocked = "exchange_block_screen" in opts
+        zeros = (lambda: np.zeros((N, N), order="F")) if blocked else (lambda: None)
+        F = gd.fock_build(C_occ, H, zeros())[0].copy()
+        F2 = gd.fock_build(C_occ, None, zeros())[0]
+        if blocked:
+            from helpers import orc
+            sd = orc.ScreeningData(mask)
+            Cfull = np.zeros((N, N), order="F")
+            Cfull[:, :occ] = C_occ
+            F_ref = orc.df_rhf_fock_build([orc.dense_to_screened(B, sd)], Cfull, occ, H, sd, "screened",
+                                          df_exchange_n_blocks=opts["exchange_block_screen"], df_screen_exchange=True)
+            assert gd.layout().exchange_blocks_kept < gd.layout().exchange_blocks_total
+        else:
+            F_ref = oracle_fock(B, C_occ, H, mask)
+        err = float(np.abs(F - F_ref).max())
         li = gd.layout()
         fuzz_note = ""
         if n_fuzz:  # schedule fuzzing (checked build): random sleeps at every barrier / copy / flag; results must not move
             worst_f, changed = 0.0, 0
             for seed in range(1, n_fuzz + 1):
                 gd.checked_set_fuzz(seed)
-                Ff = gd.fock_build(C_occ, None)[0]
+                Ff = gd.fock_build(C_occ, None, zeros())[0]
                 d = float(np.abs(Ff - F).max())
                 worst_f = max(worst_f, d)
                 changed += int(not np.array_equal(Ff, F))
