@@ -87,6 +87,26 @@ class JCDFError(RuntimeError):
         self.status = status
 
 
+def _name_shared_nccl() -> None:
+    """libjcdf binds NCCL with dlopen on its first multi-device build: an already-mapped copy if there is one, else the copy
+    named in JCDF_NCCL_LIBRARY, else the loader's default.  Whatever is mapped first serves the whole process, and PyTorch
+    cannot be imported over an NCCL older than the one it ships (undefined symbol at `import torch`), so when the pip package
+    nvidia-nccl is installed its library is the one to share.  Only the environment variable is set here: nothing is loaded
+    until a build actually needs a collective."""
+    if os.environ.get("JCDF_NCCL_LIBRARY"):
+        return
+    try:
+        import importlib.util
+        spec = importlib.util.find_spec("nvidia.nccl")
+        for loc in (spec.submodule_search_locations if spec else []):
+            path = os.path.join(loc, "lib", "libnccl.so.2")
+            if os.path.exists(path):
+                os.environ["JCDF_NCCL_LIBRARY"] = path
+                return
+    except Exception:
+        pass
+
+
 def load_library() -> C.CDLL:
     """dlopen the in-tree libjcdf.so and bind every declared entry point.  Raises if the extension has not been
     built (run `python -c 'import __graft_entry__ as g; g.build()'` or `make -C juliachem.jl_b200/csrc`)."""
@@ -95,6 +115,7 @@ def load_library() -> C.CDLL:
         return _lib
     if not os.path.exists(LIB_PATH):
         raise ImportError("libjcdf.so not built at %s — the B200 DF Fock build has no CPU fallback" % LIB_PATH)
+    _name_shared_nccl()
     lib = C.CDLL(LIB_PATH, mode=C.RTLD_GLOBAL)
     for name, (res, args) in SIGNATURES.items():
         fn = getattr(lib, name)  # AttributeError if the symbol is missing

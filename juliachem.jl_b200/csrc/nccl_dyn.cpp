@@ -1,6 +1,7 @@
 #include "nccl_dyn.h"
 
 #include <dlfcn.h>
+#include <cstdlib>
 #include <mutex>
 
 namespace jcdf {
@@ -11,6 +12,14 @@ static std::once_flag g_once;
 static void load() {
     // RTLD_NOLOAD first: reuse an already-mapped NCCL (torch's) so that one process never holds two copies.
     void* lib = dlopen("libnccl.so.2", RTLD_NOW | RTLD_NOLOAD | RTLD_GLOBAL);
+    // Nothing mapped yet: the loader would now take the first libnccl.so.2 on its search path, and whatever is mapped first
+    // serves every later request for that soname in the process.  A host that may load another NCCL user afterwards (PyTorch
+    // ships its own, newer NCCL next to its libraries and fails to import over an older one) names the copy to share in
+    // JCDF_NCCL_LIBRARY — juliachem.jl_b200/_lib.py points it at the pip package's library when there is one.
+    if (!lib) {
+        const char* named = getenv("JCDF_NCCL_LIBRARY");
+        if (named && *named) lib = dlopen(named, RTLD_NOW | RTLD_GLOBAL);
+    }
     if (!lib) lib = dlopen("libnccl.so.2", RTLD_NOW | RTLD_GLOBAL);
     if (!lib) lib = dlopen("libnccl.so", RTLD_NOW | RTLD_GLOBAL);
     if (!lib) {

@@ -183,6 +183,24 @@ def synthetic_B_rows(w: Workload, q_range: range, mask) -> np.ndarray:
     return out
 
 
+def exchange_dropped_elements(mask, n_blocks: int):
+    """Which elements of F the block-screened exchange leaves uncomputed (option "exchange_block_screen", the reference's
+    df_exchange_screen: calculate_exchange_block_screen_matrix, ScreenedDF.jl:385-457) as a Bool (N, N) matrix in the caller's
+    order, plus (lower-triangular blocks, blocks kept).  Below 100 functions one block; width N // n_blocks; a block is dropped
+    iff its sub-block of the mask holds no pair; the remainder strip is never screened."""
+    if mask is None:
+        raise ValueError("the dense statement of the contraction has no K blocks (NULL mask)")
+    N = mask.shape[0]
+    if n_blocks <= 0:
+        return np.zeros((N, N), dtype=bool), 0, 0
+    width = N if N < 100 else N // n_blocks
+    nb = 1 if N < 100 else n_blocks
+    sub = np.asarray(mask)[:nb * width, :nb * width].reshape(nb, width, nb, width).any(axis=(1, 3))
+    out = np.zeros((N, N), dtype=bool)
+    out[:nb * width, :nb * width] = ~np.kron(sub, np.ones((width, width), dtype=bool))
+    return out, nb * (nb + 1) // 2, int(np.tril(sub).sum())
+
+
 def algorithmic_work(N: int, Q: int, occ: int, pairs_kept: int, pairs_tri: int) -> dict:
     """SURVEY.md §8(d) per-build figures for a shard of Q auxiliary functions."""
     return {

@@ -20,17 +20,7 @@ import juliachem_jl_b200 as jc  # noqa: E402
 from juliachem_jl_b200 import rhf, workloads as wl  # noqa: E402
 
 
-def dropped_elements(mask, n_blocks):
-    """calculate_exchange_block_screen_matrix (ScreenedDF.jl:385-457) as a per-element Bool matrix in the caller's order."""
-    N = mask.shape[0]
-    if n_blocks <= 0:
-        return np.zeros((N, N), dtype=bool), 0, 0
-    width = N if N < 100 else N // n_blocks
-    nb = 1 if N < 100 else n_blocks
-    sub = mask[:nb * width, :nb * width].reshape(nb, width, nb, width).any(axis=(1, 3))
-    out = np.zeros((N, N), dtype=bool)
-    out[:nb * width, :nb * width] = ~np.kron(sub, np.ones((width, width), dtype=bool))
-    return out, nb * (nb + 1) // 2, int(np.tril(sub).sum())
+dropped_elements = wl.exchange_dropped_elements
 
 
 def main():
