@@ -4,6 +4,7 @@ reference functions, and the product path has no CPU fallback."""
 import ctypes
 import os
 import re
+import sys
 
 import numpy as np
 import pytest
@@ -217,3 +218,43 @@ def test_exchange_work_split_covers_the_lower_triangle_exactly_once(N):
                 assert int(cover.sum()) == 136  # exactly the 8 x 8 tiles on or below the diagonal
             if ta != tb and 128 * (ta + 1) <= N:
                 assert per_warp == [32] * 8
+
+
+@pytest.mark.parametrize("N,n_blocks,hw", [(70, 10, 9), (120, 10, 18), (203, 10, 30), (150, 7, 25), (1250, 50, 200)])
+def test_exchange_dropped_elements_equal_the_oracles_block_screen_matrix(N, n_blocks, hw):
+    """The host helper bench.py and tools/block_screen_cases.py use to know which elements of F the block-screened exchange
+    leaves uncomputed, against the oracle's restatement of calculate_exchange_block_screen_matrix (ScreenedDF.jl:385-457):
+    one block below 100 functions, width N // n_blocks, never-screened remainder strip, counts of blocks."""
+    from helpers import banded_mask
+    mask = banded_mask(N, hw, seed=N)
+    dropped, total, kept = wl.exchange_dropped_elements(mask, n_blocks)
+    nb, width, batch = orc.exchange_block_layout(N, n_blocks, 10)
+    todo, bsm = orc.exchange_block_screen_matrix(mask, nb, width, batch, True)
+    ref = np.zeros((N, N), dtype=bool)
+    ref[:nb * width, :nb * width] = ~np.kron(bsm | bsm.T, np.ones((width, width), dtype=bool))
+    assert (total, kept) == (len(batch), len(todo))
+    assert np.array_equal(dropped, ref) and np.array_equal(dropped, dropped.T)
+    assert not (dropped & mask).any()          # a dropped block holds no surviving pair
+    assert not wl.exchange_dropped_elements(mask, 0)[0].any()
+    with pytest.raises(ValueError):
+        wl.exchange_dropped_elements(None, n_blocks)
+
+
+def test_shared_nccl_is_named_without_loading_anything(monkeypatch):
+    """_lib._name_shared_nccl: JCDF_NCCL_LIBRARY is pointed at the pip package's libnccl.so.2 when there is one (so that a
+    later `import torch` finds the NCCL it was built against already mapped, not an older system copy), a value the host
+    set is kept, and nothing is dlopen'ed by naming it."""
+    import importlib.util
+    from juliachem_jl_b200 import _lib
+    monkeypatch.setenv("JCDF_NCCL_LIBRARY", "/somewhere/libnccl.so.2")
+    _lib._name_shared_nccl()
+    assert os.environ["JCDF_NCCL_LIBRARY"] == "/somewhere/libnccl.so.2"
+    monkeypatch.delenv("JCDF_NCCL_LIBRARY")
+    _lib._name_shared_nccl()
+    spec = importlib.util.find_spec("nvidia.nccl")
+    if spec is None:
+        assert "JCDF_NCCL_LIBRARY" not in os.environ
+    else:
+        path = os.environ["JCDF_NCCL_LIBRARY"]
+        assert path.endswith(os.path.join("nvidia", "nccl", "lib", "libnccl.so.2")) and os.path.exists(path)
+        assert "libnccl" not in open("/proc/self/maps").read() or "torch" in sys.modules
