@@ -258,3 +258,22 @@ def test_shared_nccl_is_named_without_loading_anything(monkeypatch):
         path = os.environ["JCDF_NCCL_LIBRARY"]
         assert path.endswith(os.path.join("nvidia", "nccl", "lib", "libnccl.so.2")) and os.path.exists(path)
         assert "libnccl" not in open("/proc/self/maps").read() or "torch" in sys.modules
+
+
+def test_layout_info_struct_matches_header_python_and_julia():
+    """jcdf_layout_info is filled by the library and read by both wrappers: same fields in the same order in include/jcdf.h
+    and _lib.LayoutInfo (all int64_t), and the Julia wrapper reads it as a vector of that many Int64 with the block counts at
+    the 1-based positions it uses."""
+    from juliachem_jl_b200 import _lib
+    src = open(os.path.join(ROOT, "include", "jcdf.h")).read()
+    body = re.search(r"typedef struct jcdf_layout_info \{(.*?)\} jcdf_layout_info;", src, flags=re.S).group(1)
+    body = re.sub(r"/\*.*?\*/", "", body, flags=re.S)
+    names = []
+    for decl in re.findall(r"int64_t\s+([^;]+);", body):
+        names += [n.strip() for n in decl.split(",")]
+    assert names == [f[0] for f in _lib.LayoutInfo._fields_]
+    assert ctypes.sizeof(_lib.LayoutInfo) == 8 * len(names)
+    jl = open(os.path.join(ROOT, "juliachem.jl_b200", "julia", "B200DF.jl")).read()
+    assert int(re.search(r"const JCDF_LAYOUT_INFO_FIELDS = (\d+)", jl).group(1)) == len(names)
+    assert names.index("exchange_blocks_total") + 1 == 16 and "string(li[16])" in jl
+    assert names.index("exchange_blocks_kept") + 1 == 17 and "string(li[17])" in jl
