@@ -545,7 +545,7 @@ def run_b200(args):
     if xs_blocks:
         cfg["exchange_block_screen"] = {"df_exchange_n_blocks": xs_blocks, "blocks_total": int(li.exchange_blocks_total),
                                         "blocks_kept": int(li.exchange_blocks_kept), "tiles_total": int(li.exchange_tiles_total),
-                                        "tiles_skipped": int(li.exchange_tiles_skipped),
+                                        "tiles_skipped": int(li.exchange_tiles_skipped), "half_tiles_skipped": int(li.exchange_half_tiles_skipped),
                                         "note": "df_exchange_screen = true: K only for the kept blocks; the exchange roofline line "
                                                 "still counts the flops of ALL blocks (its TFLOP/s is then an equivalent rate)"}
     line = {

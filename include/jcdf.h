@@ -220,6 +220,8 @@ typedef struct jcdf_layout_info {
     int64_t exchange_block_width;    /* K_block_width (:392-397)                                                            */
     int64_t exchange_tiles_total;    /* this library's own 128 x 128 lower-triangular exchange tiles (always filled)       */
     int64_t exchange_tiles_skipped;  /* ... of which left out of the work lists: every element lies in a dropped block     */
+    int64_t exchange_half_tiles_skipped; /* 64-row halves of the remaining off-diagonal tiles that lie wholly in dropped blocks
+                                      * (their warps compute nothing)                                                      */
 } jcdf_layout_info;
 int32_t jcdf_get_layout(jcdf_handle* h, jcdf_layout_info* out);
 

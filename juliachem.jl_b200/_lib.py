@@ -26,7 +26,7 @@ class LayoutInfo(C.Structure):
         "N", "Q", "occ", "n_pad", "occ_pad", "tiles_total", "tiles_kept", "pairs_kept", "pairs_tri",
         "packed_row_len", "q_local", "bytes_B", "bytes_W", "kernel_launches_per_build", "graph_replays",
         "exchange_blocks_total", "exchange_blocks_kept", "exchange_block_width", "exchange_tiles_total",
-        "exchange_tiles_skipped")]
+        "exchange_tiles_skipped", "exchange_half_tiles_skipped")]
 
 
 _p = C.c_void_p

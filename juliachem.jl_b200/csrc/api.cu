@@ -54,7 +54,7 @@ static void free_shard_buffers(Shard& s, bool keep_metric = false) {
     s.gkey = 0;
     s.graph_broken = false;
     void* ptrs[] = {s.d_pp_trirow, s.ppj_flag, s.ppj_vp, s.d_ppitems, s.d_ppoff, s.d_xcycles, s.Ksum, s.d_xitems, s.d_xoff, s.Bc, s.Ci, s.d_pp_off, s.d_pp_q, s.d_pp_src, s.d_pp_p, s.d_pp_jdst, s.dvec, s.VpartP, s.Vitem, s.Vt, s.Jpart, s.Vpart, s.Vready, s.Bp, s.W, s.Cs, s.Craw, s.dt, s.Jt, s.V, s.Kpart, s.F, s.Hdev, s.Traw, s.d_tile_index, s.d_tile_a,
-                    s.d_tile_b, s.d_dest_of_col, s.d_fn_mask, s.d_kb_list, s.d_kb_count, s.d_perm, s.d_inv, s.d_tile_strips, s.Fprev, s.d_xs_blk_of, s.d_xs_keep};
+                    s.d_tile_b, s.d_dest_of_col, s.d_fn_mask, s.d_kb_list, s.d_kb_count, s.d_perm, s.d_inv, s.d_tile_strips, s.Fprev, s.d_xs_blk_of, s.d_xs_keep, s.d_xs_half_dead};
     for (void* p : ptrs)
         if (p) cudaFree(p);
     if (!keep_metric) {
@@ -69,6 +69,7 @@ static void free_shard_buffers(Shard& s, bool keep_metric = false) {
     s.Fprev = nullptr;
     s.d_xs_blk_of = nullptr;
     s.d_xs_keep = nullptr;
+    s.d_xs_half_dead = nullptr;
     s.Bc = s.Ci = nullptr;
     s.d_pp_off = s.d_pp_q = s.d_pp_src = s.d_pp_p = s.d_pp_jdst = nullptr;
     s.dvec = s.VpartP = s.Vitem = s.Vt = s.Jpart = nullptr;
@@ -104,6 +105,8 @@ static void plan_exchange_block_screen(jcdf_handle* h, const uint8_t* fn_mask) {
     L.xs_blk_of.clear();
     L.xs_keep.clear();
     L.xs_tile_skip.clear();
+    L.xs_half_dead.clear();
+    L.xs_halves_skipped = 0;
     // the dense statement of the contraction (NULL mask) has no K blocks: DensityFitting.jl:185-224
     if (h->opt_exchange_block_screen <= 0 || fn_mask == nullptr) return;
     int nblk = (int)std::min<int64_t>(h->opt_exchange_block_screen, N);
@@ -130,24 +133,50 @@ static void plan_exchange_block_screen(jcdf_handle* h, const uint8_t* fn_mask) {
     const int n128 = L.n128;
     L.xs_tile_skip.assign((size_t)n128 * (n128 + 1) / 2, 0);
     if (!L.xs_any_dropped) return;
-    std::vector<std::vector<int32_t>> blocks_of_tile((size_t)n128);
-    std::vector<uint8_t> has_strip((size_t)n128, 0);
-    for (int t = 0; t < n128; t++) {
+    L.xs_half_dead.assign((size_t)n128 * (n128 + 1) / 2, 0);
+    // distinct K blocks of a run of internal rows / columns (caller-order block of every function in it); strip = a function
+    // of the never-screened remainder, which keeps everything it touches alive
+    auto blocks_in = [&](int64_t i0, int64_t i1, bool& strip) {
+        std::vector<int32_t> out;
         std::vector<uint8_t> seen((size_t)nblk, 0);
-        for (int64_t i = 128 * (int64_t)t; i < std::min<int64_t>(N, 128 * (int64_t)(t + 1)); i++) {
+        strip = false;
+        for (int64_t i = i0; i < std::min<int64_t>(N, i1); i++) {
             const int32_t b = L.xs_blk_of[(size_t)L.inv[(size_t)i]];
-            if (b < 0) has_strip[(size_t)t] = 1;
-            else if (!seen[(size_t)b]) { seen[(size_t)b] = 1; blocks_of_tile[(size_t)t].push_back(b); }
+            if (b < 0) strip = true;
+            else if (!seen[(size_t)b]) { seen[(size_t)b] = 1; out.push_back(b); }
         }
-    }
+        return out;
+    };
+    auto all_dropped = [&](const std::vector<int32_t>& rows, bool rstrip, const std::vector<int32_t>& cols, bool cstrip) {
+        if (rstrip || cstrip) return false;
+        for (int32_t bp : rows)
+            for (int32_t bq : cols)
+                if (L.xs_keep[(size_t)bp * nblk + bq]) return false;
+        return true;
+    };
     for (int ta = 0; ta < n128; ta++)
         for (int tb = 0; tb <= ta; tb++) {
-            bool skip = !has_strip[(size_t)ta] && !has_strip[(size_t)tb];
-            for (size_t i = 0; skip && i < blocks_of_tile[(size_t)ta].size(); i++)
-                for (int32_t bq : blocks_of_tile[(size_t)tb])
-                    if (L.xs_keep[(size_t)blocks_of_tile[(size_t)ta][i] * nblk + bq]) { skip = false; break; }
-            L.xs_tile_skip[(size_t)ta * (ta + 1) / 2 + tb] = skip ? 1 : 0;
-            L.xs_tiles_skipped += skip;
+            const size_t tile = (size_t)ta * (ta + 1) / 2 + tb;
+            bool rs, cs;
+            const std::vector<int32_t> rows = blocks_in(128 * (int64_t)ta, 128 * (int64_t)(ta + 1), rs);
+            const std::vector<int32_t> cols = blocks_in(128 * (int64_t)tb, 128 * (int64_t)(tb + 1), cs);
+            if (all_dropped(rows, rs, cols, cs)) {
+                L.xs_tile_skip[tile] = 1;
+                L.xs_tiles_skipped++;
+                continue;
+            }
+            // the two row halves of an off-diagonal tile (the rows the warps w < 4 / w >= 4 own, kernels_k.cu)
+            for (int half = 0; half < 2 && ta != tb; half++) {
+                int r_begin, r_end;
+                exchange_half_rows(ta, tb, half, (int)N, r_begin, r_end);
+                if (r_end <= r_begin) continue;
+                bool hs;
+                const std::vector<int32_t> hrows = blocks_in(128 * (int64_t)ta + r_begin, 128 * (int64_t)ta + r_end, hs);
+                if (all_dropped(hrows, hs, cols, cs)) {
+                    L.xs_half_dead[tile] |= (uint8_t)(1u << half);
+                    L.xs_halves_skipped++;
+                }
+            }
         }
 }
 
@@ -179,7 +208,8 @@ static void plan_exchange(const Layout& L, Shard& s, int sm_count, bool balance,
     x.n_ctas = std::max(1, std::min(live_tiles * x.n_slices, sm_count));
     std::vector<int64_t> cost((size_t)n_items);
     std::vector<int> tile_cost((size_t)x.n_tiles);
-    for (int t = 0; t < x.n_tiles; t++) tile_cost[(size_t)t] = exchange_tile_cost(t, (int)L.N);
+    for (int t = 0; t < x.n_tiles; t++)
+        tile_cost[(size_t)t] = exchange_tile_cost(t, (int)L.N, L.xs_half_dead.empty() ? 0 : L.xs_half_dead[(size_t)t]);
     for (int it = 0; it < n_items; it++) {
         const int slice = it / x.n_tiles;
         const int kc0 = slice * x.chunks_per_slice, kc1 = std::min(x.chunks, kc0 + x.chunks_per_slice);
@@ -250,6 +280,8 @@ static int alloc_shard_buffers(jcdf_handle* h, Shard& s) {
         if ((rc = dev_alloc(&s.Fprev, (size_t)L.N * L.N))) return rc;
         if ((rc = dev_alloc(&s.d_xs_blk_of, L.xs_blk_of.size()))) return rc;
         if ((rc = dev_alloc(&s.d_xs_keep, L.xs_keep.size()))) return rc;
+        if ((rc = dev_alloc(&s.d_xs_half_dead, L.xs_half_dead.size()))) return rc;
+        JC_CUDA(cudaMemcpyAsync(s.d_xs_half_dead, L.xs_half_dead.data(), L.xs_half_dead.size(), cudaMemcpyHostToDevice, s.stream));
         JC_CUDA(cudaMemsetAsync(s.Fprev, 0, sizeof(double) * L.N * L.N, s.stream));
         JC_CUDA(cudaMemcpyAsync(s.d_xs_blk_of, L.xs_blk_of.data(), sizeof(int32_t) * L.xs_blk_of.size(), cudaMemcpyHostToDevice, s.stream));
         JC_CUDA(cudaMemcpyAsync(s.d_xs_keep, L.xs_keep.data(), L.xs_keep.size(), cudaMemcpyHostToDevice, s.stream));
@@ -1429,6 +1461,7 @@ int32_t jcdf_get_layout(jcdf_handle* h, jcdf_layout_info* o) {
     o->exchange_block_width = L.xs_width;
     o->exchange_tiles_total = (int64_t)L.n128 * (L.n128 + 1) / 2;
     o->exchange_tiles_skipped = L.xs_tiles_skipped;
+    o->exchange_half_tiles_skipped = L.xs_halves_skipped;
     for (const Shard& s : h->shards) {
         o->q_local += s.q_len;
         o->bytes_B += s.q_len * L.row_len * 8;

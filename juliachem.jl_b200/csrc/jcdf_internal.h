@@ -57,6 +57,8 @@ struct Layout {
     std::vector<uint8_t> xs_keep;      // [xs_nblk * xs_nblk] symmetric block_screen_matrix
     std::vector<uint8_t> xs_tile_skip;  // [n128 (n128 + 1) / 2] 128 x 128 exchange tiles lying wholly inside dropped blocks
     int64_t xs_tiles_skipped = 0;
+    std::vector<uint8_t> xs_half_dead;  // per exchange tile: bit h set = the rows the warps of row half h own lie wholly in dropped blocks
+    int64_t xs_halves_skipped = 0;      // such halves in tiles that are NOT skipped as a whole
 };
 
 inline int pp_item_orbitals(const Layout& L) { return (L.pp_layout == 1 ? 8 : L.pp_layout == 2 ? 16 : 32) * L.pp_nt; }
@@ -122,6 +124,7 @@ struct Shard {
     double* Fprev = nullptr;   // N x N: the caller's F_out as it arrived (block-screened exchange: dropped blocks keep it)
     int32_t* d_xs_blk_of = nullptr;  // [N]
     uint8_t* d_xs_keep = nullptr;    // [xs_nblk * xs_nblk]
+    uint8_t* d_xs_half_dead = nullptr;  // [n_tiles]
     double* Hdev = nullptr;    // N x N (only where H is added)
     double* Traw = nullptr;    // staging window for uploads
     int64_t traw_capacity = 0;
@@ -227,7 +230,8 @@ void launch_gather_pairs(const Layout& L, Shard& s, double* T_dev, int64_t ld, i
 void launch_fill_synthetic(const Layout& L, Shard& s, uint64_t seed, double decay_length);
 size_t half_transform_smem_bytes(int bm);
 size_t exchange_smem_bytes();
-int exchange_tile_cost(int tile, int N);  // kernels_k.cu: DMMA row units per k-step on the busiest sub-partition
+int exchange_tile_cost(int tile, int N, int half_dead = 0);  // kernels_k.cu: DMMA row units per k-step on the busiest sub-partition
+void exchange_half_rows(int ta, int tb, int half, int N, int& row_begin, int& row_end);  // kernels_k.cu: rows of tile ta the warps of a row half own
 int kernels_per_build();
 
 void set_fuzz_seed_k(unsigned int seed);   // checked build: schedule-fuzzing seed of each kernel translation unit

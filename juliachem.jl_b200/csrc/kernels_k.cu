@@ -376,6 +376,7 @@ struct XParams {
     const int32_t* item_list;  // items of CTA c: item_list[item_off[c] .. item_off[c + 1])  (cost-balanced on the host)
     const int32_t* item_off;
     long long* cta_cycles;     // [gridDim.x] busy cycles of this launch (profiling aid)
+    const uint8_t* half_dead;  // block-screened exchange: per tile, bit h = row half h lies wholly in dropped K blocks (or nullptr)
     int npt64, n_tiles, n_slices, chunks, chunks_per_slice, N;
     int64_t w_elems, kpart_elems;  // buffer extents in doubles (read by the bounds-checked build only)
 };
@@ -436,7 +437,8 @@ __host__ __device__ inline void exchange_decode_tile(int tile, int& ta, int& tb)
 }
 
 // DMMA row units (x 4 column tiles) the busiest sub-partition issues per k-step of 4 for this tile: the cost model
-int exchange_tile_cost(int tile, int N) {
+// half_dead (block-screened exchange): bit h = the warps of row half h of an off-diagonal tile have nothing to compute
+int exchange_tile_cost(int tile, int N, int half_dead) {
     int ta, tb, best = 0;
     exchange_decode_tile(tile, ta, tb);
     for (int j = 0; j < 4; j++) {
@@ -444,11 +446,24 @@ int exchange_tile_cost(int tile, int N) {
         for (int w = j; w < 8; w += 4) {
             int r0, c0, mt, nt;
             exchange_warp_block(ta, tb, w, N, r0, c0, mt, nt);
+            if (ta != tb && ((half_dead >> (w >> 2)) & 1)) continue;
             c += exchange_block_tiles(ta, tb, r0, c0, mt, nt);
         }
         best = std::max(best, c);
     }
     return best;
+}
+
+// Rows [row_begin, row_end) of the 128-row tile ta (tile-local) that the four warps of row half `half` own in an off-diagonal
+// tile (ta, tb): what the block-screened planner tests against the dropped K blocks.  Empty for a diagonal tile.
+void exchange_half_rows(int ta, int tb, int half, int N, int& row_begin, int& row_end) {
+    row_begin = row_end = 0;
+    if (ta == tb) return;
+    int r0, c0, mt, nt;
+    exchange_warp_block(ta, tb, 4 * half, N, r0, c0, mt, nt);
+    row_begin = 8 * r0;
+    row_end = min(8 * (r0 + mt), N - 128 * ta);
+    if (row_end < row_begin) row_end = row_begin;
 }
 
 // One pipeline stage (32 k rows) of a warp block of MT x NT DMMA tiles.  MT and NT are compile-time so a clipped or
@@ -609,6 +624,9 @@ __device__ __forceinline__ void exchange_body(const XParams& prm) {
         decode(item, ta, tb, kc0, kc1);
         int r0, c0, mt, nt;
         exchange_warp_block(ta, tb, warp, prm.N, r0, c0, mt, nt);
+        // block-screened exchange: a row half whose every element lies in dropped K blocks is not computed (its warps only keep
+        // the ring moving); both warps of every sub-partition sit in different halves, so the saving is the same on all four
+        if (prm.half_dead != nullptr && ta != tb && ((prm.half_dead[item % prm.n_tiles] >> (warp >> 2)) & 1)) mt = nt = 0;
         const bool active = mt > 0;
         const bool whole = (mt == 8) && (nt == 4);
         const bool stair = exchange_block_is_stair(ta, tb, r0, c0) && mt > 0;  // mt <= 6 on these rectangles, nt >= min(4, mt)
@@ -673,6 +691,7 @@ void launch_exchange(const Layout& L, Shard& s, int sm_count, bool dedicated_pro
     prm.item_list = s.d_xitems;
     prm.item_off = s.d_xoff;
     prm.cta_cycles = s.d_xcycles;
+    prm.half_dead = (L.xs_halves_skipped > 0) ? s.d_xs_half_dead : nullptr;
     prm.npt64 = L.npt64;
     prm.n_tiles = s.xplan.n_tiles;
     prm.n_slices = s.xplan.n_slices;

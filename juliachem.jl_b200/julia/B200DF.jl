@@ -16,7 +16,7 @@ using Libdl
 const libjcdf = get(ENV, "JULIACHEM_LIBJCDF", "libjcdf")   # deps/build.jl puts libjcdf.so next to libjeri.so
 
 const JCDF_N_STAGES = 10
-const JCDF_LAYOUT_INFO_FIELDS = 20   # jcdf_layout_info: 20 x int64_t (include/jcdf.h); 16-17 = exchange_blocks_total / _kept
+const JCDF_LAYOUT_INFO_FIELDS = 21   # jcdf_layout_info: 21 x int64_t (include/jcdf.h); 16-17 = exchange_blocks_total / _kept
 # stage slot (0-based in jcdf.h) -> JCTiming key prefix (src/shared/JCTiming.jl:58-107).  Slot 6 (C_occ upload) is what
 # the fork's GPU path books as GPU_non_zero_coeff_time of device 1 (GPUDF.jl:288); slot 9 (J scatter + H add + mirror)
 # as gpu_copy_J_time (GPUDF.jl:289).

@@ -79,6 +79,7 @@ def main():
                           "K_block_width": int(li.exchange_block_width), "blocks_total": total, "blocks_kept": kept,
                           "elements_dropped_fraction": round(float(dropped.mean()), 4),
                           "exchange_tiles_total": int(li.exchange_tiles_total), "exchange_tiles_skipped": int(li.exchange_tiles_skipped),
+                          "exchange_half_tiles_skipped": int(li.exchange_half_tiles_skipped),
                           "stage_ms_median_of_5": {k: round(v, 4) for k, v in med.items()},
                           "max_abs_err_kept_vs_default_build": err_default,
                           "fixture_samples_in_kept_blocks": n_live, "max_abs_err_kept_vs_oracle_fixture": err_fx,
