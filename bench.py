@@ -39,9 +39,9 @@ METRIC = "DF-RHF Fock builds/sec"
 UNIT = "builds/s"
 # dram__bytes_read.sum + dram__bytes_write.sum per launch from the committed `ncu --set full` capture (not measured live:
 # a number taken under a profiler is never a bench value, and DRAM counters need the profiler)
-NCU_TRAFFIC_SOURCE = "profiles/r02_ncu_w50_full_e.txt (ncu --set full --clock-control none, per launch, bytes)"
-NCU_TRAFFIC = {("w50", 1, "exchange"): 43.258725e9 + 0.500485e9,
-               ("w50", 1, "half_transform"): 13.155567e9 + 12.394540e9}
+NCU_TRAFFIC_SOURCE = "profiles/r02_ncu_w50_full_z.txt (ncu --set full --clock-control none, per launch, bytes; final tree of round 2)"
+NCU_TRAFFIC = {("w50", 1, "exchange"): 42.984082e9 + 0.501368e9,
+               ("w50", 1, "half_transform"): 13.130969e9 + 12.393388e9}
 FP64_MICROBENCH_PEAK = 37.1  # TFLOP/s, DMMA issue peak measured by tools/microbench_fp64 (profiles/r01_microbench_fp64.log)
 
 
