@@ -137,6 +137,44 @@ def test_baseline_shapes_match_the_oracle_on_a_row_slab(name, q0, rows, ht_mode)
     assert err < TOL
 
 
+@pytest.mark.parametrize("name,q0,rows", [s for s in SLABS if s[0] != "benzene_dimer"])
+def test_chain_shapes_with_block_screened_exchange_match_the_oracle_on_a_row_slab(name, q0, rows):
+    """df_exchange_screen = true at the reference's default 10 K blocks on the chain-like benchmark shapes, where whole
+    exchange tiles and 64-row halves drop out of the work lists (C20H42 shape: 21 of 66 tiles + 6 halves; gly18: 170 of 378
+    + 22).  Oracle: in the computed blocks the reference's screened build on the device's own rows, in the dropped blocks the
+    caller's buffer + H (calculate_K_lower_diagonal_block never writes them, ScreenedDF.jl:494-512; the oracle's own
+    restatement of that equivalence is checked in tests/test_oracle_algorithms.py)."""
+    w = wl.WORKLOADS[name]
+    mask = wl.screening_mask(w)
+    C, H = wl.occupied_coefficients(w), wl.core_hamiltonian(w)
+    gd = jc.B200Data(w.N, w.Q, w.occ, 1)
+    gd.set_shards([range(q0, q0 + rows)])
+    gd.set_option("exchange_block_screen", 10)
+    gd.set_mask(jc.ScreeningData(mask, w.N))
+    gd.fill_synthetic_B(w.seed, w.decay_length)
+    li = gd.layout()
+    nb, width, batch = orc.exchange_block_layout(w.N, 10, 10)
+    todo, bsm = orc.exchange_block_screen_matrix(mask, nb, width, batch, True)
+    assert (li.exchange_blocks_total, li.exchange_blocks_kept) == (len(batch), len(todo)) and len(todo) < len(batch)
+    assert li.exchange_tiles_skipped > 0 and li.exchange_half_tiles_skipped > 0
+    dropped = np.zeros((w.N, w.N), dtype=bool)
+    dropped[:nb * width, :nb * width] = ~np.kron(bsm | bsm.T, np.ones((width, width), dtype=bool))
+    F_in = np.asfortranarray(np.random.default_rng(3).standard_normal((w.N, w.N)))
+    F_in = np.asfortranarray(F_in + F_in.T)
+    F = F_in.copy(order="F")
+    gd.fock_build(C, H, F)
+    F_orc = oracle_fock_from_device_B(gd, rows, C, H, mask, rows)
+    gd.close()
+    F_orc[dropped] = (F_in + H)[dropped]
+    err = float(np.abs(F - F_orc).max())
+    print("%s rows [%d, %d) block-screened: %d of %d blocks, %d tiles + %d halves skipped of %d, max|F_gpu - F_oracle| = %.3e" % (
+        name, q0, q0 + rows, len(todo), len(batch), li.exchange_tiles_skipped, li.exchange_half_tiles_skipped,
+        li.exchange_tiles_total, err))
+    assert np.array_equal(F, F.T)
+    assert np.array_equal(F[dropped], (F_in + H)[dropped])
+    assert err < TOL
+
+
 @pytest.mark.slow
 def test_w50_converged_energy_matches_the_oracle_scf():
     """North star: converged total energy within 1e-8 Eh.  The whole real-w50 SCF on the device with the benched (default)
